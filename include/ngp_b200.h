@@ -1,0 +1,88 @@
+/*
+ * ngp_b200.h — C ABI of the B200-native neural-field hot path (libngp_b200.so).
+ *
+ * This is the drop-in boundary: every entry point takes plain device pointers, sizes and scalars plus
+ * the CUDA stream to launch on, allocates nothing, returns 0 on success and non-zero on failure
+ * (message via ngp_last_error()).  It replaces the pybind11 `_backend.<fn>(at::Tensor...)` functions of
+ * the reference's torch extensions; each declaration cites the reference interface it replaces
+ * (paths relative to the reference root).  The reference launches on the legacy default stream without a
+ * device guard; here the caller selects the device (cudaSetDevice / torch.cuda.device) and passes a stream.
+ *
+ * Conventions: all pointers are device pointers unless named *_host; float = fp32; `table_dtype`
+ * 0 = fp32, 1 = fp16.  Row-major, contiguous.  B/N/M are element counts.
+ */
+#ifndef NGP_B200_H
+#define NGP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void *ngp_stream_t; /* cudaStream_t */
+
+#define NGP_OK 0
+#define NGP_ERR_ARG 1
+#define NGP_ERR_CUDA 2
+#define NGP_ERR_UNSUPPORTED 3
+
+#define NGP_DTYPE_F32 0
+#define NGP_DTYPE_F16 1
+
+/* thread-local last error string (never NULL) */
+const char *ngp_last_error(void);
+/* ABI version, bumped on signature changes */
+int ngp_abi_version(void);
+
+/* ---- hash-grid encoder: gridencoder/src/gridencoder.h:12-13, bindings.cpp:5-8 ------------------------- */
+
+/* Per-level scale exp2f(l*S)*H-1 evaluated ON DEVICE exactly as every kernel here evaluates it
+ * (reference: gridencoder.cu:126).  scales[L] device buffer.  Debug/test aid for index parity. */
+int ngp_grid_level_scales(float *scales, int L, float S, uint32_t H, ngp_stream_t stream);
+
+/* grid_encode_forward (gridencoder.cu:423-446).  inputs [B,D] in [0,1]; embeddings [rows,C]; offsets [L+1] i32.
+ * out_layout 0: outputs [L,B,C] (reference layout); 1: outputs [B,L*C] (what grid.py:52 permutes to).
+ * outputs / dy_dx have the table dtype.  dy_dx [B,L,D,C] written iff calc_grad_inputs && dy_dx != NULL.
+ * indices (optional, may be NULL): u32 [B,L,2^D] level-local row indices, for the bit-exact parity test. */
+int ngp_grid_encode_forward(const float *inputs, const void *embeddings, int table_dtype, const int32_t *offsets,
+                            void *outputs, int out_layout, int64_t B, int D, int C, int L, float S, uint32_t H,
+                            int calc_grad_inputs, void *dy_dx, uint32_t gridtype, int align_corners,
+                            uint32_t *indices, ngp_stream_t stream);
+
+/* grid_encode_backward, input part (gridencoder.cu:317-343, 468-476): grad_inputs [B,D] fp32 (w.r.t. the [0,1]
+ * inputs).  The reference contracts grad with a stored dy_dx; here the corners are re-gathered instead, so no
+ * dy_dx buffer is needed (same arithmetic order).  grad_layout as out_layout above. */
+int ngp_grid_encode_backward_input(const void *grad, int grad_layout, const float *inputs, const void *embeddings,
+                                   int table_dtype, const int32_t *offsets, float *grad_inputs, int64_t B, int D,
+                                   int C, int L, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                                   ngp_stream_t stream);
+
+/* grid_encode_backward, table part (gridencoder.cu:227-314, 448-466): grad_embeddings [rows,C] fp32 is
+ * OVERWRITTEN (no pre-zeroing needed) with a deterministic sorted segmented reduction (no float atomics).
+ * workspace: ngp_grid_backward_table_workspace_bytes(B,D,L) bytes of device scratch. */
+int64_t ngp_grid_backward_table_workspace_bytes(int64_t B, int D, int L);
+int ngp_grid_encode_backward_table(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
+                                   const int32_t *offsets, const int32_t *offsets_host, float *grad_embeddings,
+                                   int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
+                                   int align_corners, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+
+/* ---- fused field query: NeRFNetwork.density(), nerf/network.py:126-143 (+ grid.py:140-156, activation.py) --- */
+
+/* sigma = exp(o[0]), geo = o[1:n_out], o = W1 relu(W0 enc((x+bound)/(2 bound))).  fp32 table + fp32 MLP,
+ * D=3, C=2, L=16, hidden=64, n_out=16.  W0 [64,32], W1 [16,64] row-major (nn.Linear.weight).
+ * geo may be NULL.  relu_mask (optional): u64 [B] saved for ngp_field_query_backward. */
+int ngp_field_query_forward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                            uint32_t H, uint32_t gridtype, int align_corners, const float *W0, const float *W1,
+                            float *sigma, float *geo, uint64_t *relu_mask, int64_t B, ngp_stream_t stream);
+
+/* dL/dx [B,3] from dL/dsigma [B] (+ optional dL/dgeo [B,15]); needs sigma and relu_mask from the forward. */
+int ngp_field_query_backward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                             uint32_t H, uint32_t gridtype, int align_corners, const float *W0, const float *W1,
+                             const float *sigma, const uint64_t *relu_mask, const float *grad_sigma,
+                             const float *grad_geo, float *grad_x, int64_t B, ngp_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NGP_B200_H */

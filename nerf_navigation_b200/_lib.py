@@ -1,0 +1,78 @@
+"""ctypes binding of libngp_b200.so (the C ABI in include/ngp_b200.h).
+
+There is no CPU fallback: if the library is missing or a call fails, a RuntimeError is raised
+(the reference raises RuntimeError via TORCH_CHECK, e.g. gridencoder.cu:15-18).
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libngp_b200.so")
+
+_lib = None
+
+P = C.c_void_p
+I = C.c_int
+I64 = C.c_int64
+U32 = C.c_uint32
+F = C.c_float
+
+_SIGNATURES = {
+    "ngp_abi_version": ([], I),
+    "ngp_grid_level_scales": ([P, I, F, U32, P], I),
+    "ngp_grid_encode_forward": ([P, P, I, P, P, I, I64, I, I, I, F, U32, I, P, U32, I, P, P], I),
+    "ngp_grid_encode_backward_input": ([P, I, P, P, I, P, P, I64, I, I, I, F, U32, U32, I, P], I),
+    "ngp_field_query_forward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, I64, P], I),
+    "ngp_field_query_backward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, I64, P], I),
+}
+
+
+def declared_symbols():
+    """Every entry point include/ngp_b200.h declares (checked by the CPU test-suite)."""
+    import re
+    hdr = open(os.path.join(_HERE, "..", "include", "ngp_b200.h")).read()
+    return sorted(set(re.findall(r"\b(ngp_[a-z0-9_]+)\s*\(", hdr)))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise RuntimeError(f"{SO_PATH} is missing: build it with `python -m nerf_navigation_b200.build` "
+                               "(there is no CPU fallback)")
+        L = C.CDLL(SO_PATH)
+        L.ngp_last_error.restype = C.c_char_p
+        for name, (args, res) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.argtypes = args
+            fn.restype = res
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise RuntimeError(f"{what}: {lib().ngp_last_error().decode()}")
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("expected a CUDA tensor (nerf_navigation_b200 has no CPU path)")
+
+
+def require_contiguous(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_contiguous():
+            raise RuntimeError("expected a contiguous tensor")

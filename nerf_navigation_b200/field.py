@@ -1,0 +1,69 @@
+"""Fused field query (hash-grid encode -> sigma MLP -> trunc_exp) used by NeRFNetwork.density().
+
+Reference path: nerf/network.py:126-143 (density), gridencoder/grid.py:140-156, activation.py:5-17.
+One kernel forward, one kernel backward-to-x; the per-point features / hidden activations never reach HBM.
+"""
+import numpy as np
+import torch
+from torch.autograd import Function
+
+from . import _lib
+
+
+def fused_supported(encoder, W0, W1, x):
+    """The fused kernels cover the configuration nerf-navigation uses: 3-D, 16 levels x 2 features, fp32,
+    sigma net 32 -> 64 -> 16 (network.py:33-47)."""
+    return (encoder.input_dim == 3 and encoder.num_levels == 16 and encoder.level_dim == 2
+            and encoder.embeddings.dtype == torch.float32 and tuple(W0.shape) == (64, 32)
+            and tuple(W1.shape) == (16, 64) and x.dtype == torch.float32 and not torch.is_autocast_enabled())
+
+
+class _field_query(Function):
+    """(x [B,3] world coords, embeddings, W0, W1) -> sigma [B], geo_feat [B,15].  Backward: dL/dx only
+    (parameter gradients go through the unfused path, see NeRFNetwork.density)."""
+
+    @staticmethod
+    def forward(ctx, x, embeddings, W0, W1, offsets, bound, S, H, gridtype, align_corners):
+        _lib.require_cuda(x, embeddings, W0, W1, offsets)
+        x = x.contiguous()
+        embeddings = embeddings.contiguous(); W0 = W0.contiguous(); W1 = W1.contiguous()
+        B = x.shape[0]
+        sigma = torch.empty(B, device=x.device, dtype=torch.float32)
+        geo = torch.empty(B, 15, device=x.device, dtype=torch.float32)
+        need_bwd = x.requires_grad
+        mask = torch.empty(B, device=x.device, dtype=torch.int64) if need_bwd else None
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ngp_field_query_forward(
+                _lib.ptr(x), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, int(align_corners),
+                _lib.ptr(W0), _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(geo), _lib.ptr(mask), B, _lib.stream()),
+                "field_query_forward")
+        if need_bwd:
+            ctx.save_for_backward(x, embeddings, W0, W1, offsets, sigma, mask)
+        ctx.cfg = (float(bound), S, H, gridtype, int(align_corners))
+        return sigma, geo
+
+    @staticmethod
+    def backward(ctx, grad_sigma, grad_geo):
+        x, embeddings, W0, W1, offsets, sigma, mask = ctx.saved_tensors
+        bound, S, H, gridtype, align = ctx.cfg
+        B = x.shape[0]
+        grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
+        gg = None
+        if grad_geo is not None and ctx.needs_input_grad[0]:
+            gg = grad_geo.contiguous().float()
+        grad_x = torch.empty(B, 3, device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ngp_field_query_backward(
+                _lib.ptr(x), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align, _lib.ptr(W0),
+                _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(mask), _lib.ptr(grad_sigma), _lib.ptr(gg), _lib.ptr(grad_x), B,
+                _lib.stream()), "field_query_backward")
+        return grad_x, None, None, None, None, None, None, None, None, None
+
+
+def field_query(x, encoder, W0, W1, bound):
+    """x [..., 3] -> (sigma [...], geo_feat [..., 15])."""
+    prefix = list(x.shape[:-1])
+    S = float(np.log2(encoder.per_level_scale))
+    sigma, geo = _field_query.apply(x.reshape(-1, 3), encoder.embeddings, W0, W1, encoder.offsets, bound, S,
+                                    int(encoder.base_resolution), encoder.gridtype_id, encoder.align_corners)
+    return sigma.view(prefix), geo.view(prefix + [15])

@@ -1,0 +1,116 @@
+"""GPU parity: hash-grid encoder (C ABI) vs the CPU oracle and vs the reference's own CUDA build."""
+import numpy as np
+import pytest
+import torch
+
+from util import hashgrid_config, rel_err, load_ref
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev_scales(ngp, cfg):
+    s = torch.empty(cfg["L"], device="cuda")
+    ngp.check(ngp.lib().ngp_grid_level_scales(s.data_ptr(), cfg["L"], cfg["S"], cfg["H"], ngp.stream()))
+    return s.cpu().numpy()
+
+
+def _forward(ngp, x01, table, offsets, cfg, layout=1, calc=False, want_idx=False, D=3):
+    B = x01.shape[0]; L, C = cfg["L"], table.shape[1]
+    out = torch.empty((B, L * C) if layout == 1 else (L, B, C), device="cuda", dtype=table.dtype)
+    dy = torch.empty(B, L, D, C, device="cuda", dtype=table.dtype) if calc else None
+    ix = torch.empty(B, L, 1 << D, device="cuda", dtype=torch.int32) if want_idx else None
+    ngp.check(ngp.lib().ngp_grid_encode_forward(
+        x01.data_ptr(), table.data_ptr(), 0 if table.dtype == torch.float32 else 1, offsets.data_ptr(), out.data_ptr(),
+        layout, B, D, C, L, cfg["S"], cfg["H"], int(calc), ngp.ptr(dy), 0, 0, ngp.ptr(ix), ngp.stream()), "fwd")
+    return out, dy, ix
+
+
+@pytest.mark.parametrize("B", [1, 1000, 65537])
+def test_forward_vs_oracle(ngp, oracle, B):
+    cfg = hashgrid_config()
+    rng = np.random.default_rng(B)
+    x = rng.uniform(0, 1, (B, 3)).astype(np.float32)
+    x[0] = [0.0, 1.0, 0.5]
+    if B > 10:
+        x[3] = [1.5, 0.2, 0.2]   # out of range -> zeros (gridencoder.cu:99-123)
+        x[4] = [0.2, -0.1, 0.2]
+    scales = _dev_scales(ngp, cfg)
+    ref_out, ref_dy, ref_ix = oracle.grid_encode_forward(x, cfg["table"], cfg["offsets"], scales, True, want_indices=True)
+    xt = torch.from_numpy(x).cuda(); tt = torch.from_numpy(cfg["table"]).cuda(); ot = torch.from_numpy(cfg["offsets"]).cuda()
+    out, dy, ix = _forward(ngp, xt, tt, ot, cfg, layout=0, calc=True, want_idx=True)
+    assert np.array_equal(ix.cpu().numpy().view(np.uint32), ref_ix)          # bit-exact indices
+    assert rel_err(out.cpu().numpy(), ref_out) < 1e-5
+    assert rel_err(dy.cpu().numpy(), ref_dy) < 1e-5
+    out1, _, _ = _forward(ngp, xt, tt, ot, cfg, layout=1)
+    assert torch.equal(out1.view(B, cfg["L"], 2).permute(1, 0, 2), out)     # layouts agree (grid.py:52)
+
+
+def test_device_scales_match_libm(ngp, oracle):
+    cfg = hashgrid_config()
+    dev = _dev_scales(ngp, cfg)
+    host = oracle.level_scales(cfg["L"], cfg["per_level_scale"], cfg["H"])
+    # device exp2f is within 2 ulp of libm; cell indices are compared with the DEVICE scales on both sides
+    assert np.allclose(dev, host, rtol=3e-7)
+
+
+def test_backward_input_vs_oracle(ngp, oracle):
+    cfg = hashgrid_config()
+    B = 20000
+    rng = np.random.default_rng(7)
+    x = rng.uniform(0, 1, (B, 3)).astype(np.float32)
+    x[5] = [1.2, 0.5, 0.5]
+    g = rng.standard_normal((B, 32)).astype(np.float32)
+    scales = _dev_scales(ngp, cfg)
+    _, dy, _ = oracle.grid_encode_forward(x, cfg["table"], cfg["offsets"], scales, True)
+    ref = oracle.grid_backward_input(np.ascontiguousarray(g.reshape(B, 16, 2).transpose(1, 0, 2)), dy)
+    xt = torch.from_numpy(x).cuda(); tt = torch.from_numpy(cfg["table"]).cuda(); ot = torch.from_numpy(cfg["offsets"]).cuda()
+    gt = torch.from_numpy(g).cuda(); gx = torch.empty(B, 3, device="cuda")
+    ngp.check(ngp.lib().ngp_grid_encode_backward_input(gt.data_ptr(), 1, xt.data_ptr(), tt.data_ptr(), 0, ot.data_ptr(),
+                                                      gx.data_ptr(), B, 3, 2, 16, cfg["S"], cfg["H"], 0, 0, ngp.stream()))
+    assert rel_err(gx.cpu().numpy(), ref) < 1e-5
+
+
+@pytest.mark.parametrize("D,C", [(2, 2), (3, 1), (3, 4), (3, 8), (2, 8)])
+def test_other_shapes_vs_oracle(ngp, oracle, D, C):
+    offsets, pls = oracle.level_table(D, 8, C, 2.0, 16, 15, 512)
+    cfg = dict(L=8, S=float(np.log2(pls)), H=16)
+    rng = np.random.default_rng(D * 10 + C)
+    table = rng.uniform(-1, 1, (int(offsets[-1]), C)).astype(np.float32)
+    x = rng.uniform(0, 1, (3000, D)).astype(np.float32)
+    scales = _dev_scales(ngp, cfg)
+    ref_out, ref_dy, ref_ix = oracle.grid_encode_forward(x, table, offsets, scales, True, want_indices=True)
+    out, dy, ix = _forward(ngp, torch.from_numpy(x).cuda(), torch.from_numpy(table).cuda(),
+                           torch.from_numpy(offsets).cuda(), cfg, layout=0, calc=True, want_idx=True, D=D)
+    assert np.array_equal(ix.cpu().numpy().view(np.uint32), ref_ix)
+    assert rel_err(out.cpu().numpy(), ref_out) < 1e-5
+    assert rel_err(dy.cpu().numpy(), ref_dy) < 1e-5
+
+
+def test_forward_vs_reference_cuda(ngp):
+    """Strongest pin: the reference's own kernel (oracle/_ref, built from /root/reference) on identical tensors."""
+    ref = load_ref("gridencoder")
+    if ref is None:
+        pytest.skip("oracle/_ref/gridencoder not built")
+    cfg = hashgrid_config()
+    B = 200000
+    g = torch.Generator(device="cuda").manual_seed(0)
+    x = torch.rand(B, 3, device="cuda", generator=g)
+    tt = torch.from_numpy(cfg["table"]).cuda(); ot = torch.from_numpy(cfg["offsets"]).cuda()
+    out_ref = torch.empty(16, B, 2, device="cuda"); dy_ref = torch.empty(B, 96, device="cuda")
+    ref.grid_encode_forward(x, tt, ot, out_ref, B, 3, 2, 16, cfg["S"], cfg["H"], True, dy_ref, 0, False)
+    out, dy, _ = _forward(ngp, x, tt, ot, cfg, layout=0, calc=True)
+    torch.cuda.synchronize()
+    # same device exp2f + same fma contraction => identical cells; allow only fp32 rounding differences
+    assert rel_err(out.cpu().numpy(), out_ref.cpu().numpy()) < 1e-6
+    assert rel_err(dy.view(B, 96).cpu().numpy(), dy_ref.cpu().numpy()) < 1e-6
+    frac_equal = (out == out_ref).float().mean().item()
+    assert frac_equal > 0.99, frac_equal
+    # input backward vs reference kernel_input_backward
+    gr = torch.randn(B, 32, device="cuda", generator=g)
+    gref_in = torch.zeros(B, 3, device="cuda"); gemb = torch.zeros_like(tt)
+    ref.grid_encode_backward(gr.view(B, 16, 2).permute(1, 0, 2).contiguous(), x, tt, ot, gemb, B, 3, 2, 16, cfg["S"],
+                             cfg["H"], True, dy_ref, gref_in, 0, False)
+    gx = torch.empty(B, 3, device="cuda")
+    ngp.check(ngp.lib().ngp_grid_encode_backward_input(gr.data_ptr(), 1, x.data_ptr(), tt.data_ptr(), 0, ot.data_ptr(),
+                                                      gx.data_ptr(), B, 3, 2, 16, cfg["S"], cfg["H"], 0, 0, ngp.stream()))
+    assert rel_err(gx.cpu().numpy(), gref_in.cpu().numpy()) < 1e-5
