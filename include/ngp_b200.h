@@ -82,6 +82,58 @@ int ngp_field_query_backward(const float *x, float bound, const float *embedding
                              const float *sigma, const uint64_t *relu_mask, const float *grad_sigma,
                              const float *grad_geo, float *grad_x, int64_t B, ngp_stream_t stream);
 
+/* ---- ray ops: raymarching/src/raymarching.h:7-18, bindings.cpp:5-19 -------------------------------------------- */
+
+/* near_far_from_aabb (raymarching.cu:93-158).  rays_o/rays_d [N,3], aabb[6] -> nears/fars [N]; miss => FLT_MAX. */
+int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, int64_t N, float min_near,
+                           float *nears, float *fars, ngp_stream_t stream);
+
+/* morton3D / morton3D_invert (raymarching.cu:216-262).  coords [N,3] i32 <-> indices [N] i32. */
+int ngp_morton3D(const int32_t *coords, int64_t N, int32_t *indices, ngp_stream_t stream);
+int ngp_morton3D_invert(const int32_t *indices, int64_t N, int32_t *coords, ngp_stream_t stream);
+
+/* packbits (raymarching.cu:269-302).  grid [C*H^3] f32 (16-byte aligned), N = C*H^3/8 -> bitfield u8 [N]. */
+int ngp_packbits(const float *grid, int64_t N, float thresh, uint8_t *bitfield, ngp_stream_t stream);
+
+/* march_rays_train (raymarching.cu:313-495).  Deterministic: rays[n] = (n, offset, count) with offsets the exclusive
+ * scan of counts in ray order starting at counter[0]; counter[0] += total samples, counter[1] += N.  xyzs/dirs [M,3],
+ * deltas [M,2] must be pre-zeroed by the caller (raymarching.py:209-211); a ray with offset+count >= M writes nothing.
+ * workspace: ngp_march_rays_train_workspace_bytes(N) bytes of device scratch. */
+int64_t ngp_march_rays_train_workspace_bytes(int64_t N);
+int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                         uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M, const float *nears,
+                         const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
+                         uint32_t perturb, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+
+/* composite_rays_train_forward / _backward (raymarching.cu:505-593, 606-699).  grad_sigmas [M], grad_rgbs [M,3] must be
+ * pre-zeroed (raymarching.py:272-273). */
+int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays,
+                                     int64_t M, int64_t N, float *weights_sum, float *depth, float *image,
+                                     ngp_stream_t stream);
+int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float *grad_image, const float *sigmas,
+                                      const float *rgbs, const float *deltas, const int32_t *rays,
+                                      const float *weights_sum, const float *image, int64_t M, int64_t N,
+                                      float *grad_sigmas, float *grad_rgbs, ngp_stream_t stream);
+
+/* march_rays / composite_rays (raymarching.cu:706-825, 828-922): inference stepping of the alive rays.
+ * xyzs/dirs [n_alive*n_step,3], deltas [n_alive*n_step,2] pre-zeroed (delta == 0 marks an unused slot). */
+int ngp_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *rays_alive, const float *rays_t,
+                   const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                   uint32_t H, const uint8_t *grid, const float *nears, const float *fars, float *xyzs, float *dirs,
+                   float *deltas, uint32_t perturb, ngp_stream_t stream);
+int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, float *rays_t, const float *sigmas,
+                       const float *rgbs, const float *deltas, float *weights_sum, float *depth, float *image,
+                       ngp_stream_t stream);
+
+/* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
+
+/* sh_encode_forward (shencoder.cu:386-412).  inputs [B,3] -> outputs [B,degree^2]; dy_dx [B,3,degree^2] optional. */
+int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_t B, int D, int degree, int calc_grad_inputs,
+                          float *dy_dx, ngp_stream_t stream);
+/* sh_encode_backward (shencoder.cu:414-440): grad_inputs [B,3] overwritten; Jacobian recomputed from inputs. */
+int ngp_sh_encode_backward(const float *grad, const float *inputs, int64_t B, int D, int degree, float *grad_inputs,
+                           ngp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,18 @@ _SIGNATURES = {
     "ngp_grid_encode_forward": ([P, P, I, P, P, I, I64, I, I, I, F, U32, I, P, U32, I, P, P], I),
     "ngp_grid_encode_backward_input": ([P, I, P, P, I, P, P, I64, I, I, I, F, U32, U32, I, P], I),
     "ngp_field_query_forward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, I64, P], I),
+    "ngp_near_far_from_aabb": ([P, P, P, I64, F, P, P, P], I),
+    "ngp_morton3D": ([P, I64, P, P], I),
+    "ngp_morton3D_invert": ([P, I64, P, P], I),
+    "ngp_packbits": ([P, I64, F, P, P], I),
+    "ngp_march_rays_train_workspace_bytes": ([I64], I64),
+    "ngp_march_rays_train": ([P, P, P, F, F, U32, I64, U32, U32, I64, P, P, P, P, P, P, P, U32, P, I64, P], I),
+    "ngp_composite_rays_train_forward": ([P, P, P, P, I64, I64, P, P, P, P], I),
+    "ngp_composite_rays_train_backward": ([P, P, P, P, P, P, P, P, I64, I64, P, P, P], I),
+    "ngp_march_rays": ([I64, U32, P, P, P, P, F, F, U32, U32, U32, P, P, P, P, P, P, U32, P], I),
+    "ngp_composite_rays": ([I64, U32, P, P, P, P, P, P, P, P, P], I),
+    "ngp_sh_encode_forward": ([P, P, I64, I, I, I, P, P], I),
+    "ngp_sh_encode_backward": ([P, P, I64, I, I, P, P], I),
     "ngp_field_query_backward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, I64, P], I),
 }
 

@@ -1,0 +1,135 @@
+// march.cuh — occupancy-grid marcher shared by the standalone ray ops and the fused render kernels.
+// Reference semantics: raymarching/src/raymarching.cu:44-83 (mip level, Morton), :361-403 (one marcher iteration).
+// Arithmetic notes (bit-exact sample counts are the target): explicit fmaf where nvcc contracts the reference
+// expression under its default -fmad=true; the cell index product `0.5 * (x/mip_bound + 1) * H` is evaluated in
+// fp64 in the reference (double literal) — for power-of-two H the fp32 product is exact and identical, otherwise the
+// fp64 path is taken.
+#pragma once
+#include <stdint.h>
+
+__host__ __device__ __forceinline__ uint32_t ngp_expand_bits(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+__host__ __device__ __forceinline__ uint32_t ngp_morton3D(uint32_t x, uint32_t y, uint32_t z) {
+    return ngp_expand_bits(x) | (ngp_expand_bits(y) << 1) | (ngp_expand_bits(z) << 2);
+}
+__host__ __device__ __forceinline__ uint32_t ngp_morton_compact(uint32_t x) {
+    x &= 0x49249249u;
+    x = (x | (x >> 2)) & 0xc30c30c3u;
+    x = (x | (x >> 4)) & 0x0f00f00fu;
+    x = (x | (x >> 8)) & 0xff0000ffu;
+    x = (x | (x >> 16)) & 0x0000ffffu;
+    return x;
+}
+
+struct MarchRay {
+    float ox, oy, oz, dx, dy, dz, rdx, rdy, rdz;
+};
+
+struct MarchCfg {
+    float bound, dt_gamma, dt_min, dt_max, rH, Hf;
+    uint32_t C, H, H3;
+    int h_pow2;
+    const uint8_t *grid;
+};
+
+__host__ __device__ __forceinline__ MarchCfg ngp_march_cfg(const uint8_t *grid, float bound, float dt_gamma,
+                                                           uint32_t max_steps, uint32_t C, uint32_t H) {
+    MarchCfg c;
+    c.bound = bound;
+    c.dt_gamma = dt_gamma;
+    c.dt_min = 2.0f * 1.7320508075688772f / (float)max_steps;                   // raymarching.cu:347
+    c.dt_max = 2.0f * 1.7320508075688772f * (float)(1u << (C - 1)) / (float)H;  // :348
+    c.rH = 1.0f / (float)H;
+    c.Hf = (float)H;
+    c.C = C;
+    c.H = H;
+    c.H3 = H * H * H;
+    c.h_pow2 = (H & (H - 1)) == 0;
+    c.grid = grid;
+    return c;
+}
+
+__device__ __forceinline__ float ngp_clampf(float v, float lo, float hi) { return fminf(hi, fmaxf(lo, v)); }
+
+// frexpf exponent clamped to [0, C-1]  (raymarching.cu:44-56)
+__device__ __forceinline__ int ngp_mip_level(float v, uint32_t C) {
+    int e;
+    frexpf(v, &e);
+    return min((int)C - 1, max(0, e));
+}
+
+__device__ __forceinline__ int ngp_cell_coord(float p, float mip_rbound, const MarchCfg &c) {
+    const float u = fmaf(p, mip_rbound, 1.0f);
+    float v;
+    if (c.h_pow2) v = 0.5f * u * c.Hf;
+    else v = (float)(0.5 * (double)u * (double)c.H);
+    return (int)ngp_clampf(v, 0.0f, c.Hf - 1.0f);
+}
+
+// One marcher iteration at parameter t.  Occupied: returns true, sample position in (px,py,pz), step in dt, t unchanged.
+// Empty: returns false with t advanced past the voxel (raymarching.cu:393-402).
+__device__ __forceinline__ bool ngp_march_step(const MarchRay &r, const MarchCfg &c, float &t, float &px, float &py,
+                                               float &pz, float &dt) {
+    const float t0 = t;
+    const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
+    const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
+    const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
+    dt = ngp_clampf(t0 * c.dt_gamma, c.dt_min, c.dt_max);
+    const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+    const int level = max(ngp_mip_level(mx, c.C), ngp_mip_level(dt * c.Hf * 0.5f, c.C));
+    const float mip_bound = fminf((float)(1 << level), c.bound);
+    const float mip_rbound = 1.0f / mip_bound;
+    const int nx = ngp_cell_coord(x, mip_rbound, c);
+    const int ny = ngp_cell_coord(y, mip_rbound, c);
+    const int nz = ngp_cell_coord(z, mip_rbound, c);
+    const uint32_t index = (uint32_t)level * c.H3 + ngp_morton3D((uint32_t)nx, (uint32_t)ny, (uint32_t)nz);
+    const bool occ = (__ldg(c.grid + (index >> 3)) >> (index & 7u)) & 1u;
+    if (occ) {
+        px = x; py = y; pz = z;
+        return true;
+    }
+    const float tx = fmaf(fmaf(((float)nx + 0.5f + 0.5f * copysignf(1.0f, r.dx)) * c.rH, 2.0f, -1.0f), mip_bound, -x) * r.rdx;
+    const float ty = fmaf(fmaf(((float)ny + 0.5f + 0.5f * copysignf(1.0f, r.dy)) * c.rH, 2.0f, -1.0f), mip_bound, -y) * r.rdy;
+    const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;
+    const float tt = t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
+    float tc = t0;
+    do {
+        tc += ngp_clampf(tc * c.dt_gamma, c.dt_min, c.dt_max);
+    } while (tc < tt);
+    t = tc;
+    return false;
+}
+
+// ---- PCG32 (O'Neill) as used by raymarching/src/pcg32.h: seed(:57-72), advance(:149-170), next_float(:107-116)
+struct NgpPcg32 {
+    uint64_t state, inc;
+};
+__device__ __forceinline__ uint32_t ngp_pcg_next(NgpPcg32 &r) {
+    const uint64_t old = r.state;
+    r.state = old * 0x5851f42d4c957f2dULL + r.inc;
+    const uint32_t xs = (uint32_t)(((old >> 18u) ^ old) >> 27u);
+    const uint32_t rot = (uint32_t)(old >> 59u);
+    return (xs >> rot) | (xs << ((~rot + 1u) & 31));
+}
+__device__ __forceinline__ float ngp_pcg_jitter(uint64_t seed, uint64_t n) {
+    NgpPcg32 r;
+    r.state = 0;
+    r.inc = (1ull << 1) | 1ull;
+    ngp_pcg_next(r);
+    r.state += seed;
+    ngp_pcg_next(r);
+    uint64_t cur_mult = 0x5851f42d4c957f2dULL, cur_plus = r.inc, acc_mult = 1, acc_plus = 0, delta = n;
+    while (delta > 0) {
+        if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+        cur_plus = (cur_mult + 1) * cur_plus;
+        cur_mult *= cur_mult;
+        delta >>= 1;
+    }
+    r.state = acc_mult * r.state + acc_plus;
+    return __uint_as_float((ngp_pcg_next(r) >> 9) | 0x3f800000u) - 1.0f;
+}

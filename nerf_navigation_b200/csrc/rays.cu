@@ -1,0 +1,469 @@
+// rays.cu — ray ops behind raymarching.*: AABB near/far, Morton codes, occupancy bit packing, occupancy-grid ray
+// marching (training: count -> scan -> write, deterministic; inference: alive-ray stepping) and front-to-back
+// compositing forward/backward.  Reference semantics: raymarching/src/raymarching.cu (line ranges cited per kernel).
+// Unlike the reference (atomicAdd slot reservation, raymarching.cu:409-410) sample offsets are an exclusive scan of the
+// per-ray counts in ray order, so `rays` rows and offsets are deterministic.
+#include <float.h>
+
+#include "common.cuh"
+#include "march.cuh"
+
+#define RAY_THREADS 128
+
+// ---------------------------------------------------------------- near/far  (raymarching.cu:93-147)
+__global__ void __launch_bounds__(RAY_THREADS)
+k_near_far(const float *__restrict__ rays_o, const float *__restrict__ rays_d, const float *__restrict__ aabb, int64_t N,
+           float min_near, float *__restrict__ nears, float *__restrict__ fars) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= N) return;
+    float tn = 0.0f, tf = 0.0f;
+    bool miss = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float o = rays_o[n * 3 + a];
+        const float r = 1.0f / rays_d[n * 3 + a];
+        float lo = (__ldg(aabb + a) - o) * r, hi = (__ldg(aabb + a + 3) - o) * r;
+        if (lo > hi) { const float t = lo; lo = hi; hi = t; }
+        if (a == 0) { tn = lo; tf = hi; continue; }
+        if (!miss) {
+            if (tn > hi || lo > tf) miss = true;
+            else {
+                if (lo > tn) tn = lo;
+                if (hi < tf) tf = hi;
+            }
+        }
+    }
+    if (miss) { nears[n] = FLT_MAX; fars[n] = FLT_MAX; return; }
+    if (tn < min_near) tn = min_near;
+    nears[n] = tn;
+    fars[n] = tf;
+}
+
+extern "C" int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, int64_t N,
+                                      float min_near, float *nears, float *fars, ngp_stream_t stream) {
+    NGP_REQUIRE(rays_o && rays_d && aabb && nears && fars, NGP_ERR_ARG, "ngp_near_far_from_aabb: null pointer");
+    if (N == 0) return NGP_OK;
+    k_near_far<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N,
+                                                                                              min_near, nears, fars);
+    NGP_CHECK_LAUNCH("ngp_near_far_from_aabb");
+    return NGP_OK;
+}
+
+// ---------------------------------------------------------------- morton  (raymarching.cu:216-262)
+__global__ void k_morton3D(const int32_t *__restrict__ coords, int64_t N, int32_t *__restrict__ indices) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    indices[n] = (int32_t)ngp_morton3D((uint32_t)coords[n * 3], (uint32_t)coords[n * 3 + 1], (uint32_t)coords[n * 3 + 2]);
+}
+__global__ void k_morton3D_invert(const int32_t *__restrict__ indices, int64_t N, int32_t *__restrict__ coords) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t v = (uint32_t)indices[n];
+    coords[n * 3] = (int32_t)ngp_morton_compact(v);
+    coords[n * 3 + 1] = (int32_t)ngp_morton_compact(v >> 1);
+    coords[n * 3 + 2] = (int32_t)ngp_morton_compact(v >> 2);
+}
+extern "C" int ngp_morton3D(const int32_t *coords, int64_t N, int32_t *indices, ngp_stream_t stream) {
+    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D: null pointer");
+    if (N == 0) return NGP_OK;
+    k_morton3D<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(coords, N, indices);
+    NGP_CHECK_LAUNCH("ngp_morton3D");
+    return NGP_OK;
+}
+extern "C" int ngp_morton3D_invert(const int32_t *indices, int64_t N, int32_t *coords, ngp_stream_t stream) {
+    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D_invert: null pointer");
+    if (N == 0) return NGP_OK;
+    k_morton3D_invert<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(indices, N, coords);
+    NGP_CHECK_LAUNCH("ngp_morton3D_invert");
+    return NGP_OK;
+}
+
+// ---------------------------------------------------------------- packbits  (raymarching.cu:269-291)
+// one thread per output byte; its 8 floats are two aligned float4 loads (32 B = one sector), stores coalesce.
+__global__ void k_packbits(const float *__restrict__ grid, int64_t N, float thresh, uint8_t *__restrict__ bitfield) {
+    const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    const float4 a = __ldg(reinterpret_cast<const float4 *>(grid) + n * 2);
+    const float4 b = __ldg(reinterpret_cast<const float4 *>(grid) + n * 2 + 1);
+    uint32_t bits = 0;
+    bits |= (a.x > thresh) ? 1u : 0u;
+    bits |= (a.y > thresh) ? 2u : 0u;
+    bits |= (a.z > thresh) ? 4u : 0u;
+    bits |= (a.w > thresh) ? 8u : 0u;
+    bits |= (b.x > thresh) ? 16u : 0u;
+    bits |= (b.y > thresh) ? 32u : 0u;
+    bits |= (b.z > thresh) ? 64u : 0u;
+    bits |= (b.w > thresh) ? 128u : 0u;
+    bitfield[n] = (uint8_t)bits;
+}
+extern "C" int ngp_packbits(const float *grid, int64_t N, float thresh, uint8_t *bitfield, ngp_stream_t stream) {
+    NGP_REQUIRE(grid && bitfield, NGP_ERR_ARG, "ngp_packbits: null pointer");
+    NGP_REQUIRE(((uintptr_t)grid & 15) == 0, NGP_ERR_ARG, "ngp_packbits: grid must be 16-byte aligned");
+    if (N == 0) return NGP_OK;
+    k_packbits<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(grid, N, thresh, bitfield);
+    NGP_CHECK_LAUNCH("ngp_packbits");
+    return NGP_OK;
+}
+
+// ---------------------------------------------------------------- training marcher  (raymarching.cu:313-484)
+__device__ __forceinline__ MarchRay load_ray(const float *__restrict__ rays_o, const float *__restrict__ rays_d, int64_t n) {
+    MarchRay r;
+    r.ox = rays_o[n * 3]; r.oy = rays_o[n * 3 + 1]; r.oz = rays_o[n * 3 + 2];
+    r.dx = rays_d[n * 3]; r.dy = rays_d[n * 3 + 1]; r.dz = rays_d[n * 3 + 2];
+    r.rdx = 1.0f / r.dx; r.rdy = 1.0f / r.dy; r.rdz = 1.0f / r.dz;
+    return r;
+}
+
+// pass 1: per-ray sample count (and jittered start t0 when perturb)
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, uint32_t max_steps,
+              int64_t N, const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
+              int32_t *__restrict__ counts) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= N) return;
+    const MarchRay r = load_ray(rays_o, rays_d, n);
+    float t = nears[n];
+    if (perturb) t += cfg.dt_min * ngp_pcg_jitter(42ull, (uint64_t)n);  // :352-355, seed :489
+    const float far = fars[n];
+    uint32_t steps = 0;
+    float px, py, pz, dt;
+    while (t < far && steps < max_steps) {
+        if (ngp_march_step(r, cfg, t, px, py, pz, dt)) {
+            ++steps;
+            t += dt;
+        }
+    }
+    counts[n] = (int32_t)steps;
+}
+
+// exclusive scan of counts -> offsets (3 kernels: per-block totals, scan of totals, per-block scan + base)
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 8
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+
+__device__ __forceinline__ int32_t block_exclusive_scan(int32_t v, int32_t *total) {
+    __shared__ int32_t warp_sums[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int32_t w = lane < SCAN_THREADS / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < SCAN_THREADS / 32; o <<= 1) {
+            const int32_t u = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += u;
+        }
+        if (lane < SCAN_THREADS / 32) warp_sums[lane] = w;
+    }
+    __syncthreads();
+    const int32_t base = warp > 0 ? warp_sums[warp - 1] : 0;
+    *total = warp_sums[SCAN_THREADS / 32 - 1];
+    __syncthreads();
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan_tile_totals(const int32_t *__restrict__ counts, int64_t N, int32_t *__restrict__ tile_totals) {
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i)
+        if (base + i < N) s += counts[base + i];
+    int32_t total;
+    block_exclusive_scan(s, &total);
+    if (threadIdx.x == 0) tile_totals[blockIdx.x] = total;
+}
+
+// single block: in-place exclusive scan of tile totals, adds the incoming counter value, bumps the counters
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan_totals(int32_t *__restrict__ tile_totals, int64_t n_tiles, int32_t *__restrict__ counter, int64_t N) {
+    __shared__ int32_t carry;
+    if (threadIdx.x == 0) carry = counter[0];
+    __syncthreads();
+    for (int64_t start = 0; start < n_tiles; start += SCAN_THREADS) {
+        const int64_t i = start + threadIdx.x;
+        const int32_t v = i < n_tiles ? tile_totals[i] : 0;
+        int32_t total;
+        const int32_t ex = block_exclusive_scan(v, &total);
+        const int32_t c = carry;
+        if (i < n_tiles) tile_totals[i] = c + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        counter[0] = carry;          // total samples (reference: atomicAdd(counter, num_steps))
+        counter[1] += (int32_t)N;    // rays processed   (atomicAdd(counter + 1, 1))
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+k_scan_write_rays(const int32_t *__restrict__ counts, const int32_t *__restrict__ tile_totals, int64_t N,
+                  int32_t *__restrict__ rays) {
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int32_t c[SCAN_ITEMS];
+    int32_t s = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        c[i] = base + i < N ? counts[base + i] : 0;
+        s += c[i];
+    }
+    int32_t total;
+    int32_t off = block_exclusive_scan(s, &total) + tile_totals[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if (base + i < N) {
+            rays[(base + i) * 3] = (int32_t)(base + i);
+            rays[(base + i) * 3 + 1] = off;
+            rays[(base + i) * 3 + 2] = c[i];
+        }
+        off += c[i];
+    }
+}
+
+// pass 2: write samples at the scanned offsets
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
+              const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
+              const int32_t *__restrict__ rays, float *__restrict__ xyzs, float *__restrict__ dirs,
+              float *__restrict__ deltas) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= N) return;
+    const int64_t off = rays[n * 3 + 1];
+    const uint32_t cnt = (uint32_t)rays[n * 3 + 2];
+    if (cnt == 0 || off + cnt >= M) return;  // :419-420
+    const MarchRay r = load_ray(rays_o, rays_d, n);
+    float t = nears[n];
+    if (perturb) t += cfg.dt_min * ngp_pcg_jitter(42ull, (uint64_t)n);
+    float last_t = t;
+    const float far = fars[n];
+    uint32_t step = 0;
+    float px, py, pz, dt;
+    while (t < far && step < cnt) {
+        if (!ngp_march_step(r, cfg, t, px, py, pz, dt)) continue;
+        const int64_t k = off + step;
+        xyzs[k * 3] = px; xyzs[k * 3 + 1] = py; xyzs[k * 3 + 2] = pz;
+        dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+        t += dt;
+        deltas[k * 2] = dt;
+        deltas[k * 2 + 1] = t - last_t;
+        last_t = t;
+        ++step;
+    }
+}
+
+extern "C" int64_t ngp_march_rays_train_workspace_bytes(int64_t N) {
+    return (N + ngp_div_up(N, SCAN_TILE) + 8) * (int64_t)sizeof(int32_t);
+}
+
+extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound,
+                                    float dt_gamma, uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M,
+                                    const float *nears, const float *fars, float *xyzs, float *dirs, float *deltas,
+                                    int32_t *rays, int32_t *counter, uint32_t perturb, void *workspace,
+                                    int64_t workspace_bytes, ngp_stream_t stream) {
+    NGP_REQUIRE(rays_o && rays_d && grid && nears && fars && rays && counter, NGP_ERR_ARG,
+                "ngp_march_rays_train: null pointer");
+    NGP_REQUIRE(M == 0 || (xyzs && dirs && deltas), NGP_ERR_ARG, "ngp_march_rays_train: null sample buffers");
+    NGP_REQUIRE(C >= 1 && C <= 8 && H >= 1 && H <= 1024, NGP_ERR_ARG, "ngp_march_rays_train: bad cascade/grid size");
+    NGP_REQUIRE(workspace && workspace_bytes >= ngp_march_rays_train_workspace_bytes(N), NGP_ERR_ARG,
+                "ngp_march_rays_train: workspace too small");
+    if (N == 0) return NGP_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t *counts = (int32_t *)workspace;
+    int32_t *tile_totals = counts + N;
+    const int64_t n_tiles = ngp_div_up(N, SCAN_TILE);
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
+    const unsigned gr = (unsigned)ngp_div_up(N, RAY_THREADS);
+    k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts);
+    k_scan_tile_totals<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, N, tile_totals);
+    k_scan_totals<<<1, SCAN_THREADS, 0, st>>>(tile_totals, n_tiles, counter, N);
+    k_scan_write_rays<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, tile_totals, N, rays);
+    k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, xyzs, dirs, deltas);
+    NGP_CHECK_LAUNCH("ngp_march_rays_train");
+    return NGP_OK;
+}
+
+// ---------------------------------------------------------------- compositing, training  (raymarching.cu:505-582, 606-688)
+// __expf as in the reference (fast intrinsic) so alpha matches its CUDA build.
+__global__ void __launch_bounds__(RAY_THREADS)
+k_composite_train_fwd(const float *__restrict__ sigmas, const float *__restrict__ rgbs, const float *__restrict__ deltas,
+                      const int32_t *__restrict__ rays, int64_t M, int64_t N, float *__restrict__ weights_sum,
+                      float *__restrict__ depth, float *__restrict__ image) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)rays[n * 3], off = (uint32_t)rays[n * 3 + 1], cnt = (uint32_t)rays[n * 3 + 2];
+    float T = 1.0f, r = 0.0f, g = 0.0f, b = 0.0f, ws = 0.0f, t = 0.0f, d = 0.0f;
+    if (cnt != 0 && (int64_t)off + cnt < M) {
+        for (uint32_t s = 0; s < cnt; ++s) {
+            const int64_t k = (int64_t)off + s;
+            const float2 dl = __ldg(reinterpret_cast<const float2 *>(deltas) + k);
+            const float alpha = 1.0f - __expf(-__ldg(sigmas + k) * dl.x);
+            const float w = alpha * T;
+            r = fmaf(w, __ldg(rgbs + k * 3), r);
+            g = fmaf(w, __ldg(rgbs + k * 3 + 1), g);
+            b = fmaf(w, __ldg(rgbs + k * 3 + 2), b);
+            t += dl.y;
+            d = fmaf(w, t, d);
+            ws += w;
+            T *= 1.0f - alpha;
+            if (T < 1e-4f) break;
+        }
+    }
+    weights_sum[id] = ws;
+    depth[id] = d;
+    image[id * 3] = r; image[id * 3 + 1] = g; image[id * 3 + 2] = b;
+}
+
+__global__ void __launch_bounds__(RAY_THREADS)
+k_composite_train_bwd(const float *__restrict__ grad_ws, const float *__restrict__ grad_image,
+                      const float *__restrict__ sigmas, const float *__restrict__ rgbs, const float *__restrict__ deltas,
+                      const int32_t *__restrict__ rays, const float *__restrict__ weights_sum,
+                      const float *__restrict__ image, int64_t M, int64_t N, float *__restrict__ grad_sigmas,
+                      float *__restrict__ grad_rgbs) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)rays[n * 3], off = (uint32_t)rays[n * 3 + 1], cnt = (uint32_t)rays[n * 3 + 2];
+    if (cnt == 0 || (int64_t)off + cnt >= M) return;
+    const float gr = grad_image[id * 3], gg = grad_image[id * 3 + 1], gb = grad_image[id * 3 + 2], gws = grad_ws[id];
+    const float rf = image[id * 3], gf = image[id * 3 + 1], bf = image[id * 3 + 2], wsf = weights_sum[id];
+    float T = 1.0f, r = 0.0f, g = 0.0f, b = 0.0f;
+    for (uint32_t s = 0; s < cnt; ++s) {
+        const int64_t k = (int64_t)off + s;
+        const float dl0 = __ldg(deltas + k * 2);
+        const float c0 = __ldg(rgbs + k * 3), c1 = __ldg(rgbs + k * 3 + 1), c2 = __ldg(rgbs + k * 3 + 2);
+        const float alpha = 1.0f - __expf(-__ldg(sigmas + k) * dl0);
+        const float w = alpha * T;
+        r = fmaf(w, c0, r);
+        g = fmaf(w, c1, g);
+        b = fmaf(w, c2, b);
+        T *= 1.0f - alpha;
+        if (T < 1e-4f) break;  // before writing this sample's gradients (:658-661)
+        grad_rgbs[k * 3] = gr * w; grad_rgbs[k * 3 + 1] = gg * w; grad_rgbs[k * 3 + 2] = gb * w;
+        grad_sigmas[k] = dl0 * (gr * (T * c0 - (rf - r)) + gg * (T * c1 - (gf - g)) + gb * (T * c2 - (bf - b)) +
+                                gws * (1.0f - wsf));
+    }
+}
+
+extern "C" int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas,
+                                                const int32_t *rays, int64_t M, int64_t N, float *weights_sum,
+                                                float *depth, float *image, ngp_stream_t stream) {
+    NGP_REQUIRE(rays && weights_sum && depth && image, NGP_ERR_ARG, "ngp_composite_rays_train_forward: null pointer");
+    NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas), NGP_ERR_ARG, "ngp_composite_rays_train_forward: null samples");
+    if (N == 0) return NGP_OK;
+    k_composite_train_fwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        sigmas, rgbs, deltas, rays, M, N, weights_sum, depth, image);
+    NGP_CHECK_LAUNCH("ngp_composite_rays_train_forward");
+    return NGP_OK;
+}
+
+extern "C" int ngp_composite_rays_train_backward(const float *grad_weights_sum, const float *grad_image,
+                                                 const float *sigmas, const float *rgbs, const float *deltas,
+                                                 const int32_t *rays, const float *weights_sum, const float *image,
+                                                 int64_t M, int64_t N, float *grad_sigmas, float *grad_rgbs,
+                                                 ngp_stream_t stream) {
+    NGP_REQUIRE(grad_weights_sum && grad_image && rays && weights_sum && image, NGP_ERR_ARG,
+                "ngp_composite_rays_train_backward: null pointer");
+    NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas && grad_sigmas && grad_rgbs), NGP_ERR_ARG,
+                "ngp_composite_rays_train_backward: null samples");
+    if (N == 0) return NGP_OK;
+    k_composite_train_bwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, grad_sigmas, grad_rgbs);
+    NGP_CHECK_LAUNCH("ngp_composite_rays_train_backward");
+    return NGP_OK;
+}
+
+// ---------------------------------------------------------------- inference marcher / compositor  (:706-814, :828-913)
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *__restrict__ rays_alive, const float *__restrict__ rays_t,
+             const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg,
+             const float *__restrict__ fars, float *__restrict__ xyzs, float *__restrict__ dirs,
+             float *__restrict__ deltas, uint32_t perturb) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= n_alive) return;
+    const int32_t id = rays_alive[n];
+    const MarchRay r = load_ray(rays_o, rays_d, id);
+    float t = rays_t[id];
+    if (perturb) t += cfg.dt_min * ngp_pcg_jitter((uint64_t)perturb, (uint64_t)n);  // :745-748, seed :819
+    float last_t = t;
+    const float far = fars[id];
+    uint32_t step = 0;
+    float px, py, pz, dt;
+    while (t < far && step < n_step) {
+        if (!ngp_march_step(r, cfg, t, px, py, pz, dt)) continue;
+        const int64_t k = n * n_step + step;
+        xyzs[k * 3] = px; xyzs[k * 3 + 1] = py; xyzs[k * 3 + 2] = pz;
+        dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+        t += dt;
+        deltas[k * 2] = dt;
+        deltas[k * 2 + 1] = t - last_t;
+        last_t = t;
+        ++step;
+    }
+}
+
+__global__ void __launch_bounds__(RAY_THREADS)
+k_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *__restrict__ rays_alive, float *__restrict__ rays_t,
+                 const float *__restrict__ sigmas, const float *__restrict__ rgbs, const float *__restrict__ deltas,
+                 float *__restrict__ weights_sum, float *__restrict__ depth, float *__restrict__ image) {
+    const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (n >= n_alive) return;
+    const int32_t id = rays_alive[n];
+    float t = rays_t[id], ws = weights_sum[id], d = depth[id];
+    float r = image[id * 3], g = image[id * 3 + 1], b = image[id * 3 + 2];
+    uint32_t step = 0;
+    while (step < n_step) {
+        const int64_t k = n * n_step + step;
+        const float dl0 = deltas[k * 2];
+        if (dl0 == 0.0f) break;
+        const float alpha = 1.0f - __expf(-sigmas[k] * dl0);
+        const float T = 1.0f - ws;
+        const float w = alpha * T;
+        ws += w;
+        t += deltas[k * 2 + 1];
+        d = fmaf(w, t, d);
+        r = fmaf(w, rgbs[k * 3], r);
+        g = fmaf(w, rgbs[k * 3 + 1], g);
+        b = fmaf(w, rgbs[k * 3 + 2], b);
+        if ((double)T < 1e-4) break;  // double literal in the reference (:880)
+        ++step;
+    }
+    if (step < n_step) rays_alive[n] = -1;
+    else rays_t[id] = t;
+    weights_sum[id] = ws;
+    depth[id] = d;
+    image[id * 3] = r; image[id * 3 + 1] = g; image[id * 3 + 2] = b;
+}
+
+extern "C" int ngp_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *rays_alive, const float *rays_t,
+                              const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps,
+                              uint32_t C, uint32_t H, const uint8_t *grid, const float *nears, const float *fars,
+                              float *xyzs, float *dirs, float *deltas, uint32_t perturb, ngp_stream_t stream) {
+    (void)nears;
+    NGP_REQUIRE(rays_alive && rays_t && rays_o && rays_d && grid && fars && xyzs && dirs && deltas, NGP_ERR_ARG,
+                "ngp_march_rays: null pointer");
+    NGP_REQUIRE(C >= 1 && C <= 8 && H >= 1 && H <= 1024, NGP_ERR_ARG, "ngp_march_rays: bad cascade/grid size");
+    if (n_alive == 0) return NGP_OK;
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
+    k_march_rays<<<(unsigned)ngp_div_up(n_alive, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, cfg, fars, xyzs, dirs, deltas, perturb);
+    NGP_CHECK_LAUNCH("ngp_march_rays");
+    return NGP_OK;
+}
+
+extern "C" int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, float *rays_t,
+                                  const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum,
+                                  float *depth, float *image, ngp_stream_t stream) {
+    NGP_REQUIRE(rays_alive && rays_t && sigmas && rgbs && deltas && weights_sum && depth && image, NGP_ERR_ARG,
+                "ngp_composite_rays: null pointer");
+    if (n_alive == 0) return NGP_OK;
+    k_composite_rays<<<(unsigned)ngp_div_up(n_alive, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image);
+    NGP_CHECK_LAUNCH("ngp_composite_rays");
+    return NGP_OK;
+}

@@ -30,7 +30,7 @@ class _field_query(Function):
         B = x.shape[0]
         sigma = torch.empty(B, device=x.device, dtype=torch.float32)
         geo = torch.empty(B, 15, device=x.device, dtype=torch.float32)
-        need_bwd = x.requires_grad
+        need_bwd = ctx.needs_input_grad[0]
         mask = torch.empty(B, device=x.device, dtype=torch.int64) if need_bwd else None
         with torch.cuda.device(x.device):
             _lib.check(_lib.lib().ngp_field_query_forward(

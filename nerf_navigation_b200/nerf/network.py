@@ -1,0 +1,111 @@
+"""NeRFNetwork — host-side mirror of the reference's nerf/network.py:10-206 (same ctor kwargs, module/parameter names
+`encoder.embeddings`, `encoder.offsets`, `sigma_net.{i}.weight`, `color_net.{i}.weight`, same density()/forward()/color()
+contracts) with the hot path routed to the B200 kernels:
+
+* density(x): one fused kernel (hash-grid encode + sigma MLP + trunc_exp), one fused backward-to-x kernel, in eval
+  mode (the planner / estimator case: simulate.py:191 model.eval(), :343-347), where the field is frozen and gradients
+  flow to x only.  In training mode the unfused GridEncoder -> nn.Linear path runs so autograd produces table/MLP gradients.
+* forward(x, d) / color(): GridEncoder + SHEncoder kernels + nn.Linear (torch) — see renderer.py for the fused ray path.
+
+The background model (`bg_radius > 0`, network.py:70-92, 145-160) is out of scope: nav uses bg_radius=-1.
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..activation import trunc_exp
+from ..encoding import get_encoder
+from ..field import field_query, fused_supported
+from .renderer import NeRFRenderer
+
+
+class NeRFNetwork(NeRFRenderer):
+    def __init__(self, encoding="hashgrid", encoding_dir="sphere_harmonics", encoding_bg="hashgrid", num_layers=2,
+                 hidden_dim=64, geo_feat_dim=15, num_layers_color=3, hidden_dim_color=64, num_layers_bg=2,
+                 hidden_dim_bg=64, bound=1, **kwargs):
+        super().__init__(bound, **kwargs)
+        if self.bg_radius > 0:
+            raise NotImplementedError("background model (bg_radius > 0) is out of scope; nav uses bg_radius=-1")
+        self.num_layers = num_layers
+        self.hidden_dim = hidden_dim
+        self.geo_feat_dim = geo_feat_dim
+        self.encoder, self.in_dim = get_encoder(encoding, desired_resolution=2048 * bound)
+        sigma_net = []
+        for l in range(num_layers):
+            in_dim = self.in_dim if l == 0 else hidden_dim
+            out_dim = 1 + self.geo_feat_dim if l == num_layers - 1 else hidden_dim
+            sigma_net.append(nn.Linear(in_dim, out_dim, bias=False))
+        self.sigma_net = nn.ModuleList(sigma_net)
+
+        self.num_layers_color = num_layers_color
+        self.hidden_dim_color = hidden_dim_color
+        self.encoder_dir, self.in_dim_dir = get_encoder(encoding_dir)
+        color_net = []
+        for l in range(num_layers_color):
+            in_dim = self.in_dim_dir + self.geo_feat_dim if l == 0 else hidden_dim
+            out_dim = 3 if l == num_layers_color - 1 else hidden_dim
+            color_net.append(nn.Linear(in_dim, out_dim, bias=False))
+        self.color_net = nn.ModuleList(color_net)
+        self.bg_net = None
+        self.fused_eval = True  # route eval-mode density() through the fused kernels
+
+    # ------------------------------------------------------------------ helpers
+    def _use_fused_density(self, x):
+        # eval mode == frozen field (simulate.py:191 calls model.eval()): gradients flow to x only.
+        return (self.fused_eval and not self.training and x.is_cuda and self.num_layers == 2
+                and hasattr(self.encoder, "embeddings")
+                and fused_supported(self.encoder, self.sigma_net[0].weight, self.sigma_net[1].weight, x))
+
+    def _sigma_mlp(self, h):
+        for l in range(self.num_layers):
+            h = self.sigma_net[l](h)
+            if l != self.num_layers - 1:
+                h = F.relu(h, inplace=True)
+        return h
+
+    def _color_mlp(self, d, geo_feat):
+        d = self.encoder_dir(d)
+        h = torch.cat([d, geo_feat], dim=-1)
+        for l in range(self.num_layers_color):
+            h = self.color_net[l](h)
+            if l != self.num_layers_color - 1:
+                h = F.relu(h, inplace=True)
+        return torch.sigmoid(h)
+
+    # ------------------------------------------------------------------ reference API
+    def density(self, x):
+        """network.py:126-143 -> {'sigma': [...], 'geo_feat': [..., 15]}."""
+        if self._use_fused_density(x):
+            sigma, geo_feat = field_query(x, self.encoder, self.sigma_net[0].weight.detach(),
+                                          self.sigma_net[1].weight.detach(), self.bound)
+            return {"sigma": sigma, "geo_feat": geo_feat}
+        h = self._sigma_mlp(self.encoder(x, bound=self.bound))
+        return {"sigma": trunc_exp(h[..., 0]), "geo_feat": h[..., 1:]}
+
+    def forward(self, x, d):
+        """network.py:95-124 -> (sigma [...], color [..., 3])."""
+        dens = self.density(x)
+        return dens["sigma"], self._color_mlp(d, dens["geo_feat"])
+
+    def color(self, x, d, mask=None, geo_feat=None, **kwargs):
+        """network.py:163-191 (masked colour query used by the non-cuda_ray renderer)."""
+        if mask is not None:
+            rgbs = torch.zeros(mask.shape[0], 3, dtype=x.dtype, device=x.device)
+            if not mask.any():
+                return rgbs
+            x, d, geo_feat = x[mask], d[mask], geo_feat[mask]
+        h = self._color_mlp(d, geo_feat)
+        if mask is not None:
+            rgbs[mask] = h.to(rgbs.dtype)
+        else:
+            rgbs = h
+        return rgbs
+
+    def get_params(self, lr):
+        """network.py:194-206."""
+        return [
+            {"params": self.encoder.parameters(), "lr": lr},
+            {"params": self.sigma_net.parameters(), "lr": lr},
+            {"params": self.encoder_dir.parameters(), "lr": lr},
+            {"params": self.color_net.parameters(), "lr": lr},
+        ]

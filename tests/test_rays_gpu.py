@@ -1,0 +1,167 @@
+"""GPU parity: ray ops (C ABI via the raymarching mirror) vs the CPU oracle and vs the reference's CUDA build."""
+import numpy as np
+import pytest
+import torch
+
+from util import stonehenge_grid, orbit_rays, rel_err, load_ref
+
+pytestmark = pytest.mark.gpu
+
+BOUND, CAS, H = 2.0, 2, 128
+
+
+@pytest.fixture(scope="module")
+def scene(oracle):
+    grid = stonehenge_grid(CAS, H, BOUND)
+    bits = oracle.packbits(grid, 10.0)
+    return grid, bits
+
+
+def _rays(n, seed=0):
+    o, d = orbit_rays(n, seed)
+    return o, d
+
+
+def test_packbits_morton_bit_exact(ngp, oracle, scene):
+    from nerf_navigation_b200 import raymarching as rm
+    grid, bits = scene
+    out = rm.packbits(torch.from_numpy(grid).cuda(), 10.0)
+    assert np.array_equal(out.cpu().numpy(), bits)
+    rng = np.random.default_rng(0)
+    coords = rng.integers(0, 1024, (5000, 3)).astype(np.int32)
+    idx = rm.morton3D(torch.from_numpy(coords).cuda())
+    assert np.array_equal(idx.cpu().numpy(), oracle.morton3D(coords))
+    back = rm.morton3D_invert(idx)
+    assert np.array_equal(back.cpu().numpy(), coords)
+
+
+def test_near_far_vs_oracle(ngp, oracle):
+    from nerf_navigation_b200 import raymarching as rm
+    o, d = _rays(20000, 1)
+    d[:5] = [[0, 0, 1], [1, 0, 0], [0, -1, 0], [0.6, 0.8, 0], [0, 0, -1]]   # axis-parallel: 1/0 = inf paths
+    o[5:10] = [5.0, 5.0, 5.0]                                                # outside, most miss
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    rn, rf = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    n, f = rm.near_far_from_aabb(torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda(), torch.from_numpy(aabb).cuda(), 0.2)
+    assert np.array_equal(n.cpu().numpy(), rn, equal_nan=True) and np.array_equal(f.cpu().numpy(), rf, equal_nan=True)
+
+
+@pytest.mark.parametrize("perturb", [False, True])
+def test_march_rays_train_vs_oracle(ngp, oracle, scene, perturb):
+    from nerf_navigation_b200 import raymarching as rm
+    _, bits = scene
+    N = 8192
+    o, d = _rays(N, 2)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    M = N * 1024
+    rx, rd, rdl, rrays, rcnt = oracle.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, M, perturb=perturb)
+    t = lambda a: torch.from_numpy(a).cuda()
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    xyzs, dirs, deltas, rays = rm.march_rays_train(t(o), t(d), BOUND, t(bits), CAS, H, t(nears), t(fars), counter, -1,
+                                                   perturb, 128, True, 0, 1024)
+    assert np.array_equal(rays.cpu().numpy(), rrays)                 # ids, offsets, counts bit-exact
+    assert np.array_equal(counter.cpu().numpy(), rcnt)
+    m = int(rcnt[0])
+    assert m > 1000 and xyzs.shape[0] == m + (128 - m % 128)
+    assert np.array_equal(xyzs[:m].cpu().numpy(), rx[:m])
+    assert np.array_equal(dirs[:m].cpu().numpy(), rd[:m])
+    assert np.array_equal(deltas[:m].cpu().numpy(), rdl[:m])
+    assert not xyzs[m:].any()
+
+
+def test_march_budget_drops_rays_like_reference(ngp, oracle, scene):
+    """mean_count budget: rays whose offset+count >= M write nothing (raymarching.cu:420)."""
+    from nerf_navigation_b200 import raymarching as rm
+    _, bits = scene
+    N = 2048
+    o, d = _rays(N, 3)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    M = 4096
+    rx, rd, rdl, rrays, rcnt = oracle.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, M)
+    assert rcnt[0] > M
+    t = lambda a: torch.from_numpy(a).cuda()
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    xyzs, dirs, deltas, rays = rm.march_rays_train(t(o), t(d), BOUND, t(bits), CAS, H, t(nears), t(fars), counter, M - 128,
+                                                   False, 128, False, 0, 1024)
+    assert xyzs.shape[0] == M
+    assert np.array_equal(rays.cpu().numpy(), rrays)
+    assert np.array_equal(xyzs.cpu().numpy(), rx) and np.array_equal(deltas.cpu().numpy(), rdl)
+
+
+def test_composite_train_fwd_bwd_vs_oracle(ngp, oracle, scene):
+    from nerf_navigation_b200 import raymarching as rm
+    _, bits = scene
+    N = 4096
+    o, d = _rays(N, 4)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    xyzs, dirs, deltas, rays, cnt = oracle.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, N * 1024)
+    m = int(cnt[0]); m_al = m + (128 - m % 128)
+    deltas = deltas[:m_al]
+    rng = np.random.default_rng(0)
+    sig = (rng.uniform(0, 1, m_al) ** 4 * 300).astype(np.float32)    # some rays saturate -> early termination path
+    rgb = rng.uniform(0, 1, (m_al, 3)).astype(np.float32)
+    ws, dep, img = oracle.composite_rays_train_forward(sig, rgb, deltas, rays)
+    gws = rng.standard_normal(N).astype(np.float32); gim = rng.standard_normal((N, 3)).astype(np.float32)
+    rgs, rgc = oracle.composite_rays_train_backward(gws, gim, sig, rgb, deltas, rays, ws, img)
+    t = lambda a: torch.from_numpy(a).cuda()
+    st, rt = t(sig).requires_grad_(), t(rgb).requires_grad_()
+    w2, d2, i2 = rm.composite_rays_train(st, rt, t(deltas), t(rays))
+    (w2 * t(gws)).sum().add((i2 * t(gim)).sum()).backward()
+    # __expf (device, like the reference CUDA) vs expf (oracle): 2 ulp on alpha
+    assert rel_err(w2.detach().cpu().numpy(), ws) < 1e-5
+    assert rel_err(d2.detach().cpu().numpy(), dep) < 1e-5
+    assert rel_err(i2.detach().cpu().numpy(), img) < 1e-5
+    assert rel_err(st.grad.cpu().numpy(), rgs) < 2e-5
+    assert rel_err(rt.grad.cpu().numpy(), rgc) < 1e-5
+
+
+def test_inference_loop_vs_oracle(ngp, oracle, scene):
+    """march_rays / composite_rays alive-ray loop (renderer.py:343-369) with an analytic field."""
+    from nerf_navigation_b200 import raymarching as rm
+    _, bits = scene
+    N = 3000
+    o, d = _rays(N, 5)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    field_s = lambda p: (40.0 * (0.5 + 0.5 * np.sin(7 * p[:, 0] + 3 * p[:, 1]))).astype(np.float32)
+    field_c = lambda p: np.ascontiguousarray((0.5 + 0.5 * np.cos(p * 5.0)).astype(np.float32))
+    t = lambda a: torch.from_numpy(a).cuda()
+    # oracle loop
+    alive = np.arange(N, dtype=np.int32); rt = nears.copy()
+    ws = np.zeros(N, np.float32); dep = np.zeros(N, np.float32); img = np.zeros((N, 3), np.float32)
+    # device loop
+    alive_d = torch.arange(N, dtype=torch.int32, device="cuda"); rt_d = t(nears).clone()
+    ws_d = torch.zeros(N, device="cuda"); dep_d = torch.zeros(N, device="cuda"); img_d = torch.zeros(N, 3, device="cuda")
+    step = 0
+    while step < 1024 and alive.shape[0] > 0:
+        n_alive = alive.shape[0]
+        assert alive_d.shape[0] == n_alive
+        n_step = max(min(N // n_alive, 8), 1)
+        x, dd, dl = oracle.march_rays(n_alive, n_step, alive, rt, o, d, BOUND, bits, CAS, H, nears, fars)
+        oracle.composite_rays(n_alive, n_step, alive, rt, field_s(x), field_c(x), dl, ws, dep, img)
+        xd, ddd, dld = rm.march_rays(n_alive, n_step, alive_d, rt_d, t(o), t(d), BOUND, t(bits), CAS, H, t(nears), t(fars),
+                                     -1, False, 0, 1024)
+        assert np.array_equal(xd.cpu().numpy(), x) and np.array_equal(dld.cpu().numpy(), dl)
+        rm.composite_rays(n_alive, n_step, alive_d, rt_d, t(field_s(x)), t(field_c(x)), dld, ws_d, dep_d, img_d)
+        assert np.array_equal(alive_d.cpu().numpy(), alive)          # same rays die at the same step
+        alive = alive[alive >= 0]; alive_d = rm.compact_alive(alive_d)
+        step += n_step
+    assert rel_err(ws_d.cpu().numpy(), ws) < 1e-5 and rel_err(img_d.cpu().numpy(), img) < 1e-5
+    assert rel_err(dep_d.cpu().numpy(), dep) < 1e-5
+
+
+def test_sh_vs_oracle(ngp, oracle):
+    from nerf_navigation_b200.shencoder import SHEncoder
+    _, d = _rays(10000, 6)
+    enc = SHEncoder(3, 4)
+    dt = torch.from_numpy(d).cuda().requires_grad_()
+    out = enc(dt)
+    ro, rj = oracle.sh_encode(d, 4, True)
+    assert rel_err(out.detach().cpu().numpy(), ro) < 1e-6
+    g = torch.randn(10000, 16, device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+    out.backward(g)
+    ref = np.einsum("bc,bdc->bd", g.cpu().numpy().astype(np.float64), rj.astype(np.float64))
+    assert rel_err(dt.grad.cpu().numpy(), ref) < 1e-5

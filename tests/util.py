@@ -37,3 +37,45 @@ def load_ref(name):
     """Reference CUDA extension built by oracle/build_ref.py, or None."""
     from oracle import build_ref
     return build_ref.load_ref(name)
+
+
+def stonehenge_grid(cascade=2, H=128, bound=2.0):
+    """ring of 12 upright boxes (0.12 x 0.12 x 0.5) at radius 0.7 + floor slab z < 0.02,
+    density 20 inside / 0 outside, on the [cascade, H^3] grid in Morton order (renderer.py:464-483 cell centres)."""
+    from oracle import oracle as O
+    ar = np.arange(H, dtype=np.int32)
+    xx, yy, zz = np.meshgrid(ar, ar, ar, indexing="ij")
+    coords = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], -1).astype(np.int32)
+    idx = O.morton3D(coords).astype(np.int64)
+    unit = 2.0 * coords.astype(np.float32) / (H - 1) - 1.0
+    grid = np.zeros((cascade, H ** 3), np.float32)
+    ang = np.arange(12) * (2 * np.pi / 12)
+    centres = np.stack([0.7 * np.cos(ang), 0.7 * np.sin(ang)], -1)
+    for cas in range(cascade):
+        b = min(2 ** cas, bound)
+        p = unit * (b - b / H)
+        occ = (p[:, 2] < 0.02) & (p[:, 2] > -0.1) & (np.abs(p[:, 0]) < 1.0) & (np.abs(p[:, 1]) < 1.0)
+        for c in centres:
+            occ |= (np.abs(p[:, 0] - c[0]) < 0.06) & (np.abs(p[:, 1] - c[1]) < 0.06) & (p[:, 2] >= 0.0) & (p[:, 2] < 0.5)
+        grid[cas, idx] = np.where(occ, 20.0, 0.0)
+    return grid
+
+
+def orbit_rays(n_rays, seed=0, radius=1.2, height=0.4, H=800, W=800, focal=1111.1, jitter=0.0):
+    """Pinhole rays (nerf/utils.py:52-116 conventions: x right, y down, z forward) from a camera on an orbit looking
+    at the origin; `n_rays` random pixels."""
+    rng = np.random.default_rng(seed)
+    ang = rng.uniform(0, 2 * np.pi)
+    eye = np.array([radius * np.cos(ang), radius * np.sin(ang), height], np.float64) + rng.normal(0, jitter, 3)
+    fwd = -eye / np.linalg.norm(eye)
+    right = np.cross(fwd, np.array([0.0, 0.0, 1.0])); right /= np.linalg.norm(right)
+    down = np.cross(fwd, right)
+    R = np.stack([right, down, fwd], -1)
+    pix = rng.integers(0, H * W, n_rays)
+    i = (pix % W).astype(np.float64) + 0.5
+    j = (pix // W).astype(np.float64) + 0.5
+    d_cam = np.stack([(i - W / 2) / focal, (j - H / 2) / focal, np.ones_like(i)], -1)
+    d = d_cam @ R.T
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    o = np.broadcast_to(eye, d.shape)
+    return np.ascontiguousarray(o, np.float32), np.ascontiguousarray(d, np.float32)
