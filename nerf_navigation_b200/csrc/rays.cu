@@ -123,7 +123,7 @@ k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     if (n >= N) return;
     const MarchRay r = load_ray(rays_o, rays_d, n);
     float t = nears[n];
-    if (perturb) t += cfg.dt_min * ngp_pcg_jitter(42ull, (uint64_t)n);  // :352-355, seed :489
+    if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);  // :352-355, seed :489
     const float far = fars[n];
     uint32_t steps = 0;
     float px, py, pz, dt;
@@ -240,7 +240,7 @@ k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     if (cnt == 0 || off + cnt >= M) return;  // :419-420
     const MarchRay r = load_ray(rays_o, rays_d, n);
     float t = nears[n];
-    if (perturb) t += cfg.dt_min * ngp_pcg_jitter(42ull, (uint64_t)n);
+    if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);
     float last_t = t;
     const float far = fars[n];
     uint32_t step = 0;
@@ -389,7 +389,7 @@ k_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *__restrict__ rays_
     const int32_t id = rays_alive[n];
     const MarchRay r = load_ray(rays_o, rays_d, id);
     float t = rays_t[id];
-    if (perturb) t += cfg.dt_min * ngp_pcg_jitter((uint64_t)perturb, (uint64_t)n);  // :745-748, seed :819
+    if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter((uint64_t)perturb, (uint64_t)n), t);  // :745-748, seed :819
     float last_t = t;
     const float far = fars[id];
     uint32_t step = 0;

@@ -572,7 +572,7 @@ void orc_march_rays_train(const float *rays_o, const float *rays_d, const uint8_
             orc_pcg32 r;
             orc_pcg_seed(&r, 42, 1);
             orc_pcg_advance(&r, (uint64_t)n);
-            t += m.dt_min * orc_pcg_float(&r);
+            t = fmaf(m.dt_min, orc_pcg_float(&r), t); /* nvcc contracts near + dt_min*u to one fma */
         }
         t0s[n] = t;
         const float far = fars[n];
@@ -692,7 +692,7 @@ void orc_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *rays_alive,
             orc_pcg32 r;
             orc_pcg_seed(&r, perturb, 1);
             orc_pcg_advance(&r, (uint64_t)n);
-            t += m.dt_min * orc_pcg_float(&r);
+            t = fmaf(m.dt_min, orc_pcg_float(&r), t); /* nvcc contracts near + dt_min*u to one fma */
         }
         float last_t = t;
         const float far = fars[id];

@@ -115,3 +115,22 @@ def test_sh_vs_reference_cuda(ngp):
     ref.sh_encode_backward(g, d, 50000, 3, 4, dy, gi_r)
     out.backward(g)
     assert rel_err(dt.grad.cpu().numpy(), gi_r.cpu().numpy()) < 1e-5
+
+
+def test_perturbed_march_vs_reference_cuda(ngp, ref):
+    """perturb=True: pcg32(seed 42).advance(n) jitter (raymarching.cu:352-355, 489) must reproduce bit-exactly."""
+    from nerf_navigation_b200 import raymarching as rm
+    N = 8192
+    grid, bits, o, d, aabb, nears, fars = _setup(ref, N, 13)
+    M = N * 1024
+    xr = torch.zeros(M, 3, device="cuda"); dr = torch.zeros(M, 3, device="cuda"); dlr = torch.zeros(M, 2, device="cuda")
+    rays_ref = torch.empty(N, 3, dtype=torch.int32, device="cuda"); cnt_ref = torch.zeros(2, dtype=torch.int32, device="cuda")
+    ref.march_rays_train(o, d, bits, BOUND, 0.0, 1024, N, CAS, H, M, nears, fars, xr, dr, dlr, rays_ref, cnt_ref, 1)
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    xyzs, dirs, deltas, rays = rm.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, counter, -1, True, 128, True, 0, 1024)
+    assert torch.equal(counter, cnt_ref)
+    rr = rays_ref[torch.argsort(rays_ref[:, 0].long())]
+    assert torch.equal(rr[:, 2], rays[:, 2])
+    for n in torch.nonzero(rays[:, 2] > 0).squeeze(-1)[::16].tolist():
+        a0, c, b0 = int(rays[n, 1]), int(rays[n, 2]), int(rr[n, 1])
+        assert torch.equal(xyzs[a0:a0 + c], xr[b0:b0 + c]) and torch.equal(deltas[a0:a0 + c], dlr[b0:b0 + c])
