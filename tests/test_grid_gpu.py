@@ -114,3 +114,71 @@ def test_forward_vs_reference_cuda(ngp):
     ngp.check(ngp.lib().ngp_grid_encode_backward_input(gr.data_ptr(), 1, x.data_ptr(), tt.data_ptr(), 0, ot.data_ptr(),
                                                       gx.data_ptr(), B, 3, 2, 16, cfg["S"], cfg["H"], 0, 0, ngp.stream()))
     assert rel_err(gx.cpu().numpy(), gref_in.cpu().numpy()) < 1e-5
+
+
+def _table_grad(ngp, g, x, cfg, layout=1):
+    from nerf_navigation_b200.gridencoder.table_grad import grid_backward_table
+    tt = torch.from_numpy(cfg["table"]).cuda(); ot = torch.from_numpy(cfg["offsets"]).cuda()
+    B = x.shape[0]
+    return grid_backward_table(g, x, tt, ot, (B, 3, 2, 16, cfg["S"], cfg["H"], 0), False, layout)
+
+
+def test_table_gradient_vs_oracle_and_deterministic(ngp, oracle):
+    cfg = hashgrid_config()
+    B = 50000
+    rng = np.random.default_rng(11)
+    x = rng.uniform(0, 1, (B, 3)).astype(np.float32)
+    x[7] = [1.1, 0.5, 0.5]                                  # out of range: contributes nothing
+    g = rng.standard_normal((B, 32)).astype(np.float32)
+    scales = _dev_scales(ngp, cfg)
+    ref = oracle.grid_backward_table(np.ascontiguousarray(g.reshape(B, 16, 2).transpose(1, 0, 2)), x, cfg["offsets"], scales, 2)
+    xt, gt = torch.from_numpy(x).cuda(), torch.from_numpy(g).cuda()
+    a = _table_grad(ngp, gt, xt, cfg)
+    b = _table_grad(ngp, gt, xt, cfg)
+    assert torch.equal(a, b)                                # bit-identical run to run (no float atomics)
+    assert rel_err(a.cpu().numpy(), ref) < 1e-5
+    assert (a.cpu().numpy() != 0).sum() == (ref != 0).sum()
+
+
+def test_table_gradient_vs_reference_cuda(ngp):
+    ref = load_ref("gridencoder")
+    if ref is None:
+        pytest.skip("oracle/_ref/gridencoder not built")
+    cfg = hashgrid_config()
+    B = 100000
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.rand(B, 3, device="cuda", generator=gen)
+    gr = torch.randn(B, 32, device="cuda", generator=gen)
+    tt = torch.from_numpy(cfg["table"]).cuda(); ot = torch.from_numpy(cfg["offsets"]).cuda()
+    gemb = torch.zeros_like(tt); dummy = torch.zeros(1, device="cuda")
+    ref.grid_encode_backward(gr.view(B, 16, 2).permute(1, 0, 2).contiguous(), x, tt, ot, gemb, B, 3, 2, 16, cfg["S"],
+                             cfg["H"], False, dummy, dummy, 0, False)
+    ours = _table_grad(ngp, gr, x, cfg)
+    assert rel_err(ours.cpu().numpy(), gemb.cpu().numpy()) < 1e-5   # atomics order noise only
+
+
+def test_grid_encoder_module_autograd(ngp, oracle):
+    """GridEncoder module (grid.py:93-156 contract): forward, dL/dx and dL/dtable through autograd."""
+    from nerf_navigation_b200.gridencoder import GridEncoder
+    torch.manual_seed(0)
+    enc = GridEncoder(desired_resolution=4096).cuda()
+    enc.embeddings.data.uniform_(-0.5, 0.5)
+    assert enc.embeddings.shape == (6328848, 2) and enc.offsets.dtype == torch.int32 and enc.output_dim == 32
+    x = (torch.rand(5000, 3, device="cuda") * 4 - 2).requires_grad_()
+    out = enc(x, bound=2)
+    w = torch.randn_like(out)
+    (out * w).sum().backward()
+    cfg = dict(L=16, S=float(np.log2(enc.per_level_scale)), H=16)
+    scales = _dev_scales(ngp, cfg)
+    x01 = ((x.detach() + 2) / 4).cpu().numpy()
+    ro, rdy, _ = oracle.grid_encode_forward(x01, enc.embeddings.detach().cpu().numpy(), enc.offsets.cpu().numpy(), scales, True)
+    assert rel_err(out.detach().cpu().numpy(), ro.transpose(1, 0, 2).reshape(5000, 32)) < 1e-5
+    gl = np.ascontiguousarray(w.cpu().numpy().reshape(5000, 16, 2).transpose(1, 0, 2))
+    assert rel_err(x.grad.cpu().numpy(), oracle.grid_backward_input(gl, rdy) / 4.0) < 1e-5
+    rt = oracle.grid_backward_table(gl, x01, enc.offsets.cpu().numpy(), scales, 2)
+    assert rel_err(enc.embeddings.grad.cpu().numpy(), rt) < 1e-5
+    # fp16 table under autocast (grid.py:36-39): output dtype half, 2e-3 bar
+    with torch.autocast("cuda", dtype=torch.float16):
+        oh = enc(x.detach(), bound=2)
+    assert oh.dtype == torch.float16
+    assert rel_err(oh.float().cpu().numpy(), ro.transpose(1, 0, 2).reshape(5000, 32)) < 2e-3
