@@ -181,4 +181,4 @@ def test_grid_encoder_module_autograd(ngp, oracle):
     with torch.autocast("cuda", dtype=torch.float16):
         oh = enc(x.detach(), bound=2)
     assert oh.dtype == torch.float16
-    assert rel_err(oh.float().cpu().numpy(), ro.transpose(1, 0, 2).reshape(5000, 32)) < 2e-3
+    assert rel_err(oh.detach().float().cpu().numpy(), ro.transpose(1, 0, 2).reshape(5000, 32)) < 2e-3

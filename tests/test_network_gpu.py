@@ -89,7 +89,8 @@ def test_run_cuda_train_and_eval_agree(model):
     with torch.no_grad():
         ev = model.render(ro, rd, bg_color=1.0, perturb=False, dt_gamma=0, max_steps=1024)
     assert rel_err(tr["image"].cpu().numpy(), ev["image"].cpu().numpy()) < 1e-5
-    assert rel_err(tr["depth"].cpu().numpy(), ev["depth"].cpu().numpy()) < 1e-4
+    # depth is NOT compared: the reference's training compositor integrates t from 0 (raymarching.cu:552) while the
+    # inference one starts at rays_t = near (:855), so the two branches differ by design.
     assert (ev["image"] < 0.999).any()          # the scene is actually hit
 
 
