@@ -134,6 +134,14 @@ int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_t B, int D,
 int ngp_sh_encode_backward(const float *grad, const float *inputs, int64_t B, int D, int degree, float *grad_inputs,
                            ngp_stream_t stream);
 
+/* ---- measurement aid (not on the product path) ----------------------------------------------------------------- */
+
+/* L2-gather roofline probe: blocks x 256 threads each issue iters x 8 independent pseudo-random
+ * loads of elem_bytes (4, 8 or 16) from buf[0:buf_bytes].  pattern 0 = independent rows, 1 = the 8 hashed corners of a
+ * random cell.  Useful bytes = blocks*256*iters*8*elem_bytes; the caller times it with CUDA events. */
+int ngp_probe_gather(const void *buf, int64_t buf_bytes, int elem_bytes, int iters, int pattern, int blocks,
+                     uint32_t *sink, ngp_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
