@@ -9,7 +9,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libngp_b200.so")
+SO_PATH = os.environ.get("NGP_B200_LIB") or os.path.join(_HERE, "libngp_b200.so")  # env override: dev experiments only
 
 _lib = None
 

@@ -14,8 +14,8 @@
 //    pre-split and pre-ordered as B fragments: one LDS.128 per (n-tile, k-tile) feeds both row tiles.
 //  * Gathers: the two x-neighbours of a cell are the same aligned 16-byte row pair whenever their row indices differ
 //    only in bit 0 (always for hashed levels with even x, for dense levels with even row) -> one LDG.128 instead of
-//    two LDG.64; the odd case adds a predicated LDG.64.  Levels >= 4 stream through L1 with no_allocate so the small
-//    dense levels 0-3 stay L1-resident.  The measured bound is one L1-miss sector per clock per SM
+//    two LDG.64; the odd case adds a predicated LDG.64.  L1 eviction hints (no_allocate / evict_first) on the hashed
+//    levels were measured to cut the L2 hit rate to ~50 % and are NOT used.  The measured bound is one L1-miss sector per clock per SM
 //    (scripts/probe_l2.py), ~91 distinct sectors per point per pass.
 //  * Persistent CTAs (grid = SMs x resident CTAs) loop over 128-point tiles; warps never synchronise after staging.
 #include "common.cuh"
@@ -81,22 +81,39 @@ __device__ __forceinline__ void fq_mma3(float (&d)[4], const uint32_t (&ahi)[4],
 }
 
 // ------------------------------------------------------------------------------------------------ gathers
+#ifndef FQ_HINT
+#define FQ_HINT 0
+#endif
+#if FQ_HINT == 1
+#define FQ_LD_COARSE "ld.global.nc.L1::evict_last"
+#define FQ_LD_STREAM "ld.global.nc.L1::evict_first"
+#elif FQ_HINT == 2
+#define FQ_LD_COARSE "ld.global.nc.L1::evict_last"
+#define FQ_LD_STREAM "ld.global.nc"
+#elif FQ_HINT == 3
+#define FQ_LD_COARSE "ld.global.nc"
+#define FQ_LD_STREAM "ld.global.nc.L1::evict_first"
+#else
+#define FQ_LD_COARSE "ld.global.nc"
+#define FQ_LD_STREAM "ld.global.nc"
+#endif
+// STREAM = 0: levels 0-3 (small, dense, L1-resident candidates); 1: levels 4-15 (no reuse inside an SM)
 template <int STREAM>
 __device__ __forceinline__ float4 fq_ld16(const float4 *p) {
     float4 v;
     if (STREAM)
-        asm("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+        asm(FQ_LD_STREAM ".v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     else
-        asm("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+        asm(FQ_LD_COARSE ".v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
 }
 template <int STREAM>
 __device__ __forceinline__ float2 fq_ld8(const float2 *p) {
     float2 v;
     if (STREAM)
-        asm("ld.global.nc.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+        asm(FQ_LD_STREAM ".v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
     else
-        asm("ld.global.nc.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+        asm(FQ_LD_COARSE ".v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
     return v;
 }
 template <int STREAM>
@@ -104,10 +121,10 @@ __device__ __forceinline__ float2 fq_ld8_if(const float2 *p, bool pred) {  // pr
     float2 v;
     if (STREAM)
         asm("{\n .reg .pred p;\n setp.ne.u32 p, %3, 0;\n mov.f32 %0, 0f00000000;\n mov.f32 %1, 0f00000000;\n"
-            " @p ld.global.nc.v2.f32 {%0,%1}, [%2];\n}" : "=&f"(v.x), "=&f"(v.y) : "l"(p), "r"((uint32_t)pred));
+            " @p " FQ_LD_STREAM ".v2.f32 {%0,%1}, [%2];\n}" : "=&f"(v.x), "=&f"(v.y) : "l"(p), "r"((uint32_t)pred));
     else
         asm("{\n .reg .pred p;\n setp.ne.u32 p, %3, 0;\n mov.f32 %0, 0f00000000;\n mov.f32 %1, 0f00000000;\n"
-            " @p ld.global.nc.v2.f32 {%0,%1}, [%2];\n}" : "=&f"(v.x), "=&f"(v.y) : "l"(p), "r"((uint32_t)pred));
+            " @p " FQ_LD_COARSE ".v2.f32 {%0,%1}, [%2];\n}" : "=&f"(v.x), "=&f"(v.y) : "l"(p), "r"((uint32_t)pred));
     return v;
 }
 
@@ -334,7 +351,13 @@ __device__ __forceinline__ void fq_forward_tiles(const FieldSmem &s, const float
     }
 }
 
-__global__ void __launch_bounds__(FQ_THREADS, 4)
+#ifndef FQ_MINB_FWD
+#define FQ_MINB_FWD 3
+#endif
+#ifndef FQ_MINB_BWD
+#define FQ_MINB_BWD 3
+#endif
+__global__ void __launch_bounds__(FQ_THREADS, FQ_MINB_FWD)
 k_field_forward(const float *__restrict__ x, float bound, const float *__restrict__ table,
                 const int32_t *__restrict__ offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
                 const float *__restrict__ W0, const float *__restrict__ W1, float *__restrict__ sigma,
@@ -498,7 +521,7 @@ __device__ __forceinline__ void fq_backward_tiles(const FieldSmem &s, const floa
 }
 
 template <bool HAS_GEO>
-__global__ void __launch_bounds__(FQ_THREADS, 4)
+__global__ void __launch_bounds__(FQ_THREADS, FQ_MINB_BWD)
 k_field_backward(const float *__restrict__ x, float bound, const float *__restrict__ table,
                  const int32_t *__restrict__ offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
                  const float *__restrict__ W0, const float *__restrict__ W1, const float *__restrict__ sigma,
