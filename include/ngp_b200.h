@@ -134,6 +134,18 @@ int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_t B, int D,
 int ngp_sh_encode_backward(const float *grad, const float *inputs, int64_t B, int D, int degree, float *grad_inputs,
                            ngp_stream_t stream);
 
+/* ---- fully fused MLP: ffmlp/src/ffmlp.h:8-14, bindings.cpp:5-11 ---------------------------------------------------- */
+
+/* ffmlp_forward / ffmlp_inference (ffmlp.cu:629-700).  inputs [B,input_dim] f16; weights flat f16
+ * [64 x input_dim][64 x 64]*(num_layers-1)[16 x 64], each block row-major [out,in]; outputs [B,16] f16.
+ * forward_buffer [num_layers,B,64] f16 receives the post-activation hidden layers (training); NULL = inference
+ * (the reference's inference_buffer scratch is not needed).  hidden_dim must be 64, output_dim 16 (the padded width),
+ * input_dim a multiple of 16 (<= 256); activation 0 = ReLU | 6 = None, output_activation 6 = None (ffmlp.py:107-108).
+ * B needs no padding to a multiple of 128. */
+int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int input_dim, int output_dim,
+                      int hidden_dim, int num_layers, int activation, int output_activation, void *forward_buffer,
+                      void *outputs, ngp_stream_t stream);
+
 /* ---- measurement aid (not on the product path) ----------------------------------------------------------------- */
 
 /* L2-gather roofline probe: blocks x 256 threads each issue iters x 8 independent pseudo-random

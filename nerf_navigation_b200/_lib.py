@@ -39,6 +39,7 @@ _SIGNATURES = {
     "ngp_composite_rays": ([I64, U32, P, P, P, P, P, P, P, P, P], I),
     "ngp_sh_encode_forward": ([P, P, I64, I, I, I, P, P], I),
     "ngp_sh_encode_backward": ([P, P, I64, I, I, P, P], I),
+    "ngp_ffmlp_forward": ([P, P, I64, I, I, I, I, I, I, P, P, P], I),
     "ngp_probe_gather": ([P, I64, I, I, I, I, P, P], I),
     "ngp_field_query_backward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, I64, P], I),
 }

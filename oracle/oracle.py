@@ -239,3 +239,58 @@ def composite_rays(n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, we
 
 def pcg32_jitter(seed, n):
     return float(lib().orc_pcg32_jitter(seed, n))
+
+
+# --------------------------------------------------------------------------------------------- FFMLP (numpy restatement)
+def ffmlp_split_weights(weights, input_dim, hidden_dim, num_layers, padded_out=16):
+    """Flat fp16 weight vector -> [W_in, W_h..., W_out], each [out, in] (ffmlp.cu:632 layout)."""
+    w = np.asarray(weights)
+    mats, o = [], 0
+    for (r, c) in [(hidden_dim, input_dim)] + [(hidden_dim, hidden_dim)] * (num_layers - 1) + [(padded_out, hidden_dim)]:
+        mats.append(w[o:o + r * c].reshape(r, c)); o += r * c
+    assert o == w.size
+    return mats
+
+
+def ffmlp_forward(inputs, weights, input_dim, hidden_dim, num_layers, relu=True):
+    """kernel_mlp_fused (ffmlp.cu:331-407): h_l = act(h_{l-1} W_l^T) rounded to fp16 after every layer; the products
+    are accumulated here in fp32 (the reference accumulates in fp16 wmma fragments; the 2e-3 bar covers the difference).
+    Returns (outputs [B,16] f16, forward_buffer [n,B,hidden] f16)."""
+    mats = ffmlp_split_weights(weights, input_dim, hidden_dim, num_layers)
+    h = np.asarray(inputs, np.float16)
+    fwd = []
+    for l in range(num_layers):
+        z = h.astype(np.float32) @ mats[l].astype(np.float32).T
+        if relu:
+            z = np.maximum(z, 0)
+        h = z.astype(np.float16)
+        fwd.append(h)
+    out = (h.astype(np.float32) @ mats[-1].astype(np.float32).T).astype(np.float16)
+    return out, np.stack(fwd)
+
+
+def ffmlp_backward(grad, inputs, weights, forward_buffer, input_dim, hidden_dim, num_layers, relu=True):
+    """kernel_mlp_fused_backward (ffmlp.cu:410-518) + the weight-gradient products (ffmlp.cu:795-887).
+    Returns (grad_inputs [B,in] f16, grad_weights flat f16, backward_buffer [n,B,hidden] f16); backward_buffer[k] is the
+    gradient at hidden layer n-1-k (post-ReLU-transfer), as the reference lays it out."""
+    mats = ffmlp_split_weights(weights, input_dim, hidden_dim, num_layers)
+    g = np.asarray(grad, np.float16)
+    x = np.asarray(inputs, np.float16)
+    fwd = np.asarray(forward_buffer, np.float16)
+    n = num_layers
+    gw = [None] * (n + 1)
+    bwd = []
+    gw[n] = g.astype(np.float32).T @ fwd[n - 1].astype(np.float32)
+    d = g.astype(np.float32) @ mats[n].astype(np.float32)
+    for k in range(n):
+        layer = n - 1 - k                      # hidden layer this gradient belongs to
+        if relu:
+            d = d * (fwd[layer] > 0)
+        dh = d.astype(np.float16)
+        bwd.append(dh)
+        src = fwd[layer - 1] if layer > 0 else x
+        gw[layer] = dh.astype(np.float32).T @ src.astype(np.float32)
+        d = dh.astype(np.float32) @ mats[layer].astype(np.float32)
+    grad_inputs = d.astype(np.float16)
+    grad_weights = np.concatenate([m.reshape(-1) for m in gw]).astype(np.float16)
+    return grad_inputs, grad_weights, np.stack(bwd)
