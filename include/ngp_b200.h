@@ -146,6 +146,18 @@ int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int in
                       int hidden_dim, int num_layers, int activation, int output_activation, void *forward_buffer,
                       void *outputs, ngp_stream_t stream);
 
+/* ffmlp_backward (ffmlp.cu:754-895).  grad [B,16] f16 (zero in the padded columns); forward_buffer from
+ * ngp_ffmlp_forward.  Writes grad_weights (flat f16, same layout as weights; may be NULL), grad_inputs [B,input_dim] f16
+ * iff calc_grad_inputs (any input_dim; the reference needs CUTLASS unless input_dim == 64), and, when not NULL,
+ * backward_buffer [num_layers,B,64] f16 (entry k = gradient at hidden layer num_layers-1-k, as the reference).
+ * Nothing needs pre-zeroing.  Weight gradients are summed per CTA in TMEM (fp32) and reduced in CTA order
+ * (bit-reproducible).  workspace: ngp_ffmlp_backward_workspace_bytes(B, input_dim, num_layers) bytes. */
+int64_t ngp_ffmlp_backward_workspace_bytes(int64_t B, int input_dim, int num_layers);
+int ngp_ffmlp_backward(const void *grad, const void *inputs, const void *weights, const void *forward_buffer,
+                       int64_t B, int input_dim, int output_dim, int hidden_dim, int num_layers, int activation,
+                       int output_activation, int calc_grad_inputs, void *backward_buffer, void *grad_inputs,
+                       void *grad_weights, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+
 /* ---- measurement aid (not on the product path) ----------------------------------------------------------------- */
 
 /* L2-gather roofline probe: blocks x 256 threads each issue iters x 8 independent pseudo-random

@@ -40,6 +40,8 @@ _SIGNATURES = {
     "ngp_sh_encode_forward": ([P, P, I64, I, I, I, P, P], I),
     "ngp_sh_encode_backward": ([P, P, I64, I, I, P, P], I),
     "ngp_ffmlp_forward": ([P, P, I64, I, I, I, I, I, I, P, P, P], I),
+    "ngp_ffmlp_backward_workspace_bytes": ([I64, I, I], I64),
+    "ngp_ffmlp_backward": ([P, P, P, P, I64, I, I, I, I, I, I, I, P, P, P, P, I64, P], I),
     "ngp_probe_gather": ([P, I64, I, I, I, I, P, P], I),
     "ngp_field_query_backward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, I64, P], I),
 }
