@@ -105,6 +105,16 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
                          const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
                          uint32_t perturb, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
 
+/* EXTENSION (no reference counterpart; the reference's cuda_ray path is not differentiable w.r.t. the pose): gradient
+ * of a loss w.r.t. rays_o / rays_d through the samples of ngp_march_rays_train, with the sample abscissae held constant
+ * as the reference's torch sampler does (renderer.py:159-160).  grad_xyzs [M,3], grad_dirs [M,3]
+ * (may be NULL) -> grad_rays_o, grad_rays_d [N,3] (overwritten).  nears / deltas / rays / perturb / max_steps as given
+ * to / returned by ngp_march_rays_train. */
+int ngp_march_rays_train_backward(const float *grad_xyzs, const float *grad_dirs, const float *rays_o,
+                                  const float *rays_d, const float *nears, const float *deltas, const int32_t *rays,
+                                  float bound, uint32_t max_steps, uint32_t perturb, int64_t N, int64_t M,
+                                  float *grad_rays_o, float *grad_rays_d, ngp_stream_t stream);
+
 /* composite_rays_train_forward / _backward (raymarching.cu:505-593, 606-699).  grad_sigmas [M], grad_rgbs [M,3] must be
  * pre-zeroed (raymarching.py:272-273). */
 int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas, const int32_t *rays,

@@ -289,6 +289,65 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
     return NGP_OK;
 }
 
+// ---------------------------------------------------------------- training marcher, gradient to the rays
+// EXTENSION (absent in the reference, whose cuda_ray path returns no pose gradient): the sample
+// abscissae t_k are constants w.r.t. the pose, x_k = clamp(o + t_k d, -bound, bound), dirs_k = d, exactly what the torch
+// sampler differentiates (renderer.py:159-160):
+//   dL/do = sum_k m_k * dL/dx_k,   dL/dd = sum_k t_k (m_k * dL/dx_k) + sum_k dL/ddir_k,   m_k = per-axis "not clamped".
+// t_k is rebuilt from the emitted deltas: t_k + dt_k = t_start + cumsum(deltas[:,1])_k.
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_train_bwd(const float *__restrict__ grad_xyzs, const float *__restrict__ grad_dirs,
+                  const float *__restrict__ rays_o, const float *__restrict__ rays_d, const float *__restrict__ nears,
+                  const float *__restrict__ deltas, const int32_t *__restrict__ rays, float bound, float dt_min,
+                  uint32_t perturb, int64_t N, int64_t M, float *__restrict__ grad_o, float *__restrict__ grad_d) {
+    const int64_t i = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (i >= N) return;
+    const int64_t n = rays[i * 3], off = rays[i * 3 + 1];
+    const uint32_t cnt = (uint32_t)rays[i * 3 + 2];
+    float go[3] = {0.f, 0.f, 0.f}, gd[3] = {0.f, 0.f, 0.f};
+    if (cnt != 0 && off + cnt < M) {
+        const float o[3] = {rays_o[n * 3], rays_o[n * 3 + 1], rays_o[n * 3 + 2]};
+        const float d[3] = {rays_d[n * 3], rays_d[n * 3 + 1], rays_d[n * 3 + 2]};
+        float tc = nears[n];
+        if (perturb) tc = fmaf(dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), tc);
+        for (uint32_t s = 0; s < cnt; ++s) {
+            const int64_t k = off + s;
+            const float2 dl = __ldg(reinterpret_cast<const float2 *>(deltas) + k);
+            tc += dl.y;
+            const float t = tc - dl.x;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const float p = fmaf(t, d[a], o[a]);
+                const float g = (p >= -bound && p <= bound) ? __ldg(grad_xyzs + k * 3 + a) : 0.0f;
+                go[a] += g;
+                gd[a] = fmaf(t, g, gd[a]);
+                if (grad_dirs) gd[a] += __ldg(grad_dirs + k * 3 + a);
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        grad_o[n * 3 + a] = go[a];
+        grad_d[n * 3 + a] = gd[a];
+    }
+}
+
+extern "C" int ngp_march_rays_train_backward(const float *grad_xyzs, const float *grad_dirs, const float *rays_o,
+                                             const float *rays_d, const float *nears, const float *deltas,
+                                             const int32_t *rays, float bound, uint32_t max_steps, uint32_t perturb,
+                                             int64_t N, int64_t M, float *grad_rays_o, float *grad_rays_d,
+                                             ngp_stream_t stream) {
+    NGP_REQUIRE(rays_o && rays_d && nears && rays && grad_rays_o && grad_rays_d, NGP_ERR_ARG,
+                "ngp_march_rays_train_backward: null pointer");
+    NGP_REQUIRE(M == 0 || (grad_xyzs && deltas), NGP_ERR_ARG, "ngp_march_rays_train_backward: null sample buffers");
+    if (N == 0) return NGP_OK;
+    const float dt_min = 2.0f * 1.7320508075688772f / (float)max_steps;
+    k_march_train_bwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        grad_xyzs, grad_dirs, rays_o, rays_d, nears, deltas, rays, bound, dt_min, perturb, N, M, grad_rays_o, grad_rays_d);
+    NGP_CHECK_LAUNCH("ngp_march_rays_train_backward");
+    return NGP_OK;
+}
+
 // ---------------------------------------------------------------- compositing, training  (raymarching.cu:505-582, 606-688)
 // __expf as in the reference (fast intrinsic) so alpha matches its CUDA build.
 __global__ void __launch_bounds__(RAY_THREADS)

@@ -137,7 +137,31 @@ class _march_rays_train(Function):
                                               M if exact else M_alloc, _lib.ptr(nears), _lib.ptr(fars), _lib.ptr(xyzs),
                                               _lib.ptr(dirs), _lib.ptr(deltas), _lib.ptr(rays), _lib.ptr(step_counter),
                                               int(perturb), _lib.ptr(ws), ws_bytes, _lib.stream()), "march_rays_train")
+        if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
+            ctx.save_for_backward(rays_o, rays_d, nears, deltas, rays)
+            ctx.cfg = (float(bound), int(max_steps), int(perturb), N, M if exact else M_alloc)
+        ctx.mark_non_differentiable(deltas, rays)
         return xyzs, dirs, deltas, rays
+
+    @staticmethod
+    @_bwd
+    def backward(ctx, grad_xyzs, grad_dirs, grad_deltas, grad_rays):
+        """EXTENSION (the reference op has no backward): dL/drays_o, dL/drays_d with the sample abscissae held
+        constant, i.e. what the reference's torch sampler differentiates (renderer.py:159-160)."""
+        rays_o, rays_d, nears, deltas, rays = ctx.saved_tensors
+        bound, max_steps, perturb, N, M = ctx.cfg
+        dev = rays_o.device
+        if grad_xyzs is None:
+            grad_xyzs = torch.zeros(deltas.shape[0], 3, device=dev)
+        grad_xyzs = grad_xyzs.contiguous().float()
+        grad_dirs = None if grad_dirs is None else grad_dirs.contiguous().float()
+        go = torch.empty(N, 3, device=dev); gd = torch.empty(N, 3, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().ngp_march_rays_train_backward(
+                _lib.ptr(grad_xyzs), _lib.ptr(grad_dirs), _lib.ptr(rays_o), _lib.ptr(rays_d), _lib.ptr(nears),
+                _lib.ptr(deltas), _lib.ptr(rays), bound, max_steps, perturb, N, M, _lib.ptr(go), _lib.ptr(gd),
+                _lib.stream()), "march_rays_train_backward")
+        return (go, gd) + (None,) * 13
 
 
 march_rays_train = _march_rays_train.apply

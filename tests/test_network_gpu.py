@@ -117,3 +117,38 @@ def test_update_extra_state_runs(model):
     m.reset_extra_state()
     m.update_extra_state()
     assert m.iter_density == 1 and m.density_bitfield.dtype == torch.uint8 and m.mean_density > 0
+
+
+def test_network_ff_variant():
+    """nerf/network_ff.py mirror: FFMLP parameters with the reference names/sizes, forward/density/color contracts, and
+    agreement with a torch restatement of the same fp16 network (2e-3 bar)."""
+    from nerf_navigation_b200.nerf.network_ff import NeRFNetwork as NetFF
+    m = NetFF(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    keys = set(m.state_dict().keys())
+    assert {"encoder.embeddings", "encoder.offsets", "sigma_net.weights", "color_net.weights"} <= keys
+    assert m.sigma_net.weights.numel() == 64 * (32 + 64 + 16) and m.color_net.weights.numel() == 64 * (32 + 128 + 16)
+    x = torch.rand(5000, 3, device="cuda") * 2 - 1
+    d = torch.nn.functional.normalize(torch.randn(5000, 3, device="cuda"), dim=-1)
+    with torch.no_grad():
+        sigma, rgb = m(x, d)
+        dens = m.density(x)
+        rgb2 = m.color(x, d, geo_feat=dens["geo_feat"])
+        # torch restatement
+        enc = m.encoder(x, bound=2).half()
+        Ws = m.sigma_net.weights.half()
+        h = torch.relu(enc.float() @ Ws[:2048].view(64, 32).float().t()).half()
+        h = torch.relu(h.float() @ Ws[2048:6144].view(64, 64).float().t()).half()
+        o = (h.float() @ Ws[6144:].view(16, 64).float().t()).half()
+        sig_ref = torch.exp(o[:, 0].float())
+        cin = torch.cat([m.encoder_dir(d).half(), o[:, 1:], torch.zeros_like(o[:, :1])], -1)
+        Wc = m.color_net.weights.half()
+        c = torch.relu(cin.float() @ Wc[:2048].view(64, 32).float().t()).half()
+        c = torch.relu(c.float() @ Wc[2048:6144].view(64, 64).float().t()).half()
+        c = torch.relu(c.float() @ Wc[6144:10240].view(64, 64).float().t()).half()
+        rgb_ref = torch.sigmoid((c.float() @ Wc[10240:].view(16, 64).float().t()).half()[:, :3])
+    assert sigma.shape == (5000,) and rgb.shape == (5000, 3)
+    assert rel_err(sigma.float().cpu().numpy(), sig_ref.cpu().numpy()) < 2e-3
+    assert rel_err(rgb.float().cpu().numpy(), rgb_ref.float().cpu().numpy()) < 2e-3
+    assert rel_err(dens["sigma"].float().cpu().numpy(), sigma.float().cpu().numpy()) < 1e-6
+    assert rel_err(rgb2.float().cpu().numpy(), rgb.float().cpu().numpy()) < 1e-6

@@ -165,3 +165,37 @@ def test_sh_vs_oracle(ngp, oracle):
     out.backward(g)
     ref = np.einsum("bc,bdc->bd", g.cpu().numpy().astype(np.float64), rj.astype(np.float64))
     assert rel_err(dt.grad.cpu().numpy(), ref) < 1e-5
+
+
+def test_march_rays_train_pose_gradient(ngp):
+    """EXTENSION: dL/drays_o, dL/drays_d through march_rays_train equals torch autograd through
+    x_k = clamp(o + t_k d), dirs_k = d with the marcher's own (detached) abscissae t_k."""
+    from nerf_navigation_b200 import raymarching as rm
+    N = 3000
+    grid = torch.from_numpy(stonehenge_grid()).cuda()
+    bits = rm.packbits(grid, 10.0)
+    o, d = orbit_rays(N, 5)
+    o = torch.from_numpy(o).cuda().requires_grad_(True); d = torch.from_numpy(d).cuda().requires_grad_(True)
+    aabb = torch.tensor([-2.0] * 3 + [2.0] * 3, device="cuda")
+    nears, fars = rm.near_far_from_aabb(o.detach(), d.detach(), aabb, 0.2)
+    xyzs, dirs, deltas, rays = rm.march_rays_train(o, d, 2.0, bits, 2, 128, nears, fars, None, -1, False, -1, True, 0, 1024)
+    M = xyzs.shape[0]
+    assert M > N and xyzs.requires_grad
+    w1 = torch.randn(M, 3, device="cuda"); w2 = torch.randn(M, 3, device="cuda")
+    ((xyzs * w1).sum() + (dirs * w2).sum()).backward()
+    go, gd = o.grad.clone(), d.grad.clone()
+    # torch restatement on the same abscissae
+    r = rays.long()
+    cnt, off = r[:, 2], r[:, 1]
+    ray_of = torch.repeat_interleave(r[:, 0], cnt)
+    assert ray_of.shape[0] <= M
+    m = ray_of.shape[0]
+    csum = torch.cumsum(deltas[:m, 1].double(), 0)
+    start = torch.repeat_interleave(torch.cat([torch.zeros(1, device="cuda", dtype=torch.double), csum])[off], cnt)
+    t = (nears.double()[ray_of] + (csum - start) - deltas[:m, 0].double()).float()
+    o2 = o.detach().clone().requires_grad_(True); d2 = d.detach().clone().requires_grad_(True)
+    x2 = torch.clamp(o2[ray_of] + t[:, None] * d2[ray_of], -2.0, 2.0)
+    assert rel_err(x2.detach().cpu().numpy(), xyzs[:m].detach().cpu().numpy()) < 1e-6
+    ((x2 * w1[:m]).sum() + (d2[ray_of] * w2[:m]).sum()).backward()
+    assert rel_err(go.cpu().numpy(), o2.grad.cpu().numpy()) < 1e-5
+    assert rel_err(gd.cpu().numpy(), d2.grad.cpu().numpy()) < 1e-5
