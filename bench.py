@@ -244,6 +244,22 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
+    # ---- L2-gather roofline measured live: independent 8-byte corner gathers from a table-sized buffer
+    probe_buf = torch.randint(0, 2 ** 31 - 1, (tab.numel(),), device=dev, dtype=torch.int32)
+    sink = torch.zeros(4, device=dev, dtype=torch.int32)
+    pb_blocks, pb_iters = 148 * 16, 64
+    probe = lambda: ngp.check(L.ngp_probe_gather(probe_buf.data_ptr(), probe_buf.numel() * 4, 8, pb_iters, 1, pb_blocks,
+                                                 sink.data_ptr(), st))
+    for _ in range(3):
+        probe()
+    pe = [(ev(), ev()) for _ in range(5)]
+    for a, b in pe:
+        a.record(); probe(); b.record()
+    torch.cuda.synchronize()
+    probe_ms = min(a.elapsed_time(b) for a, b in pe)
+    gather_peak = pb_blocks * 256 * pb_iters * 8 * 8 / (probe_ms / 1e3) / 1e9
+    del probe_buf
+
     peaks, peak_kind = measured_peaks()
     value = world * B * args.steps / t_dev / 1e6
     e2e_val = world * B * e2e_steps / t_e2e / 1e6
@@ -264,6 +280,13 @@ def run_b200(args):
                      "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
                      "note": "algorithmic bytes = 1024 B of table gathers per point per pass; gathers are served by L2 "
                              "(table resident), so the binding limit is L1/L2 request rate, not HBM"},
+        "l2_gather_roofline": {
+            "peak": gather_peak, "unit": "GB/s useful", "how": "ngp_probe_gather live: 8-byte hashed-cell corner gathers "
+            "from a 48 MiB L2-resident buffer, all SMs (the binding unit is one L1-miss sector per clock per SM)",
+            "k_field_forward": {"achieved": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9,
+                                "frac": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak},
+            "k_field_backward": {"achieved": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9,
+                                 "frac": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}},
         "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:

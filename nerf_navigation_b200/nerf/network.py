@@ -3,8 +3,8 @@
 contracts) with the hot path routed to the B200 kernels:
 
 * density(x): one fused kernel (hash-grid encode + sigma MLP + trunc_exp), one fused backward-to-x kernel, in eval
-  mode (the planner / estimator case: simulate.py:191 model.eval(), :343-347), where the field is frozen and gradients
-  flow to x only.  In training mode the unfused GridEncoder -> nn.Linear path runs so autograd produces table/MLP gradients.
+  mode (the planner / estimator case: simulate.py:191 model.eval(), :343-347) or whenever the field parameters do
+  not require grad, i.e. the field is frozen and gradients flow to x only.  In training mode the unfused GridEncoder -> nn.Linear path runs so autograd produces table/MLP gradients.
 * forward(x, d) / color(): GridEncoder + SHEncoder kernels + nn.Linear (torch) — see renderer.py for the fused ray path.
 
 The background model (`bg_radius > 0`, network.py:70-92, 145-160) is out of scope: nav uses bg_radius=-1.
@@ -52,7 +52,9 @@ class NeRFNetwork(NeRFRenderer):
     # ------------------------------------------------------------------ helpers
     def _use_fused_density(self, x):
         # eval mode == frozen field (simulate.py:191 calls model.eval()): gradients flow to x only.
-        return (self.fused_eval and not self.training and x.is_cuda and self.num_layers == 2
+        frozen = not self.training or not (self.encoder.embeddings.requires_grad or self.sigma_net[0].weight.requires_grad
+                                           or self.sigma_net[1].weight.requires_grad)
+        return (self.fused_eval and frozen and x.is_cuda and self.num_layers == 2
                 and hasattr(self.encoder, "embeddings")
                 and fused_supported(self.encoder, self.sigma_net[0].weight, self.sigma_net[1].weight, x))
 
