@@ -82,6 +82,23 @@ int ngp_field_query_backward(const float *x, float bound, const float *embedding
                              const float *sigma, const uint64_t *relu_mask, const float *grad_sigma,
                              const float *grad_geo, float *grad_x, int64_t B, ngp_stream_t stream);
 
+/* ---- fused per-sample field for the ray paths: NeRFNetwork.forward(x, d), nerf/network.py:95-124 ------------------- */
+
+/* sigma [M] = exp(o[0]), rgb [M,3] = sigmoid(colour_net([SH4(d) | o[1:16]])), o = sigma_net(encode(x)); fp32 table and
+ * weights of the configuration nav uses: D=3, L=16, C=2, sigma net 32-64-16 (Ws0 [64,32], Ws1 [16,64]), colour net
+ * 31-64-64-3 (Wc0 [64,31], Wc1 [64,64], Wc2 [3,64]), all nn.Linear.weight layouts.  masks (optional): u16 [M,3,4] ReLU
+ * bits saved for ngp_field_color_backward. */
+int ngp_field_color_forward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                            const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                            const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                            float *sigma, float *rgb, void *masks, int64_t M, ngp_stream_t stream);
+/* dL/dxyzs [M,3] and dL/ddirs [M,3] (may be NULL) from dL/dsigma [M], dL/drgb [M,3] (frozen field). */
+int ngp_field_color_backward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                             const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                             const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                             const float *sigma, const float *rgb, const void *masks, const float *grad_sigma,
+                             const float *grad_rgb, float *grad_xyzs, float *grad_dirs, int64_t M, ngp_stream_t stream);
+
 /* ---- ray ops: raymarching/src/raymarching.h:7-18, bindings.cpp:5-19 -------------------------------------------- */
 
 /* near_far_from_aabb (raymarching.cu:93-158).  rays_o/rays_d [N,3], aabb[6] -> nears/fars [N]; miss => FLT_MAX. */

@@ -1,0 +1,489 @@
+// renderfield.cu — fused per-sample field for the ray paths: hash-grid encode -> sigma MLP (32-64-16) -> trunc_exp,
+// SH(4) of the view direction, colour MLP ([SH 16 | geo 15] -> 64 -> 64 -> 3) -> sigmoid, in ONE kernel, and its
+// backward to the sample position and direction (the pose-estimator gradient).  Reference path being fused:
+// NeRFNetwork.forward(x, d) (nerf/network.py:95-124) = density (:126-143) + SHEncoder (shencoder.cu:44-70) +
+// color_net (:54-68, 163-191) as called per sample by NeRFRenderer.run_cuda (renderer.py:303-305, 352-354).
+// Per-sample features, hidden activations and geo_feat stay in registers; HBM sees 24 B in and 16 B out per sample
+// (+ 24 B of ReLU bits when a backward follows) instead of the reference's ~2.5 KB of intermediate tensors.
+//
+// Same warp-cooperative layout as field.cu (fieldcore.cuh): a warp owns 16 samples, the interpolated features are the
+// mma.sync m16n8k8 A fragments, every layer's accumulator fragment (columns 2t, 2t+1 of n-tile nt) is re-used as the next
+// layer's A fragment (slots t, t+4 of k-tile nt) by ordering that layer's weights accordingly, 3xTF32 split products.
+// One 384-thread CTA per SM shares the 76 KB of pre-split weight fragments.
+#include "fieldcore.cuh"
+#include "sh.cuh"
+
+#define RF_WARPS 12
+#define RF_THREADS (RF_WARPS * 32)
+#define RF_TILE (RF_WARPS * 16)
+#define RF_GEO 15
+#define RF_CIN 31  // 16 SH + 15 geo (network.py:60)
+
+struct __align__(16) RenderFieldSmem {
+    float4 s0[1024];  // fwd: sigma L1 [nt 8][kt 4][lane]        bwd: dFeat  = dHs  W_s0   [nt 4][kt 8][lane]
+    float4 s1[512];   // fwd: sigma L2 [nt 2][kt 8][lane]        bwd: dHs    = dO   W_s1   [nt 8][kt 2][lane]
+    float4 c0[1024];  // fwd: colour L1 [nt 8][kt 4][lane]       bwd: dIn    = dHc1 W_c0   [nt 4][kt 8][lane]
+    float4 c1[2048];  // fwd: colour L2 [nt 8][kt 8][lane]       bwd: dHc1   = dHc2 W_c1   [nt 8][kt 8][lane]
+    float4 c2[256];   // fwd: colour L3 [kt 8][lane] (N = 3 -> 8) bwd: dHc2   = dRGB W_c2   [nt 8][lane] (K = 3 -> 8)
+    FqLevel lv[FQ_L];
+    int all_safe;
+};
+
+__device__ __forceinline__ float rf_sel4(int t, float a, float b, float c, float d) {
+    return t == 0 ? a : (t == 1 ? b : (t == 2 ? c : d));
+}
+
+// ReLU the 64-wide accumulator fragment `in` (recording the sign bits) and multiply by the next layer's weights:
+// out[nt] += relu(in) * W, W fragments laid out [nt NT][kt 8][lane].
+template <int NT>
+__device__ __forceinline__ void rf_relu_layer(const float (&in)[8][4], const float4 *__restrict__ frags, int lane,
+                                              float (&out)[NT][4], uint32_t (&mbits)[2]) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) out[nt][c] = 0.0f;
+    mbits[0] = mbits[1] = 0u;
+#pragma unroll
+    for (int kt = 0; kt < 8; ++kt) {
+        const float c0 = in[kt][0], c1 = in[kt][1], c2 = in[kt][2], c3 = in[kt][3];
+        mbits[0] |= ((c0 > 0.0f ? 1u : 0u) | (c1 > 0.0f ? 2u : 0u)) << (2 * kt);
+        mbits[1] |= ((c2 > 0.0f ? 1u : 0u) | (c3 > 0.0f ? 2u : 0u)) << (2 * kt);
+        uint32_t ahi[4], alo[4];
+        fq_split(fmaxf(c0, 0.0f), ahi[0], alo[0]);
+        fq_split(fmaxf(c2, 0.0f), ahi[1], alo[1]);
+        fq_split(fmaxf(c1, 0.0f), ahi[2], alo[2]);
+        fq_split(fmaxf(c3, 0.0f), ahi[3], alo[3]);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) fq_mma3(out[nt], ahi, alo, frags[(nt * 8 + kt) * 32 + lane]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ forward
+// masks (optional, consumed by the backward): u16 [M][3][4]: (sigma hidden | colour hidden 1 | colour hidden 2) x quad
+// lane t; bit (2*nt + c) of entry t = unit 8*nt + 2*t + c.
+template <bool SAFE>
+__device__ __forceinline__ void rf_forward_tiles(const RenderFieldSmem &s, const float *__restrict__ x,
+                                                 const float *__restrict__ dirs, float bound,
+                                                 const float *__restrict__ table, int align_corners,
+                                                 float *__restrict__ sigma, float *__restrict__ rgb,
+                                                 uint16_t *__restrict__ masks, int64_t B) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int64_t ntiles = (B + RF_TILE - 1) / RF_TILE;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t base = tile * RF_TILE + warp * 16;
+        if (base >= B) continue;
+        float x01[2][3];
+        bool valid[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) valid[h] = fq_load_point(x, base + 8 * h + g, B, bound, x01[h]);
+        FqRaw raw[2];
+        float frac[2][3];
+        fq_group_issue<0, SAFE>(table, s.lv[t], x01, align_corners, raw, frac);
+
+        // ---- sigma layer 1 over the four level groups (gathers of group kt+1 in flight during the MMAs of group kt)
+        float acc[8][4];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[nt][c] = 0.0f;
+#pragma unroll 1
+        for (int kt = 0; kt < 4; ++kt) {
+            float a[4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float2 v[8];
+                fq_select(raw[h], v);
+                float f0 = 0.0f, f1 = 0.0f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    float w = (k & 1) ? frac[h][0] : 1.0f - frac[h][0];
+                    w *= (k & 2) ? frac[h][1] : 1.0f - frac[h][1];
+                    w *= (k & 4) ? frac[h][2] : 1.0f - frac[h][2];
+                    f0 = fmaf(w, v[k].x, f0);
+                    f1 = fmaf(w, v[k].y, f1);
+                }
+                a[h] = valid[h] ? f0 : 0.0f;
+                a[2 + h] = valid[h] ? f1 : 0.0f;
+            }
+            if (kt < 3) fq_group_issue<1, SAFE>(table, s.lv[4 * (kt + 1) + t], x01, align_corners, raw, frac);
+            uint32_t ahi[4], alo[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) fq_split(a[c], ahi[c], alo[c]);
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) fq_mma3(acc[nt], ahi, alo, s.s0[(nt * 4 + kt) * 32 + lane]);
+        }
+        // ---- sigma layer 2: o = columns 8nt+2t, 8nt+2t+1 (column 0 = log sigma, 1..15 = geo_feat)
+        float o[2][4];
+        uint32_t m_sig[2], m_c1[2], m_c2[2];
+        rf_relu_layer<2>(acc, s.s1, lane, o, m_sig);
+
+        // ---- colour layer 1: K = [SH 0-7 | SH 8-15 | o 0-7 | o 8-15]; the weight of o column 0 is zero
+        float sh[2][4];  // the lane's SH slots: indices t, t+4, 8+t, 12+t of rows g, g+8
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t b = base + 8 * h + g;
+            float d[3] = {0.0f, 0.0f, 0.0f};
+            if (b < B) {
+                d[0] = __ldg(dirs + b * 3);
+                d[1] = __ldg(dirs + b * 3 + 1);
+                d[2] = __ldg(dirs + b * 3 + 2);
+            }
+            float v[16];
+            ngp_sh4(d[0], d[1], d[2], v);
+            sh[h][0] = rf_sel4(t, v[0], v[1], v[2], v[3]);
+            sh[h][1] = rf_sel4(t, v[4], v[5], v[6], v[7]);
+            sh[h][2] = rf_sel4(t, v[8], v[9], v[10], v[11]);
+            sh[h][3] = rf_sel4(t, v[12], v[13], v[14], v[15]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[nt][c] = 0.0f;
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt) {
+            float a[4];
+            if (kt < 2) {
+                a[0] = sh[0][2 * kt]; a[1] = sh[1][2 * kt]; a[2] = sh[0][2 * kt + 1]; a[3] = sh[1][2 * kt + 1];
+            } else {
+                a[0] = o[kt - 2][0]; a[1] = o[kt - 2][2]; a[2] = o[kt - 2][1]; a[3] = o[kt - 2][3];
+            }
+            uint32_t ahi[4], alo[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) fq_split(a[c], ahi[c], alo[c]);
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) fq_mma3(acc[nt], ahi, alo, s.c0[(nt * 4 + kt) * 32 + lane]);
+        }
+        // ---- colour layers 2 and 3
+        float acc2[8][4], o3[1][4];
+        rf_relu_layer<8>(acc, s.c1, lane, acc2, m_c1);
+        rf_relu_layer<1>(acc2, s.c2, lane, o3, m_c2);
+
+        // ---- outputs
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t b = base + 8 * h + g;
+            if (b >= B) continue;
+            if (masks) {
+                masks[(b * 3 + 0) * 4 + t] = (uint16_t)m_sig[h];
+                masks[(b * 3 + 1) * 4 + t] = (uint16_t)m_c1[h];
+                masks[(b * 3 + 2) * 4 + t] = (uint16_t)m_c2[h];
+            }
+            if (t == 0) sigma[b] = expf(o[0][2 * h]);  // trunc_exp forward (activation.py:9-11)
+            const float v0 = 1.0f / (1.0f + expf(-o3[0][2 * h])), v1 = 1.0f / (1.0f + expf(-o3[0][2 * h + 1]));
+            if (t == 0) {
+                rgb[b * 3] = v0;
+                rgb[b * 3 + 1] = v1;
+            } else if (t == 1) {
+                rgb[b * 3 + 2] = v0;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(RF_THREADS, 1)
+k_render_field_forward(const float *__restrict__ x, const float *__restrict__ dirs, float bound,
+                       const float *__restrict__ table, const int32_t *__restrict__ offsets, float S, uint32_t H,
+                       uint32_t gridtype, int align_corners, const float *__restrict__ Ws0,
+                       const float *__restrict__ Ws1, const float *__restrict__ Wc0, const float *__restrict__ Wc1,
+                       const float *__restrict__ Wc2, float *__restrict__ sigma, float *__restrict__ rgb,
+                       uint16_t *__restrict__ masks, int64_t B) {
+    extern __shared__ __align__(16) unsigned char rf_smem_raw[];
+    RenderFieldSmem &s = *reinterpret_cast<RenderFieldSmem *>(rf_smem_raw);
+    const int tid = threadIdx.x;
+    fq_stage_levels(s.lv, &s.all_safe, offsets, S, H, gridtype, align_corners);
+    for (int i = tid; i < 1024; i += RF_THREADS) {  // sigma L1: slot t -> feature 8kt+2t, t+4 -> 8kt+2t+1
+        const int ln = i & 31, kt = (i >> 5) & 3, nt = i >> 7, gg = ln >> 2, tt = ln & 3;
+        const float *w = Ws0 + (8 * nt + gg) * FQ_F + 8 * kt + 2 * tt;
+        s.s0[i] = fq_split_pair(w[0], w[1]);
+    }
+    for (int i = tid; i < 512; i += RF_THREADS) {  // sigma L2
+        const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
+        const float *w = Ws1 + (8 * nt + gg) * FQ_HID + 8 * kt + 2 * tt;
+        s.s1[i] = fq_split_pair(w[0], w[1]);
+    }
+    for (int i = tid; i < 1024; i += RF_THREADS) {  // colour L1, Wc0 [64][31]
+        const int ln = i & 31, kt = (i >> 5) & 3, nt = i >> 7, gg = ln >> 2, tt = ln & 3;
+        const float *w = Wc0 + (8 * nt + gg) * RF_CIN;
+        float b0, b1;
+        if (kt < 2) {
+            b0 = w[8 * kt + tt];
+            b1 = w[8 * kt + tt + 4];
+        } else {
+            const int col = 8 * (kt - 2) + 2 * tt;  // o column; geo index = col - 1
+            b0 = col == 0 ? 0.0f : w[16 + col - 1];
+            b1 = w[16 + col];
+        }
+        s.c0[i] = fq_split_pair(b0, b1);
+    }
+    for (int i = tid; i < 2048; i += RF_THREADS) {  // colour L2
+        const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
+        const float *w = Wc1 + (8 * nt + gg) * FQ_HID + 8 * kt + 2 * tt;
+        s.c1[i] = fq_split_pair(w[0], w[1]);
+    }
+    for (int i = tid; i < 256; i += RF_THREADS) {  // colour L3, Wc2 [3][64] padded to 8 rows
+        const int ln = i & 31, kt = i >> 5, gg = ln >> 2, tt = ln & 3;
+        const float b0 = gg < 3 ? Wc2[gg * FQ_HID + 8 * kt + 2 * tt] : 0.0f;
+        const float b1 = gg < 3 ? Wc2[gg * FQ_HID + 8 * kt + 2 * tt + 1] : 0.0f;
+        s.c2[i] = fq_split_pair(b0, b1);
+    }
+    __syncthreads();
+    if (s.all_safe) rf_forward_tiles<true>(s, x, dirs, bound, table, align_corners, sigma, rgb, masks, B);
+    else rf_forward_tiles<false>(s, x, dirs, bound, table, align_corners, sigma, rgb, masks, B);
+}
+
+// ------------------------------------------------------------------------------------------------ backward to (x, d)
+// out[nt] = (in .* mask) * W for a 64-wide accumulator-fragment input; W fragments [nt NT][kt 8][lane]
+template <int NT>
+__device__ __forceinline__ void rf_masked_layer(const float (&in)[8][4], const uint32_t (&mbits)[2],
+                                                const float4 *__restrict__ frags, int lane, float (&out)[NT][4]) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) out[nt][c] = 0.0f;
+#pragma unroll
+    for (int kt = 0; kt < 8; ++kt) {
+        const uint32_t m0 = mbits[0] >> (2 * kt), m1 = mbits[1] >> (2 * kt);
+        uint32_t ahi[4], alo[4];
+        fq_split((m0 & 1u) ? in[kt][0] : 0.0f, ahi[0], alo[0]);
+        fq_split((m1 & 1u) ? in[kt][2] : 0.0f, ahi[1], alo[1]);
+        fq_split((m0 & 2u) ? in[kt][1] : 0.0f, ahi[2], alo[2]);
+        fq_split((m1 & 2u) ? in[kt][3] : 0.0f, ahi[3], alo[3]);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) fq_mma3(out[nt], ahi, alo, frags[(nt * 8 + kt) * 32 + lane]);
+    }
+}
+
+template <bool SAFE>
+__device__ __forceinline__ void rf_backward_tiles(const RenderFieldSmem &s, const float *__restrict__ x,
+                                                  const float *__restrict__ dirs, float bound,
+                                                  const float *__restrict__ table, int align_corners,
+                                                  const float *__restrict__ sigma, const float *__restrict__ rgb,
+                                                  const uint16_t *__restrict__ masks,
+                                                  const float *__restrict__ grad_sigma,
+                                                  const float *__restrict__ grad_rgb, float *__restrict__ grad_x,
+                                                  float *__restrict__ grad_d, int64_t B) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const float e_lo = expf(-15.0f), e_hi = expf(15.0f);
+    const float den = 2.0f * bound;
+    const int64_t ntiles = (B + RF_TILE - 1) / RF_TILE;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t base = tile * RF_TILE + warp * 16;
+        if (base >= B) continue;
+        float x01[2][3], dir[2][3], go0[2], d3[2];  // d3: dL/d(colour logit t) of the lane's two rows (t < 3)
+        bool valid[2];
+        uint32_t m_sig[2], m_c1[2], m_c2[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t b = base + 8 * h + g;
+            valid[h] = fq_load_point(x, b, B, bound, x01[h]);
+            const bool inb = b < B;
+            go0[h] = inb ? __ldg(grad_sigma + b) * fminf(fmaxf(__ldg(sigma + b), e_lo), e_hi) : 0.0f;
+            float c = 0.0f, gc = 0.0f;
+            if (inb && t < 3) {
+                c = __ldg(rgb + b * 3 + t);
+                gc = __ldg(grad_rgb + b * 3 + t);
+            }
+            d3[h] = gc * c * (1.0f - c);  // sigmoid'
+#pragma unroll
+            for (int a = 0; a < 3; ++a) dir[h][a] = inb ? __ldg(dirs + b * 3 + a) : 0.0f;
+            m_sig[h] = inb ? (uint32_t)__ldg(masks + (b * 3 + 0) * 4 + t) : 0u;
+            m_c1[h] = inb ? (uint32_t)__ldg(masks + (b * 3 + 1) * 4 + t) : 0u;
+            m_c2[h] = inb ? (uint32_t)__ldg(masks + (b * 3 + 2) * 4 + t) : 0u;
+        }
+        // ---- colour layer 3 backward: dHc2 = dRGB W_c2 (K = 3 padded to one k-tile)
+        float dh2[8][4];
+        {
+            uint32_t ahi[4], alo[4];
+            fq_split(d3[0], ahi[0], alo[0]);
+            fq_split(d3[1], ahi[1], alo[1]);
+            ahi[2] = ahi[3] = alo[2] = alo[3] = 0u;
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+                dh2[nt][0] = dh2[nt][1] = dh2[nt][2] = dh2[nt][3] = 0.0f;
+                fq_mma3(dh2[nt], ahi, alo, s.c2[nt * 32 + lane]);
+            }
+        }
+        // ---- colour layers 2, 1 backward
+        float dh1[8][4], din[4][4];
+        rf_masked_layer<8>(dh2, m_c2, s.c1, lane, dh1);
+        rf_masked_layer<4>(dh1, m_c1, s.c0, lane, din);  // din[0..1] = dL/dSH 8nt+2t(+1); din[2..3] = dL/do 8(nt-2)+2t(+1)
+
+        // ---- SH backward: the lane holds dL/dSH at indices {2t, 2t+1, 8+2t, 9+2t}; J^T v, summed over the quad below
+        float gdir[2][3];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            float jx[16], jy[16], jz[16];
+            ngp_sh4_jac(dir[h][0], dir[h][1], dir[h][2], jx, jy, jz);
+            gdir[h][0] = gdir[h][1] = gdir[h][2] = 0.0f;
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const int o8 = 8 * nt + c;
+                    const float v = din[nt][2 * h + c];
+                    gdir[h][0] = fmaf(v, rf_sel4(t, jx[o8], jx[o8 + 2], jx[o8 + 4], jx[o8 + 6]), gdir[h][0]);
+                    gdir[h][1] = fmaf(v, rf_sel4(t, jy[o8], jy[o8 + 2], jy[o8 + 4], jy[o8 + 6]), gdir[h][1]);
+                    gdir[h][2] = fmaf(v, rf_sel4(t, jz[o8], jz[o8 + 2], jz[o8 + 4], jz[o8 + 6]), gdir[h][2]);
+                }
+        }
+        // ---- sigma net backward: dO = [dL/dsigma * exp'(.) | dL/dgeo], dHs = dO W_s1 (K = 16), ReLU mask
+        if (t == 0) {
+            din[2][0] += go0[0];  // column 0 (its colour weight is zero, so din holds 0 there)
+            din[2][2] += go0[1];
+        }
+        float dhm[8][4];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) dhm[nt][0] = dhm[nt][1] = dhm[nt][2] = dhm[nt][3] = 0.0f;
+#pragma unroll
+        for (int kt = 0; kt < 2; ++kt) {
+            uint32_t ahi[4], alo[4];
+            fq_split(din[2 + kt][0], ahi[0], alo[0]);
+            fq_split(din[2 + kt][2], ahi[1], alo[1]);
+            fq_split(din[2 + kt][1], ahi[2], alo[2]);
+            fq_split(din[2 + kt][3], ahi[3], alo[3]);
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) fq_mma3(dhm[nt], ahi, alo, s.s1[(nt * 2 + kt) * 32 + lane]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const uint32_t m0 = m_sig[0] >> (2 * nt), m1 = m_sig[1] >> (2 * nt);
+            dhm[nt][0] = (m0 & 1u) ? dhm[nt][0] : 0.0f;
+            dhm[nt][1] = (m0 & 2u) ? dhm[nt][1] : 0.0f;
+            dhm[nt][2] = (m1 & 1u) ? dhm[nt][2] : 0.0f;
+            dhm[nt][3] = (m1 & 2u) ? dhm[nt][3] : 0.0f;
+        }
+        // ---- encoder input-backward, one level group at a time (fieldcore.cuh)
+        float gx[2][3];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) gx[h][0] = gx[h][1] = gx[h][2] = 0.0f;
+        fq_backward_group<0, SAFE>(s.lv, s.s0, table, 0, lane, x01, valid, align_corners, dhm, gx);
+#pragma unroll 1
+        for (int nt = 1; nt < 4; ++nt) fq_backward_group<1, SAFE>(s.lv, s.s0, table, nt, lane, x01, valid, align_corners, dhm, gx);
+
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                gx[h][a] += __shfl_xor_sync(0xffffffffu, gx[h][a], 1);
+                gx[h][a] += __shfl_xor_sync(0xffffffffu, gx[h][a], 2);
+                gdir[h][a] += __shfl_xor_sync(0xffffffffu, gdir[h][a], 1);
+                gdir[h][a] += __shfl_xor_sync(0xffffffffu, gdir[h][a], 2);
+            }
+            const int64_t b = base + 8 * h + g;
+            if (b < B && t < 3) {
+                grad_x[b * 3 + t] = __fdiv_rn(t == 0 ? gx[h][0] : (t == 1 ? gx[h][1] : gx[h][2]), den);
+                if (grad_d) grad_d[b * 3 + t] = t == 0 ? gdir[h][0] : (t == 1 ? gdir[h][1] : gdir[h][2]);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(RF_THREADS, 1)
+k_render_field_backward(const float *__restrict__ x, const float *__restrict__ dirs, float bound,
+                        const float *__restrict__ table, const int32_t *__restrict__ offsets, float S, uint32_t H,
+                        uint32_t gridtype, int align_corners, const float *__restrict__ Ws0,
+                        const float *__restrict__ Ws1, const float *__restrict__ Wc0, const float *__restrict__ Wc1,
+                        const float *__restrict__ Wc2, const float *__restrict__ sigma, const float *__restrict__ rgb,
+                        const uint16_t *__restrict__ masks, const float *__restrict__ grad_sigma,
+                        const float *__restrict__ grad_rgb, float *__restrict__ grad_x, float *__restrict__ grad_d,
+                        int64_t B) {
+    extern __shared__ __align__(16) unsigned char rf_smem_raw[];
+    RenderFieldSmem &s = *reinterpret_cast<RenderFieldSmem *>(rf_smem_raw);
+    const int tid = threadIdx.x;
+    fq_stage_levels(s.lv, &s.all_safe, offsets, S, H, gridtype, align_corners);
+    // every product below is (row fragment) x W: B[k][n] = W[k-th unit of the upstream layer][n-th unit downstream],
+    // k slots (t, t+4) of k-tile kt = upstream units 8kt+2t, 8kt+2t+1 (the accumulator-fragment columns)
+    for (int i = tid; i < 1024; i += RF_THREADS) {  // dFeat = dHs W_s0: [nt 4][kt 8]
+        const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
+        s.s0[i] = fq_split_pair(Ws0[(8 * kt + 2 * tt) * FQ_F + n], Ws0[(8 * kt + 2 * tt + 1) * FQ_F + n]);
+    }
+    for (int i = tid; i < 512; i += RF_THREADS) {  // dHs = dO W_s1: [nt 8][kt 2], k = output columns
+        const int ln = i & 31, kt = (i >> 5) & 1, nt = i >> 6, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
+        s.s1[i] = fq_split_pair(Ws1[(8 * kt + 2 * tt) * FQ_HID + n], Ws1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
+    }
+    for (int i = tid; i < 1024; i += RF_THREADS) {  // dIn = dHc1 W_c0: [nt 4][kt 8]; n-tiles 0,1 = SH, 2,3 = o columns
+        const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
+        const float *w0 = Wc0 + (8 * kt + 2 * tt) * RF_CIN, *w1 = w0 + RF_CIN;
+        float b0, b1;
+        if (nt < 2) {
+            b0 = w0[8 * nt + gg];
+            b1 = w1[8 * nt + gg];
+        } else {
+            const int col = 8 * (nt - 2) + gg;
+            b0 = col == 0 ? 0.0f : w0[16 + col - 1];
+            b1 = col == 0 ? 0.0f : w1[16 + col - 1];
+        }
+        s.c0[i] = fq_split_pair(b0, b1);
+    }
+    for (int i = tid; i < 2048; i += RF_THREADS) {  // dHc1 = dHc2 W_c1: [nt 8][kt 8]
+        const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
+        s.c1[i] = fq_split_pair(Wc1[(8 * kt + 2 * tt) * FQ_HID + n], Wc1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
+    }
+    for (int i = tid; i < 256; i += RF_THREADS) {  // dHc2 = dRGB W_c2: [nt 8], k slot t = colour channel t (< 3)
+        const int ln = i & 31, nt = i >> 5, gg = ln >> 2, tt = ln & 3;
+        s.c2[i] = fq_split_pair(tt < 3 ? Wc2[tt * FQ_HID + 8 * nt + gg] : 0.0f, 0.0f);
+    }
+    __syncthreads();
+    if (s.all_safe)
+        rf_backward_tiles<true>(s, x, dirs, bound, table, align_corners, sigma, rgb, masks, grad_sigma, grad_rgb, grad_x, grad_d, B);
+    else
+        rf_backward_tiles<false>(s, x, dirs, bound, table, align_corners, sigma, rgb, masks, grad_sigma, grad_rgb, grad_x, grad_d, B);
+}
+
+// ------------------------------------------------------------------------------------------------ C ABI
+template <typename K>
+static int rf_launch_cfg(K kernel, int64_t B, int *grid) {
+    const int smem = (int)sizeof(RenderFieldSmem);
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+        ngp_set_error("render field: cannot reserve %d B of shared memory", smem);
+        return NGP_ERR_CUDA;
+    }
+    int dev = 0, sms = NGP_SM_COUNT;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t tiles = ngp_div_up(B, RF_TILE);
+    *grid = (int)(tiles < sms ? tiles : sms);
+    return NGP_OK;
+}
+
+extern "C" int ngp_field_color_forward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                                       const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
+                                       int align_corners, const float *Ws0, const float *Ws1, const float *Wc0,
+                                       const float *Wc1, const float *Wc2, float *sigma, float *rgb, void *masks,
+                                       int64_t M, ngp_stream_t stream) {
+    NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb, NGP_ERR_ARG,
+                "ngp_field_color_forward: null pointer");
+    NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_forward: bad bound / M");
+    NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_forward: embeddings must be 16-byte aligned");
+    if (M == 0) return NGP_OK;
+    int grid = 1;
+    int rc = rf_launch_cfg(k_render_field_forward, M, &grid);
+    if (rc) return rc;
+    k_render_field_forward<<<grid, RF_THREADS, sizeof(RenderFieldSmem), (cudaStream_t)stream>>>(
+        xyzs, dirs, bound, embeddings, offsets, S, H, gridtype, align_corners, Ws0, Ws1, Wc0, Wc1, Wc2, sigma, rgb,
+        (uint16_t *)masks, M);
+    NGP_CHECK_LAUNCH("ngp_field_color_forward");
+    return NGP_OK;
+}
+
+extern "C" int ngp_field_color_backward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                                        const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
+                                        int align_corners, const float *Ws0, const float *Ws1, const float *Wc0,
+                                        const float *Wc1, const float *Wc2, const float *sigma, const float *rgb,
+                                        const void *masks, const float *grad_sigma, const float *grad_rgb,
+                                        float *grad_xyzs, float *grad_dirs, int64_t M, ngp_stream_t stream) {
+    NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb && masks &&
+                    grad_sigma && grad_rgb && grad_xyzs,
+                NGP_ERR_ARG, "ngp_field_color_backward: null pointer");
+    NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_backward: bad bound / M");
+    NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_backward: embeddings must be 16-byte aligned");
+    if (M == 0) return NGP_OK;
+    int grid = 1;
+    int rc = rf_launch_cfg(k_render_field_backward, M, &grid);
+    if (rc) return rc;
+    k_render_field_backward<<<grid, RF_THREADS, sizeof(RenderFieldSmem), (cudaStream_t)stream>>>(
+        xyzs, dirs, bound, embeddings, offsets, S, H, gridtype, align_corners, Ws0, Ws1, Wc0, Wc1, Wc2, sigma, rgb,
+        (const uint16_t *)masks, grad_sigma, grad_rgb, grad_xyzs, grad_dirs, M);
+    NGP_CHECK_LAUNCH("ngp_field_color_backward");
+    return NGP_OK;
+}

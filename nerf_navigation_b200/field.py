@@ -67,3 +67,67 @@ def field_query(x, encoder, W0, W1, bound):
     sigma, geo = _field_query.apply(x.reshape(-1, 3), encoder.embeddings, W0, W1, encoder.offsets, bound, S,
                                     int(encoder.base_resolution), encoder.gridtype_id, encoder.align_corners)
     return sigma.view(prefix), geo.view(prefix + [15])
+
+
+def fused_color_supported(model, x, d):
+    """The fused sample kernel covers nav's network: fused_supported() + SH degree 4 + colour net 31-64-64-3."""
+    cn = model.color_net
+    return (len(cn) == 3 and tuple(cn[0].weight.shape) == (64, 31) and tuple(cn[1].weight.shape) == (64, 64)
+            and tuple(cn[2].weight.shape) == (3, 64) and getattr(model.encoder_dir, "degree", None) == 4
+            and d.dtype == torch.float32
+            and fused_supported(model.encoder, model.sigma_net[0].weight, model.sigma_net[1].weight, x))
+
+
+class _field_color(Function):
+    """(xyzs [M,3], dirs [M,3]) -> sigma [M], rgb [M,3] with a frozen field; backward: dL/dxyzs, dL/ddirs.
+    One kernel each way (csrc/renderfield.cu); replaces GridEncoder + 2 Linear + trunc_exp + SHEncoder + cat + 3 Linear +
+    sigmoid of NeRFNetwork.forward (network.py:95-124)."""
+
+    @staticmethod
+    def forward(ctx, x, d, embeddings, offsets, Ws0, Ws1, Wc0, Wc1, Wc2, bound, S, H, gridtype, align_corners):
+        _lib.require_cuda(x, d, embeddings)
+        x = x.contiguous(); d = d.contiguous()
+        ws = [w.contiguous() for w in (Ws0, Ws1, Wc0, Wc1, Wc2)]
+        M = x.shape[0]
+        sigma = torch.empty(M, device=x.device, dtype=torch.float32)
+        rgb = torch.empty(M, 3, device=x.device, dtype=torch.float32)
+        need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        masks = torch.empty(M, 12, device=x.device, dtype=torch.int16) if need_bwd else None
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ngp_field_color_forward(
+                _lib.ptr(x), _lib.ptr(d), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype,
+                int(align_corners), *[_lib.ptr(w) for w in ws], _lib.ptr(sigma), _lib.ptr(rgb), _lib.ptr(masks), M,
+                _lib.stream()), "field_color_forward")
+        if need_bwd:
+            ctx.save_for_backward(x, d, embeddings, offsets, *ws, sigma, rgb, masks)
+        ctx.cfg = (float(bound), S, H, gridtype, int(align_corners))
+        return sigma, rgb
+
+    @staticmethod
+    def backward(ctx, grad_sigma, grad_rgb):
+        x, d, embeddings, offsets, Ws0, Ws1, Wc0, Wc1, Wc2, sigma, rgb, masks = ctx.saved_tensors
+        bound, S, H, gridtype, align = ctx.cfg
+        M = x.shape[0]
+        grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
+        grad_rgb = torch.zeros_like(rgb) if grad_rgb is None else grad_rgb.contiguous().float()
+        gx = torch.empty(M, 3, device=x.device, dtype=torch.float32)
+        gd = torch.empty(M, 3, device=x.device, dtype=torch.float32) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ngp_field_color_backward(
+                _lib.ptr(x), _lib.ptr(d), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align,
+                _lib.ptr(Ws0), _lib.ptr(Ws1), _lib.ptr(Wc0), _lib.ptr(Wc1), _lib.ptr(Wc2), _lib.ptr(sigma), _lib.ptr(rgb),
+                _lib.ptr(masks), _lib.ptr(grad_sigma), _lib.ptr(grad_rgb), _lib.ptr(gx), _lib.ptr(gd), M, _lib.stream()),
+                "field_color_backward")
+        return (gx, gd) + (None,) * 12
+
+
+def field_color(model, x, d):
+    """Fused NeRFNetwork.forward(x, d) for a frozen field: x, d [..., 3] -> (sigma [...], rgb [..., 3])."""
+    prefix = list(x.shape[:-1])
+    enc = model.encoder
+    S = float(np.log2(enc.per_level_scale))
+    sigma, rgb = _field_color.apply(
+        x.reshape(-1, 3), d.reshape(-1, 3), enc.embeddings.detach(), enc.offsets, model.sigma_net[0].weight.detach(),
+        model.sigma_net[1].weight.detach(), model.color_net[0].weight.detach(), model.color_net[1].weight.detach(),
+        model.color_net[2].weight.detach(), model.bound, S, int(enc.base_resolution), enc.gridtype_id, enc.align_corners)
+    return sigma.view(prefix), rgb.view(prefix + [3])

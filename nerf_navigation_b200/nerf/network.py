@@ -15,7 +15,7 @@ import torch.nn.functional as F
 
 from ..activation import trunc_exp
 from ..encoding import get_encoder
-from ..field import field_query, fused_supported
+from ..field import field_color, field_query, fused_color_supported, fused_supported
 from .renderer import NeRFRenderer
 
 
@@ -84,8 +84,14 @@ class NeRFNetwork(NeRFRenderer):
         h = self._sigma_mlp(self.encoder(x, bound=self.bound))
         return {"sigma": trunc_exp(h[..., 0]), "geo_feat": h[..., 1:]}
 
+    def _frozen(self):
+        return not self.training or not any(p.requires_grad for p in self.parameters())
+
     def forward(self, x, d):
-        """network.py:95-124 -> (sigma [...], color [..., 3])."""
+        """network.py:95-124 -> (sigma [...], color [..., 3]).  Frozen field on CUDA: one fused kernel each way."""
+        if (self.fused_eval and self._frozen() and x.is_cuda and self.num_layers == 2 and hasattr(self.encoder, "embeddings")
+                and fused_color_supported(self, x, d)):
+            return field_color(self, x, d)
         dens = self.density(x)
         return dens["sigma"], self._color_mlp(d, dens["geo_feat"])
 
