@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--points", type=int, default=1 << 22, help="points per GPU per step")
     ap.add_argument("--cpu-points", type=int, default=1 << 18, help="points per CPU-baseline step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-estimator", action="store_true")
+    ap.add_argument("--hypotheses", type=int, default=256)
+    ap.add_argument("--estimator-steps", type=int, default=3)
     return ap.parse_args()
 
 
@@ -235,10 +238,40 @@ def run_b200(args):
     t_end = time.perf_counter()
     clocks = sampler.stop(t_begin, t_end) if sampler else None
 
+    # ---- BASELINE config 3 (second half of the metric): pose-estimator photometric loss, 256 hypotheses x 4096 rays
+    # sharded by hypothesis over the ranks (strong scaling, no collective), forward + backward to the poses
+    est = None
+    if not args.no_estimator:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_estimator as BE
+        from nerf_navigation_b200.sharding import shard_range
+        emodel, eposes, epix, etarget, ekw = BE.setup(dev, args.hypotheses, 4096)
+        lo, hi = shard_range(args.hypotheses, rank, world)
+        eposes = eposes[lo:hi]
+        BE.step(emodel, eposes, epix, etarget, ekw, 32)
+        barrier()
+        e4, e5 = ev(), ev()
+        e4.record()
+        for _ in range(args.estimator_steps):
+            BE.step(emodel, eposes, epix, etarget, ekw, 32)
+        e5.record()
+        barrier()
+        t_est = e4.elapsed_time(e5) / 1e3 / args.estimator_steps
+        del emodel
+
     if world > 1:
-        tt = torch.tensor([t_dev, t_e2e], device=dev, dtype=torch.float64)
+        tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_dev, t_e2e = tt.tolist()
+        t_dev, t_e2e, t_est_max = tt.tolist()
+        if not args.no_estimator:
+            t_est = t_est_max
+    if not args.no_estimator:
+        est = {"metric": "estimator rays/s (photometric loss fwd + bwd to pose)", "value": args.hypotheses * 4096 / t_est,
+               "unit": "rays/s", "ms_per_step": t_est * 1e3, "hypotheses": args.hypotheses, "rays_per_hypothesis": 4096,
+               "scaling": "strong", "sharding": "pose hypotheses by rank, replicated field, no collective",
+               "scene": "synthetic stonehenge occupancy (128^3 x 2 cascades), random-init field, ~75 samples/ray",
+               "path": "near_far -> march_rays_train -> fused field+colour kernel -> composite_rays_train, and backward",
+               "reference_cuda_build_same_box": "profiles/r1_reference_cuda_build.json (scripts/bench_ref_cuda.py)"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -289,6 +322,7 @@ def run_b200(args):
                                  "frac": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}},
         "clocks": clocks,
     }
+    out["estimator"] = est
     if world == 1 and not args.no_cpu_baseline:
         cstep, cores = cpu_field_setup(args.cpu_points)
         cstep()
