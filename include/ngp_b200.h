@@ -152,6 +152,23 @@ int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, fl
                        const float *rgbs, const float *deltas, float *weights_sum, float *depth, float *image,
                        ngp_stream_t stream);
 
+/* ---- fused inference renderer: NeRFRenderer.run_cuda eval branch, nerf/renderer.py:325-374 ----------------------- */
+
+/* One persistent kernel for: near_far_from_aabb -> loop { march_rays -> NeRFNetwork.forward(x, d) -> composite_rays ->
+ * compact alive rays } -> image + (1 - weights_sum) * bg, clamp(depth - near, 0) / (far - near).  Per-sample data never
+ * reach HBM.  rays_o/rays_d [N,3]; aabb [6]; grid = density_bitfield u8 [C*Hgrid^3/8]; field arguments as in
+ * ngp_field_color_forward; bg_color NULL (= 1), 3 floats (bg_stride 0) or [N,3] (bg_stride 3).  Outputs image [N,3],
+ * depth [N], weights_sum [N] (may be NULL).  workspace: ngp_render_rays_infer_workspace_bytes() bytes, 8-byte aligned;
+ * after the call its second u64 holds the number of samples evaluated.  dt_gamma/max_steps as in march_rays; a ray takes
+ * at most max_steps samples; no perturbation. */
+int64_t ngp_render_rays_infer_workspace_bytes(void);
+int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                          const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
+                          const float *embeddings, const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
+                          int align_corners, const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1,
+                          const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
+                          float *depth, float *weights_sum, void *workspace, ngp_stream_t stream);
+
 /* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
 
 /* sh_encode_forward (shencoder.cu:386-412).  inputs [B,3] -> outputs [B,degree^2]; dy_dx [B,3,degree^2] optional. */

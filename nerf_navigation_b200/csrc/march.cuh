@@ -105,6 +105,31 @@ __device__ __forceinline__ bool ngp_march_step(const MarchRay &r, const MarchCfg
     return false;
 }
 
+// AABB slab test of one ray (raymarching.cu:93-147): near clamped to min_near; a miss returns FLT_MAX for both.
+__device__ __forceinline__ void ngp_near_far_ray(const float (&o)[3], const float (&d)[3], const float *__restrict__ aabb,
+                                                 float min_near, float &near, float &far) {
+    float tn = 0.0f, tf = 0.0f;
+    bool miss = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float r = 1.0f / d[a];
+        float lo = (__ldg(aabb + a) - o[a]) * r, hi = (__ldg(aabb + a + 3) - o[a]) * r;
+        if (lo > hi) { const float t = lo; lo = hi; hi = t; }
+        if (a == 0) { tn = lo; tf = hi; continue; }
+        if (!miss) {
+            if (tn > hi || lo > tf) miss = true;
+            else {
+                if (lo > tn) tn = lo;
+                if (hi < tf) tf = hi;
+            }
+        }
+    }
+    if (miss) { near = 3.402823466e+38f; far = 3.402823466e+38f; return; }
+    if (tn < min_near) tn = min_near;
+    near = tn;
+    far = tf;
+}
+
 // ---- PCG32 (O'Neill) as used by raymarching/src/pcg32.h: seed(:57-72), advance(:149-170), next_float(:107-116)
 struct NgpPcg32 {
     uint64_t state, inc;

@@ -16,27 +16,12 @@ k_near_far(const float *__restrict__ rays_o, const float *__restrict__ rays_d, c
            float min_near, float *__restrict__ nears, float *__restrict__ fars) {
     const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
     if (n >= N) return;
-    float tn = 0.0f, tf = 0.0f;
-    bool miss = false;
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-        const float o = rays_o[n * 3 + a];
-        const float r = 1.0f / rays_d[n * 3 + a];
-        float lo = (__ldg(aabb + a) - o) * r, hi = (__ldg(aabb + a + 3) - o) * r;
-        if (lo > hi) { const float t = lo; lo = hi; hi = t; }
-        if (a == 0) { tn = lo; tf = hi; continue; }
-        if (!miss) {
-            if (tn > hi || lo > tf) miss = true;
-            else {
-                if (lo > tn) tn = lo;
-                if (hi < tf) tf = hi;
-            }
-        }
-    }
-    if (miss) { nears[n] = FLT_MAX; fars[n] = FLT_MAX; return; }
-    if (tn < min_near) tn = min_near;
-    nears[n] = tn;
-    fars[n] = tf;
+    const float o[3] = {rays_o[n * 3], rays_o[n * 3 + 1], rays_o[n * 3 + 2]};
+    const float d[3] = {rays_d[n * 3], rays_d[n * 3 + 1], rays_d[n * 3 + 2]};
+    float near, far;
+    ngp_near_far_ray(o, d, aabb, min_near, near, far);
+    nears[n] = near;
+    fars[n] = far;
 }
 
 extern "C" int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, int64_t N,

@@ -131,3 +131,42 @@ def field_color(model, x, d):
         model.sigma_net[1].weight.detach(), model.color_net[0].weight.detach(), model.color_net[1].weight.detach(),
         model.color_net[2].weight.detach(), model.bound, S, int(enc.base_resolution), enc.gridtype_id, enc.align_corners)
     return sigma.view(prefix), rgb.view(prefix + [3])
+
+
+@torch.no_grad()
+def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, max_steps=1024, return_stats=False):
+    """Fused eval branch of NeRFRenderer.run_cuda (renderer.py:325-374): near/far, the alive-ray loop of march_rays ->
+    forward(x, d) -> composite_rays, and the background / depth post-processing in ONE kernel (csrc/render.cu).
+    rays_o, rays_d [N,3] -> image [N,3], depth [N], weights_sum [N] (already post-processed like run_cuda's results)."""
+    _lib.require_cuda(rays_o, rays_d, model.density_bitfield)
+    rays_o = rays_o.contiguous().float()
+    rays_d = rays_d.contiguous().float()
+    N = rays_o.shape[0]
+    dev = rays_o.device
+    enc = model.encoder
+    image = torch.empty(N, 3, device=dev)
+    depth = torch.empty(N, device=dev)
+    wsum = torch.empty(N, device=dev)
+    bg, stride = None, 0
+    if bg_color is not None:
+        bg = torch.as_tensor(bg_color, dtype=torch.float32, device=dev)
+        if bg.numel() == 1:
+            bg = bg.reshape(1).expand(3)
+        if bg.numel() == 3:
+            bg = bg.reshape(3).contiguous()
+        else:
+            bg, stride = bg.expand(N, 3).contiguous(), 3
+    work = torch.empty(2, device=dev, dtype=torch.int64)
+    ws = [w.detach().contiguous() for w in (model.sigma_net[0].weight, model.sigma_net[1].weight, model.color_net[0].weight,
+                                            model.color_net[1].weight, model.color_net[2].weight)]
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().ngp_render_rays_infer(
+            _lib.ptr(rays_o), _lib.ptr(rays_d), N, _lib.ptr(aabb.contiguous()), float(model.min_near),
+            _lib.ptr(model.density_bitfield), float(model.bound), float(dt_gamma), int(max_steps), int(model.cascade),
+            int(model.grid_size), _lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets),
+            float(np.log2(enc.per_level_scale)), int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners),
+            *[_lib.ptr(w) for w in ws], float(model.density_scale), _lib.ptr(bg), stride, _lib.ptr(image),
+            _lib.ptr(depth), _lib.ptr(wsum), _lib.ptr(work), _lib.stream()), "render_rays_infer")
+    if return_stats:
+        return image, depth, wsum, work
+    return image, depth, wsum

@@ -74,6 +74,19 @@ class NeRFRenderer(nn.Module):
     def color(self, x, d, mask=None, **kwargs):
         raise NotImplementedError()
 
+    def _fused_render_supported(self, rays_o, rays_d, perturb):
+        """The fused inference renderer covers nav's model (NeRFNetwork: 16x2 hash grid, 64-wide torch MLPs, SH 4) with a
+        frozen field, fp32, no perturbation; anything else takes the op-by-op loop below."""
+        if perturb or not getattr(self, "fused_eval", False) or not getattr(self, "fused_render", True) or torch.is_grad_enabled() and (
+                rays_o.requires_grad or rays_d.requires_grad):
+            return False
+        try:
+            from ..field import fused_color_supported
+            return (rays_o.is_cuda and getattr(self, "num_layers", 0) == 2 and hasattr(self.encoder, "embeddings")
+                    and hasattr(self, "color_net") and fused_color_supported(self, rays_o, rays_d))
+        except AttributeError:
+            return False
+
     def reset_extra_state(self):
         if not self.cuda_ray:
             return
@@ -173,6 +186,10 @@ class NeRFRenderer(nn.Module):
             image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
             depth = torch.clamp(depth - nears, min=0) / (fars - nears)
             results["weights_sum"] = weights_sum
+        elif self._fused_render_supported(rays_o, rays_d, perturb):
+            # one persistent kernel for the whole alive-ray loop + post-processing (csrc/render.cu)
+            from ..field import render_rays_infer
+            image, depth, weights_sum = render_rays_infer(self, rays_o, rays_d, aabb, bg_color, dt_gamma, max_steps)
         else:
             weights_sum = torch.zeros(N, dtype=torch.float32, device=device)
             depth = torch.zeros(N, dtype=torch.float32, device=device)
