@@ -41,6 +41,10 @@ def parse():
     ap.add_argument("--no-estimator", action="store_true")
     ap.add_argument("--hypotheses", type=int, default=256)
     ap.add_argument("--estimator-steps", type=int, default=3)
+    ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--frames", type=int, default=64, help="config 4: 800x800 frames in the batch (whole job)")
+    ap.add_argument("--frames-per-step", type=int, default=8, help="frames rendered per kernel launch on a rank")
+    ap.add_argument("--render-steps", type=int, default=1)
     return ap.parse_args()
 
 
@@ -259,12 +263,45 @@ def run_b200(args):
         t_est = e4.elapsed_time(e5) / 1e3 / args.estimator_steps
         del emodel
 
+    # ---- BASELINE config 4: full-frame cuda_ray render, 800x800 x `frames` poses on an orbit, inference path through the
+    # fused kernel (csrc/render.cu); frames sharded by rank (strong scaling, no collective)
+    t_ren, ren_samples, ren_frames = 0.0, 0, 0
+    if not args.no_render:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_render as BR
+        from nerf_navigation_b200.field import render_rays_infer
+        from nerf_navigation_b200.sharding import shard_range
+        flo, fhi = shard_range(args.frames, rank, world)
+        ren_frames = fhi - flo
+        chunks = [(a, min(a + args.frames_per_step, fhi)) for a in range(flo, fhi, args.frames_per_step)]
+        rmodel, rays = None, []
+        for a, b in chunks:   # rays of every chunk are resident before the timed region (12 + 12 B per ray)
+            rmodel, ro, rd = BR.setup(dev, b - a, first=a, total=args.frames)
+            rays.append((ro, rd))
+        for ro, rd in rays[:1]:
+            BR.step(rmodel, ro, rd)
+        barrier()
+        e6, e7 = ev(), ev()
+        e6.record()
+        for _ in range(args.render_steps):
+            for ro, rd in rays:
+                BR.step(rmodel, ro, rd)
+        e7.record()
+        barrier()
+        t_ren = e6.elapsed_time(e7) / 1e3 / args.render_steps
+        for ro, rd in rays:
+            ren_samples += int(render_rays_infer(rmodel, ro, rd, rmodel.aabb_infer, 1.0, return_stats=True)[3][1].item())
+        del rmodel, rays
+
     if world > 1:
-        tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est], device=dev, dtype=torch.float64)
+        tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est, t_ren], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_dev, t_e2e, t_est_max = tt.tolist()
+        t_dev, t_e2e, t_est_max, t_ren = tt.tolist()
         if not args.no_estimator:
             t_est = t_est_max
+        cnt = torch.tensor([ren_samples], device=dev, dtype=torch.int64)
+        dist.all_reduce(cnt)
+        ren_samples = int(cnt.item())
     if not args.no_estimator:
         est = {"metric": "estimator rays/s (photometric loss fwd + bwd to pose)", "value": args.hypotheses * 4096 / t_est,
                "unit": "rays/s", "ms_per_step": t_est * 1e3, "hypotheses": args.hypotheses, "rays_per_hypothesis": 4096,
@@ -323,6 +360,20 @@ def run_b200(args):
         "clocks": clocks,
     }
     out["estimator"] = est
+    if not args.no_render:
+        nrays = args.frames * 800 * 800
+        # per-sample bounds of the fused kernel: 1024 B of L2 gathers (same unit as the field query) and 1368 mma.sync
+        # m16n8k8 TF32 per 16 samples (456 products x 3 for the 3xTF32 split)
+        out["render"] = {
+            "metric": "full-frame render (config 4)", "frames": args.frames, "rays": nrays, "ms_per_step": t_ren * 1e3,
+            "ms_per_frame": t_ren * 1e3 / args.frames, "frames_per_s": args.frames / t_ren, "rays_per_s": nrays / t_ren,
+            "samples": ren_samples, "samples_per_ray": ren_samples / nrays, "samples_per_s": ren_samples / t_ren,
+            "scaling": "strong", "sharding": "frames by rank, replicated field + bitfield, no collective",
+            "path": "ngp_render_rays_infer: near/far + march + field + colour + composite + post in one persistent kernel",
+            "gpu_launches": args.render_steps * ((ren_frames + args.frames_per_step - 1) // args.frames_per_step),
+            "l2_gather": {"achieved": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world, "peak": gather_peak,
+                          "unit": "GB/s useful per GPU",
+                          "frac": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak}}
     if world == 1 and not args.no_cpu_baseline:
         cstep, cores = cpu_field_setup(args.cpu_points)
         cstep()

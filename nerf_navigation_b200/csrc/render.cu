@@ -5,12 +5,14 @@
 //                             -> composite_rays (:828-913) -> rays_alive = rays_alive[rays_alive >= 0]   (host sync)
 // Per-sample positions, sigma and rgb never reach HBM: HBM sees 24 B in and 20 B out per RAY.
 //
-// Organisation (same warp-cooperative field core as renderfield.cu): a warp owns 16 ray slots; lane (g, t) marches
-// slot g + 8 (t & 1) (two lanes per slot compute identical values), the 16 pending samples form one mma.sync row tile,
-// the field is evaluated, every slot composites its sample, and a slot whose ray ended (t >= far, T < 1e-4, sample
-// cap) writes its pixel and takes the next ray from a global counter (one warp-aggregated atomic per refill).  So the
-// row tile stays full while rays of very different lengths come and go — the role of the reference's alive-list
-// compaction, without its per-iteration host round trip.
+// Organisation (same warp-cooperative field core as renderfield.cu): a warp owns 32 ray slots, one per lane.  Each lane
+// marches its own ray a bounded number of voxel steps at a time and queues the samples it finds (t, dt) in a small
+// per-slot FIFO in shared memory, so a ray crossing a long empty stretch never stalls the others.  The heads of up to 16
+// non-empty FIFOs form one mma.sync row tile, the field is evaluated, and each of those lanes composites its sample in
+// ray order.  A slot whose ray ended (t >= far with an empty FIFO, T < 1e-4, sample cap) writes its pixel and takes the
+// next ray from a global counter (one warp-aggregated atomic per refill).  The row tile stays full while rays of very
+// different lengths come and go — the role of the reference's alive-list compaction, without its per-iteration host
+// round trip.
 //
 // Differences from the reference loop, all inside its fp tolerance: t is the marcher's own abscissa (the reference
 // re-sums deltas in composite_rays, :876, a <= 1 ulp wobble that depends on how its n_step chunks fall); a ray takes at
@@ -20,14 +22,25 @@
 #include "march.cuh"
 #include "renderfield.cuh"
 
-#define RI_SLOTS (RF_WARPS * 16)
+#define RI_SLOTS (RF_WARPS * 32)
+#ifndef RI_FIFO
+#define RI_FIFO 8          // queued samples per slot
+#endif
+#ifndef RI_BUDGET
+#define RI_BUDGET 16       // voxel steps a lane may take per marching phase
+#endif
+#ifndef RI_MARCH_BELOW
+#define RI_MARCH_BELOW 20  // march when fewer slots than this have a queued sample
+#endif
 
 struct __align__(16) RenderRaysSmem {
     RenderFieldSmem f;
     float ox[RI_SLOTS], oy[RI_SLOTS], oz[RI_SLOTS], dx[RI_SLOTS], dy[RI_SLOTS], dz[RI_SLOTS];
     float t[RI_SLOTS], near[RI_SLOTS], far[RI_SLOTS];
     float ws[RI_SLOTS], depth[RI_SLOTS], r[RI_SLOTS], g[RI_SLOTS], b[RI_SLOTS];
-    uint32_t nsamp[RI_SLOTS];
+    float qt[RI_FIFO][RI_SLOTS], qdt[RI_FIFO][RI_SLOTS];  // per-slot FIFO of pending samples
+    float tin[RF_WARPS][6][16];                            // the warp's row tile: sample position, view direction
+    float tout[RF_WARPS][4][16];                           // log sigma, colour logits of the tile rows
 };
 
 struct RenderRaysParams {
@@ -59,125 +72,141 @@ __device__ __forceinline__ void ri_finish(const RenderRaysSmem &S, const RenderR
 template <bool SAFE>
 __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams &P, const MarchCfg &cfg) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
-    const int myh = t & 1;                    // which row of the lane's pair (g, g + 8) this lane marches
-    const int slot = warp * 16 + g + 8 * myh;
-    const bool writer = t < 2;                // one of the slot's two lanes does the global writes / atomics
-    const int primary = lane & ~2;
+    const int slot = tid;                     // lane-private ray slot
     int64_t id = -1;                          // -1: slot wants a ray; -2: no rays left
-    bool have = false;
-    float px = 0.0f, py = 0.0f, pz = 0.0f, dt = 0.0f;
+    int cnt = 0, head = 0;                    // FIFO fill / read position
+    uint32_t marched = 0;                     // samples queued so far for this ray (<= max_steps)
+    bool mend = false;                        // the march of this ray is over (t >= far or sample cap)
+    unsigned rot = 0;
     unsigned long long evaluated = 0;
+    float (*tin)[16] = S.tin[warp];
+    float (*tout)[16] = S.tout[warp];
 
     for (;;) {
-        // ---- phase A: every slot ends up with a pending sample (or permanently empty)
-        for (;;) {
-            const unsigned need = __ballot_sync(0xffffffffu, id == -1 && writer);
-            if (need) {
-                unsigned long long base = 0;
-                if (lane == 0) base = atomicAdd(P.counter, (unsigned long long)__popc(need));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (id == -1) {
-                    const int64_t nid = (int64_t)base + __popc(need & ((1u << primary) - 1u));
-                    if (nid < P.N) {
-                        id = nid;
-                        const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
-                        const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
-                        float near, far;
-                        ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
-                        S.ox[slot] = o[0]; S.oy[slot] = o[1]; S.oz[slot] = o[2];
-                        S.dx[slot] = d[0]; S.dy[slot] = d[1]; S.dz[slot] = d[2];
-                        S.t[slot] = near; S.near[slot] = near; S.far[slot] = far;
-                        S.ws[slot] = 0.0f; S.depth[slot] = 0.0f; S.r[slot] = 0.0f; S.g[slot] = 0.0f; S.b[slot] = 0.0f;
-                        S.nsamp[slot] = 0u;
-                    } else {
-                        id = -2;
+        // ---- A1: refill empty slots (one atomic per warp)
+        const unsigned need = __ballot_sync(0xffffffffu, id == -1);
+        if (need) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(P.counter, (unsigned long long)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (id == -1) {
+                const int64_t nid = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                if (nid < P.N) {
+                    id = nid;
+                    const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
+                    const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
+                    float near, far;
+                    ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
+                    S.ox[slot] = o[0]; S.oy[slot] = o[1]; S.oz[slot] = o[2];
+                    S.dx[slot] = d[0]; S.dy[slot] = d[1]; S.dz[slot] = d[2];
+                    S.t[slot] = near; S.near[slot] = near; S.far[slot] = far;
+                    S.ws[slot] = 0.0f; S.depth[slot] = 0.0f; S.r[slot] = 0.0f; S.g[slot] = 0.0f; S.b[slot] = 0.0f;
+                    cnt = 0; head = 0; marched = 0; mend = false;
+                } else {
+                    id = -2;
+                }
+            }
+        }
+        // ---- A2: bounded marching, only when the queues run low
+        if (__popc(__ballot_sync(0xffffffffu, cnt > 0)) < RI_MARCH_BELOW) {
+            if (id >= 0 && !mend && cnt < RI_FIFO) {
+                MarchRay r;
+                r.ox = S.ox[slot]; r.oy = S.oy[slot]; r.oz = S.oz[slot];
+                r.dx = S.dx[slot]; r.dy = S.dy[slot]; r.dz = S.dz[slot];
+                r.rdx = 1.0f / r.dx; r.rdy = 1.0f / r.dy; r.rdz = 1.0f / r.dz;
+                float tc = S.t[slot];
+                const float far = S.far[slot];
+                float px, py, pz, dt;
+                for (int budget = RI_BUDGET; budget > 0 && cnt < RI_FIFO; --budget) {
+                    if (!(tc < far) || marched >= P.max_steps) { mend = true; break; }
+                    if (ngp_march_step(r, cfg, tc, px, py, pz, dt)) {
+                        const int w = (head + cnt) % RI_FIFO;
+                        S.qt[w][slot] = tc;
+                        S.qdt[w][slot] = dt;
+                        tc += dt;
+                        ++cnt;
+                        ++marched;
                     }
                 }
-            }
-            __syncwarp();
-            // both lanes of a slot read its state, then (after the barrier) both write back identical values
-            const bool go = id >= 0 && !have;
-            MarchRay r;
-            r.ox = S.ox[slot]; r.oy = S.oy[slot]; r.oz = S.oz[slot];
-            r.dx = S.dx[slot]; r.dy = S.dy[slot]; r.dz = S.dz[slot];
-            r.rdx = 1.0f / r.dx; r.rdy = 1.0f / r.dy; r.rdz = 1.0f / r.dz;
-            float tc = S.t[slot];
-            const float far = S.far[slot];
-            bool done = go && S.nsamp[slot] >= P.max_steps;
-            __syncwarp();
-            if (go) {
-                while (!done) {
-                    if (!(tc < far)) { done = true; break; }
-                    if (ngp_march_step(r, cfg, tc, px, py, pz, dt)) { have = true; break; }
-                }
                 S.t[slot] = tc;
-                if (done) {
-                    if (writer) ri_finish(S, P, slot, id);
-                    id = -1;
-                }
             }
-            __syncwarp();
-            if (!__any_sync(0xffffffffu, id == -1)) break;
         }
-        if (!__any_sync(0xffffffffu, id >= 0)) break;
-
-        // ---- phase B: the field at the warp's 16 pending samples
+        // ---- A3: rays whose march is over and whose queue is drained are done
+        if (id >= 0 && mend && cnt == 0) {
+            ri_finish(S, P, slot, id);
+            id = -1;
+        }
+        const unsigned avail = __ballot_sync(0xffffffffu, cnt > 0);
+        if (avail == 0) {
+            if (!__any_sync(0xffffffffu, id != -2)) break;   // every slot has run out of rays
+            continue;
+        }
+        // ---- B: tile = heads of up to 16 non-empty queues (rotating priority), row = rank among them
+        const unsigned ravail = __funnelshift_r(avail, avail, rot);
+        const int pos = (lane - (int)rot) & 31;
+        const int row = __popc(ravail & ((1u << pos) - 1u));
+        const bool sel = cnt > 0 && row < 16;
+        const int nrows = min(__popc(avail), 16);
+        rot = (rot + 13u) & 31u;
+        float st = 0.0f, sdt = 0.0f;
+        if (sel) {
+            st = S.qt[head][slot];
+            sdt = S.qdt[head][slot];
+            const float dxv = S.dx[slot], dyv = S.dy[slot], dzv = S.dz[slot];
+            tin[0][row] = ngp_clampf(fmaf(st, dxv, S.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
+            tin[1][row] = ngp_clampf(fmaf(st, dyv, S.oy[slot]), -P.bound, P.bound);
+            tin[2][row] = ngp_clampf(fmaf(st, dzv, S.oz[slot]), -P.bound, P.bound);
+            tin[3][row] = dxv; tin[4][row] = dyv; tin[5][row] = dzv;
+        }
+        __syncwarp();
         float x01[2][3], dir[2][3];
         bool valid[2];
         {
-            const float qx = __shfl_xor_sync(0xffffffffu, px, 1), qy = __shfl_xor_sync(0xffffffffu, py, 1);
-            const float qz = __shfl_xor_sync(0xffffffffu, pz, 1);
-            const bool qhave = __shfl_xor_sync(0xffffffffu, (int)have, 1) != 0;
             const float den = 2.0f * P.bound;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const bool mine = h == myh;
-                valid[h] = mine ? have : qhave;
-                const float sx = mine ? px : qx, sy = mine ? py : qy, sz = mine ? pz : qz;
-                x01[h][0] = valid[h] ? __fdiv_rn(sx + P.bound, den) : 0.5f;   // grid.py:144
-                x01[h][1] = valid[h] ? __fdiv_rn(sy + P.bound, den) : 0.5f;
-                x01[h][2] = valid[h] ? __fdiv_rn(sz + P.bound, den) : 0.5f;
-                const int sl = warp * 16 + g + 8 * h;
-                dir[h][0] = S.dx[sl]; dir[h][1] = S.dy[sl]; dir[h][2] = S.dz[sl];
+                const int rr = g + 8 * h;
+                valid[h] = rr < nrows;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    x01[h][a] = valid[h] ? __fdiv_rn(tin[a][rr] + P.bound, den) : 0.5f;   // grid.py:144
+                    dir[h][a] = valid[h] ? tin[3 + a][rr] : 0.0f;
+                }
             }
         }
         float o[2][4], o3[1][4];
         uint32_t m_sig[2], m_c1[2], m_c2[2];
         rf_eval16<SAFE>(S.f, P.table, P.align_corners, lane, x01, valid, dir, o, o3, m_sig, m_c1, m_c2);
-
-        // results live on quad lanes 0 (sigma, r, g) and 1 (b) of each row pair: hand them to the slot's lanes
-        const int q0 = lane & ~3;
-        const float sg0 = __shfl_sync(0xffffffffu, o[0][0], q0), sg1 = __shfl_sync(0xffffffffu, o[0][2], q0);
-        const float r0 = __shfl_sync(0xffffffffu, o3[0][0], q0), r1 = __shfl_sync(0xffffffffu, o3[0][2], q0);
-        const float g0 = __shfl_sync(0xffffffffu, o3[0][1], q0), g1 = __shfl_sync(0xffffffffu, o3[0][3], q0);
-        const float b0 = __shfl_sync(0xffffffffu, o3[0][0], q0 + 1), b1 = __shfl_sync(0xffffffffu, o3[0][2], q0 + 1);
-
-        // ---- phase C: composite the slot's sample (raymarching.cu:860-893)
-        const float ws = S.ws[slot], tprev = S.t[slot], dprev = S.depth[slot];
-        const float rprev = S.r[slot], gprev = S.g[slot], bprev = S.b[slot];
-        const uint32_t nprev = S.nsamp[slot];
-        __syncwarp();
-        bool ended = false;
-        if (have) {
-            const float sigma = expf(myh ? sg1 : sg0) * P.density_scale;   // trunc_exp fwd; renderer.py:355
-            const float cr = 1.0f / (1.0f + expf(-(myh ? r1 : r0)));
-            const float cg = 1.0f / (1.0f + expf(-(myh ? g1 : g0)));
-            const float cb = 1.0f / (1.0f + expf(-(myh ? b1 : b0)));
-            const float alpha = 1.0f - __expf(-sigma * dt);
-            const float T = 1.0f - ws;
-            const float w = alpha * T;
-            const float tn = tprev + dt;
-            S.ws[slot] = ws + w; S.t[slot] = tn; S.depth[slot] = fmaf(w, tn, dprev);
-            S.r[slot] = fmaf(w, cr, rprev); S.g[slot] = fmaf(w, cg, gprev); S.b[slot] = fmaf(w, cb, bprev);
-            S.nsamp[slot] = nprev + 1u;
-            have = false;
-            if (writer) ++evaluated;
-            ended = (double)T < 1e-4;   // :880 (the sample that saw T < 1e-4 is still accumulated)
+        if (t == 0) {
+            tout[0][g] = o[0][0]; tout[0][g + 8] = o[0][2];
+            tout[1][g] = o3[0][0]; tout[1][g + 8] = o3[0][2];
+            tout[2][g] = o3[0][1]; tout[2][g + 8] = o3[0][3];
+        } else if (t == 1) {
+            tout[3][g] = o3[0][0]; tout[3][g + 8] = o3[0][2];
         }
         __syncwarp();
-        if (ended) {
-            if (writer) ri_finish(S, P, slot, id);
-            id = -1;
+        // ---- C: composite the slot's sample (raymarching.cu:860-893)
+        if (sel) {
+            const float sigma = expf(tout[0][row]) * P.density_scale;   // trunc_exp fwd; renderer.py:355
+            const float cr = 1.0f / (1.0f + expf(-tout[1][row]));
+            const float cg = 1.0f / (1.0f + expf(-tout[2][row]));
+            const float cb = 1.0f / (1.0f + expf(-tout[3][row]));
+            const float ws = S.ws[slot];
+            const float alpha = 1.0f - __expf(-sigma * sdt);
+            const float T = 1.0f - ws;
+            const float w = alpha * T;
+            const float tn = st + sdt;
+            S.ws[slot] = ws + w;
+            S.depth[slot] = fmaf(w, tn, S.depth[slot]);
+            S.r[slot] = fmaf(w, cr, S.r[slot]); S.g[slot] = fmaf(w, cg, S.g[slot]); S.b[slot] = fmaf(w, cb, S.b[slot]);
+            head = (head + 1) % RI_FIFO;
+            --cnt;
+            ++evaluated;
+            if ((double)T < 1e-4) {   // :880 (the sample that saw T < 1e-4 is still accumulated); queued samples are dropped
+                ri_finish(S, P, slot, id);
+                id = -1;
+                cnt = 0;
+            }
         }
         __syncwarp();
     }
