@@ -12,6 +12,8 @@ region.  Points are sharded by rank with replicated weights and no collective (w
 import argparse
 import json
 import os
+
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")  # two OpenMP runtimes share the host cores (torch, the C oracle)
 import subprocess
 import sys
 import threading
@@ -42,6 +44,7 @@ def parse():
     ap.add_argument("--hypotheses", type=int, default=256)
     ap.add_argument("--estimator-steps", type=int, default=3)
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--no-config1", action="store_true", help="skip the config-1 CPU legs (reference torch path)")
     ap.add_argument("--frames", type=int, default=64, help="config 4: 800x800 frames in the batch (whole job)")
     ap.add_argument("--frames-per-step", type=int, default=8, help="frames rendered per kernel launch on a rank")
     ap.add_argument("--render-steps", type=int, default=1)
@@ -73,12 +76,73 @@ def cpu_field_setup(points, seed=0):
     return step, O.num_threads()
 
 
+def cpu_config1(reps=5, warm=2, hash_points=1 << 18):
+    """BASELINE.md §2 / north_star: the reference's CPU path (config 1) timed on this box's host cores —
+    NeRFNetwork with frequency encoding + torch MLP + the non-cuda_ray renderer.run branch (oracle/cfg1_torch.py, a port
+    pinned to the real reference by tests/golden/cfg1.npz), plus a torch transcription of the hash-grid lookup.
+    2 warm-ups + 5 repetitions, median wall time, all host threads."""
+    import torch
+    from oracle import cfg1_torch as C1
+    from oracle import oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    field = C1.Cfg1Field.random(seed=0, bound=BOUND)
+    g = torch.Generator().manual_seed(0)
+
+    def med(fn, warm=warm, reps=reps):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter(); fn(); ts.append(time.perf_counter() - t0)
+        return float(np.median(ts))
+
+    x = torch.rand(2000, 3, generator=g) * 2 - 1
+
+    def planner():
+        xi = x.clone().requires_grad_(True)
+        sigma, _ = field.density(xi)
+        (sigma ** 2).mean().backward()
+
+    # 1024 rays of an 800x800 pinhole at (0, 0, -1.5) looking +z
+    pix = torch.randint(0, 640000, (1024,), generator=g)
+    d = torch.stack((((pix % 800).float() + 0.5 - 400.0) / 1111.1, ((pix // 800).float() + 0.5 - 400.0) / 1111.1,
+                     torch.ones(1024)), -1)
+    d = d / d.norm(dim=-1, keepdim=True)
+    o = torch.tensor([0.0, 0.0, -1.5]).expand(1024, 3).contiguous()
+    target = torch.rand(1024, 3, generator=g)
+
+    def estimator():
+        oi, di = o.clone().requires_grad_(True), d.clone().requires_grad_(True)
+        image, _ = C1.render_run(field, oi, di, num_steps=512, bg_color=1.0)
+        ((image - target) ** 2).mean().backward()
+
+    offsets, pls = O.level_table(3, 16, 2, 2.0, 16, 19, 2048 * BOUND)
+    scales = O.level_scales(16, pls, 16)
+    table = ((torch.rand(int(offsets[-1]), 2, generator=g) * 2 - 1) * 1e-4).requires_grad_(True)
+    xh = torch.rand(hash_points, 3, generator=g)
+
+    def hashgrid():
+        xi = xh.clone().requires_grad_(True)
+        C1.hashgrid_encode(xi, table, offsets, scales).sum().backward()
+        table.grad = None
+
+    tp, te, th = med(planner), med(estimator), med(hashgrid, 1, 3)
+    return {"cores": cores, "kind": "port", "harness": f"{warm} warm-ups + {reps} reps, median wall, torch {torch.__version__} CPU",
+            "planner_density": {"points": 2000, "ms": tp * 1e3, "Msamples_per_s": 2000 / tp / 1e6},
+            "estimator_photometric": {"rays": 1024, "samples": 524288, "ms": te * 1e3, "rays_per_s": 1024 / te,
+                                      "Msamples_per_s": 524288 / te / 1e6},
+            "hashgrid_torch_transcription": {"points": hash_points, "ms": th * 1e3, "Msamples_per_s": hash_points / th / 1e6,
+                                             "what": "encode fwd + autograd bwd to x and table; 1 warm-up + 3 reps"}}
+
+
 def run_reference(args):
     """The reference's CPU implementation of the path = the oracle port (the reference's own CPU-capable code has no
     hash-grid path: its gridencoder is CUDA-only), all host threads, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    cfg1 = None if args.no_config1 else cpu_config1()
     step, cores = cpu_field_setup(args.cpu_points)
     for _ in range(max(args.warmup, 1)):
         step()
@@ -97,6 +161,7 @@ def run_reference(args):
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "config1_cpu": cfg1,
     }))
 
 
@@ -375,6 +440,7 @@ def run_b200(args):
                           "unit": "GB/s useful per GPU",
                           "frac": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak}}
     if world == 1 and not args.no_cpu_baseline:
+        cfg1 = None if args.no_config1 else cpu_config1()
         cstep, cores = cpu_field_setup(args.cpu_points)
         cstep()
         reps = 8
@@ -384,6 +450,8 @@ def run_b200(args):
         dt = time.perf_counter() - t0
         out["cpu_baseline"] = {"value": args.cpu_points * reps / dt / 1e6, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{reps} x {args.cpu_points} of the {B} points, fwd + dL/dx bwd, C/OpenMP oracle"}
+        if cfg1 is not None:
+            out["cpu_baseline"]["config1"] = cfg1
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -206,3 +206,41 @@ def test_fused_forward_xd_vs_oracle(model, oracle, ngp):
     ref_rgb = 1.0 / (1.0 + np.exp(-h.astype(np.float64)))
     assert rel_err(sigma.cpu().numpy(), rs) < 1e-5
     assert rel_err(rgb.cpu().numpy(), ref_rgb) < 1e-5
+
+
+def test_cfg1_frequency_network_vs_reference_golden():
+    """BASELINE config 1 through the host mirror ON THE GPU (NeRFNetwork(frequency), cuda_ray=False, render staged ->
+    run -> density / masked color) against tests/golden/cfg1.npz, which scripts/make_golden.py produced by importing the
+    real reference.  Pins the host logic of N3/N5 (renderer.py:125-254, 542-575) and near_far.  fp32: 1e-5 on values;
+    1e-4 on the ray gradients (512-long cumprod chains, CPU-vs-GPU libm)."""
+    import os
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cfg1.npz"))
+    m = NeRFNetwork(encoding="frequency", encoding_dir="frequency", bound=2, cuda_ray=False, density_scale=1, min_near=0.2,
+                    density_thresh=10, bg_radius=-1)
+    sd = {k[3:].replace("__", "."): torch.from_numpy(g[k]) for k in g.files if k.startswith("sd_")}
+    missing = m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        x = torch.from_numpy(g["x"]).cuda().requires_grad_(True)
+        sigma = m.density(x.reshape(-1, 3))["sigma"]
+        (sigma ** 2).mean().backward()
+        assert rel_err(sigma.detach().cpu().numpy(), g["sigma"]) < 1e-5
+        assert rel_err(x.grad.cpu().numpy(), g["dx"]) < 1e-5
+        ro = torch.from_numpy(g["rays_o"]).cuda().requires_grad_(True)
+        rd = torch.from_numpy(g["rays_d"]).cuda().requires_grad_(True)
+        out = m.render(ro, rd, staged=True, bg_color=1.0, perturb=False, num_steps=512, upsample_steps=0, max_ray_batch=4096)
+        loss = ((out["image"] - torch.from_numpy(g["target"]).cuda()) ** 2).mean()
+        loss.backward()
+        assert rel_err(out["image"].detach().cpu().numpy(), g["image"]) < 1e-5
+        assert rel_err(out["depth"].detach().cpu().numpy(), g["depth"]) < 1e-5
+        assert abs(loss.item() - float(g["loss"])) < 1e-5 * float(g["loss"])
+        assert rel_err(ro.grad.cpu().numpy(), g["d_rays_o"]) < 1e-4 and rel_err(rd.grad.cpu().numpy(), g["d_rays_d"]) < 1e-4
+        with torch.no_grad():
+            up = m.render(ro[:, :64], rd[:, :64], staged=True, bg_color=1.0, perturb=False, num_steps=64, upsample_steps=32,
+                          max_ray_batch=4096)
+        assert rel_err(up["image"].cpu().numpy(), g["image_up"]) < 1e-4 and rel_err(up["depth"].cpu().numpy(), g["depth_up"]) < 1e-4
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
