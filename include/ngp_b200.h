@@ -169,6 +169,15 @@ int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, c
                           const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
                           float *depth, float *weights_sum, void *workspace, ngp_stream_t stream);
 
+/* ---- training-step tail: torch.optim.Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:126) + EMA (nerf/utils.py:814) - */
+
+/* One fused pass over a parameter tensor: g *= grad_scale (all-reduce mean / GradScaler), Adam moments and update with
+ * torch's single-tensor arithmetic, optional EMA shadow update (ema may be NULL).  step counts from 1.  All pointers
+ * 16-byte aligned, n fp32 elements. */
+int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float *ema, int64_t n, float lr,
+                  float beta1, float beta2, float eps, int64_t step, float grad_scale, float ema_decay,
+                  ngp_stream_t stream);
+
 /* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
 
 /* sh_encode_forward (shencoder.cu:386-412).  inputs [B,3] -> outputs [B,degree^2]; dy_dx [B,3,degree^2] optional. */

@@ -56,27 +56,45 @@ k_tg_keys(const float *__restrict__ inputs, const int32_t *__restrict__ offsets,
     }
 }
 
-// one thread per sorted element; segment heads add their segment in sorted (= ascending contribution id) order
+// Segmented reduction of the sorted contributions, in two fixed-shape levels (bit-reproducible: the association depends
+// only on positions in the sorted order, and the sort is stable):
+//   level 1 (k_tg_reduce): one thread per sorted element computes w * grad; a block of 256 consecutive elements does a
+//     segmented inclusive scan (warp shuffles, then an in-order carry across its 8 warps).  A run that starts and ends
+//     inside the block is written to the table; a run that crosses the block's edges leaves a per-block partial
+//     (`lead`: continues from the previous block; `trail`: starts here and continues into the next).
+//   level 2 (k_tg_stitch): one thread per block whose trailing run continues adds the following blocks' lead partials
+//     in block order.  A row hit by every sample (e.g. the zero padding of march_rays_train) is thus summed as
+//     256-element trees + a short serial pass instead of one thread walking 10^5 elements.
+struct TgPartial {
+    uint32_t trail_key;   // key of the trailing run (valid iff trail_open)
+    uint32_t lead_cont;   // the lead run covers the whole block and continues into the next block
+    uint32_t trail_open;  // the trailing run starts in this block and continues into the next
+    uint32_t pad;
+};
+
 template <typename G, int D, int C>
 __global__ void __launch_bounds__(TG_THREADS)
 k_tg_reduce(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ ids, int64_t n, uint32_t sentinel,
             const G *__restrict__ grad, int grad_layout, const float *__restrict__ inputs,
             const int32_t *__restrict__ offsets, int64_t B, int L, float S, uint32_t H, uint32_t gridtype, int align,
-            float *__restrict__ grad_table) {
+            float *__restrict__ grad_table, TgPartial *__restrict__ part, float *__restrict__ lead_sum,
+            float *__restrict__ trail_sum) {
     __shared__ LevelMeta meta[TG_MAX_L];
+    __shared__ uint32_t w_first[TG_THREADS / 32], w_last[TG_THREADS / 32];
+    __shared__ float w_sum[TG_THREADS / 32][C];
     if (threadIdx.x < L) meta[threadIdx.x] = ngp_level_meta<D>(threadIdx.x, offsets, S, H, gridtype, align);
     __syncthreads();
-    const int64_t i = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t key = keys[i];
-    if (key == sentinel) return;
-    if (i > 0 && keys[i - 1] == key) return;  // not a segment head
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t block0 = (int64_t)blockIdx.x * TG_THREADS;
+    const int64_t i = block0 + threadIdx.x;
+    const bool in = i < n;
+    const uint32_t key = in ? keys[i] : 0xffffffffu;   // past-the-end elements form their own run (never written)
     constexpr int NC = 1 << D;
-    float acc[C];
+    float val[C];
 #pragma unroll
-    for (int c = 0; c < C; ++c) acc[c] = 0.0f;
-    for (int64_t j = i; j < n && keys[j] == key; ++j) {
-        const uint32_t id = ids[j];
+    for (int c = 0; c < C; ++c) val[c] = 0.0f;
+    if (in && key != sentinel) {
+        const uint32_t id = ids[i];
         const int k = (int)(id % NC);
         const int64_t t = id / NC;
         const int64_t b = t / L;
@@ -89,10 +107,93 @@ k_tg_reduce(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ ids,
         for (int d = 0; d < D; ++d) w *= (k >> d) & 1 ? frac[d] : 1.0f - frac[d];
         const G *g = grad_layout == 0 ? grad + ((int64_t)l * B + b) * C : grad + (b * L + l) * C;
 #pragma unroll
-        for (int c = 0; c < C; ++c) acc[c] = __fadd_rn(acc[c], __fmul_rn(w, (float)g[c]));  // product then add, as the atomics do
+        for (int c = 0; c < C; ++c) val[c] = __fmul_rn(w, (float)g[c]);  // product then add, as the atomics do
+    }
+    // warp-level segmented inclusive scan (keys are sorted: equal keys are contiguous)
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t ku = __shfl_up_sync(0xffffffffu, key, o);
+        const bool take = lane >= o && ku == key;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const float vu = __shfl_up_sync(0xffffffffu, val[c], o);
+            if (take) val[c] = __fadd_rn(val[c], vu);
+        }
+    }
+    if (lane == 0) w_first[warp] = key;
+    if (lane == 31) {
+        w_last[warp] = key;
+#pragma unroll
+        for (int c = 0; c < C; ++c) w_sum[warp][c] = val[c];
+    }
+    __syncthreads();
+    // carry from the previous warps of the block for threads in their warp's leading run (fixed order: nearest first)
+    if (key == w_first[warp]) {
+        for (int w = warp - 1; w >= 0 && w_last[w] == key; --w) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) val[c] = __fadd_rn(val[c], w_sum[w][c]);
+            if (w_first[w] != key) break;
+        }
+    }
+    if (!in || key == sentinel) {
+        if (threadIdx.x == TG_THREADS - 1) part[blockIdx.x] = TgPartial{0u, 0u, 0u, 0u};
+        if (threadIdx.x == 0) {  // a block starting in the sentinel / past-the-end zone has no lead run worth keeping
+#pragma unroll
+            for (int c = 0; c < C; ++c) lead_sum[(int64_t)blockIdx.x * C + c] = 0.0f;
+        }
+        return;
+    }
+    const bool last_in_block = threadIdx.x == TG_THREADS - 1 || i + 1 == n;
+    const uint32_t next_key = i + 1 < n ? keys[i + 1] : 0xffffffffu;
+    const bool run_end_here = last_in_block || next_key != key;
+    if (!run_end_here) return;
+    const uint32_t block_first = w_first[0];
+    const bool from_prev = key == block_first && block0 > 0 && keys[block0 - 1] == key;   // run continues from block-1
+    const bool to_next = last_in_block && next_key == key;                                // run continues into block+1
+    if (from_prev) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) lead_sum[(int64_t)blockIdx.x * C + c] = val[c];
+    } else if (key == block_first) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) lead_sum[(int64_t)blockIdx.x * C + c] = 0.0f;
+    }
+    if (last_in_block) {
+        TgPartial p;
+        p.trail_key = key;
+        p.lead_cont = (from_prev && to_next) ? 1u : 0u;
+        p.trail_open = (!from_prev && to_next) ? 1u : 0u;
+        p.pad = 0u;
+        part[blockIdx.x] = p;
+        if (p.trail_open) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) trail_sum[(int64_t)blockIdx.x * C + c] = val[c];
+        }
+    }
+    if (!from_prev && !to_next) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) grad_table[(int64_t)key * C + c] = val[c];
+    }
+}
+
+// level 2: stitch the runs that cross block edges, in block order
+template <int C>
+__global__ void __launch_bounds__(TG_THREADS)
+k_tg_stitch(const TgPartial *__restrict__ part, const float *__restrict__ lead_sum, const float *__restrict__ trail_sum,
+            int64_t nblocks, float *__restrict__ grad_table) {
+    const int64_t b = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x;
+    if (b >= nblocks) return;
+    const TgPartial p = part[b];
+    if (!p.trail_open) return;
+    float acc[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) acc[c] = trail_sum[b * C + c];
+    for (int64_t q = b + 1; q < nblocks; ++q) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) acc[c] = __fadd_rn(acc[c], lead_sum[q * C + c]);
+        if (!part[q].lead_cont) break;
     }
 #pragma unroll
-    for (int c = 0; c < C; ++c) grad_table[(int64_t)key * C + c] = acc[c];
+    for (int c = 0; c < C; ++c) grad_table[(int64_t)p.trail_key * C + c] = acc[c];
 }
 
 static int tg_bits(uint32_t v) {
@@ -104,17 +205,21 @@ static int tg_bits(uint32_t v) {
 extern "C" int64_t ngp_grid_backward_table_workspace_bytes(int64_t B, int D, int L) {
     const int64_t n = B * L * (1ll << D);
     // 2 key buffers + 2 payload buffers + radix-sort scratch (histograms / tile descriptors: well under n/4 + 16 MiB)
-    return 4 * n * 4 + n / 4 + (16ll << 20);
+    // + per-256-element-block partials of the segmented reduction (16 B flags + 2 x 8 floats)
+    return 4 * n * 4 + n / 4 + (16ll << 20) + (n / TG_THREADS + 2) * 80;
 }
 
 template <typename G, int D>
 static int tg_launch_reduce(int C, const uint32_t *keys, const uint32_t *ids, int64_t n, uint32_t sentinel,
                             const void *grad, int grad_layout, const float *inputs, const int32_t *offsets, int64_t B,
-                            int L, float S, uint32_t H, uint32_t gridtype, int align, float *gt, cudaStream_t st) {
+                            int L, float S, uint32_t H, uint32_t gridtype, int align, float *gt, TgPartial *part,
+                            float *lead, float *trail, cudaStream_t st) {
     const unsigned grid = (unsigned)ngp_div_up(n, TG_THREADS);
+    const unsigned sgrid = (unsigned)ngp_div_up((int64_t)grid, TG_THREADS);
 #define TG_RED(CC)                                                                                                       \
     k_tg_reduce<G, D, CC><<<grid, TG_THREADS, 0, st>>>(keys, ids, n, sentinel, (const G *)grad, grad_layout, inputs, \
-                                                       offsets, B, L, S, H, gridtype, align, gt)
+                                                       offsets, B, L, S, H, gridtype, align, gt, part, lead, trail); \
+    k_tg_stitch<CC><<<sgrid, TG_THREADS, 0, st>>>(part, lead, trail, (int64_t)grid, gt)
     switch (C) {
         case 1: TG_RED(1); break;
         case 2: TG_RED(2); break;
@@ -145,8 +250,11 @@ extern "C" int ngp_grid_encode_backward_table(const void *grad, int grad_layout,
     NGP_REQUIRE(workspace && workspace_bytes >= ngp_grid_backward_table_workspace_bytes(B, D, L), NGP_ERR_ARG,
                 "ngp_grid_encode_backward_table: workspace too small");
     uint32_t *keys_a = (uint32_t *)workspace, *keys_b = keys_a + n, *ids_a = keys_b + n, *ids_b = ids_a + n;
-    void *cub_tmp = (void *)(ids_b + n);
-    size_t cub_avail = (size_t)workspace_bytes - (size_t)(4 * n * 4);
+    const int64_t nblk = n / TG_THREADS + 2;
+    TgPartial *part = (TgPartial *)(ids_b + n);
+    float *lead = (float *)(part + nblk), *trail = lead + nblk * 8;
+    void *cub_tmp = (void *)(trail + nblk * 8);
+    size_t cub_avail = (size_t)workspace_bytes - (size_t)(4 * n * 4) - (size_t)(nblk * 80);
     const uint32_t sentinel = total_rows;
     const unsigned kgrid = (unsigned)ngp_div_up(B * L, TG_THREADS);
     if (D == 3)
@@ -163,14 +271,14 @@ extern "C" int ngp_grid_encode_backward_table(const void *grad, int grad_layout,
     int rc;
     if (grad_dtype == NGP_DTYPE_F32)
         rc = D == 3 ? tg_launch_reduce<float, 3>(C, dk.Current(), dv.Current(), n, sentinel, grad, grad_layout, inputs,
-                                                 offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st)
+                                                 offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, part, lead, trail, st)
                     : tg_launch_reduce<float, 2>(C, dk.Current(), dv.Current(), n, sentinel, grad, grad_layout, inputs,
-                                                 offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st);
+                                                 offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, part, lead, trail, st);
     else if (grad_dtype == NGP_DTYPE_F16)
         rc = D == 3 ? tg_launch_reduce<__half, 3>(C, dk.Current(), dv.Current(), n, sentinel, grad, grad_layout, inputs,
-                                                  offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st)
+                                                  offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, part, lead, trail, st)
                     : tg_launch_reduce<__half, 2>(C, dk.Current(), dv.Current(), n, sentinel, grad, grad_layout, inputs,
-                                                  offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st);
+                                                  offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, part, lead, trail, st);
     else {
         ngp_set_error("ngp_grid_encode_backward_table: bad grad_dtype");
         return NGP_ERR_UNSUPPORTED;

@@ -42,6 +42,14 @@ def _worker(rank, world, port, ret):
     g1 = torch.full((5,), float(rank + 1)); g2 = torch.full((2, 2), float(10 * (rank + 1)), dtype=torch.float64)
     allreduce_mean_([g1, g2], world)
     ok = ok and torch.allclose(g1, torch.full((5,), 1.5)) and torch.allclose(g2, torch.full((2, 2), 15.0, dtype=torch.float64))
+    # the training step's gradient exchange (training.allreduce_grads_): SUM over ranks into .grad, in place
+    from nerf_navigation_b200.training import allreduce_grads_
+    ps = [torch.nn.Parameter(torch.zeros(6)), torch.nn.Parameter(torch.zeros(3, 2)), torch.nn.Parameter(torch.zeros(4))]
+    ps[0].grad = torch.arange(6, dtype=torch.float32) * (rank + 1)
+    ps[1].grad = torch.full((3, 2), 2.0 * (rank + 1))
+    allreduce_grads_(ps, world)                                     # ps[2] has no gradient and is skipped
+    ok = ok and torch.equal(ps[0].grad, torch.arange(6, dtype=torch.float32) * 3) and torch.equal(ps[1].grad, torch.full((3, 2), 6.0))
+    ok = ok and ps[2].grad is None
     ret[rank] = bool(ok)
     dist.destroy_process_group()
 

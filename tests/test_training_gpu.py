@@ -1,0 +1,85 @@
+"""GPU: the training configuration (BASELINE config 5) — fused Adam against torch.optim.Adam, gradient averaging over
+emulated ranks against the single-process gradient of the concatenated batch, and a few optimiser steps end to end."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from util import stonehenge_grid, orbit_rays, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n", [1, 7, 4096, 100003])
+def test_fused_adam_matches_torch_adam(n):
+    from nerf_navigation_b200.optim import FusedAdam
+    torch.manual_seed(n)
+    p0 = torch.randn(n, device="cuda")
+    pa = torch.nn.Parameter(p0.clone()); pb = torch.nn.Parameter(p0.clone())
+    oa = FusedAdam([pa], lr=1e-2, betas=(0.9, 0.99), eps=1e-15, ema_decay=0.95)
+    ob = torch.optim.Adam([pb], lr=1e-2, betas=(0.9, 0.99), eps=1e-15)
+    shadow = p0.clone()
+    for step in range(6):
+        g = torch.randn(n, device="cuda") * (10.0 ** (step - 3))
+        pa.grad = g.clone() * 4.0          # as if 4 ranks' gradients had been summed
+        oa.grad_scale = 0.25
+        pb.grad = g.clone()
+        oa.step(); ob.step()
+        shadow = shadow - (1 - 0.95) * (shadow - pb.detach())       # torch_ema update (nerf/utils.py:814)
+    assert rel_err(pa.detach().cpu().numpy(), pb.detach().cpu().numpy()) < 1e-6
+    sa, sb = oa.state[pa], ob.state[pb]
+    assert rel_err(sa["exp_avg"].cpu().numpy(), sb["exp_avg"].cpu().numpy()) < 1e-6
+    assert rel_err(sa["exp_avg_sq"].cpu().numpy(), sb["exp_avg_sq"].cpu().numpy()) < 1e-6
+    assert rel_err(oa.ema_shadow(pa).cpu().numpy(), shadow.cpu().numpy()) < 1e-6
+    assert sa["step"] == 6
+
+
+@pytest.fixture(scope="module")
+def model():
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    from nerf_navigation_b200 import raymarching as rm
+    torch.manual_seed(0)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=True, density_scale=1, min_near=0.2, density_thresh=10).cuda()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    m.density_grid.copy_(torch.from_numpy(stonehenge_grid()))
+    m.density_bitfield = rm.packbits(m.density_grid, 10.0, m.density_bitfield)
+    return m
+
+
+def _grads(model, ro, rd, target):
+    model.train()
+    model.zero_grad(set_to_none=True)
+    out = model.render(ro.unsqueeze(0), rd.unsqueeze(0), bg_color=1.0, perturb=False, force_all_rays=True, dt_gamma=0,
+                       max_steps=1024)
+    ((out["image"].reshape(-1, 3) - target) ** 2).mean().backward()
+    return [p.grad.clone() for p in model.parameters() if p.requires_grad]
+
+
+def test_rank_mean_gradient_equals_concatenated_batch(model):
+    """the reduced (mean over ranks) table / MLP gradients equal a single-process computation on the
+    concatenated batch (equal shard sizes, loss = mean over rays).  fp32, different summation order: 1e-5."""
+    o, d = orbit_rays(2048, 4)
+    ro, rd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    target = torch.rand(2048, 3, device="cuda")
+    full = _grads(model, ro, rd, target)
+    parts = [_grads(model, ro[a:a + 1024], rd[a:a + 1024], target[a:a + 1024]) for a in (0, 1024)]
+    for gf, g0, g1 in zip(full, parts[0], parts[1]):
+        assert rel_err(((g0 + g1) * 0.5).cpu().numpy(), gf.cpu().numpy()) < 1e-5
+    assert (full[0] != 0).any()
+
+
+def test_train_steps_reduce_loss(model):
+    from nerf_navigation_b200.training import make_optimizer, train_step
+    m = copy.deepcopy(model)
+    opt = make_optimizer(m, lr=1e-2, ema_decay=0.95)
+    assert len(opt.param_groups) == 3      # encoder, sigma_net, color_net (the SH encoder has no parameters)
+    o, d = orbit_rays(4096, 6)
+    ro, rd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    target = torch.full((4096, 3), 0.3, device="cuda")
+    before = m.encoder.embeddings.detach().clone()
+    losses = [float(train_step(m, opt, ro, rd, target, world=1, perturb=False, force_all_rays=True, dt_gamma=0,
+                               max_steps=1024)) for _ in range(8)]
+    assert losses[-1] < losses[0] and np.isfinite(losses).all()
+    assert (m.encoder.embeddings.detach() != before).any()
+    assert opt.state[m.encoder.embeddings]["step"] == 8
