@@ -48,6 +48,9 @@ def parse():
     ap.add_argument("--frames", type=int, default=64, help="config 4: 800x800 frames in the batch (whole job)")
     ap.add_argument("--frames-per-step", type=int, default=8, help="frames rendered per kernel launch on a rank")
     ap.add_argument("--render-steps", type=int, default=1)
+    ap.add_argument("--no-train", action="store_true")
+    ap.add_argument("--train-steps", type=int, default=20)
+    ap.add_argument("--train-rays", type=int, default=4096, help="config 5: rays per GPU per optimiser step")
     return ap.parse_args()
 
 
@@ -358,10 +361,29 @@ def run_b200(args):
             ren_samples += int(render_rays_infer(rmodel, ro, rd, rmodel.aabb_infer, 1.0, return_stats=True)[3][1].item())
         del rmodel, rays
 
+    # ---- BASELINE config 5: training step, 4096 rays per GPU (weak scaling), table + MLP gradient all-reduce over NCCL
+    t_trn, trn_loss = 0.0, (0.0, 0.0)
+    if not args.no_train:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_train as BT
+        tmodel, topt, tro, trd, ttarget = BT.setup(dev, args.train_rays, rank)
+        first = [float(BT.step(tmodel, topt, tro, trd, ttarget, world)) for _ in range(5)][0]
+        barrier()
+        e8, e9 = ev(), ev()
+        e8.record()
+        for _ in range(args.train_steps):
+            tl = BT.step(tmodel, topt, tro, trd, ttarget, world)
+        e9.record()
+        barrier()
+        t_trn = e8.elapsed_time(e9) / 1e3 / args.train_steps
+        trn_loss = (first, float(tl))
+        trn_bytes = sum(p.numel() for p in tmodel.parameters() if p.requires_grad) * 4
+        del tmodel, topt
+
     if world > 1:
-        tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est, t_ren], device=dev, dtype=torch.float64)
+        tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est, t_ren, t_trn], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_dev, t_e2e, t_est_max, t_ren = tt.tolist()
+        t_dev, t_e2e, t_est_max, t_ren, t_trn = tt.tolist()
         if not args.no_estimator:
             t_est = t_est_max
         cnt = torch.tensor([ren_samples], device=dev, dtype=torch.int64)
@@ -425,6 +447,13 @@ def run_b200(args):
         "clocks": clocks,
     }
     out["estimator"] = est
+    if not args.no_train:
+        out["train"] = {"metric": "training step (config 5)", "rays_per_gpu": args.train_rays, "ms_per_step": t_trn * 1e3,
+                        "steps_per_s": 1.0 / t_trn, "rays_per_s": world * args.train_rays / t_trn, "scaling": "weak",
+                        "loss_first": trn_loss[0], "loss_last": trn_loss[1],
+                        "collective": "none (1 GPU)" if world == 1 else f"NCCL all-reduce (sum) of {trn_bytes} gradient bytes per step, 1/world folded into the Adam kernel",
+                        "path": "march_rays_train -> GridEncoder/SH kernels + torch Linear -> composite_rays_train; "
+                                "backward incl. deterministic table gradient; fused Adam + EMA"}
     if not args.no_render:
         nrays = args.frames * 800 * 800
         # per-sample bounds of the fused kernel: 1024 B of L2 gathers (same unit as the field query) and 1368 mma.sync
