@@ -54,6 +54,27 @@ def parse():
     return ap.parse_args()
 
 
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed `ncu --set full` capture
+    of this same workload (profiles/r1_field_v2_ncu_keys.txt); None if the capture is not there."""
+    p = os.path.join(ROOT, "profiles", "r1_field_v2_ncu_keys.txt")
+    if not os.path.exists(p):
+        return None
+    cur, tot = None, {}
+    for line in open(p):
+        if line.startswith("----"):
+            cur = line
+        elif cur and "dram__bytes_" in line and ".sum" in line:
+            unit = line.split("[")[1].split("]")[0]
+            val = float(line.split("=")[1].strip().replace(",", ""))
+            mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+            tot[cur] = tot.get(cur, 0.0) + val * mul
+    for k, v in tot.items():
+        if kernel in k:
+            return v
+    return None
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -287,7 +308,7 @@ def run_b200(args):
     gxh = torch.empty(B, 3).pin_memory()
     xd = torch.empty(B, 3, device=dev)
 
-    def e2e_step():
+    def e2e_autograd_step():   # the reference-shaped call on device tensors, copies serialised around it
         xd.copy_(xh, non_blocking=True)
         xin = xd.detach().requires_grad_(True)
         s = model.density(xin)["sigma"]
@@ -296,10 +317,30 @@ def run_b200(args):
         gxh.copy_(xin.grad, non_blocking=True)
         return loss.item()
 
+    from nerf_navigation_b200.field import HostFieldQuery
+    hq = HostFieldQuery(model, B, chunk=1 << 19)
+    loss_acc = torch.zeros((), device=dev)
+
+    def dloss(sig):            # loss = mean(sigma^2): accumulate the loss, return dL/dsigma for the chunk
+        loss_acc.add_((sig * sig).sum())
+        return sig * (2.0 / B)
+
+    def e2e_step():            # host-resident points -> dL/dx on the host + the loss scalar, chunks pipelined over PCIe
+        loss_acc.zero_()
+        hq(xh, dloss, None, gxh)
+        return loss_acc.item() / B
+
     e2e_steps = max(3, min(args.steps, 30))
     for _ in range(3):
-        e2e_step()
+        e2e_step(); e2e_autograd_step()
     barrier()
+    ea0, ea1 = ev(), ev()
+    ea0.record()
+    for _ in range(e2e_steps):
+        e2e_autograd_step()
+    ea1.record()
+    barrier()
+    t_e2e_autograd = ea0.elapsed_time(ea1) / 1e3
     e2, e3 = ev(), ev()
     e2.record()
     for _ in range(e2e_steps):
@@ -430,11 +471,16 @@ def run_b200(args):
                    "mlp": "32-64-16", "bound": BOUND, "points": "uniform[-1,1]^3", "sharding": "points by rank, replicated weights, no collective",
                    "l2": "streams ~470 MB/step (> 126 MB L2) of points/outputs; the 48 MiB table is L2-resident by design"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * 12, "d2h_bytes_per_step": B * 12 + 4,
-                "steps": e2e_steps, "api": "NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad"},
-        "gpu_launches": 2 * args.steps,
+                "steps": e2e_steps, "api": "field.HostFieldQuery(model)(x_pinned, dloss_dsigma, None, grad_pinned): 8 chunks, "
+                "H2D / fwd+bwd kernels / D2H overlapped on 3 streams; loss scalar read back",
+                "autograd_api": {"value": world * B * e2e_steps / t_e2e_autograd / 1e6,
+                                 "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
+        "gpu_launches": 2 * args.steps,  # device-resident region; the e2e region launches 2 per chunk
         "kernels_ms": {"k_field_forward": fwd_ms, "k_field_backward": bwd_ms},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
+                     "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(dom), "peak_source": peak_kind,
+                     "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture: ~0.2 GB of point/"
+                                     "output streaming against 4.3 GB of algorithmic (L2-served) gather bytes",
                      "note": "algorithmic bytes = 1024 B of table gathers per point per pass; gathers are served by L2 "
                              "(table resident), so the binding limit is L1/L2 request rate, not HBM"},
         "l2_gather_roofline": {

@@ -62,3 +62,27 @@ def perturb_poses(pose, n, sigma_t=0.02, sigma_r=0.02, generator=None):
     out[:, :3, :3] = Rm @ pose[:3, :3]
     out[:, :3, 3] = pose[:3, 3] + dt
     return out
+
+
+# NeRF training looks along +z, Blender along -z: the planner's points are rotated before the query (simulate.py:341)
+NAV_ROT = ((0.0, 0.0, 1.0), (1.0, 0.0, 0.0), (0.0, 1.0, 0.0))
+
+
+def make_density_fn(model, rot=NAV_ROT):
+    """The planner's closure (simulate.py:343): x [..., 3] -> sigma [...] = model.density(x @ rot)['sigma'].  With the
+    model in eval() this is the fused field query (one kernel forward, one backward to x)."""
+    def density_fn(x):
+        r = torch.as_tensor(rot, dtype=torch.float32, device=x.device)
+        return model.density(x.reshape((-1, 3)) @ r)["sigma"].reshape(x.shape[:-1])
+    return density_fn
+
+
+@torch.no_grad()
+def astar_occupancy(density_fn, side=100, kernel_size=5, thresh=0.3, lo=(-1.0, -1.0, -1.0), hi=(1.0, 1.0, 1.0),
+                    device="cuda"):
+    """The planner's A* occupancy grid (nav/quad_plot.py:64-83): density at a side^3 lattice over [lo, hi], max-pooled by
+    kernel_size^3, thresholded -> bool [side//k]^3.  One fused field query of side^3 points (10^6 at the defaults)."""
+    axes = [torch.linspace(l, h, side, device=device) for l, h in zip(lo, hi)]
+    coods = torch.stack(torch.meshgrid(*axes, indexing="ij"), dim=-1)
+    sigma = density_fn(coods)
+    return torch.nn.functional.max_pool3d(sigma[None, None], kernel_size)[0, 0] > thresh

@@ -170,3 +170,72 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
     if return_stats:
         return image, depth, wsum, work
     return image, depth, wsum
+
+
+class HostFieldQuery:
+    """Field query for HOST-resident points (pinned memory): sigma and d(sum_i f(sigma_i))/dx for points that live on the
+    host, e.g. a planner running on the CPU (the reference's nav/ code keeps its states in host tensors until the query,
+    nav/quad_plot.py:224-250).  The batch is cut into chunks and H2D copy / forward+backward kernels / D2H copy of
+    consecutive chunks overlap on three streams (PCIe is full duplex), so the step costs max(copies, kernels) instead of
+    their sum.  `dloss_dsigma(sigma_chunk) -> grad_chunk` supplies the upstream gradient (elementwise in sigma)."""
+
+    def __init__(self, model, max_points, chunk=1 << 19):
+        enc = model.encoder
+        if not fused_supported(enc, model.sigma_net[0].weight, model.sigma_net[1].weight,
+                               torch.empty(0, 3, dtype=torch.float32)):
+            raise RuntimeError("HostFieldQuery needs the fused field configuration (16x2 hash grid, 32-64-16 sigma net, fp32)")
+        self.model, self.chunk = model, int(chunk)
+        dev = enc.embeddings.device
+        self.dev = dev
+        self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.nbuf = 3
+        c = self.chunk
+        self.bufs = [dict(x=torch.empty(c, 3, device=dev), sigma=torch.empty(c, device=dev),
+                          mask=torch.empty(c, device=dev, dtype=torch.int64), gx=torch.empty(c, 3, device=dev),
+                          e_in=torch.cuda.Event(), e_cmp=torch.cuda.Event(), e_out=torch.cuda.Event())
+                     for _ in range(self.nbuf)]
+        self.S = float(np.log2(enc.per_level_scale))
+
+    @torch.no_grad()
+    def __call__(self, x_host, dloss_dsigma, sigma_host=None, grad_host=None):
+        """x_host [B,3] pinned fp32 -> writes sigma_host [B] / grad_host [B,3] (pinned, optional).  Returns when the
+        results are on the host."""
+        m, enc, L = self.model, self.model.encoder, _lib.lib()
+        if not (x_host.is_pinned() and x_host.dtype == torch.float32 and x_host.is_contiguous()):
+            raise RuntimeError("HostFieldQuery: x_host must be a contiguous pinned fp32 tensor")
+        B = x_host.shape[0]
+        W0 = m.sigma_net[0].weight.detach(); W1 = m.sigma_net[1].weight.detach()
+        tab = enc.embeddings.detach(); off = enc.offsets
+        H, gt, al, bound = int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners), float(m.bound)
+        cur = torch.cuda.current_stream(self.dev)
+        for s in (self.s_in, self.s_cmp, self.s_out):
+            s.wait_stream(cur)
+        with torch.cuda.device(self.dev):
+            for k, a in enumerate(range(0, B, self.chunk)):
+                n = min(self.chunk, B - a)
+                b = self.bufs[k % self.nbuf]
+                with torch.cuda.stream(self.s_in):
+                    self.s_in.wait_event(b["e_out"])          # the slot's previous results have left the device
+                    b["x"][:n].copy_(x_host[a:a + n], non_blocking=True)
+                    b["e_in"].record(self.s_in)
+                with torch.cuda.stream(self.s_cmp):
+                    self.s_cmp.wait_event(b["e_in"])
+                    st = self.s_cmp.cuda_stream
+                    _lib.check(L.ngp_field_query_forward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
+                                                         gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(), None,
+                                                         b["mask"].data_ptr(), n, st), "field_query_forward")
+                    gs = dloss_dsigma(b["sigma"][:n]).contiguous()
+                    _lib.check(L.ngp_field_query_backward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
+                                                          gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(),
+                                                          b["mask"].data_ptr(), gs.data_ptr(), None, b["gx"].data_ptr(), n,
+                                                          st), "field_query_backward")
+                    gs.record_stream(self.s_cmp)
+                    b["e_cmp"].record(self.s_cmp)
+                with torch.cuda.stream(self.s_out):
+                    self.s_out.wait_event(b["e_cmp"])
+                    if sigma_host is not None:
+                        sigma_host[a:a + n].copy_(b["sigma"][:n], non_blocking=True)
+                    if grad_host is not None:
+                        grad_host[a:a + n].copy_(b["gx"][:n], non_blocking=True)
+                    b["e_out"].record(self.s_out)
+        self.s_out.synchronize()

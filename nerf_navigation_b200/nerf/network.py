@@ -52,8 +52,10 @@ class NeRFNetwork(NeRFRenderer):
     # ------------------------------------------------------------------ helpers
     def _use_fused_density(self, x):
         # eval mode == frozen field (simulate.py:191 calls model.eval()): gradients flow to x only.
-        frozen = not self.training or not (self.encoder.embeddings.requires_grad or self.sigma_net[0].weight.requires_grad
-                                           or self.sigma_net[1].weight.requires_grad)
+        # under torch.no_grad() nothing needs parameter gradients either (update_extra_state's 2 x 128^3 density sweep)
+        frozen = not self.training or not torch.is_grad_enabled() or not (
+            self.encoder.embeddings.requires_grad or self.sigma_net[0].weight.requires_grad
+            or self.sigma_net[1].weight.requires_grad)
         return (self.fused_eval and frozen and x.is_cuda and self.num_layers == 2
                 and hasattr(self.encoder, "embeddings")
                 and fused_supported(self.encoder, self.sigma_net[0].weight, self.sigma_net[1].weight, x))
@@ -85,7 +87,7 @@ class NeRFNetwork(NeRFRenderer):
         return {"sigma": trunc_exp(h[..., 0]), "geo_feat": h[..., 1:]}
 
     def _frozen(self):
-        return not self.training or not any(p.requires_grad for p in self.parameters())
+        return not self.training or not torch.is_grad_enabled() or not any(p.requires_grad for p in self.parameters())
 
     def forward(self, x, d):
         """network.py:95-124 -> (sigma [...], color [..., 3]).  Frozen field on CUDA: one fused kernel each way."""

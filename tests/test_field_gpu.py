@@ -47,3 +47,25 @@ def test_field_query_vs_oracle(ngp, oracle, B, with_geo):
     assert rel_err(gx, rgx) < 1e-5
     if B > 10:
         assert sigma[2] == 1.0 and np.all(gx[2] == 0.0)
+
+
+def test_host_field_query_pipeline_matches_device_path():
+    """HostFieldQuery (chunked H2D / kernels / D2H overlap) == NeRFNetwork.density + autograd on device tensors, incl. a
+    ragged last chunk and repeated use of the slots."""
+    import torch
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    from nerf_navigation_b200.field import HostFieldQuery
+    torch.manual_seed(0)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    B = 100003
+    xh = (torch.rand(B, 3) * 2 - 1).pin_memory()
+    sh = torch.empty(B).pin_memory(); gh = torch.empty(B, 3).pin_memory()
+    q = HostFieldQuery(m, B, chunk=8192)
+    for _ in range(2):
+        q(xh, lambda s: s * (2.0 / B), sh, gh)
+    xd = xh.cuda().requires_grad_(True)
+    s = m.density(xd)["sigma"]
+    (s ** 2).mean().backward()
+    assert torch.equal(sh, s.detach().cpu())
+    assert rel_err(gh.numpy(), xd.grad.cpu().numpy()) < 1e-6
