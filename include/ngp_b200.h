@@ -178,6 +178,13 @@ int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_av
                   float beta1, float beta2, float eps, int64_t step, float grad_scale, float ema_decay,
                   ngp_stream_t stream);
 
+/* Weight gradient of a bias-free Linear of the field MLPs (nn.Linear backward inside Trainer.train_step,
+ * nerf/network.py:33-68): dW [n_out, n_in] = dY^T X with dY [M, n_out], X [M, n_in] row-major fp32, n_out, n_in <= 64.
+ * fp32 accuracy (3xTF32 split products), deterministic (per-CTA partials summed in CTA order).  dW is overwritten. */
+int64_t ngp_linear_wgrad_workspace_bytes(int64_t M);
+int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, void *workspace,
+                     int64_t workspace_bytes, ngp_stream_t stream);
+
 /* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
 
 /* sh_encode_forward (shencoder.cu:386-412).  inputs [B,3] -> outputs [B,degree^2]; dy_dx [B,3,degree^2] optional. */

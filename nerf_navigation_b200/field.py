@@ -239,3 +239,43 @@ class HostFieldQuery:
                         grad_host[a:a + n].copy_(b["gx"][:n], non_blocking=True)
                     b["e_out"].record(self.s_out)
         self.s_out.synchronize()
+
+
+class _linear_nobias(Function):
+    """y = x W^T for the bias-free Linear layers of the field MLPs when they train (nerf/network.py:33-68).  Forward and
+    dL/dx are library GEMMs with a long M; the weight gradient dW = dY^T X (K = all samples of the step, output <= 64x64)
+    is the B200 kernel csrc/wgrad.cu."""
+
+    @staticmethod
+    def forward(ctx, x, W):
+        ctx.save_for_backward(x, W)
+        return torch.nn.functional.linear(x, W)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, W = ctx.saved_tensors
+        gx = gW = None
+        gy = gy.contiguous()
+        if ctx.needs_input_grad[0]:
+            gx = gy @ W
+        if ctx.needs_input_grad[1]:
+            x2 = x.reshape(-1, x.shape[-1]).contiguous()
+            g2 = gy.reshape(-1, gy.shape[-1])
+            M = x2.shape[0]
+            L = _lib.lib()
+            nb = L.ngp_linear_wgrad_workspace_bytes(M)
+            ws = torch.empty(nb, dtype=torch.uint8, device=x.device)
+            gW = torch.empty_like(W)
+            with torch.cuda.device(x.device):
+                _lib.check(L.ngp_linear_wgrad(_lib.ptr(g2), _lib.ptr(x2), _lib.ptr(gW), M, W.shape[0], W.shape[1], _lib.ptr(ws),
+                                              nb, _lib.stream()), "linear_wgrad")
+        return gx, gW
+
+
+def linear_nobias(layer, x):
+    """nn.Linear(bias=False) call that routes the weight gradient through csrc/wgrad.cu when it applies."""
+    W = layer.weight
+    if (layer.bias is None and x.is_cuda and x.dtype == torch.float32 and W.dtype == torch.float32 and W.requires_grad
+            and torch.is_grad_enabled() and W.shape[0] <= 64 and W.shape[1] <= 64 and not torch.is_autocast_enabled()):
+        return _linear_nobias.apply(x, W)
+    return layer(x)

@@ -15,7 +15,7 @@ import torch.nn.functional as F
 
 from ..activation import trunc_exp
 from ..encoding import get_encoder
-from ..field import field_color, field_query, fused_color_supported, fused_supported
+from ..field import field_color, field_query, fused_color_supported, fused_supported, linear_nobias
 from .renderer import NeRFRenderer
 
 
@@ -62,7 +62,7 @@ class NeRFNetwork(NeRFRenderer):
 
     def _sigma_mlp(self, h):
         for l in range(self.num_layers):
-            h = self.sigma_net[l](h)
+            h = linear_nobias(self.sigma_net[l], h)
             if l != self.num_layers - 1:
                 h = F.relu(h, inplace=True)
         return h
@@ -71,7 +71,7 @@ class NeRFNetwork(NeRFRenderer):
         d = self.encoder_dir(d)
         h = torch.cat([d, geo_feat], dim=-1)
         for l in range(self.num_layers_color):
-            h = self.color_net[l](h)
+            h = linear_nobias(self.color_net[l], h)
             if l != self.num_layers_color - 1:
                 h = F.relu(h, inplace=True)
         return torch.sigmoid(h)
