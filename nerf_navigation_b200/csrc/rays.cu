@@ -103,7 +103,7 @@ __device__ __forceinline__ MarchRay load_ray(const float *__restrict__ rays_o, c
 __global__ void __launch_bounds__(RAY_THREADS)
 k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, uint32_t max_steps,
               int64_t N, const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
-              int32_t *__restrict__ counts) {
+              int32_t *__restrict__ counts, float *__restrict__ t_first) {
     const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
     if (n >= N) return;
     const MarchRay r = load_ray(rays_o, rays_d, n);
@@ -111,14 +111,16 @@ k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);  // :352-355, seed :489
     const float far = fars[n];
     uint32_t steps = 0;
-    float px, py, pz, dt;
+    float px, py, pz, dt, tf = t;
     while (t < far && steps < max_steps) {
         if (ngp_march_step(r, cfg, t, px, py, pz, dt)) {
+            if (steps == 0) tf = t;   // the march is memoryless in t: pass 2 resumes here, skipping the leading empty space
             ++steps;
             t += dt;
         }
     }
     counts[n] = (int32_t)steps;
+    t_first[n] = tf;
 }
 
 // exclusive scan of counts -> offsets (3 kernels: per-block totals, scan of totals, per-block scan + base)
@@ -216,8 +218,8 @@ k_scan_write_rays(const int32_t *__restrict__ counts, const int32_t *__restrict_
 __global__ void __launch_bounds__(RAY_THREADS)
 k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
               const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
-              const int32_t *__restrict__ rays, float *__restrict__ xyzs, float *__restrict__ dirs,
-              float *__restrict__ deltas) {
+              const int32_t *__restrict__ rays, const float *__restrict__ t_first, float *__restrict__ xyzs,
+              float *__restrict__ dirs, float *__restrict__ deltas) {
     const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
     if (n >= N) return;
     const int64_t off = rays[n * 3 + 1];
@@ -226,7 +228,8 @@ k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     const MarchRay r = load_ray(rays_o, rays_d, n);
     float t = nears[n];
     if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);
-    float last_t = t;
+    float last_t = t;      // the first delta is measured from the ray's start (:470-473)
+    t = t_first[n];        // resume at the first occupied sample found by pass 1
     const float far = fars[n];
     uint32_t step = 0;
     float px, py, pz, dt;
@@ -244,7 +247,7 @@ k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d
 }
 
 extern "C" int64_t ngp_march_rays_train_workspace_bytes(int64_t N) {
-    return (N + ngp_div_up(N, SCAN_TILE) + 8) * (int64_t)sizeof(int32_t);
+    return (2 * N + ngp_div_up(N, SCAN_TILE) + 8) * (int64_t)sizeof(int32_t);  // counts, tile totals, t_first
 }
 
 extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound,
@@ -263,13 +266,14 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
     int32_t *counts = (int32_t *)workspace;
     int32_t *tile_totals = counts + N;
     const int64_t n_tiles = ngp_div_up(N, SCAN_TILE);
+    float *t_first = (float *)(tile_totals + n_tiles + 8);
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
     const unsigned gr = (unsigned)ngp_div_up(N, RAY_THREADS);
-    k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts);
+    k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
     k_scan_tile_totals<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, N, tile_totals);
     k_scan_totals<<<1, SCAN_THREADS, 0, st>>>(tile_totals, n_tiles, counter, N);
     k_scan_write_rays<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, tile_totals, N, rays);
-    k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, xyzs, dirs, deltas);
+    k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
     NGP_CHECK_LAUNCH("ngp_march_rays_train");
     return NGP_OK;
 }

@@ -14,7 +14,9 @@
 #include "fieldcore.cuh"
 #include "sh.cuh"
 
+#ifndef RF_WARPS
 #define RF_WARPS 12
+#endif
 #define RF_THREADS (RF_WARPS * 32)
 #define RF_TILE (RF_WARPS * 16)
 #define RF_GEO 15
