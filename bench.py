@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--frames", type=int, default=64, help="config 4: 800x800 frames in the batch (whole job)")
     ap.add_argument("--frames-per-step", type=int, default=8, help="frames rendered per kernel launch on a rank")
     ap.add_argument("--render-steps", type=int, default=1)
+    ap.add_argument("--e2e-chunk", type=int, default=1 << 19, help="points per pipelined chunk of the host-fed query")
     ap.add_argument("--no-train", action="store_true")
     ap.add_argument("--train-steps", type=int, default=20)
     ap.add_argument("--train-rays", type=int, default=4096, help="config 5: rays per GPU per optimiser step")
@@ -318,7 +319,7 @@ def run_b200(args):
         return loss.item()
 
     from nerf_navigation_b200.field import HostFieldQuery
-    hq = HostFieldQuery(model, B, chunk=1 << 19)
+    hq = HostFieldQuery(model, B, chunk=args.e2e_chunk)
     loss_acc = torch.zeros((), device=dev)
 
     def dloss(sig):            # loss = mean(sigma^2): accumulate the loss, return dL/dsigma for the chunk
@@ -471,7 +472,7 @@ def run_b200(args):
                    "mlp": "32-64-16", "bound": BOUND, "points": "uniform[-1,1]^3", "sharding": "points by rank, replicated weights, no collective",
                    "l2": "streams ~470 MB/step (> 126 MB L2) of points/outputs; the 48 MiB table is L2-resident by design"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * 12, "d2h_bytes_per_step": B * 12 + 4,
-                "steps": e2e_steps, "api": "field.HostFieldQuery(model)(x_pinned, dloss_dsigma, None, grad_pinned): 8 chunks, "
+                "steps": e2e_steps, "api": f"field.HostFieldQuery(model)(x_pinned, dloss_dsigma, None, grad_pinned): chunks of {args.e2e_chunk} points, "
                 "H2D / fwd+bwd kernels / D2H overlapped on 3 streams; loss scalar read back",
                 "autograd_api": {"value": world * B * e2e_steps / t_e2e_autograd / 1e6,
                                  "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
