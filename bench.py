@@ -304,6 +304,23 @@ def run_b200(args):
     fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in e_fwd]))
     bwd_ms = float(np.mean([a.elapsed_time(b) for a, b in e_bwd]))
 
+    # ---- the same step as ONE kernel (csrc/fieldvg.cu: sigma and dL/dx = (2 sigma / B) dsigma/dx, corners kept in shared
+    # memory between the two halves: 1.25 table passes instead of 2)
+    def vg_step():
+        ngp.check(L.ngp_field_query_value_grad(x.data_ptr(), BOUND, tab.data_ptr(), off.data_ptr(), S, H, 0, 0, W0.data_ptr(),
+                                               W1.data_ptr(), None, None, 0.0, 2.0 / B, sigma.data_ptr(), geo.data_ptr(),
+                                               gx.data_ptr(), B, st))
+    for _ in range(3):
+        vg_step()
+    ev0, ev1 = ev(), ev()
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        vg_step()
+    ev1.record()
+    barrier()
+    t_vg = ev0.elapsed_time(ev1) / 1e3
+
     # ---- end-to-end: public API, pinned host input, H2D + D2H inside the timed region
     xh = x.cpu().pin_memory()
     gxh = torch.empty(B, 3).pin_memory()
@@ -477,7 +494,10 @@ def run_b200(args):
                 "autograd_api": {"value": world * B * e2e_steps / t_e2e_autograd / 1e6,
                                  "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
         "gpu_launches": 2 * args.steps,  # device-resident region; the e2e region launches 2 per chunk
-        "kernels_ms": {"k_field_forward": fwd_ms, "k_field_backward": bwd_ms},
+        "kernels_ms": {"k_field_forward": fwd_ms, "k_field_backward": bwd_ms, "k_field_value_grad": t_vg / args.steps * 1e3},
+        "single_pass": {"value": world * B * args.steps / t_vg / 1e6, "unit": UNIT,
+                        "what": "ngp_field_query_value_grad: the same sigma + dL/dx in ONE kernel (rank-0 time), "
+                                "1280 B of table gathers per point instead of 2048"},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(dom), "peak_source": peak_kind,
                      "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture: ~0.2 GB of point/"

@@ -82,6 +82,16 @@ int ngp_field_query_backward(const float *x, float bound, const float *embedding
                              const float *sigma, const uint64_t *relu_mask, const float *grad_sigma,
                              const float *grad_geo, float *grad_x, int64_t B, ngp_stream_t stream);
 
+/* Density value AND gradient in one pass (csrc/fieldvg.cu): sigma [B], geo [B,15] (may be NULL) and
+ * grad_x [B,3] = u_i * d sigma_i / d x_i with the per-point upstream factor u_i = a_i + b_i * sigma_i
+ * (coef_a / coef_b [B] may be NULL -> the scalars a0 / b0).  a0 = 1, b0 = 0 gives the Jacobian rows; coef_b = 2 c_i the
+ * planner's collision cost sum_i c_i sigma_i^2 (nav/quad_plot.py:224-250); b0 = 2/B the gradient of mean(sigma^2).
+ * Equals ngp_field_query_forward followed by ngp_field_query_backward with grad_sigma = u, in one table pass. */
+int ngp_field_query_value_grad(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                               uint32_t H, uint32_t gridtype, int align_corners, const float *W0, const float *W1,
+                               const float *coef_a, const float *coef_b, float a0, float b0, float *sigma, float *geo,
+                               float *grad_x, int64_t B, ngp_stream_t stream);
+
 /* ---- fused per-sample field for the ray paths: NeRFNetwork.forward(x, d), nerf/network.py:95-124 ------------------- */
 
 /* sigma [M] = exp(o[0]), rgb [M,3] = sigmoid(colour_net([SH4(d) | o[1:16]])), o = sigma_net(encode(x)); fp32 table and

@@ -68,12 +68,16 @@ def perturb_poses(pose, n, sigma_t=0.02, sigma_r=0.02, generator=None):
 NAV_ROT = ((0.0, 0.0, 1.0), (1.0, 0.0, 0.0), (0.0, 1.0, 0.0))
 
 
-def make_density_fn(model, rot=NAV_ROT):
+def make_density_fn(model, rot=NAV_ROT, single_pass=True):
     """The planner's closure (simulate.py:343): x [..., 3] -> sigma [...] = model.density(x @ rot)['sigma'].  With the
     model in eval() this is the fused field query (one kernel forward, one backward to x)."""
     def density_fn(x):
         r = torch.as_tensor(rot, dtype=torch.float32, device=x.device)
-        return model.density(x.reshape((-1, 3)) @ r)["sigma"].reshape(x.shape[:-1])
+        p = x.reshape((-1, 3)) @ r
+        if single_pass and p.is_cuda and not model.training and getattr(model, "fused_eval", False) and p.dtype == torch.float32:
+            from .field import sigma_single_pass
+            return sigma_single_pass(model, p).reshape(x.shape[:-1])      # value + Jacobian in one kernel (csrc/fieldvg.cu)
+        return model.density(p)["sigma"].reshape(x.shape[:-1])
     return density_fn
 
 

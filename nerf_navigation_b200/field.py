@@ -279,3 +279,53 @@ def linear_nobias(layer, x):
             and torch.is_grad_enabled() and W.shape[0] <= 64 and W.shape[1] <= 64 and not torch.is_autocast_enabled()):
         return _linear_nobias.apply(x, W)
     return layer(x)
+
+
+@torch.no_grad()
+def field_value_grad(model, x, coef_a=None, coef_b=None, a0=1.0, b0=0.0, want_geo=False):
+    """sigma(x) and u * d sigma / d x in ONE kernel (csrc/fieldvg.cu), u_i = a_i + b_i sigma_i per point (scalars a0 / b0
+    when the arrays are None).  a0 = 1, b0 = 0: the Jacobian rows d sigma_i / d x_i, from which ANY loss of the densities
+    back-propagates with one elementwise product (sigma_i depends on x_i only); coef_b = 2 c_i: the gradient of the
+    planner's collision cost sum_i c_i sigma_i^2 (nav/quad_plot.py:224-250) directly.  x [..., 3] -> sigma [...],
+    grad [..., 3] (, geo_feat [..., 15])."""
+    enc = model.encoder
+    W0, W1 = model.sigma_net[0].weight.detach().contiguous(), model.sigma_net[1].weight.detach().contiguous()
+    if not fused_supported(enc, W0, W1, x):
+        raise RuntimeError("field_value_grad needs the fused field configuration (16x2 hash grid, 32-64-16 sigma net, fp32)")
+    _lib.require_cuda(x, enc.embeddings)
+    prefix = list(x.shape[:-1])
+    xf = x.detach().reshape(-1, 3).contiguous()
+    B = xf.shape[0]
+    sigma = torch.empty(B, device=x.device); gx = torch.empty(B, 3, device=x.device)
+    geo = torch.empty(B, 15, device=x.device) if want_geo else None
+    ca = None if coef_a is None else coef_a.reshape(-1).contiguous().float()
+    cb = None if coef_b is None else coef_b.reshape(-1).contiguous().float()
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ngp_field_query_value_grad(
+            _lib.ptr(xf), float(model.bound), _lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets),
+            float(np.log2(enc.per_level_scale)), int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners),
+            _lib.ptr(W0), _lib.ptr(W1), _lib.ptr(ca), _lib.ptr(cb), float(a0), float(b0), _lib.ptr(sigma), _lib.ptr(geo),
+            _lib.ptr(gx), B, _lib.stream()), "field_query_value_grad")
+    out = (sigma.view(prefix), gx.view(prefix + [3]))
+    return out + (geo.view(prefix + [15]),) if want_geo else out
+
+
+class _sigma_with_jacobian(Function):
+    """sigma(x) whose backward is one elementwise product with the Jacobian rows computed in the forward's own kernel."""
+
+    @staticmethod
+    def forward(ctx, x, model):
+        sigma, jac = field_value_grad(model, x)
+        ctx.save_for_backward(jac)
+        return sigma
+
+    @staticmethod
+    def backward(ctx, grad_sigma):
+        (jac,) = ctx.saved_tensors
+        return grad_sigma.unsqueeze(-1) * jac, None
+
+
+def sigma_single_pass(model, x):
+    """Differentiable sigma(x) for a frozen field when only the density is needed (the planner's closure): forward AND the
+    later backward cost one table pass in total."""
+    return _sigma_with_jacobian.apply(x, model)

@@ -69,3 +69,40 @@ def test_host_field_query_pipeline_matches_device_path():
     (s ** 2).mean().backward()
     assert torch.equal(sh, s.detach().cpu())
     assert rel_err(gh.numpy(), xd.grad.cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("B,mode", [(1, "jac"), (191, "quad"), (4097, "coef"), (30000, "quad")])
+def test_field_value_grad_vs_oracle_and_two_pass(ngp, oracle, B, mode):
+    """ngp_field_query_value_grad (one table pass, corners cached in shared memory) == forward + backward kernels and
+    == the CPU oracle, for the three upstream forms: Jacobian rows (u = 1), mean(sigma^2) (u = 2 sigma / B) and per-point
+    collision-cost coefficients (u = a_i + b_i sigma_i)."""
+    cfg = hashgrid_config(bound=2.0, table_std=0.5)
+    W0, W1 = sigma_net_weights()
+    rng = np.random.default_rng(B)
+    x = rng.uniform(-1, 1, (B, 3)).astype(np.float32)
+    if B > 10:
+        x[1] = [2.0, -2.0, 0.0]
+        x[2] = [2.5, 0.0, 0.0]
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    xt, tt, ot, w0, w1 = dev(x), dev(cfg["table"]), dev(cfg["offsets"]), dev(W0), dev(W1)
+    ca = cb = None
+    a0, b0 = 1.0, 0.0
+    if mode == "quad":
+        a0, b0 = 0.0, 2.0 / B
+    elif mode == "coef":
+        ca, cb = dev(rng.standard_normal(B).astype(np.float32)), dev(rng.uniform(0, 2, B).astype(np.float32))
+    sigma = torch.empty(B, device="cuda"); geo = torch.empty(B, 15, device="cuda"); gx = torch.empty(B, 3, device="cuda")
+    ngp.check(ngp.lib().ngp_field_query_value_grad(xt.data_ptr(), cfg["bound"], tt.data_ptr(), ot.data_ptr(), cfg["S"], cfg["H"],
+                                                   0, 0, w0.data_ptr(), w1.data_ptr(), ngp.ptr(ca), ngp.ptr(cb), a0, b0,
+                                                   sigma.data_ptr(), geo.data_ptr(), gx.data_ptr(), B, ngp.stream()), "vg")
+    u = (ca if ca is not None else a0) + (cb if cb is not None else b0) * sigma
+    s2, g2, gx2 = _run(ngp, cfg, W0, W1, x, u.cpu().numpy())
+    assert np.array_equal(sigma.cpu().numpy(), s2) and np.array_equal(geo.cpu().numpy(), g2)   # same forward arithmetic
+    assert rel_err(gx.cpu().numpy(), gx2) < 1e-6
+    s16 = torch.empty(16, device="cuda")
+    ngp.check(ngp.lib().ngp_grid_level_scales(s16.data_ptr(), 16, cfg["S"], cfg["H"], ngp.stream()))
+    rs, rg, rgx = oracle.field_query(x, cfg["bound"], cfg["table"], cfg["offsets"], s16.cpu().numpy(), W0, W1, u.cpu().numpy())
+    assert rel_err(sigma.cpu().numpy(), rs) < 1e-5 and rel_err(geo.cpu().numpy(), rg) < 1e-5
+    assert rel_err(gx.cpu().numpy(), rgx) < 1e-5
+    if B > 10:
+        assert sigma[2] == 1.0 and (gx[2] == 0).all()

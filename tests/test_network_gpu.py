@@ -286,3 +286,22 @@ def test_reference_checkpoint_layout_loads(model):
     sd2 = {k: v for k, v in sd.items() if not k.startswith("density") and k != "step_counter"}
     missing, unexpected = m.load_state_dict(sd2, strict=False)
     assert set(missing) == {"density_grid", "density_bitfield", "step_counter"} and not unexpected
+
+
+def test_single_pass_density_closure(model):
+    """closures.make_density_fn(single_pass=True): sigma and dL/dx from ONE kernel == the two-kernel autograd path, for
+    the planner's cost shape (quad_plot.py:224-250: mean over the body cloud of sigma^2 * distance)."""
+    from nerf_navigation_b200.closures import make_density_fn
+    model.eval()
+    x = (torch.rand(20, 500, 3, device="cuda") * 1.6 - 0.8)
+    dist = torch.rand(20, 1, device="cuda") + 0.5
+    outs = []
+    for sp in (True, False):
+        xi = x.clone().requires_grad_(True)
+        sig = make_density_fn(model, single_pass=sp)(xi)
+        cost = (torch.mean(sig ** 2 * dist, dim=-1) * 1e6).mean()
+        cost.backward()
+        outs.append((sig.detach(), xi.grad.clone(), cost.item()))
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert rel_err(outs[0][1].cpu().numpy(), outs[1][1].cpu().numpy()) < 1e-5
+    assert abs(outs[0][2] - outs[1][2]) <= 1e-6 * abs(outs[1][2])
