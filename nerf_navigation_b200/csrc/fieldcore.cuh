@@ -58,6 +58,19 @@ __device__ __forceinline__ void fq_mma3(float (&d)[4], const uint32_t (&ahi)[4],
     fq_mma(d, ahi, bh0, bh1);
 }
 
+// same product with the weight pair stored unsplit (8 B instead of 16 B of shared memory per fragment entry: half the
+// LDS wavefronts on the L1 data pipe, which is what binds the colour kernels) and split in registers
+__device__ __forceinline__ void fq_mma3(float (&d)[4], const uint32_t (&ahi)[4], const uint32_t (&alo)[4], float2 w) {
+    uint32_t bh0, bl0, bh1, bl1;
+    fq_split(w.x, bh0, bl0);
+    fq_split(w.y, bh1, bl1);
+    fq_mma(d, alo, bh0, bh1);
+    fq_mma(d, ahi, bl0, bl1);
+    fq_mma(d, ahi, bh0, bh1);
+}
+__device__ __forceinline__ void fq_store_frag(float4 &dst, float b0, float b1) { dst = fq_split_pair(b0, b1); }
+__device__ __forceinline__ void fq_store_frag(float2 &dst, float b0, float b1) { dst = make_float2(b0, b1); }
+
 // ------------------------------------------------------------------------------------------------ gathers
 #ifndef FQ_HINT
 #define FQ_HINT 0
@@ -234,8 +247,8 @@ __device__ __forceinline__ void fq_group_issue(const float *__restrict__ table, 
 // One level group of the backward (frags = dFeat weight fragments [nt 4][kt 8][lane]): issue the gathers of level 4nt+t, compute that group's feature gradients on the
 // tensor cores while they are in flight (dFeat[:, 8nt..8nt+7] = dHm W0[:, 8nt..8nt+7]), then contract them with the
 // encoder Jacobian (gridencoder.cu:180-223 contracted with :317-343).
-template <int STREAM, bool SAFE>
-__device__ __forceinline__ void fq_backward_group(const FqLevel *__restrict__ lvs, const float4 *__restrict__ frags,
+template <int STREAM, bool SAFE, typename FRAG>
+__device__ __forceinline__ void fq_backward_group(const FqLevel *__restrict__ lvs, const FRAG *__restrict__ frags,
                                                   const float *__restrict__ table, int nt, int lane,
                                                   const float (&x01)[2][3], const bool (&valid)[2], int align_corners,
                                                   const float (&dhm)[8][4], float (&gx)[2][3]) {

@@ -73,7 +73,7 @@ k_render_field_forward(const float *__restrict__ x, const float *__restrict__ di
 // out[nt] = (in .* mask) * W for a 64-wide accumulator-fragment input; W fragments [nt NT][kt 8][lane]
 template <int NT>
 __device__ __forceinline__ void rf_masked_layer(const float (&in)[8][4], const uint32_t (&mbits)[2],
-                                                const float4 *__restrict__ frags, int lane, float (&out)[NT][4]) {
+                                                const RfFrag *__restrict__ frags, int lane, float (&out)[NT][4]) {
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -233,11 +233,11 @@ k_render_field_backward(const float *__restrict__ x, const float *__restrict__ d
     // k slots (t, t+4) of k-tile kt = upstream units 8kt+2t, 8kt+2t+1 (the accumulator-fragment columns)
     for (int i = tid; i < 1024; i += RF_THREADS) {  // dFeat = dHs W_s0: [nt 4][kt 8]
         const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
-        s.s0[i] = fq_split_pair(Ws0[(8 * kt + 2 * tt) * FQ_F + n], Ws0[(8 * kt + 2 * tt + 1) * FQ_F + n]);
+        fq_store_frag(s.s0[i], Ws0[(8 * kt + 2 * tt) * FQ_F + n], Ws0[(8 * kt + 2 * tt + 1) * FQ_F + n]);
     }
     for (int i = tid; i < 512; i += RF_THREADS) {  // dHs = dO W_s1: [nt 8][kt 2], k = output columns
         const int ln = i & 31, kt = (i >> 5) & 1, nt = i >> 6, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
-        s.s1[i] = fq_split_pair(Ws1[(8 * kt + 2 * tt) * FQ_HID + n], Ws1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
+        fq_store_frag(s.s1[i], Ws1[(8 * kt + 2 * tt) * FQ_HID + n], Ws1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
     }
     for (int i = tid; i < 1024; i += RF_THREADS) {  // dIn = dHc1 W_c0: [nt 4][kt 8]; n-tiles 0,1 = SH, 2,3 = o columns
         const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
@@ -251,15 +251,15 @@ k_render_field_backward(const float *__restrict__ x, const float *__restrict__ d
             b0 = col == 0 ? 0.0f : w0[16 + col - 1];
             b1 = col == 0 ? 0.0f : w1[16 + col - 1];
         }
-        s.c0[i] = fq_split_pair(b0, b1);
+        fq_store_frag(s.c0[i], b0, b1);
     }
     for (int i = tid; i < 2048; i += RF_THREADS) {  // dHc1 = dHc2 W_c1: [nt 8][kt 8]
         const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3, n = 8 * nt + gg;
-        s.c1[i] = fq_split_pair(Wc1[(8 * kt + 2 * tt) * FQ_HID + n], Wc1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
+        fq_store_frag(s.c1[i], Wc1[(8 * kt + 2 * tt) * FQ_HID + n], Wc1[(8 * kt + 2 * tt + 1) * FQ_HID + n]);
     }
     for (int i = tid; i < 256; i += RF_THREADS) {  // dHc2 = dRGB W_c2: [nt 8], k slot t = colour channel t (< 3)
         const int ln = i & 31, nt = i >> 5, gg = ln >> 2, tt = ln & 3;
-        s.c2[i] = fq_split_pair(tt < 3 ? Wc2[tt * FQ_HID + 8 * nt + gg] : 0.0f, 0.0f);
+        fq_store_frag(s.c2[i], tt < 3 ? Wc2[tt * FQ_HID + 8 * nt + gg] : 0.0f, 0.0f);
     }
     __syncthreads();
     if (s.all_safe)

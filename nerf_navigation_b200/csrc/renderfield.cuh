@@ -22,12 +22,21 @@
 #define RF_GEO 15
 #define RF_CIN 31  // 16 SH + 15 geo (network.py:60)
 
+#ifndef RF_WSPLIT
+#define RF_WSPLIT 0   // 1: weight fragments stored unsplit (float2) and split hi/lo in registers (measured slower: render 173 vs 118 ms); 0: pre-split float4
+#endif
+#if RF_WSPLIT
+typedef float2 RfFrag;
+#else
+typedef float4 RfFrag;
+#endif
+
 struct __align__(16) RenderFieldSmem {
-    float4 s0[1024];  // fwd: sigma L1 [nt 8][kt 4][lane]        bwd: dFeat  = dHs  W_s0   [nt 4][kt 8][lane]
-    float4 s1[512];   // fwd: sigma L2 [nt 2][kt 8][lane]        bwd: dHs    = dO   W_s1   [nt 8][kt 2][lane]
-    float4 c0[1024];  // fwd: colour L1 [nt 8][kt 4][lane]       bwd: dIn    = dHc1 W_c0   [nt 4][kt 8][lane]
-    float4 c1[2048];  // fwd: colour L2 [nt 8][kt 8][lane]       bwd: dHc1   = dHc2 W_c1   [nt 8][kt 8][lane]
-    float4 c2[256];   // fwd: colour L3 [kt 8][lane] (N = 3 -> 8) bwd: dHc2   = dRGB W_c2   [nt 8][lane] (K = 3 -> 8)
+    RfFrag s0[1024];  // fwd: sigma L1 [nt 8][kt 4][lane]        bwd: dFeat  = dHs  W_s0   [nt 4][kt 8][lane]
+    RfFrag s1[512];   // fwd: sigma L2 [nt 2][kt 8][lane]        bwd: dHs    = dO   W_s1   [nt 8][kt 2][lane]
+    RfFrag c0[1024];  // fwd: colour L1 [nt 8][kt 4][lane]       bwd: dIn    = dHc1 W_c0   [nt 4][kt 8][lane]
+    RfFrag c1[2048];  // fwd: colour L2 [nt 8][kt 8][lane]       bwd: dHc1   = dHc2 W_c1   [nt 8][kt 8][lane]
+    RfFrag c2[256];   // fwd: colour L3 [kt 8][lane] (N = 3 -> 8) bwd: dHc2   = dRGB W_c2   [nt 8][lane] (K = 3 -> 8)
     FqLevel lv[FQ_L];
     int all_safe;
 };
@@ -39,7 +48,7 @@ __device__ __forceinline__ float rf_sel4(int t, float a, float b, float c, float
 // ReLU the 64-wide accumulator fragment `in` (recording the sign bits) and multiply by the next layer's weights:
 // out[nt] += relu(in) * W, W fragments laid out [nt NT][kt 8][lane].
 template <int NT>
-__device__ __forceinline__ void rf_relu_layer(const float (&in)[8][4], const float4 *__restrict__ frags, int lane,
+__device__ __forceinline__ void rf_relu_layer(const float (&in)[8][4], const RfFrag *__restrict__ frags, int lane,
                                               float (&out)[NT][4], uint32_t (&mbits)[2]) {
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt)
@@ -154,12 +163,12 @@ __device__ __forceinline__ void rf_stage_forward_weights(RenderFieldSmem &s, con
     for (int i = tid; i < 1024; i += nthreads) {  // sigma L1: slot t -> feature 8kt+2t, t+4 -> 8kt+2t+1
         const int ln = i & 31, kt = (i >> 5) & 3, nt = i >> 7, gg = ln >> 2, tt = ln & 3;
         const float *w = Ws0 + (8 * nt + gg) * FQ_F + 8 * kt + 2 * tt;
-        s.s0[i] = fq_split_pair(w[0], w[1]);
+        fq_store_frag(s.s0[i], w[0], w[1]);
     }
     for (int i = tid; i < 512; i += nthreads) {  // sigma L2
         const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
         const float *w = Ws1 + (8 * nt + gg) * FQ_HID + 8 * kt + 2 * tt;
-        s.s1[i] = fq_split_pair(w[0], w[1]);
+        fq_store_frag(s.s1[i], w[0], w[1]);
     }
     for (int i = tid; i < 1024; i += nthreads) {  // colour L1, Wc0 [64][31]
         const int ln = i & 31, kt = (i >> 5) & 3, nt = i >> 7, gg = ln >> 2, tt = ln & 3;
@@ -173,18 +182,18 @@ __device__ __forceinline__ void rf_stage_forward_weights(RenderFieldSmem &s, con
             b0 = col == 0 ? 0.0f : w[16 + col - 1];
             b1 = w[16 + col];
         }
-        s.c0[i] = fq_split_pair(b0, b1);
+        fq_store_frag(s.c0[i], b0, b1);
     }
     for (int i = tid; i < 2048; i += nthreads) {  // colour L2
         const int ln = i & 31, kt = (i >> 5) & 7, nt = i >> 8, gg = ln >> 2, tt = ln & 3;
         const float *w = Wc1 + (8 * nt + gg) * FQ_HID + 8 * kt + 2 * tt;
-        s.c1[i] = fq_split_pair(w[0], w[1]);
+        fq_store_frag(s.c1[i], w[0], w[1]);
     }
     for (int i = tid; i < 256; i += nthreads) {  // colour L3, Wc2 [3][64] padded to 8 rows
         const int ln = i & 31, kt = i >> 5, gg = ln >> 2, tt = ln & 3;
         const float b0 = gg < 3 ? Wc2[gg * FQ_HID + 8 * kt + 2 * tt] : 0.0f;
         const float b1 = gg < 3 ? Wc2[gg * FQ_HID + 8 * kt + 2 * tt + 1] : 0.0f;
-        s.c2[i] = fq_split_pair(b0, b1);
+        fq_store_frag(s.c2[i], b0, b1);
     }
 }
 
