@@ -61,11 +61,11 @@ k_adam_step(float *__restrict__ p, const float *__restrict__ g, float *__restric
 extern "C" int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float *ema, int64_t n,
                              float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                              float ema_decay, ngp_stream_t stream) {
+    if (n == 0) return NGP_OK;
     NGP_REQUIRE(param && grad && exp_avg && exp_avg_sq, NGP_ERR_ARG, "ngp_adam_step: null pointer");
     NGP_REQUIRE(n >= 0 && step >= 1, NGP_ERR_ARG, "ngp_adam_step: bad n / step (step counts from 1)");
     NGP_REQUIRE((((uintptr_t)param | (uintptr_t)grad | (uintptr_t)exp_avg | (uintptr_t)exp_avg_sq | (uintptr_t)ema) & 15u) == 0,
                 NGP_ERR_ARG, "ngp_adam_step: pointers must be 16-byte aligned");
-    if (n == 0) return NGP_OK;
     AdamScalars s;
     // bias corrections in double like torch's python scalars (1 - beta ** step), then rounded once
     const double c1 = 1.0 - pow((double)beta1, (double)step), c2 = 1.0 - pow((double)beta2, (double)step);

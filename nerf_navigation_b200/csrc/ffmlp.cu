@@ -189,10 +189,10 @@ static int ff_sm_count() {
 extern "C" int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int input_dim, int output_dim,
                                  int hidden_dim, int num_layers, int activation, int output_activation,
                                  void *forward_buffer, void *outputs, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && weights && outputs, NGP_ERR_ARG, "ngp_ffmlp_forward: null pointer");
     int rc = ff_check(B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, "ngp_ffmlp_forward");
     if (rc) return rc;
-    if (B == 0) return NGP_OK;
     const size_t smem = ff_forward_smem(input_dim, num_layers);
     NGP_REQUIRE(smem <= 227 * 1024, NGP_ERR_UNSUPPORTED, "ngp_ffmlp_forward: configuration needs %zu B of shared memory", smem);
     if (cudaFuncSetAttribute(k_ffmlp_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {

@@ -302,11 +302,11 @@ extern "C" int ngp_field_query_forward(const float *x, float bound, const float 
                                        float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                        const float *W1, float *sigma, float *geo, uint64_t *relu_mask, int64_t B,
                                        ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma, NGP_ERR_ARG, "ngp_field_query_forward: null pointer");
     NGP_REQUIRE(bound > 0.0f, NGP_ERR_ARG, "ngp_field_query_forward: bound must be > 0");
     int rc = fq_check(embeddings, B, "ngp_field_query_forward");
     if (rc) return rc;
-    if (B == 0) return NGP_OK;
     k_field_forward<<<fq_grid(k_field_forward, B), FQ_THREADS, 0, (cudaStream_t)stream>>>(
         x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, geo, relu_mask, B);
     NGP_CHECK_LAUNCH("ngp_field_query_forward");
@@ -318,12 +318,12 @@ extern "C" int ngp_field_query_backward(const float *x, float bound, const float
                                         const float *W1, const float *sigma, const uint64_t *relu_mask,
                                         const float *grad_sigma, const float *grad_geo, float *grad_x, int64_t B,
                                         ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma && relu_mask && grad_sigma && grad_x, NGP_ERR_ARG,
                 "ngp_field_query_backward: null pointer");
     NGP_REQUIRE(bound > 0.0f, NGP_ERR_ARG, "ngp_field_query_backward: bound must be > 0");
     int rc = fq_check(embeddings, B, "ngp_field_query_backward");
     if (rc) return rc;
-    if (B == 0) return NGP_OK;
     if (grad_geo)
         k_field_backward<true><<<fq_grid(k_field_backward<true>, B), FQ_THREADS, 0, (cudaStream_t)stream>>>(
             x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, relu_mask, grad_sigma,

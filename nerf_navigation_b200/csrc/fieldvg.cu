@@ -307,11 +307,11 @@ extern "C" int ngp_field_query_value_grad(const float *x, float bound, const flo
                                           float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                           const float *W1, const float *coef_a, const float *coef_b, float a0, float b0,
                                           float *sigma, float *geo, float *grad_x, int64_t B, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma && grad_x, NGP_ERR_ARG,
                 "ngp_field_query_value_grad: null pointer");
     NGP_REQUIRE(bound > 0.0f && B >= 0, NGP_ERR_ARG, "ngp_field_query_value_grad: bad bound / B");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_query_value_grad: embeddings must be 16-byte aligned");
-    if (B == 0) return NGP_OK;
     const int smem = (int)sizeof(FieldVGSmem);
     if (cudaFuncSetAttribute(k_field_value_grad, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         ngp_set_error("ngp_field_query_value_grad: cannot reserve %d B of shared memory", smem);

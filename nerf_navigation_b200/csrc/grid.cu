@@ -253,11 +253,11 @@ extern "C" int ngp_grid_encode_forward(const float *inputs, const void *embeddin
                                        const int32_t *offsets, void *outputs, int out_layout, int64_t B, int D, int C,
                                        int L, float S, uint32_t H, int calc_grad_inputs, void *dy_dx, uint32_t gridtype,
                                        int align_corners, uint32_t *indices, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && embeddings && offsets && outputs, NGP_ERR_ARG, "ngp_grid_encode_forward: null pointer");
     NGP_REQUIRE(L > 0 && L <= GRID_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_forward: L must be in [1,%d]", GRID_MAX_L);
     NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
     NGP_REQUIRE(out_layout == 0 || out_layout == 1, NGP_ERR_ARG, "ngp_grid_encode_forward: bad out_layout");
-    if (B == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
     if (table_dtype == NGP_DTYPE_F32)
@@ -303,11 +303,11 @@ extern "C" int ngp_grid_encode_backward_input(const void *grad, int grad_layout,
                                               const void *embeddings, int table_dtype, const int32_t *offsets,
                                               float *grad_inputs, int64_t B, int D, int C, int L, float S, uint32_t H,
                                               uint32_t gridtype, int align_corners, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(grad && inputs && embeddings && offsets && grad_inputs, NGP_ERR_ARG,
                 "ngp_grid_encode_backward_input: null pointer");
     NGP_REQUIRE(L > 0 && L <= GRID_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_backward_input: L out of range");
     NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
-    if (B == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int rc;
     if (table_dtype == NGP_DTYPE_F32)

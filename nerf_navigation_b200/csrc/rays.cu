@@ -26,8 +26,8 @@ k_near_far(const float *__restrict__ rays_o, const float *__restrict__ rays_d, c
 
 extern "C" int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, int64_t N,
                                       float min_near, float *nears, float *fars, ngp_stream_t stream) {
-    NGP_REQUIRE(rays_o && rays_d && aabb && nears && fars, NGP_ERR_ARG, "ngp_near_far_from_aabb: null pointer");
     if (N == 0) return NGP_OK;
+    NGP_REQUIRE(rays_o && rays_d && aabb && nears && fars, NGP_ERR_ARG, "ngp_near_far_from_aabb: null pointer");
     k_near_far<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N,
                                                                                               min_near, nears, fars);
     NGP_CHECK_LAUNCH("ngp_near_far_from_aabb");
@@ -49,15 +49,15 @@ __global__ void k_morton3D_invert(const int32_t *__restrict__ indices, int64_t N
     coords[n * 3 + 2] = (int32_t)ngp_morton_compact(v >> 2);
 }
 extern "C" int ngp_morton3D(const int32_t *coords, int64_t N, int32_t *indices, ngp_stream_t stream) {
-    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D: null pointer");
     if (N == 0) return NGP_OK;
+    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D: null pointer");
     k_morton3D<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(coords, N, indices);
     NGP_CHECK_LAUNCH("ngp_morton3D");
     return NGP_OK;
 }
 extern "C" int ngp_morton3D_invert(const int32_t *indices, int64_t N, int32_t *coords, ngp_stream_t stream) {
-    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D_invert: null pointer");
     if (N == 0) return NGP_OK;
+    NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D_invert: null pointer");
     k_morton3D_invert<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(indices, N, coords);
     NGP_CHECK_LAUNCH("ngp_morton3D_invert");
     return NGP_OK;
@@ -82,9 +82,9 @@ __global__ void k_packbits(const float *__restrict__ grid, int64_t N, float thre
     bitfield[n] = (uint8_t)bits;
 }
 extern "C" int ngp_packbits(const float *grid, int64_t N, float thresh, uint8_t *bitfield, ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(grid && bitfield, NGP_ERR_ARG, "ngp_packbits: null pointer");
     NGP_REQUIRE(((uintptr_t)grid & 15) == 0, NGP_ERR_ARG, "ngp_packbits: grid must be 16-byte aligned");
-    if (N == 0) return NGP_OK;
     k_packbits<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(grid, N, thresh, bitfield);
     NGP_CHECK_LAUNCH("ngp_packbits");
     return NGP_OK;
@@ -255,13 +255,13 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
                                     const float *nears, const float *fars, float *xyzs, float *dirs, float *deltas,
                                     int32_t *rays, int32_t *counter, uint32_t perturb, void *workspace,
                                     int64_t workspace_bytes, ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && grid && nears && fars && rays && counter, NGP_ERR_ARG,
                 "ngp_march_rays_train: null pointer");
     NGP_REQUIRE(M == 0 || (xyzs && dirs && deltas), NGP_ERR_ARG, "ngp_march_rays_train: null sample buffers");
     NGP_REQUIRE(C >= 1 && C <= 8 && H >= 1 && H <= 1024, NGP_ERR_ARG, "ngp_march_rays_train: bad cascade/grid size");
     NGP_REQUIRE(workspace && workspace_bytes >= ngp_march_rays_train_workspace_bytes(N), NGP_ERR_ARG,
                 "ngp_march_rays_train: workspace too small");
-    if (N == 0) return NGP_OK;
     cudaStream_t st = (cudaStream_t)stream;
     int32_t *counts = (int32_t *)workspace;
     int32_t *tile_totals = counts + N;
@@ -326,10 +326,10 @@ extern "C" int ngp_march_rays_train_backward(const float *grad_xyzs, const float
                                              const int32_t *rays, float bound, uint32_t max_steps, uint32_t perturb,
                                              int64_t N, int64_t M, float *grad_rays_o, float *grad_rays_d,
                                              ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && nears && rays && grad_rays_o && grad_rays_d, NGP_ERR_ARG,
                 "ngp_march_rays_train_backward: null pointer");
     NGP_REQUIRE(M == 0 || (grad_xyzs && deltas), NGP_ERR_ARG, "ngp_march_rays_train_backward: null sample buffers");
-    if (N == 0) return NGP_OK;
     const float dt_min = 2.0f * 1.7320508075688772f / (float)max_steps;
     k_march_train_bwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
         grad_xyzs, grad_dirs, rays_o, rays_d, nears, deltas, rays, bound, dt_min, perturb, N, M, grad_rays_o, grad_rays_d);
@@ -401,9 +401,9 @@ k_composite_train_bwd(const float *__restrict__ grad_ws, const float *__restrict
 extern "C" int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas,
                                                 const int32_t *rays, int64_t M, int64_t N, float *weights_sum,
                                                 float *depth, float *image, ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays && weights_sum && depth && image, NGP_ERR_ARG, "ngp_composite_rays_train_forward: null pointer");
     NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas), NGP_ERR_ARG, "ngp_composite_rays_train_forward: null samples");
-    if (N == 0) return NGP_OK;
     k_composite_train_fwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
         sigmas, rgbs, deltas, rays, M, N, weights_sum, depth, image);
     NGP_CHECK_LAUNCH("ngp_composite_rays_train_forward");
@@ -415,11 +415,11 @@ extern "C" int ngp_composite_rays_train_backward(const float *grad_weights_sum, 
                                                  const int32_t *rays, const float *weights_sum, const float *image,
                                                  int64_t M, int64_t N, float *grad_sigmas, float *grad_rgbs,
                                                  ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(grad_weights_sum && grad_image && rays && weights_sum && image, NGP_ERR_ARG,
                 "ngp_composite_rays_train_backward: null pointer");
     NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas && grad_sigmas && grad_rgbs), NGP_ERR_ARG,
                 "ngp_composite_rays_train_backward: null samples");
-    if (N == 0) return NGP_OK;
     k_composite_train_bwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
         grad_weights_sum, grad_image, sigmas, rgbs, deltas, rays, weights_sum, image, M, N, grad_sigmas, grad_rgbs);
     NGP_CHECK_LAUNCH("ngp_composite_rays_train_backward");
@@ -492,11 +492,11 @@ extern "C" int ngp_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *r
                               const float *rays_o, const float *rays_d, float bound, float dt_gamma, uint32_t max_steps,
                               uint32_t C, uint32_t H, const uint8_t *grid, const float *nears, const float *fars,
                               float *xyzs, float *dirs, float *deltas, uint32_t perturb, ngp_stream_t stream) {
+    if (n_alive == 0) return NGP_OK;
     (void)nears;
     NGP_REQUIRE(rays_alive && rays_t && rays_o && rays_d && grid && fars && xyzs && dirs && deltas, NGP_ERR_ARG,
                 "ngp_march_rays: null pointer");
     NGP_REQUIRE(C >= 1 && C <= 8 && H >= 1 && H <= 1024, NGP_ERR_ARG, "ngp_march_rays: bad cascade/grid size");
-    if (n_alive == 0) return NGP_OK;
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
     k_march_rays<<<(unsigned)ngp_div_up(n_alive, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
         n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, cfg, fars, xyzs, dirs, deltas, perturb);
@@ -507,9 +507,9 @@ extern "C" int ngp_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *r
 extern "C" int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, float *rays_t,
                                   const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum,
                                   float *depth, float *image, ngp_stream_t stream) {
+    if (n_alive == 0) return NGP_OK;
     NGP_REQUIRE(rays_alive && rays_t && sigmas && rgbs && deltas && weights_sum && depth && image, NGP_ERR_ARG,
                 "ngp_composite_rays: null pointer");
-    if (n_alive == 0) return NGP_OK;
     k_composite_rays<<<(unsigned)ngp_div_up(n_alive, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
         n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth, image);
     NGP_CHECK_LAUNCH("ngp_composite_rays");

@@ -239,6 +239,7 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
                                      const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
                                      const float *bg_color, int bg_stride, float *image, float *depth,
                                      float *weights_sum, void *workspace, ngp_stream_t stream) {
+    if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && aabb && grid && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && image &&
                     depth && workspace,
                 NGP_ERR_ARG, "ngp_render_rays_infer: null pointer");
@@ -247,7 +248,6 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
     NGP_REQUIRE(bg_stride == 0 || bg_stride == 3, NGP_ERR_ARG, "ngp_render_rays_infer: bg_stride must be 0 or 3");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0 && ((uintptr_t)workspace & 7u) == 0, NGP_ERR_ARG,
                 "ngp_render_rays_infer: embeddings must be 16-byte aligned, workspace 8-byte aligned");
-    if (N == 0) return NGP_OK;
     const int smem = (int)sizeof(RenderRaysSmem);
     if (cudaFuncSetAttribute(k_render_rays_infer, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         ngp_set_error("ngp_render_rays_infer: cannot reserve %d B of shared memory", smem);

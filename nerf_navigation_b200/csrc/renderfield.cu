@@ -289,11 +289,11 @@ extern "C" int ngp_field_color_forward(const float *xyzs, const float *dirs, flo
                                        int align_corners, const float *Ws0, const float *Ws1, const float *Wc0,
                                        const float *Wc1, const float *Wc2, float *sigma, float *rgb, void *masks,
                                        int64_t M, ngp_stream_t stream) {
+    if (M == 0) return NGP_OK;
     NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb, NGP_ERR_ARG,
                 "ngp_field_color_forward: null pointer");
     NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_forward: bad bound / M");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_forward: embeddings must be 16-byte aligned");
-    if (M == 0) return NGP_OK;
     int grid = 1;
     int rc = rf_launch_cfg(k_render_field_forward, M, &grid);
     if (rc) return rc;
@@ -310,12 +310,12 @@ extern "C" int ngp_field_color_backward(const float *xyzs, const float *dirs, fl
                                         const float *Wc1, const float *Wc2, const float *sigma, const float *rgb,
                                         const void *masks, const float *grad_sigma, const float *grad_rgb,
                                         float *grad_xyzs, float *grad_dirs, int64_t M, ngp_stream_t stream) {
+    if (M == 0) return NGP_OK;
     NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb && masks &&
                     grad_sigma && grad_rgb && grad_xyzs,
                 NGP_ERR_ARG, "ngp_field_color_backward: null pointer");
     NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_backward: bad bound / M");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_backward: embeddings must be 16-byte aligned");
-    if (M == 0) return NGP_OK;
     int grid = 1;
     int rc = rf_launch_cfg(k_render_field_backward, M, &grid);
     if (rc) return rc;

@@ -51,10 +51,10 @@ k_sh_backward(const float *__restrict__ grad, const float *__restrict__ inputs, 
 
 extern "C" int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_t B, int D, int degree,
                                      int calc_grad_inputs, float *dy_dx, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && outputs, NGP_ERR_ARG, "ngp_sh_encode_forward: null pointer");
     NGP_REQUIRE(D == 3, NGP_ERR_UNSUPPORTED, "SHEncoder: input_dim must be 3 (got %d)", D);
     NGP_REQUIRE(degree >= 1 && degree <= 4, NGP_ERR_UNSUPPORTED, "SHEncoder: degree must be in [1,4] (got %d)", degree);
-    if (B == 0) return NGP_OK;
     k_sh_forward<<<(unsigned)ngp_div_up(B, 256), 256, 0, (cudaStream_t)stream>>>(inputs, outputs, B, degree,
                                                                                calc_grad_inputs ? dy_dx : nullptr);
     NGP_CHECK_LAUNCH("ngp_sh_encode_forward");
@@ -63,10 +63,10 @@ extern "C" int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_
 
 extern "C" int ngp_sh_encode_backward(const float *grad, const float *inputs, int64_t B, int D, int degree,
                                       float *grad_inputs, ngp_stream_t stream) {
+    if (B == 0) return NGP_OK;
     NGP_REQUIRE(grad && inputs && grad_inputs, NGP_ERR_ARG, "ngp_sh_encode_backward: null pointer");
     NGP_REQUIRE(D == 3, NGP_ERR_UNSUPPORTED, "SHEncoder: input_dim must be 3 (got %d)", D);
     NGP_REQUIRE(degree >= 1 && degree <= 4, NGP_ERR_UNSUPPORTED, "SHEncoder: degree must be in [1,4] (got %d)", degree);
-    if (B == 0) return NGP_OK;
     k_sh_backward<<<(unsigned)ngp_div_up(B, 256), 256, 0, (cudaStream_t)stream>>>(grad, inputs, B, degree, grad_inputs);
     NGP_CHECK_LAUNCH("ngp_sh_encode_backward");
     return NGP_OK;
