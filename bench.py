@@ -57,8 +57,9 @@ def parse():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed `ncu --set full` capture
-    of this same workload (profiles/r1_field_v2_ncu_keys.txt); None if the capture is not there."""
-    p = os.path.join(ROOT, "profiles", "r1_field_v2_ncu_keys.txt")
+    of this same workload at the same 4,194,304 points (profiles/r1_field_4m_ncu_keys.txt); None if the capture is not
+    there."""
+    p = os.path.join(ROOT, "profiles", "r1_field_4m_ncu_keys.txt")
     if not os.path.exists(p):
         return None
     cur, tot = None, {}
@@ -500,8 +501,9 @@ def run_b200(args):
                                 "1280 B of table gathers per point instead of 2048"},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(dom), "peak_source": peak_kind,
-                     "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture: ~0.2 GB of point/"
-                                     "output streaming against 4.3 GB of algorithmic (L2-served) gather bytes",
+                     "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture at the same size: ~0.4 GB of "
+                                     "point/output streaming against 4.3 GB of algorithmic (L2-served) gather bytes; the "
+                                     "same capture shows the L1 data pipe at 90-92 % of its wavefront slots",
                      "note": "algorithmic bytes = 1024 B of table gathers per point per pass; gathers are served by L2 "
                              "(table resident), so the binding limit is L1/L2 request rate, not HBM"},
         "l2_gather_roofline": {
