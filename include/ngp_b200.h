@@ -195,6 +195,18 @@ int64_t ngp_linear_wgrad_workspace_bytes(int64_t M);
 int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, void *workspace,
                      int64_t workspace_bytes, ngp_stream_t stream);
 
+/* ---- occupancy-grid maintenance: NeRFRenderer.update_extra_state full sweep, nerf/renderer.py:457-486, 519-530 ---- */
+
+/* xyz [G^3, 3]: jittered query position of every cell of `cascade`, in Morton order (so the densities come back in grid
+ * order); jitter scales the uniform [-1, 1) half-cell noise (0 = cell centres), seed selects the noise. */
+int ngp_occ_grid_positions(int cascade, uint32_t G, float bound, float jitter, uint32_t seed, float *xyz,
+                           ngp_stream_t stream);
+/* grid[i] = max(grid[i] * decay, sigma[i] * density_scale) where grid[i] >= 0; block_sums [ngp_occ_grid_update_blocks(n)]
+ * receives partial sums of max(grid, 0) (their total / n is the mean density of renderer.py:521). */
+int64_t ngp_occ_grid_update_blocks(int64_t n);
+int ngp_occ_grid_update(float *grid, const float *sigma, int64_t n, float decay, float density_scale, float *block_sums,
+                        ngp_stream_t stream);
+
 /* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
 
 /* sh_encode_forward (shencoder.cu:386-412).  inputs [B,3] -> outputs [B,degree^2]; dy_dx [B,3,degree^2] optional. */

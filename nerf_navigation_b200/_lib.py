@@ -47,6 +47,9 @@ _SIGNATURES = {
     "ngp_adam_step": ([P, P, P, P, P, I64, F, F, F, F, I64, F, F, P], I),
     "ngp_linear_wgrad_workspace_bytes": ([I64], I64),
     "ngp_linear_wgrad": ([P, P, P, I64, I, I, P, I64, P], I),
+    "ngp_occ_grid_positions": ([I, U32, F, F, U32, P, P], I),
+    "ngp_occ_grid_update_blocks": ([I64], I64),
+    "ngp_occ_grid_update": ([P, P, I64, F, F, P, P], I),
     "ngp_sh_encode_forward": ([P, P, I64, I, I, I, P, P], I),
     "ngp_sh_encode_backward": ([P, P, I64, I, I, P, P], I),
     "ngp_ffmlp_forward": ([P, P, I64, I, I, I, I, I, I, P, P, P], I),

@@ -236,6 +236,8 @@ class NeRFRenderer(nn.Module):
             sig = self.density(cas_xyzs)["sigma"].reshape(-1).detach()
             return sig * self.density_scale
 
+        if self.iter_density < 16 and getattr(self, "fused_occ_sweep", True) and self.density_grid.is_cuda:
+            return self._update_extra_state_sweep(decay)
         if self.iter_density < 16:
             ar = torch.arange(G, dtype=torch.int32, device=dev)
             for xs in ar.split(S):
@@ -261,6 +263,34 @@ class NeRFRenderer(nn.Module):
         valid = (self.density_grid >= 0) & (tmp_grid >= 0)
         self.density_grid[valid] = torch.maximum(self.density_grid[valid] * decay, tmp_grid[valid])
         self.mean_density = torch.mean(self.density_grid.clamp(min=0)).item()
+        self.iter_density += 1
+        density_thresh = min(self.mean_density, self.density_thresh)
+        self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
+        total_step = min(16, self.local_step)
+        if total_step > 0:
+            self.mean_count = int(self.step_counter[:total_step, 0].sum().item() / total_step)
+        self.local_step = 0
+
+    @torch.no_grad()
+    def _update_extra_state_sweep(self, decay, jitter=1.0):
+        """Full-sweep branch of update_extra_state (renderer.py:457-486, 519-539) on the occupancy kernels (csrc/occgrid.cu):
+        positions in Morton order -> density() (the fused field query) -> EMA-max + mean partials -> packbits."""
+        from .. import _lib
+        L = _lib.lib()
+        G, n = self.grid_size, self.grid_size ** 3
+        dev = self.density_grid.device
+        xyz = torch.empty(n, 3, device=dev)
+        nblk = L.ngp_occ_grid_update_blocks(n)
+        sums = torch.empty(self.cascade, nblk, device=dev)
+        seed = (int(self.iter_density) * 2654435761 + 12345) & 0xFFFFFFFF
+        with torch.cuda.device(dev):
+            for cas in range(self.cascade):
+                _lib.check(L.ngp_occ_grid_positions(cas, G, float(self.bound), float(jitter), seed, _lib.ptr(xyz), _lib.stream()),
+                           "occ_grid_positions")
+                sigma = self.density(xyz)["sigma"].reshape(-1).float().contiguous()
+                _lib.check(L.ngp_occ_grid_update(self.density_grid[cas].data_ptr(), _lib.ptr(sigma), n, float(decay),
+                                                 float(self.density_scale), sums[cas].data_ptr(), _lib.stream()), "occ_grid_update")
+        self.mean_density = float(sums.double().sum().item() / (self.cascade * n))
         self.iter_density += 1
         density_thresh = min(self.mean_density, self.density_thresh)
         self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
