@@ -82,65 +82,77 @@ __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams
     float (*tin)[16] = S.tin[warp];
     float (*tout)[16] = S.tout[warp];
 
+#ifndef RI_LOCKSTEP
+#define RI_LOCKSTEP 0   // 1: one CTA barrier per round so the 12 warps walk the unrolled MLP code together (I-cache
+                        // experiment; measured slower, 179 vs 118 ms: warps in different phases overlap gathers and MMAs)
+#endif
+    bool warp_done = false;
     for (;;) {
-        // ---- A1: refill empty slots (one atomic per warp)
-        const unsigned need = __ballot_sync(0xffffffffu, id == -1);
-        if (need) {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(P.counter, (unsigned long long)__popc(need));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (id == -1) {
-                const int64_t nid = (int64_t)base + __popc(need & ((1u << lane) - 1u));
-                if (nid < P.N) {
-                    id = nid;
-                    const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
-                    const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
-                    float near, far;
-                    ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
-                    S.ox[slot] = o[0]; S.oy[slot] = o[1]; S.oz[slot] = o[2];
-                    S.dx[slot] = d[0]; S.dy[slot] = d[1]; S.dz[slot] = d[2];
-                    S.t[slot] = near; S.near[slot] = near; S.far[slot] = far;
-                    S.ws[slot] = 0.0f; S.depth[slot] = 0.0f; S.r[slot] = 0.0f; S.g[slot] = 0.0f; S.b[slot] = 0.0f;
-                    cnt = 0; head = 0; marched = 0; mend = false;
-                } else {
-                    id = -2;
-                }
-            }
-        }
-        // ---- A2: bounded marching, only when the queues run low
-        if (__popc(__ballot_sync(0xffffffffu, cnt > 0)) < RI_MARCH_BELOW) {
-            if (id >= 0 && !mend && cnt < RI_FIFO) {
-                MarchRay r;
-                r.ox = S.ox[slot]; r.oy = S.oy[slot]; r.oz = S.oz[slot];
-                r.dx = S.dx[slot]; r.dy = S.dy[slot]; r.dz = S.dz[slot];
-                r.rdx = 1.0f / r.dx; r.rdy = 1.0f / r.dy; r.rdz = 1.0f / r.dz;
-                float tc = S.t[slot];
-                const float far = S.far[slot];
-                float px, py, pz, dt;
-                for (int budget = RI_BUDGET; budget > 0 && cnt < RI_FIFO; --budget) {
-                    if (!(tc < far) || marched >= P.max_steps) { mend = true; break; }
-                    if (ngp_march_step(r, cfg, tc, px, py, pz, dt)) {
-                        const int w = (head + cnt) % RI_FIFO;
-                        S.qt[w][slot] = tc;
-                        S.qdt[w][slot] = dt;
-                        tc += dt;
-                        ++cnt;
-                        ++marched;
+        unsigned avail = 0u;
+        if (!warp_done) {
+            // ---- A1: refill empty slots (one atomic per warp)
+            const unsigned need = __ballot_sync(0xffffffffu, id == -1);
+            if (need) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(P.counter, (unsigned long long)__popc(need));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (id == -1) {
+                    const int64_t nid = (int64_t)base + __popc(need & ((1u << lane) - 1u));
+                    if (nid < P.N) {
+                        id = nid;
+                        const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
+                        const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
+                        float near, far;
+                        ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
+                        S.ox[slot] = o[0]; S.oy[slot] = o[1]; S.oz[slot] = o[2];
+                        S.dx[slot] = d[0]; S.dy[slot] = d[1]; S.dz[slot] = d[2];
+                        S.t[slot] = near; S.near[slot] = near; S.far[slot] = far;
+                        S.ws[slot] = 0.0f; S.depth[slot] = 0.0f; S.r[slot] = 0.0f; S.g[slot] = 0.0f; S.b[slot] = 0.0f;
+                        cnt = 0; head = 0; marched = 0; mend = false;
+                    } else {
+                        id = -2;
                     }
                 }
-                S.t[slot] = tc;
             }
+            // ---- A2: bounded marching, only when the queues run low
+            if (__popc(__ballot_sync(0xffffffffu, cnt > 0)) < RI_MARCH_BELOW) {
+                if (id >= 0 && !mend && cnt < RI_FIFO) {
+                    MarchRay r;
+                    r.ox = S.ox[slot]; r.oy = S.oy[slot]; r.oz = S.oz[slot];
+                    r.dx = S.dx[slot]; r.dy = S.dy[slot]; r.dz = S.dz[slot];
+                    r.rdx = 1.0f / r.dx; r.rdy = 1.0f / r.dy; r.rdz = 1.0f / r.dz;
+                    float tc = S.t[slot];
+                    const float far = S.far[slot];
+                    float px, py, pz, dt;
+                    for (int budget = RI_BUDGET; budget > 0 && cnt < RI_FIFO; --budget) {
+                        if (!(tc < far) || marched >= P.max_steps) { mend = true; break; }
+                        if (ngp_march_step(r, cfg, tc, px, py, pz, dt)) {
+                            const int w = (head + cnt) % RI_FIFO;
+                            S.qt[w][slot] = tc;
+                            S.qdt[w][slot] = dt;
+                            tc += dt;
+                            ++cnt;
+                            ++marched;
+                        }
+                    }
+                    S.t[slot] = tc;
+                }
+            }
+            // ---- A3: rays whose march is over and whose queue is drained are done
+            if (id >= 0 && mend && cnt == 0) {
+                ri_finish(S, P, slot, id);
+                id = -1;
+            }
+
+            avail = __ballot_sync(0xffffffffu, cnt > 0);
+            if (avail == 0 && !__any_sync(0xffffffffu, id != -2)) warp_done = true;   // every slot has run out of rays
         }
-        // ---- A3: rays whose march is over and whose queue is drained are done
-        if (id >= 0 && mend && cnt == 0) {
-            ri_finish(S, P, slot, id);
-            id = -1;
-        }
-        const unsigned avail = __ballot_sync(0xffffffffu, cnt > 0);
-        if (avail == 0) {
-            if (!__any_sync(0xffffffffu, id != -2)) break;   // every slot has run out of rays
-            continue;
-        }
+#if RI_LOCKSTEP
+        if (!__syncthreads_or(!warp_done)) break;
+#else
+        if (warp_done) break;
+#endif
+        if (avail == 0) continue;
         // ---- B: tile = heads of up to 16 non-empty queues (rotating priority), row = rank among them
         const unsigned ravail = __funnelshift_r(avail, avail, rot);
         const int pos = (lane - (int)rot) & 31;
