@@ -87,6 +87,7 @@ def measured_peaks():
 # --------------------------------------------------------------------------------------------- CPU (oracle) leg
 def cpu_field_setup(points, seed=0):
     from oracle import oracle as O
+    O.set_num_threads(os.cpu_count() or 1)   # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every host core
     offsets, pls = O.level_table(3, 16, 2, 2.0, 16, 19, 2048 * BOUND)
     scales = O.level_scales(16, pls, 16)
     rng = np.random.default_rng(seed)
