@@ -323,6 +323,43 @@ def run_b200(args):
     barrier()
     t_vg = ev0.elapsed_time(ev1) / 1e3
 
+    # ---- locality legs (rank-0 figures, same kernels): SURVEY §8d config 2 (ii) trajectory-clustered points — 8-cubed body
+    # clouds (quad_plot.py:224-250) around waypoints on a helix — and the uniform batch pre-sorted along a Morton curve
+    # (the upper bound a caller gets by handing over spatially ordered queries; results are order-independent)
+    x_uniform = x
+    def timed_steps(pts):
+        nonlocal x
+        x = pts
+        for _ in range(3):
+            step()
+        a, b = ev(), ev()
+        barrier()
+        a.record()
+        for _ in range(args.steps):
+            step()
+        b.record()
+        barrier()
+        x = x_uniform
+        return world * B * args.steps / (a.elapsed_time(b) / 1e3) / 1e6
+    locality = None
+    if B % 512 == 0:
+        nw = B // 512
+        k = torch.arange(nw, device=dev, dtype=torch.float32) / nw
+        way = torch.stack([0.6 * torch.cos(6 * np.pi * k), 0.6 * torch.sin(6 * np.pi * k), 0.1 + 0.5 * k], -1)
+        lx = torch.linspace(-0.05, 0.05, 8, device=dev); lz = torch.linspace(-0.02, 0.02, 8, device=dev)
+        body = torch.stack(torch.meshgrid(lx, lx, lz, indexing="ij"), -1).reshape(-1, 3)
+        xc = (way[:, None, :] + body[None, :, :]).reshape(-1, 3).contiguous()
+        q = ((x_uniform + BOUND) / (2 * BOUND) * 256).long().clamp_(0, 255)
+        key = torch.zeros(B, dtype=torch.long, device=dev)
+        for i in range(8):
+            for d in range(3):
+                key |= ((q[:, d] >> i) & 1) << (3 * i + d)
+        xs = x_uniform[torch.argsort(key)].contiguous()
+        locality = {"unit": UNIT, "clustered": timed_steps(xc), "uniform_morton_sorted": timed_steps(xs),
+                    "what": "fwd+bwd on (a) trajectory-clustered body clouds (config 2 (ii)), (b) the uniform batch handed "
+                            "over in Morton order (8 bits/axis; sorting not timed); `value` is the uniform batch in arrival order"}
+        del xc, xs, q, key
+
     # ---- end-to-end: public API, pinned host input, H2D + D2H inside the timed region
     xh = x.cpu().pin_memory()
     gxh = torch.empty(B, 3).pin_memory()
@@ -497,6 +534,7 @@ def run_b200(args):
                                  "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
         "gpu_launches": 2 * args.steps,  # device-resident region; the e2e region launches 2 per chunk
         "kernels_ms": {"k_field_forward": fwd_ms, "k_field_backward": bwd_ms, "k_field_value_grad": t_vg / args.steps * 1e3},
+        "locality": locality,
         "single_pass": {"value": world * B * args.steps / t_vg / 1e6, "unit": UNIT,
                         "what": "ngp_field_query_value_grad: the same sigma + dL/dx in ONE kernel (rank-0 time), "
                                 "1280 B of table gathers per point instead of 2048"},
