@@ -177,14 +177,18 @@ class HostFieldQuery:
     host, e.g. a planner running on the CPU (the reference's nav/ code keeps its states in host tensors until the query,
     nav/quad_plot.py:224-250).  The batch is cut into chunks and H2D copy / forward+backward kernels / D2H copy of
     consecutive chunks overlap on three streams (PCIe is full duplex), so the step costs max(copies, kernels) instead of
-    their sum.  `dloss_dsigma(sigma_chunk) -> grad_chunk` supplies the upstream gradient (elementwise in sigma)."""
+    their sum.  `dloss_dsigma(sigma_chunk) -> grad_chunk` supplies the upstream gradient (elementwise in sigma); a pair
+    `(a0, b0)` instead of a callable means dL/dsigma_i = a0 + b0 * sigma_i (b0 = 2/B: mean(sigma^2), the planner's density
+    cost) and runs each chunk as ONE kernel (ngp_field_query_value_grad).  `sigma_hook(sigma_chunk)`, if given, is called
+    on the compute stream for every chunk (e.g. to accumulate the loss value on the device).  With `ramp=True` the first
+    and last chunks are shorter (chunk/4, chunk/2) so less of the first upload and last download is exposed."""
 
-    def __init__(self, model, max_points, chunk=1 << 19):
+    def __init__(self, model, max_points, chunk=1 << 19, ramp=True):
         enc = model.encoder
         if not fused_supported(enc, model.sigma_net[0].weight, model.sigma_net[1].weight,
                                torch.empty(0, 3, dtype=torch.float32)):
             raise RuntimeError("HostFieldQuery needs the fused field configuration (16x2 hash grid, 32-64-16 sigma net, fp32)")
-        self.model, self.chunk = model, int(chunk)
+        self.model, self.chunk, self.ramp = model, int(chunk), ramp
         dev = enc.embeddings.device
         self.dev = dev
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
@@ -196,8 +200,21 @@ class HostFieldQuery:
                      for _ in range(self.nbuf)]
         self.S = float(np.log2(enc.per_level_scale))
 
+    def _schedule(self, B):
+        """Chunk sizes covering B points, in order."""
+        c = self.chunk
+        levels = int(self.ramp)          # True -> 1 halving step ... here 2 = (c/4, c/2)
+        levels = 2 if self.ramp is True else levels
+        if levels <= 0 or (c >> levels) < 1 or B < 4 * c:
+            return [min(c, B - a) for a in range(0, B, c)]
+        head = [c >> k for k in range(levels, 0, -1)]
+        mid = B - 2 * sum(head)
+        sizes = head + [c] * (mid // c) + ([mid % c] if mid % c else []) + head[::-1]
+        assert sum(sizes) == B
+        return sizes
+
     @torch.no_grad()
-    def __call__(self, x_host, dloss_dsigma, sigma_host=None, grad_host=None):
+    def __call__(self, x_host, dloss_dsigma, sigma_host=None, grad_host=None, sigma_hook=None):
         """x_host [B,3] pinned fp32 -> writes sigma_host [B] / grad_host [B,3] (pinned, optional).  Returns when the
         results are on the host."""
         m, enc, L = self.model, self.model.encoder, _lib.lib()
@@ -211,8 +228,12 @@ class HostFieldQuery:
         for s in (self.s_in, self.s_cmp, self.s_out):
             s.wait_stream(cur)
         with torch.cuda.device(self.dev):
-            for k, a in enumerate(range(0, B, self.chunk)):
-                n = min(self.chunk, B - a)
+            affine = None if callable(dloss_dsigma) else tuple(float(v) for v in dloss_dsigma)
+            a = 0
+            for k, n in enumerate(self._schedule(B)):
+                if k:
+                    a += prev_n
+                prev_n = n
                 b = self.bufs[k % self.nbuf]
                 with torch.cuda.stream(self.s_in):
                     self.s_in.wait_event(b["e_out"])          # the slot's previous results have left the device
@@ -221,15 +242,25 @@ class HostFieldQuery:
                 with torch.cuda.stream(self.s_cmp):
                     self.s_cmp.wait_event(b["e_in"])
                     st = self.s_cmp.cuda_stream
-                    _lib.check(L.ngp_field_query_forward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
-                                                         gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(), None,
-                                                         b["mask"].data_ptr(), n, st), "field_query_forward")
-                    gs = dloss_dsigma(b["sigma"][:n]).contiguous()
-                    _lib.check(L.ngp_field_query_backward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
-                                                          gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(),
-                                                          b["mask"].data_ptr(), gs.data_ptr(), None, b["gx"].data_ptr(), n,
-                                                          st), "field_query_backward")
-                    gs.record_stream(self.s_cmp)
+                    if affine is not None:
+                        _lib.check(L.ngp_field_query_value_grad(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S,
+                                                                H, gt, al, W0.data_ptr(), W1.data_ptr(), None, None, affine[0],
+                                                                affine[1], b["sigma"].data_ptr(), None, b["gx"].data_ptr(), n,
+                                                                st), "field_query_value_grad")
+                        if sigma_hook is not None:
+                            sigma_hook(b["sigma"][:n])
+                    else:
+                        _lib.check(L.ngp_field_query_forward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
+                                                             gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(), None,
+                                                             b["mask"].data_ptr(), n, st), "field_query_forward")
+                        if sigma_hook is not None:
+                            sigma_hook(b["sigma"][:n])
+                        gs = dloss_dsigma(b["sigma"][:n]).contiguous()
+                        _lib.check(L.ngp_field_query_backward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
+                                                              gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(),
+                                                              b["mask"].data_ptr(), gs.data_ptr(), None, b["gx"].data_ptr(), n,
+                                                              st), "field_query_backward")
+                        gs.record_stream(self.s_cmp)
                     b["e_cmp"].record(self.s_cmp)
                 with torch.cuda.stream(self.s_out):
                     self.s_out.wait_event(b["e_cmp"])

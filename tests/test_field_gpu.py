@@ -69,6 +69,20 @@ def test_host_field_query_pipeline_matches_device_path():
     (s ** 2).mean().backward()
     assert torch.equal(sh, s.detach().cpu())
     assert rel_err(gh.numpy(), xd.grad.cpu().numpy()) < 1e-6
+    # ramped chunk schedule (shorter first / last chunks) covers the batch exactly, in order
+    for ramp in (False, True, 3):
+        qr = HostFieldQuery(m, B, chunk=8192, ramp=ramp)
+        sizes = qr._schedule(B)
+        assert sum(sizes) == B and max(sizes) <= 8192 and min(sizes) > 0
+        if ramp:
+            assert sizes[0] < 8192 and sizes[-1] < 8192 and sizes[0] == sizes[-1]
+    # affine upstream (a0 + b0 sigma) = one kernel per chunk; sigma_hook sees every chunk on the compute stream
+    sh2 = torch.empty(B).pin_memory(); gh2 = torch.empty(B, 3).pin_memory()
+    acc = torch.zeros((), device="cuda", dtype=torch.float64)
+    qr(xh, (0.0, 2.0 / B), sh2, gh2, sigma_hook=lambda sig: acc.add_((sig.double() ** 2).sum()))
+    assert torch.equal(sh2, sh)
+    assert rel_err(gh2.numpy(), gh.numpy()) < 1e-5
+    assert abs(float(acc) / B - float((s.detach().double() ** 2).mean())) < 1e-9 * max(1.0, float(acc) / B)
 
 
 @pytest.mark.parametrize("B,mode", [(1, "jac"), (191, "quad"), (4097, "coef"), (30000, "quad")])
