@@ -490,6 +490,22 @@ def run_b200(args):
         barrier()
         t_trn = e8.elapsed_time(e9) / 1e3 / args.train_steps
         trn_loss = (first, float(tl))
+        # the same step with the reference's own table-gradient method (float atomics: not bit-reproducible), rank-0 figure
+        from nerf_navigation_b200.gridencoder import table_grad
+        table_grad.DETERMINISTIC = False
+        try:
+            for _ in range(3):
+                BT.step(tmodel, topt, tro, trd, ttarget, world)
+            barrier()
+            e10, e11 = ev(), ev()
+            e10.record()
+            for _ in range(args.train_steps):
+                BT.step(tmodel, topt, tro, trd, ttarget, world)
+            e11.record()
+            barrier()
+            t_trn_atomic = e10.elapsed_time(e11) / 1e3 / args.train_steps
+        finally:
+            table_grad.DETERMINISTIC = True
         trn_bytes = sum(p.numel() for p in tmodel.parameters() if p.requires_grad) * 4
         del tmodel, topt
 
@@ -578,7 +594,10 @@ def run_b200(args):
                         "loss_first": trn_loss[0], "loss_last": trn_loss[1],
                         "collective": "none (1 GPU)" if world == 1 else f"NCCL all-reduce (sum) of {trn_bytes} gradient bytes per step, 1/world folded into the Adam kernel",
                         "path": "march_rays_train -> GridEncoder/SH kernels + torch Linear -> composite_rays_train; "
-                                "backward incl. deterministic table gradient; fused Adam + EMA"}
+                                "backward incl. deterministic table gradient; fused Adam + EMA",
+                        "atomic_table_grad": {"ms_per_step": t_trn_atomic * 1e3, "steps_per_s": 1.0 / t_trn_atomic,
+                                              "what": "gridencoder.table_grad.DETERMINISTIC = False: float atomics like the "
+                                                      "reference (not bit-reproducible), rank-0 time"}}
     if not args.no_render:
         nrays = args.frames * 800 * 800
         # per-sample bounds of the fused kernel: 1024 B of L2 gathers (same unit as the field query) and 1368 mma.sync

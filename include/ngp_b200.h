@@ -67,6 +67,14 @@ int ngp_grid_encode_backward_table(const void *grad, int grad_layout, int grad_d
                                    int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
                                    int align_corners, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
 
+/* The same gradient by the reference's own method (float atomics in arrival order, gridencoder.cu:227-314): NOT
+ * bit-reproducible, no workspace, skips (point, level) pairs whose upstream gradient is exactly zero.  Opt-in
+ * (gridencoder.table_grad.DETERMINISTIC = False); grad_embeddings is overwritten. */
+int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
+                                          const int32_t *offsets, const int32_t *offsets_host, float *grad_embeddings,
+                                          int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
+                                          int align_corners, ngp_stream_t stream);
+
 /* ---- fused field query: NeRFNetwork.density(), nerf/network.py:126-143 (+ grid.py:140-156, activation.py) --- */
 
 /* sigma = exp(o[0]), geo = o[1:n_out], o = W1 relu(W0 enc((x+bound)/(2 bound))).  fp32 table + fp32 MLP,

@@ -196,6 +196,104 @@ k_tg_stitch(const TgPartial *__restrict__ part, const float *__restrict__ lead_s
     for (int c = 0; c < C; ++c) grad_table[(int64_t)p.trail_key * C + c] = acc[c];
 }
 
+// ------------------------------------------------------------------------------------------------ atomic variant
+// The reference's own method (kernel_grid_backward, gridencoder.cu:227-314): scatter w * grad with float atomics, sums in
+// arrival order (NOT bit-reproducible).  Kept as an opt-in for throughput: no keys, no sort, and (point, level) pairs
+// whose upstream gradient is exactly zero (march_rays_train's zero padding, terminated rays) issue nothing.  One thread
+// per (point, level); C = 2 / 4 rows go out as one vector RED (red.global.add.v2/v4.f32).
+template <typename G, int D, int C>
+__global__ void __launch_bounds__(TG_THREADS)
+k_tg_atomic(const G *__restrict__ grad, int grad_layout, const float *__restrict__ inputs,
+            const int32_t *__restrict__ offsets, int64_t B, int L, float S, uint32_t H, uint32_t gridtype, int align,
+            float *__restrict__ grad_table) {
+    __shared__ LevelMeta meta[TG_MAX_L];
+    if (threadIdx.x < L) meta[threadIdx.x] = ngp_level_meta<D>(threadIdx.x, offsets, S, H, gridtype, align);
+    __syncthreads();
+    const int64_t t = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x;
+    if (t >= B * L) return;
+    const int64_t b = t / L;
+    const int l = (int)(t - b * L);
+    const G *g = grad_layout == 0 ? grad + ((int64_t)l * B + b) * C : grad + (b * L + l) * C;
+    float gv[C];
+    bool any = false;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        gv[c] = (float)g[c];
+        any |= gv[c] != 0.0f;
+    }
+    if (!any) return;
+    const LevelMeta m = meta[l];
+    uint32_t cell[D];
+    float frac[D];
+    if (!tg_locate<D>(inputs, b, m, align, cell, frac)) return;
+    constexpr int NC = 1 << D;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        float w = 1.0f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) w *= (k >> d) & 1 ? frac[d] : 1.0f - frac[d];
+        float *dst = grad_table + ((int64_t)m.row_offset + tg_row<D>(cell, k, m)) * C;
+        if (C == 2) {
+            atomicAdd(reinterpret_cast<float2 *>(dst), make_float2(__fmul_rn(w, gv[0]), __fmul_rn(w, gv[1])));
+        } else if (C == 4) {
+            atomicAdd(reinterpret_cast<float4 *>(dst),
+                      make_float4(__fmul_rn(w, gv[0]), __fmul_rn(w, gv[1]), __fmul_rn(w, gv[2]), __fmul_rn(w, gv[3])));
+        } else {
+#pragma unroll
+            for (int c = 0; c < C; ++c) atomicAdd(dst + c, __fmul_rn(w, gv[c]));
+        }
+    }
+}
+
+template <typename G, int D>
+static int tg_launch_atomic(int C, const void *grad, int grad_layout, const float *inputs, const int32_t *offsets, int64_t B,
+                            int L, float S, uint32_t H, uint32_t gridtype, int align, float *gt, cudaStream_t st) {
+    const unsigned grid = (unsigned)ngp_div_up(B * L, TG_THREADS);
+#define TG_ATOM(CC)                                                                                                        \
+    k_tg_atomic<G, D, CC><<<grid, TG_THREADS, 0, st>>>((const G *)grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, \
+                                                       align, gt)
+    switch (C) {
+        case 1: TG_ATOM(1); break;
+        case 2: TG_ATOM(2); break;
+        case 4: TG_ATOM(4); break;
+        case 8: TG_ATOM(8); break;
+        default: ngp_set_error("GridEncoder: C must be 1, 2, 4 or 8 (got %d)", C); return NGP_ERR_UNSUPPORTED;
+    }
+#undef TG_ATOM
+    return NGP_OK;
+}
+
+extern "C" int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
+                                                     const int32_t *offsets, const int32_t *offsets_host,
+                                                     float *grad_embeddings, int64_t B, int D, int C, int L, float S,
+                                                     uint32_t H, uint32_t gridtype, int align_corners,
+                                                     ngp_stream_t stream) {
+    NGP_REQUIRE(grad && inputs && offsets && offsets_host && grad_embeddings, NGP_ERR_ARG,
+                "ngp_grid_encode_backward_table_atomic: null pointer");
+    NGP_REQUIRE(L > 0 && L <= TG_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_backward_table_atomic: L out of range");
+    NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
+    NGP_REQUIRE(((uintptr_t)grad_embeddings & 15u) == 0, NGP_ERR_ARG,
+                "ngp_grid_encode_backward_table_atomic: grad_embeddings must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(grad_embeddings, 0, (size_t)offsets_host[L] * C * sizeof(float), st);
+    NGP_REQUIRE(e == cudaSuccess, NGP_ERR_CUDA, "ngp_grid_encode_backward_table_atomic: memset: %s", cudaGetErrorString(e));
+    if (B == 0) return NGP_OK;
+    int rc;
+    if (grad_dtype == NGP_DTYPE_F32)
+        rc = D == 3 ? tg_launch_atomic<float, 3>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st)
+                    : tg_launch_atomic<float, 2>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st);
+    else if (grad_dtype == NGP_DTYPE_F16)
+        rc = D == 3 ? tg_launch_atomic<__half, 3>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st)
+                    : tg_launch_atomic<__half, 2>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, grad_embeddings, st);
+    else {
+        ngp_set_error("ngp_grid_encode_backward_table_atomic: bad grad_dtype");
+        return NGP_ERR_UNSUPPORTED;
+    }
+    if (rc != NGP_OK) return rc;
+    NGP_CHECK_LAUNCH("ngp_grid_encode_backward_table_atomic");
+    return NGP_OK;
+}
+
 static int tg_bits(uint32_t v) {
     int b = 0;
     while ((1ull << b) <= v) ++b;
