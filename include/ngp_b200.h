@@ -203,6 +203,12 @@ int64_t ngp_linear_wgrad_workspace_bytes(int64_t M);
 int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, void *workspace,
                      int64_t workspace_bytes, ngp_stream_t stream);
 
+/* Forward / input-gradient product of the same layers (csrc/linear.cu), W = nn.Linear.weight [n_out, n_in] row-major:
+ * transpose_w = 0: Y [M, n_out] = X [M, n_in] W^T;  transpose_w = 1: Y [M, n_in] = X [M, n_out] W.  n_out, n_in <= 64,
+ * 3xTF32 tensor-core products with fp32 accumulation (relative error ~1e-6 against an fp32 GEMM). */
+int ngp_linear_small(const float *X, const float *W, float *Y, int64_t M, int n_out, int n_in, int transpose_w,
+                     ngp_stream_t stream);
+
 /* ---- occupancy-grid maintenance: NeRFRenderer.update_extra_state full sweep, nerf/renderer.py:457-486, 519-530 ---- */
 
 /* xyz [G^3, 3]: jittered query position of every cell of `cascade`, in Morton order (so the densities come back in grid

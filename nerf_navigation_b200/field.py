@@ -272,15 +272,27 @@ class HostFieldQuery:
         self.s_out.synchronize()
 
 
+def _linear_small(x, W, transpose_w):
+    """x [..., k] fp32 -> x W^T (transpose_w = 0) or x W (1) through csrc/linear.cu; the result is a fresh (non-view)
+    tensor of shape [..., n] so in-place activations may follow."""
+    x2 = x.contiguous()
+    M = x2.numel() // x2.shape[-1] if x2.shape[-1] else 0
+    y = torch.empty(*x.shape[:-1], W.shape[1] if transpose_w else W.shape[0], device=x2.device, dtype=torch.float32)
+    with torch.cuda.device(x2.device):
+        _lib.check(_lib.lib().ngp_linear_small(_lib.ptr(x2), _lib.ptr(W), _lib.ptr(y), M, W.shape[0], W.shape[1],
+                                               int(transpose_w), _lib.stream()), "linear_small")
+    return y
+
+
 class _linear_nobias(Function):
-    """y = x W^T for the bias-free Linear layers of the field MLPs when they train (nerf/network.py:33-68).  Forward and
-    dL/dx are library GEMMs with a long M; the weight gradient dW = dY^T X (K = all samples of the step, output <= 64x64)
-    is the B200 kernel csrc/wgrad.cu."""
+    """y = x W^T for the bias-free Linear layers of the field MLPs when they train (nerf/network.py:33-68): forward and
+    dL/dx are csrc/linear.cu (one streaming pass, 3xTF32 tensor-core products), the weight gradient dW = dY^T X (K = all
+    samples of the step, output <= 64x64) is csrc/wgrad.cu."""
 
     @staticmethod
     def forward(ctx, x, W):
         ctx.save_for_backward(x, W)
-        return torch.nn.functional.linear(x, W)
+        return _linear_small(x, W.contiguous(), 0)
 
     @staticmethod
     def backward(ctx, gy):
@@ -288,7 +300,7 @@ class _linear_nobias(Function):
         gx = gW = None
         gy = gy.contiguous()
         if ctx.needs_input_grad[0]:
-            gx = gy @ W
+            gx = _linear_small(gy, W.contiguous(), 1)
         if ctx.needs_input_grad[1]:
             x2 = x.reshape(-1, x.shape[-1]).contiguous()
             g2 = gy.reshape(-1, gy.shape[-1])

@@ -107,6 +107,24 @@ def test_linear_wgrad_kernel(ngp, M, n_out, n_in):
     assert err < 1e-5 and err < 4 * err_sgemm + 2e-6, (err, err_sgemm)   # fp32 bar of north_star; on par with the library GEMM
 
 
+@pytest.mark.parametrize("M,n_out,n_in", [(1, 3, 64), (17, 16, 64), (1000, 64, 31), (12345, 64, 32), (327683, 64, 64), (4096, 3, 64), (999, 15, 7)])
+def test_linear_small_kernel(ngp, M, n_out, n_in):
+    """csrc/linear.cu: y = x W^T and dx = dy W at fp32 accuracy (3xTF32) against fp64 products, ragged M / odd widths."""
+    g = torch.Generator(device="cuda").manual_seed(M + n_out)
+    W = torch.randn(n_out, n_in, device="cuda", generator=g) / n_in ** 0.5
+    X = torch.randn(M, n_in, device="cuda", generator=g)
+    dY = torch.randn(M, n_out, device="cuda", generator=g)
+    L = ngp.lib()
+    Y = torch.full((M, n_out), float("nan"), device="cuda"); dX = torch.full((M, n_in), float("nan"), device="cuda")
+    ngp.check(L.ngp_linear_small(X.data_ptr(), W.data_ptr(), Y.data_ptr(), M, n_out, n_in, 0, ngp.stream()))
+    ngp.check(L.ngp_linear_small(dY.data_ptr(), W.data_ptr(), dX.data_ptr(), M, n_out, n_in, 1, ngp.stream()))
+    ref_y = (X.double() @ W.double().t()).cpu().numpy(); ref_dx = (dY.double() @ W.double()).cpu().numpy()
+    ey, ex = rel_err(Y.cpu().numpy(), ref_y), rel_err(dX.cpu().numpy(), ref_dx)
+    sy = rel_err((X @ W.t()).double().cpu().numpy(), ref_y)
+    print(f"linear M={M} {n_out}x{n_in}: rel err y {ey:.2e} dx {ex:.2e} (torch sgemm {sy:.2e})")
+    assert ey < 2e-6 and ex < 2e-6
+
+
 def test_linear_nobias_autograd_matches_nn_linear():
     from nerf_navigation_b200.field import linear_nobias
     torch.manual_seed(0)
