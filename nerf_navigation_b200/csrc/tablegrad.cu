@@ -200,7 +200,8 @@ k_tg_stitch(const TgPartial *__restrict__ part, const float *__restrict__ lead_s
 // The reference's own method (kernel_grid_backward, gridencoder.cu:227-314): scatter w * grad with float atomics, sums in
 // arrival order (NOT bit-reproducible).  Kept as an opt-in for throughput: no keys, no sort, and (point, level) pairs
 // whose upstream gradient is exactly zero (march_rays_train's zero padding, terminated rays) issue nothing.  One thread
-// per (point, level); C = 2 / 4 rows go out as one vector RED (red.global.add.v2/v4.f32).
+// per (point, level), level-major, with runs of neighbouring lanes that share a cell pre-summed in registers; C = 2 / 4
+// rows go out as one vector RED (red.global.add.v2/v4.f32).
 template <typename G, int D, int C>
 __global__ void __launch_bounds__(TG_THREADS)
 k_tg_atomic(const G *__restrict__ grad, int grad_layout, const float *__restrict__ inputs,
@@ -209,38 +210,86 @@ k_tg_atomic(const G *__restrict__ grad, int grad_layout, const float *__restrict
     __shared__ LevelMeta meta[TG_MAX_L];
     if (threadIdx.x < L) meta[threadIdx.x] = ngp_level_meta<D>(threadIdx.x, offsets, S, H, gridtype, align);
     __syncthreads();
+    // level-major: the lanes of a warp are consecutive points at one level.  Consecutive samples of a ray fall into the
+    // same cell on the coarse and middle levels, so runs of lanes with equal cells are summed in registers first
+    // (segmented warp reduction) and only the run heads issue atomics.
     const int64_t t = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x;
-    if (t >= B * L) return;
-    const int64_t b = t / L;
-    const int l = (int)(t - b * L);
-    const G *g = grad_layout == 0 ? grad + ((int64_t)l * B + b) * C : grad + (b * L + l) * C;
+    const int lane = threadIdx.x & 31;
+    const bool in = t < B * L;
+    const int l = in ? (int)(t / B) : 0;
+    const int64_t b = in ? t - (int64_t)l * B : 0;
+    constexpr int NC = 1 << D;
     float gv[C];
     bool any = false;
+    if (in) {
+        const G *g = grad_layout == 0 ? grad + ((int64_t)l * B + b) * C : grad + (b * L + l) * C;
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
-        gv[c] = (float)g[c];
-        any |= gv[c] != 0.0f;
+        for (int c = 0; c < C; ++c) {
+            gv[c] = (float)g[c];
+            any |= gv[c] != 0.0f;
+        }
     }
-    if (!any) return;
     const LevelMeta m = meta[l];
     uint32_t cell[D];
     float frac[D];
-    if (!tg_locate<D>(inputs, b, m, align, cell, frac)) return;
-    constexpr int NC = 1 << D;
+    bool live = in && any;
+    if (live) live = tg_locate<D>(inputs, b, m, align, cell, frac);
+    if (!live) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            cell[d] = 0xffffffffu;
+            frac[d] = 0.0f;
+        }
+    }
+    // run heads: first lane, or (level, cell, liveness) differs from the previous lane
+    bool same_prev = lane > 0;
+    {
+        const int lp = __shfl_up_sync(0xffffffffu, l, 1);
+        const int vp = __shfl_up_sync(0xffffffffu, (int)live, 1);
+        same_prev = same_prev && lp == l && vp == (int)live;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const uint32_t cp = __shfl_up_sync(0xffffffffu, cell[d], 1);   // every lane shuffles: no short-circuit
+            same_prev = same_prev && cp == cell[d];
+        }
+    }
+    const unsigned heads = __ballot_sync(0xffffffffu, !same_prev);
+    float val[NC][C];
 #pragma unroll
     for (int k = 0; k < NC; ++k) {
         float w = 1.0f;
 #pragma unroll
         for (int d = 0; d < D; ++d) w *= (k >> d) & 1 ? frac[d] : 1.0f - frac[d];
+#pragma unroll
+        for (int c = 0; c < C; ++c) val[k][c] = live ? __fmul_rn(w, gv[c]) : 0.0f;
+    }
+    if (__popc(heads) <= 24) {   // enough merging to pay for the shuffles (warp-uniform decision)
+        const int seg = __popc(heads & (0xffffffffu >> (31 - lane)));   // run id of this lane
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int oseg = __shfl_down_sync(0xffffffffu, seg, o);
+            const bool take = lane + o < 32 && oseg == seg;
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const float v = __shfl_down_sync(0xffffffffu, val[k][c], o);
+                    if (take) val[k][c] += v;
+                }
+        }
+        if (same_prev) live = false;   // only run heads write
+    }
+    if (!live) return;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
         float *dst = grad_table + ((int64_t)m.row_offset + tg_row<D>(cell, k, m)) * C;
         if (C == 2) {
-            atomicAdd(reinterpret_cast<float2 *>(dst), make_float2(__fmul_rn(w, gv[0]), __fmul_rn(w, gv[1])));
+            atomicAdd(reinterpret_cast<float2 *>(dst), make_float2(val[k][0], val[k][1]));
         } else if (C == 4) {
-            atomicAdd(reinterpret_cast<float4 *>(dst),
-                      make_float4(__fmul_rn(w, gv[0]), __fmul_rn(w, gv[1]), __fmul_rn(w, gv[2]), __fmul_rn(w, gv[3])));
+            atomicAdd(reinterpret_cast<float4 *>(dst), make_float4(val[k][0], val[k][1], val[k][2], val[k][3]));
         } else {
 #pragma unroll
-            for (int c = 0; c < C; ++c) atomicAdd(dst + c, __fmul_rn(w, gv[c]));
+            for (int c = 0; c < C; ++c) atomicAdd(dst + c, val[k][c]);
         }
     }
 }
