@@ -71,11 +71,10 @@ __device__ __forceinline__ int ngp_cell_coord(float p, float mip_rbound, const M
     return (int)ngp_clampf(v, 0.0f, c.Hf - 1.0f);
 }
 
-// One marcher iteration at parameter t.  Occupied: returns true, sample position in (px,py,pz), step in dt, t unchanged.
-// Empty: returns false with t advanced past the voxel (raymarching.cu:393-402).
-__device__ __forceinline__ bool ngp_march_step(const MarchRay &r, const MarchCfg &c, float &t, float &px, float &py,
-                                               float &pz, float &dt) {
-    const float t0 = t;
+// Probe of the marcher at parameter t0 (no state change): occupancy of the cell holding the sample, the sample position
+// and step, and for an empty cell the parameter `tt` at which the ray leaves the voxel (raymarching.cu:361-396).
+__device__ __forceinline__ bool ngp_march_probe(const MarchRay &r, const MarchCfg &c, float t0, float &px, float &py,
+                                                float &pz, float &dt, float &tt) {
     const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
     const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
     const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
@@ -89,17 +88,32 @@ __device__ __forceinline__ bool ngp_march_step(const MarchRay &r, const MarchCfg
     const int nz = ngp_cell_coord(z, mip_rbound, c);
     const uint32_t index = (uint32_t)level * c.H3 + ngp_morton3D((uint32_t)nx, (uint32_t)ny, (uint32_t)nz);
     const bool occ = (__ldg(c.grid + (index >> 3)) >> (index & 7u)) & 1u;
-    if (occ) {
-        px = x; py = y; pz = z;
-        return true;
-    }
+    px = x; py = y; pz = z;
+    tt = t0;
+    if (occ) return true;
     const float tx = fmaf(fmaf(((float)nx + 0.5f + 0.5f * copysignf(1.0f, r.dx)) * c.rH, 2.0f, -1.0f), mip_bound, -x) * r.rdx;
     const float ty = fmaf(fmaf(((float)ny + 0.5f + 0.5f * copysignf(1.0f, r.dy)) * c.rH, 2.0f, -1.0f), mip_bound, -y) * r.rdy;
     const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;
-    const float tt = t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
-    float tc = t0;
+    tt = t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
+    return false;
+}
+
+// One step of the parameter sequence of a ray: t_{k+1} = t_k + clamp(t_k dt_gamma, dt_min, dt_max).  Both branches of the
+// marcher advance by this recurrence (occupied: t += dt, :478; empty: the do-while of :398-402), so the sequence a ray
+// visits does not depend on the occupancy — only which of its elements are visited does.
+__device__ __forceinline__ float ngp_march_advance(float t, const MarchCfg &c) {
+    return t + ngp_clampf(t * c.dt_gamma, c.dt_min, c.dt_max);
+}
+
+// One marcher iteration at parameter t.  Occupied: returns true, sample position in (px,py,pz), step in dt, t unchanged.
+// Empty: returns false with t advanced past the voxel (raymarching.cu:393-402).
+__device__ __forceinline__ bool ngp_march_step(const MarchRay &r, const MarchCfg &c, float &t, float &px, float &py,
+                                               float &pz, float &dt) {
+    float tt;
+    if (ngp_march_probe(r, c, t, px, py, pz, dt, tt)) return true;
+    float tc = t;
     do {
-        tc += ngp_clampf(tc * c.dt_gamma, c.dt_min, c.dt_max);
+        tc = ngp_march_advance(tc, c);
     } while (tc < tt);
     t = tc;
     return false;

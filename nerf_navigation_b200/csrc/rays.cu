@@ -246,6 +246,112 @@ k_march_write(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     }
 }
 
+// ---- warp-per-ray variants for small ray batches (training step: 4096 rays; the estimator's real use: 1024 rays).
+// With one thread per ray a batch of a few thousand rays is pure latency: < 1 warp per SM walking ~10^3 dependent
+// steps.  The parameter sequence t_k of a ray does not depend on the occupancy (march.cuh: ngp_march_advance), so the 32
+// lanes of a warp probe 32 consecutive t_k of ONE ray at once and the warp then replays the reference's sequential
+// decisions (sample / skip to the voxel exit) on the probe results with ballots and shuffles — same visits, same
+// samples, bit for bit.
+#ifndef MARCH_WARP_MAX_RAYS
+#define MARCH_WARP_MAX_RAYS 8192
+#endif
+
+template <bool WRITE>
+__device__ __forceinline__ uint32_t march_ray_warp(const MarchRay &r, const MarchCfg &cfg, float t_cur, float far,
+                                                   uint32_t limit, float last_t, int64_t off, float *__restrict__ xyzs,
+                                                   float *__restrict__ dirs, float *__restrict__ deltas, float &t_first) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    uint32_t steps = 0;
+    bool done = false;
+    while (!done && t_cur < far && steps < limit) {
+        float w = t_cur;                       // lane i: the i-th successor of t_cur
+        for (int j = 0; j < lane; ++j) w = ngp_march_advance(w, cfg);
+        const float wn = ngp_march_advance(w, cfg);
+        float px = 0.f, py = 0.f, pz = 0.f, dt = 0.f, tt = w;
+        bool occ = false;
+        if (w < far) occ = ngp_march_probe(r, cfg, w, px, py, pz, dt, tt);
+        const unsigned occ_mask = __ballot_sync(FULL, occ);
+        const float w_window_end = __shfl_sync(FULL, wn, 31);
+        float t_next = w_window_end;
+        int my_s = -1;
+        float my_last = 0.0f;
+        int c = 0;                              // lane whose t the reference marcher is at (warp-uniform)
+        while (c < 32) {
+            const float tw = __shfl_sync(FULL, w, c);
+            if (!(tw < far) || steps >= limit) {
+                done = true;
+                break;
+            }
+            if ((occ_mask >> c) & 1u) {         // sample here, go to the next t
+                if (lane == c) {
+                    my_s = (int)steps;
+                    my_last = last_t;
+                }
+                if (steps == 0) t_first = tw;
+                last_t = __shfl_sync(FULL, wn, c);
+                ++steps;
+                ++c;
+            } else {                            // empty: first t of the sequence at or past the voxel exit
+                const float ttc = __shfl_sync(FULL, tt, c);
+                const unsigned ahead = c >= 31 ? 0u : (FULL << (c + 1));
+                const unsigned m = __ballot_sync(FULL, w >= ttc) & ahead;
+                if (m) {
+                    c = __ffs(m) - 1;
+                } else {                        // the voxel ends beyond this window
+                    float tc = w_window_end;
+                    while (tc < ttc) tc = ngp_march_advance(tc, cfg);
+                    t_next = tc;
+                    break;
+                }
+            }
+        }
+        if (WRITE && my_s >= 0) {
+            const int64_t k = off + my_s;
+            xyzs[k * 3] = px; xyzs[k * 3 + 1] = py; xyzs[k * 3 + 2] = pz;
+            dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+            deltas[k * 2] = dt;
+            deltas[k * 2 + 1] = wn - my_last;
+        }
+        t_cur = t_next;
+    }
+    return steps;
+}
+
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_count_warp(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, uint32_t max_steps,
+                   int64_t N, const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
+                   int32_t *__restrict__ counts, float *__restrict__ t_first) {
+    const int64_t n = ((int64_t)blockIdx.x * RAY_THREADS + threadIdx.x) >> 5;
+    if (n >= N) return;
+    const MarchRay r = load_ray(rays_o, rays_d, n);
+    float t = nears[n];
+    if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);
+    float tf = t;
+    const uint32_t steps = march_ray_warp<false>(r, cfg, t, fars[n], max_steps, t, 0, nullptr, nullptr, nullptr, tf);
+    if ((threadIdx.x & 31) == 0) {
+        counts[n] = (int32_t)steps;
+        t_first[n] = tf;
+    }
+}
+
+__global__ void __launch_bounds__(RAY_THREADS)
+k_march_write_warp(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
+                   const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
+                   const int32_t *__restrict__ rays, const float *__restrict__ t_first, float *__restrict__ xyzs,
+                   float *__restrict__ dirs, float *__restrict__ deltas) {
+    const int64_t n = ((int64_t)blockIdx.x * RAY_THREADS + threadIdx.x) >> 5;
+    if (n >= N) return;
+    const int64_t off = rays[n * 3 + 1];
+    const uint32_t cnt = (uint32_t)rays[n * 3 + 2];
+    if (cnt == 0 || off + cnt >= M) return;  // :419-420
+    const MarchRay r = load_ray(rays_o, rays_d, n);
+    float t = nears[n];
+    if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);
+    float tf = 0.0f;
+    march_ray_warp<true>(r, cfg, t_first[n], fars[n], cnt, t, off, xyzs, dirs, deltas, tf);
+}
+
 extern "C" int64_t ngp_march_rays_train_workspace_bytes(int64_t N) {
     return (2 * N + ngp_div_up(N, SCAN_TILE) + 8) * (int64_t)sizeof(int32_t);  // counts, tile totals, t_first
 }
@@ -269,11 +375,19 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
     float *t_first = (float *)(tile_totals + n_tiles + 8);
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
     const unsigned gr = (unsigned)ngp_div_up(N, RAY_THREADS);
-    k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
+    const bool by_warp = N <= MARCH_WARP_MAX_RAYS;
+    const unsigned gw = (unsigned)ngp_div_up(N * 32, RAY_THREADS);
+    if (by_warp)
+        k_march_count_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
+    else
+        k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
     k_scan_tile_totals<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, N, tile_totals);
     k_scan_totals<<<1, SCAN_THREADS, 0, st>>>(tile_totals, n_tiles, counter, N);
     k_scan_write_rays<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, tile_totals, N, rays);
-    k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
+    if (by_warp)
+        k_march_write_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
+    else
+        k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
     NGP_CHECK_LAUNCH("ngp_march_rays_train");
     return NGP_OK;
 }
