@@ -70,6 +70,38 @@ def test_march_rays_train_vs_oracle(ngp, oracle, scene, perturb):
     assert not xyzs[m:].any()
 
 
+@pytest.mark.parametrize("N,dt_gamma,max_steps", [(3000, 1.0 / 128, 1024), (8192, 1.0 / 64, 512), (20000, 1.0 / 128, 1024),
+                                                  (20000, 0.0, 1024), (33, 0.0, 16)])
+def test_march_rays_train_both_kernels_and_cone_steps(ngp, oracle, scene, N, dt_gamma, max_steps):
+    """The marcher has two forms — one warp per ray for N <= 8192 (32 consecutive steps probed at once, the reference's
+    decisions replayed on the probes) and one thread per ray above — and both must reproduce the reference's samples bit for
+    bit, also with dt_gamma > 0 where the step grows along the ray (raymarching.cu:369) and with a tight max_steps."""
+    from nerf_navigation_b200 import raymarching as rm
+    _, bits = scene
+    o, d = _rays(N, 7)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    M = N * max_steps
+    rx, rd, rdl, rrays, rcnt = oracle.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, M, dt_gamma=dt_gamma,
+                                                       max_steps=max_steps, perturb=True)
+    t = lambda a: torch.from_numpy(a).cuda()
+    counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+    xyzs, dirs, deltas, rays = rm.march_rays_train(t(o), t(d), BOUND, t(bits), CAS, H, t(nears), t(fars), counter, -1,
+                                                   True, 128, True, dt_gamma, max_steps)
+    assert np.array_equal(rays.cpu().numpy(), rrays) and np.array_equal(counter.cpu().numpy(), rcnt)
+    m = int(rcnt[0])
+    assert m > 0 and (rrays[:, 2] <= max_steps).all()
+    assert np.array_equal(xyzs[:m].cpu().numpy(), rx[:m]) and np.array_equal(deltas[:m].cpu().numpy(), rdl[:m])
+    if N == 20000:   # the first 8192 rays through the warp-per-ray kernels: same counts and samples as the thread form
+        c2 = torch.zeros(2, dtype=torch.int32, device="cuda")
+        n2 = 8192
+        x2, _, dl2, r2 = rm.march_rays_train(t(o[:n2]), t(d[:n2]), BOUND, t(bits), CAS, H, t(nears[:n2]), t(fars[:n2]), c2, -1,
+                                             True, 128, True, dt_gamma, max_steps)
+        assert torch.equal(r2, rays[:n2])
+        m2 = int(c2[0])
+        assert torch.equal(x2[:m2], xyzs[:m2]) and torch.equal(dl2[:m2], deltas[:m2])
+
+
 def test_march_budget_drops_rays_like_reference(ngp, oracle, scene):
     """mean_count budget: rays whose offset+count >= M write nothing (raymarching.cu:420)."""
     from nerf_navigation_b200 import raymarching as rm
