@@ -13,7 +13,11 @@
 #define LIN_THREADS 128
 #define LIN_MAX 64
 
-template <int NT>
+// VEC (k_dim % 16 == 0, X 16-byte aligned): the order of the K index inside an MMA is free as long as A and B agree, so
+// lane t takes the four CONSECUTIVE inputs 16j + 4t .. 4t+3 of its rows with one 16-byte load and feeds them to two
+// k-tiles (slots t / t+4 of tile 2j = inputs 4t, 4t+1; of tile 2j+1 = inputs 4t+2, 4t+3): a quarter of the load
+// instructions and L1 wavefronts of the scalar fragment order (the scalar form is LSU-bound: 64-77 % of the data pipe).
+template <int NT, bool VEC>
 __global__ void __launch_bounds__(LIN_THREADS)
 k_linear_small(const float *__restrict__ X, const float *__restrict__ W, float *__restrict__ Y, int64_t M, int k_dim,
                int n_dim, int ld_n, int ld_k) {
@@ -22,7 +26,8 @@ k_linear_small(const float *__restrict__ X, const float *__restrict__ W, float *
     const int ktiles = (k_dim + 7) >> 3;
     for (int i = tid; i < NT * ktiles * 32; i += LIN_THREADS) {
         const int ln = i & 31, kt = (i >> 5) % ktiles, nt = (i >> 5) / ktiles, gg = ln >> 2, tt = ln & 3;
-        const int n = 8 * nt + gg, k0 = 8 * kt + tt, k1 = k0 + 4;
+        const int n = 8 * nt + gg;
+        const int k0 = VEC ? 16 * (kt >> 1) + 4 * tt + 2 * (kt & 1) : 8 * kt + tt, k1 = VEC ? k0 + 1 : k0 + 4;
         const float b0 = (n < n_dim && k0 < k_dim) ? W[(int64_t)n * ld_n + (int64_t)k0 * ld_k] : 0.0f;
         const float b1 = (n < n_dim && k1 < k_dim) ? W[(int64_t)n * ld_n + (int64_t)k1 * ld_k] : 0.0f;
         frag[(nt * (LIN_MAX / 8) + kt) * 32 + ln] = fq_split_pair(b0, b1);
@@ -37,18 +42,37 @@ k_linear_small(const float *__restrict__ X, const float *__restrict__ W, float *
         float acc[NT][4];
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
-        for (int kt = 0; kt < ktiles; ++kt) {
-            const int ka = 8 * kt + t, kb = ka + 4;
-            float a[4];
-            a[0] = (v0 && ka < k_dim) ? __ldg(x0 + ka) : 0.0f;
-            a[1] = (v1 && ka < k_dim) ? __ldg(x1 + ka) : 0.0f;
-            a[2] = (v0 && kb < k_dim) ? __ldg(x0 + kb) : 0.0f;
-            a[3] = (v1 && kb < k_dim) ? __ldg(x1 + kb) : 0.0f;
-            uint32_t ahi[4], alo[4];
+        if (VEC) {
+            for (int j = 0; j < (ktiles >> 1); ++j) {
+                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 p0 = v0 ? __ldg(reinterpret_cast<const float4 *>(x0 + 16 * j) + t) : z;
+                const float4 p1 = v1 ? __ldg(reinterpret_cast<const float4 *>(x1 + 16 * j) + t) : z;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) fq_split(a[c], ahi[c], alo[c]);
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t ahi[4], alo[4];
+                    fq_split(h ? p0.z : p0.x, ahi[0], alo[0]);
+                    fq_split(h ? p1.z : p1.x, ahi[1], alo[1]);
+                    fq_split(h ? p0.w : p0.y, ahi[2], alo[2]);
+                    fq_split(h ? p1.w : p1.y, ahi[3], alo[3]);
 #pragma unroll
-            for (int nt = 0; nt < NT; ++nt) fq_mma3(acc[nt], ahi, alo, frag[(nt * (LIN_MAX / 8) + kt) * 32 + lane]);
+                    for (int nt = 0; nt < NT; ++nt)
+                        fq_mma3(acc[nt], ahi, alo, frag[(nt * (LIN_MAX / 8) + 2 * j + h) * 32 + lane]);
+                }
+            }
+        } else {
+            for (int kt = 0; kt < ktiles; ++kt) {
+                const int ka = 8 * kt + t, kb = ka + 4;
+                float a[4];
+                a[0] = (v0 && ka < k_dim) ? __ldg(x0 + ka) : 0.0f;
+                a[1] = (v1 && ka < k_dim) ? __ldg(x1 + ka) : 0.0f;
+                a[2] = (v0 && kb < k_dim) ? __ldg(x0 + kb) : 0.0f;
+                a[3] = (v1 && kb < k_dim) ? __ldg(x1 + kb) : 0.0f;
+                uint32_t ahi[4], alo[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) fq_split(a[c], ahi[c], alo[c]);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) fq_mma3(acc[nt], ahi, alo, frag[(nt * (LIN_MAX / 8) + kt) * 32 + lane]);
+            }
         }
         // c0,c1: (row g, cols 8nt+2t, +1); c2,c3: (row g+8, ...)
 #pragma unroll
@@ -90,7 +114,10 @@ extern "C" int ngp_linear_small(const float *X, const float *W, float *Y, int64_
     const unsigned grid = (unsigned)(want < cap ? want : cap);
     cudaStream_t st = (cudaStream_t)stream;
     const int nt = (n_dim + 7) >> 3;
-#define LIN_GO(NT) k_linear_small<NT><<<grid, LIN_THREADS, 0, st>>>(X, W, Y, M, k_dim, n_dim, ld_n, ld_k)
+    const bool vec = (k_dim % 16) == 0 && ((uintptr_t)X & 15u) == 0;
+#define LIN_GO(NT)                                                                                        \
+    if (vec) k_linear_small<NT, true><<<grid, LIN_THREADS, 0, st>>>(X, W, Y, M, k_dim, n_dim, ld_n, ld_k); \
+    else k_linear_small<NT, false><<<grid, LIN_THREADS, 0, st>>>(X, W, Y, M, k_dim, n_dim, ld_n, ld_k)
     switch (nt) {
         case 1: LIN_GO(1); break;
         case 2: LIN_GO(2); break;
