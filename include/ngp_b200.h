@@ -102,6 +102,12 @@ int ngp_field_query_value_grad(const float *x, float bound, const float *embeddi
 
 /* ---- fused per-sample field for the ray paths: NeRFNetwork.forward(x, d), nerf/network.py:95-124 ------------------- */
 
+/* Implementation of the fused colour-field / render kernels: 1 = warp-specialised tcgen05 (TMEM accumulators and A
+ * operands, 3xTF32; the default), 0 = the mma.sync 3xTF32 kernels kept as an independent fp32 cross-check.  Process-wide;
+ * the initial value can also be set with the environment variable NGP_B200_FIELD_IMPL=mma|tc5.  Returns the previous
+ * value; impl < 0 only queries.  (No reference counterpart: the reference has one implementation.) */
+int ngp_set_field_impl(int impl);
+
 /* sigma [M] = exp(o[0]), rgb [M,3] = sigmoid(colour_net([SH4(d) | o[1:16]])), o = sigma_net(encode(x)); fp32 table and
  * weights of the configuration nav uses: D=3, L=16, C=2, sigma net 32-64-16 (Ws0 [64,32], Ws1 [16,64]), colour net
  * 31-64-64-3 (Wc0 [64,31], Wc1 [64,64], Wc2 [3,64]), all nn.Linear.weight layouts.  masks (optional): u16 [M,3,4] ReLU

@@ -1,0 +1,451 @@
+// cfield5.cu — warp-specialised tcgen05 kernels of the fused per-sample field (building blocks in cfield5.cuh):
+// forward (x, d) -> (sigma, rgb) and backward to (x, d) for the ray paths of NeRFRenderer.run_cuda (renderer.py:303-305,
+// 352-354) / the pose estimator.  These are the default implementation behind ngp_field_color_forward/backward
+// (renderfield.cu keeps the mma.sync 3xTF32 kernels as the cross-check, NGP_B200_FIELD_IMPL=mma).
+#include <stdlib.h>
+#include <string.h>
+
+#include "cfield5.cuh"
+
+// 1: tcgen05 kernels (default), 0: legacy mma.sync kernels
+static int g_field_impl = -1;
+int ngp_field_impl_tc5() {
+    if (g_field_impl < 0) {
+        const char *e = getenv("NGP_B200_FIELD_IMPL");
+        g_field_impl = (e && strcmp(e, "mma") == 0) ? 0 : 1;
+    }
+    return g_field_impl;
+}
+extern "C" int ngp_set_field_impl(int impl) {
+    const int prev = ngp_field_impl_tc5();
+    if (impl >= 0) g_field_impl = impl ? 1 : 0;
+    return prev;
+}
+
+struct __align__(128) C5FwdSmem {
+    C5FwdWeights w;
+    FqLevel lv[FQ_L];
+    C5Bars bars[2];
+    uint32_t tmem;
+    int all_safe;
+};
+
+struct C5FwdParams {
+    const float *x, *dirs, *table;
+    float bound;
+    int align_corners;
+    float *sigma, *rgb;
+    uint64_t *masks;
+    int64_t B;
+};
+
+// ------------------------------------------------------------------------------------------------ forward
+template <bool SAFE>
+__device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem, int warp, int lane) {
+    const int s = warp >> 2, q = warp & 3, row = 32 * q + lane;
+    const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
+    const uint32_t bar_full = tc5::smem_u32(&S.bars[s].f_full), bar_empty = tc5::smem_u32(&S.bars[s].f_empty);
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    for (int64_t it = 0;; ++it) {
+        const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+        if (tile >= ntiles) break;
+        const int64_t b = tile * C5_ROWS + row;
+        float x01[3];
+        const bool valid = fq_load_point(P.x, b, P.B, P.bound, x01);
+#pragma unroll 1
+        for (int lp = 0; lp < 8; ++lp) {
+            float feat[4];
+            c5_encode_pair<SAFE>(P.table, S.lv, lp, x01, valid, P.align_corners, feat);
+            if (lp == 0) {
+                // the previous tile's first-layer products have read the feature columns (long done unless the chain is behind)
+                if (it > 0) tc5::mbar_wait_wd(bar_empty, (uint32_t)((it - 1) & 1));
+                tc5::fence_after_sync();
+            }
+            c5_put_features(lane_addr, lp, feat);
+        }
+        tc5::tmem_st_wait();
+        tc5::fence_before_sync();
+        tc5::mbar_arrive(bar_full);
+    }
+}
+
+template <bool MASK>
+__device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem, int warp, int lane) {
+    const int q = warp & 3, row = 32 * q + lane;
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    uint32_t pd[2] = {0u, 0u};
+    for (int64_t it = 0;; ++it) {
+        bool any = false;
+#pragma unroll 1
+        for (int s = 0; s < 2; ++s) {
+            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+            if (tile >= ntiles) break;
+            any = true;
+            const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
+            const int64_t b = tile * C5_ROWS + row;
+            const bool inb = b < P.B;
+            float dir[3];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) dir[a] = inb ? __ldg(P.dirs + b * 3 + a) : 0.0f;
+            float log_sigma, logit[3];
+            uint64_t mask[3];
+            c5_chain_forward_tile<MASK>(lane_addr, dir, tc5::smem_u32(&S.bars[s].d_full), tc5::smem_u32(&S.bars[s].a_ready), pd[s],
+                                  log_sigma, logit, mask);
+            tc5::fence_before_sync();
+            tc5::mbar_arrive(tc5::smem_u32(&S.bars[s].t_free));
+            if (inb) {
+                P.sigma[b] = expf(log_sigma);  // trunc_exp forward (activation.py:9-11)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) P.rgb[b * 3 + c] = 1.0f / (1.0f + expf(-logit[c]));
+                if (MASK) {
+                    P.masks[b * 3] = mask[0];
+                    P.masks[b * 3 + 1] = mask[1];
+                    P.masks[b * 3 + 2] = mask[2];
+                }
+            }
+        }
+        if (!any) break;
+    }
+}
+
+__device__ __forceinline__ void c5_forward_mma(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem) {
+    const C5FwdAddrs W = c5_fwd_addrs(S.w);
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    uint32_t pa[2] = {0u, 0u};
+    for (int64_t it = 0;; ++it) {
+        bool any = false;
+#pragma unroll 1
+        for (int s = 0; s < 2; ++s) {
+            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+            if (tile >= ntiles) break;
+            any = true;
+            tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].f_full), (uint32_t)(it & 1));
+            if (it > 0) tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].t_free), (uint32_t)((it - 1) & 1));
+            tc5::fence_after_sync();
+            c5_mma_forward_tile(tmem + s * C5_SLOT_COLS, W, tc5::smem_u32(&S.bars[s].f_empty),
+                                tc5::smem_u32(&S.bars[s].d_full), tc5::smem_u32(&S.bars[s].a_ready), pa[s]);
+        }
+        if (!any) break;
+    }
+}
+
+__device__ __forceinline__ void c5_init_bars(C5Bars *bars) {
+    for (int s = 0; s < 2; ++s) {
+        tc5::mbar_init(tc5::smem_u32(&bars[s].f_full), 128);
+        tc5::mbar_init(tc5::smem_u32(&bars[s].f_empty), 1);
+        tc5::mbar_init(tc5::smem_u32(&bars[s].d_full), 1);
+        tc5::mbar_init(tc5::smem_u32(&bars[s].a_ready), 128);
+        tc5::mbar_init(tc5::smem_u32(&bars[s].t_free), 128);
+        tc5::mbar_init(tc5::smem_u32(&bars[s].g_full), 1);
+    }
+    tc5::fence_mbar_init();
+}
+
+__global__ void __launch_bounds__(C5_THREADS, 1)
+k_cfield5_forward(C5FwdParams P, const int32_t *__restrict__ offsets, float S_, uint32_t H, uint32_t gridtype,
+                  const float *__restrict__ Ws0, const float *__restrict__ Ws1, const float *__restrict__ Wc0,
+                  const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
+    extern __shared__ __align__(128) unsigned char c5_smem_raw[];
+    C5FwdSmem &S = *reinterpret_cast<C5FwdSmem *>(c5_smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
+    c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
+    if (tid == 0) c5_init_bars(S.bars);
+    if (warp == C5_MMA_WARP) tc5::tmem_alloc(tc5::smem_u32(&S.tmem), 512);
+    tc5::fence_async_smem();
+    tc5::fence_before_sync();
+    __syncthreads();
+    tc5::fence_after_sync();
+    const uint32_t tmem = S.tmem;
+
+    if (warp < C5_GATHER_WARPS) {
+        if (S.all_safe) c5_forward_gather<true>(S, P, tmem, warp, lane);
+        else c5_forward_gather<false>(S, P, tmem, warp, lane);
+    } else if (warp < C5_MMA_WARP) {
+        if (P.masks) c5_forward_chain<true>(S, P, tmem, warp, lane);
+        else c5_forward_chain<false>(S, P, tmem, warp, lane);
+    } else {
+        if (lane == 0) c5_forward_mma(S, P, tmem);
+        __syncwarp();
+    }
+    tc5::fence_before_sync();
+    __syncthreads();
+    if (warp == C5_MMA_WARP) tc5::tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------ backward to (x, d)
+// Every product is (row gradient) x W: the B tile of a layer is W^T, B(n, k) = W[k-th downstream unit][n-th upstream unit].
+struct __align__(128) C5BwdWeights {
+    float c2[2][64 * 8];   // dHc2 = dRGB  W_c2   [64 x 8]  (K = 3 -> 8)
+    float c1[2][64 * 64];  // dHc1 = dHc2m W_c1   [64 x 64]
+    float c0[2][32 * 64];  // dIn  = dHc1m W_c0   [32 x 64]: n < 16 SH, n >= 16 sigma-net output n-16 (n = 16: zero)
+    float s1[2][64 * 16];  // dHs  = dO    W_s1   [64 x 16]
+    float s0[2][32 * 64];  // dFeat = dHsm W_s0   [32 x 64]
+};
+struct __align__(128) C5BwdSmem {
+    C5BwdWeights w;
+    FqLevel lv[FQ_L];
+    C5Bars bars[2];
+    uint32_t tmem;
+    int all_safe;
+};
+struct C5BwdParams {
+    const float *x, *dirs, *table;
+    float bound;
+    int align_corners;
+    const float *sigma, *rgb;
+    const uint64_t *masks;
+    const float *grad_sigma, *grad_rgb;
+    float *grad_x, *grad_d;
+    int64_t B;
+};
+
+// chain: the MLP chain backwards for one tile; leaves dFeat in the accumulator (MMA thread commits g_full)
+__device__ __forceinline__ void c5_backward_chain(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem, int warp, int lane) {
+    const int q = warp & 3, row = 32 * q + lane;
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    const float e_lo = expf(-15.0f), e_hi = expf(15.0f);
+    uint32_t pd[2] = {0u, 0u};
+    for (int64_t it = 0;; ++it) {
+        bool any = false;
+#pragma unroll 1
+        for (int s = 0; s < 2; ++s) {
+            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+            if (tile >= ntiles) break;
+            any = true;
+            const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
+            const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready);
+            const int64_t b = tile * C5_ROWS + row;
+            const bool inb = b < P.B;
+            float dir[3] = {0.0f, 0.0f, 0.0f}, go0 = 0.0f;
+            float a0[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a0[i] = 0.0f;
+            uint64_t m_sig = 0, m_c1 = 0, m_c2 = 0;
+            if (inb) {
+                go0 = __ldg(P.grad_sigma + b) * fminf(fmaxf(__ldg(P.sigma + b), e_lo), e_hi);  // trunc_exp backward (activation.py:13-17)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float cv = __ldg(P.rgb + b * 3 + c);
+                    a0[c] = __ldg(P.grad_rgb + b * 3 + c) * cv * (1.0f - cv);  // sigmoid'
+                    dir[c] = __ldg(P.dirs + b * 3 + c);
+                }
+                m_sig = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3);
+                m_c1 = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3 + 1);
+                m_c2 = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3 + 2);
+            }
+            // the slot is free once the gather warps have taken the previous tile's dFeat
+            if (it > 0) tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].t_free), (uint32_t)((it - 1) & 1));
+            tc5::fence_after_sync();
+            c5_put16(lane_addr, 0, a0);  // dRGB (K = 8 of these 16 columns are read)
+            c5_chain_arrive(bar_a);
+            // dHc2 .* relu'
+            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
+            tc5::fence_after_sync();
+            c5_mask_to_a(lane_addr, m_c2);
+            c5_chain_arrive(bar_a);
+            // dHc1 .* relu'
+            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
+            tc5::fence_after_sync();
+            c5_mask_to_a(lane_addr, m_c1);
+            c5_chain_arrive(bar_a);
+            // dIn = [dSH 16 | dO 16]: SH backward to the direction; dO (+ the sigma gradient on column 0) goes on
+            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
+            tc5::fence_after_sync();
+            {
+                float dsh[16], dout[16];
+                c5_get16(lane_addr, 0, dsh);
+                c5_get16(lane_addr, 16, dout);
+                dout[0] += go0;  // its colour weight is zero, so the product left 0 there
+                c5_put16(lane_addr, 0, dout);
+                c5_chain_arrive(bar_a);
+                if (P.grad_d) {
+                    float jx[16], jy[16], jz[16];
+                    ngp_sh4_jac(dir[0], dir[1], dir[2], jx, jy, jz);
+                    float g0 = 0.0f, g1 = 0.0f, g2 = 0.0f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        g0 = fmaf(dsh[i], jx[i], g0);
+                        g1 = fmaf(dsh[i], jy[i], g1);
+                        g2 = fmaf(dsh[i], jz[i], g2);
+                    }
+                    if (inb) {
+                        P.grad_d[b * 3] = g0;
+                        P.grad_d[b * 3 + 1] = g1;
+                        P.grad_d[b * 3 + 2] = g2;
+                    }
+                }
+            }
+            // dHs .* relu'
+            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
+            tc5::fence_after_sync();
+            c5_mask_to_a(lane_addr, m_sig);
+            c5_chain_arrive(bar_a);
+        }
+        if (!any) break;
+    }
+}
+
+__device__ __forceinline__ void c5_backward_mma(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem) {
+    uint32_t W[5][2];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        W[0][p] = tc5::smem_u32(S.w.c2[p]);
+        W[1][p] = tc5::smem_u32(S.w.c1[p]);
+        W[2][p] = tc5::smem_u32(S.w.c0[p]);
+        W[3][p] = tc5::smem_u32(S.w.s1[p]);
+        W[4][p] = tc5::smem_u32(S.w.s0[p]);
+    }
+    const int NN[5] = {64, 64, 32, 64, 32}, KK[5] = {8, 64, 64, 16, 64};
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    uint32_t pa[2] = {0u, 0u};
+    for (int64_t it = 0;; ++it) {
+        bool any = false;
+#pragma unroll 1
+        for (int s = 0; s < 2; ++s) {
+            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+            if (tile >= ntiles) break;
+            any = true;
+            const uint32_t t = tmem + s * C5_SLOT_COLS;
+            const uint32_t bar_a = tc5::smem_u32(&S.bars[s].a_ready);
+#pragma unroll
+            for (int l = 0; l < 5; ++l) {
+                tc5::mbar_wait_wd(bar_a, pa[s]); pa[s] ^= 1u;
+                tc5::fence_after_sync();
+                c5_issue_layer(t + C5_D, t + C5_HHI, t + C5_HLO, W[l][0], W[l][1], NN[l], KK[l]);
+                tc5::mma_commit(tc5::smem_u32(l < 4 ? &S.bars[s].d_full : &S.bars[s].g_full));
+            }
+        }
+        if (!any) break;
+    }
+}
+
+template <bool SAFE>
+__device__ __forceinline__ void c5_backward_gather(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem, int warp, int lane) {
+    const int s = warp >> 2, q = warp & 3, row = 32 * q + lane;
+    const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
+    const uint32_t bar_g = tc5::smem_u32(&S.bars[s].g_full), bar_free = tc5::smem_u32(&S.bars[s].t_free);
+    const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    const float den = 2.0f * P.bound;
+    for (int64_t it = 0;; ++it) {
+        const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+        if (tile >= ntiles) break;
+        const int64_t b = tile * C5_ROWS + row;
+        float x01[3], gx[3] = {0.0f, 0.0f, 0.0f};
+        const bool valid = fq_load_point(P.x, b, P.B, P.bound, x01);
+        tc5::mbar_wait_wd(bar_g, (uint32_t)(it & 1));
+        tc5::fence_after_sync();
+        // move the thread's 32 feature gradients to its private columns and hand the accumulator back to the chain
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            uint32_t r[16];
+            tc5::tmem_ld16_nowait(lane_addr + C5_D + 16 * c, r);
+            tc5::tmem_ld_wait();
+            if (!valid) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) r[i] = 0u;
+            }
+            tc5::tmem_st16(lane_addr + C5_DF + 16 * c, r);
+        }
+        tc5::tmem_st_wait();
+        tc5::fence_before_sync();
+        tc5::mbar_arrive(bar_free);
+#pragma unroll 1
+        for (int lp = 0; lp < 8; ++lp) {
+            uint32_t r[4];
+            tc5::tmem_ld4_nowait(lane_addr + C5_DF + 4 * lp, r);
+            tc5::tmem_ld_wait();
+            const float df[4] = {__uint_as_float(r[0]), __uint_as_float(r[1]), __uint_as_float(r[2]), __uint_as_float(r[3])};
+            c5_encode_pair_backward<SAFE>(P.table, S.lv, lp, x01, P.align_corners, df, gx);
+        }
+        if (b < P.B) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) P.grad_x[b * 3 + a] = __fdiv_rn(gx[a], den);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(C5_THREADS, 1)
+k_cfield5_backward(C5BwdParams P, const int32_t *__restrict__ offsets, float S_, uint32_t H, uint32_t gridtype,
+                   const float *__restrict__ Ws0, const float *__restrict__ Ws1, const float *__restrict__ Wc0,
+                   const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
+    extern __shared__ __align__(128) unsigned char c5_smem_raw[];
+    C5BwdSmem &S = *reinterpret_cast<C5BwdSmem *>(c5_smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
+    c5_stage_tile(S.w.c2[0], S.w.c2[1], 64, 8, [&](int n, int k) { return k < 3 ? Wc2[k * FQ_HID + n] : 0.0f; });
+    c5_stage_tile(S.w.c1[0], S.w.c1[1], 64, 64, [&](int n, int k) { return Wc1[k * FQ_HID + n]; });
+    c5_stage_tile(S.w.c0[0], S.w.c0[1], 32, 64, [&](int n, int k) {
+        return n < 16 ? Wc0[k * 31 + n] : (n == 16 ? 0.0f : Wc0[k * 31 + n - 1]);
+    });
+    c5_stage_tile(S.w.s1[0], S.w.s1[1], 64, 16, [&](int n, int k) { return Ws1[k * FQ_HID + n]; });
+    c5_stage_tile(S.w.s0[0], S.w.s0[1], 32, 64, [&](int n, int k) { return Ws0[k * FQ_F + n]; });
+    if (tid == 0) c5_init_bars(S.bars);
+    if (warp == C5_MMA_WARP) tc5::tmem_alloc(tc5::smem_u32(&S.tmem), 512);
+    tc5::fence_async_smem();
+    tc5::fence_before_sync();
+    __syncthreads();
+    tc5::fence_after_sync();
+    const uint32_t tmem = S.tmem;
+
+    if (warp < C5_GATHER_WARPS) {
+        if (S.all_safe) c5_backward_gather<true>(S, P, tmem, warp, lane);
+        else c5_backward_gather<false>(S, P, tmem, warp, lane);
+    } else if (warp < C5_MMA_WARP) {
+        c5_backward_chain(S, P, tmem, warp, lane);
+    } else {
+        if (lane == 0) c5_backward_mma(S, P, tmem);
+        __syncwarp();
+    }
+    tc5::fence_before_sync();
+    __syncthreads();
+    if (warp == C5_MMA_WARP) tc5::tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------ launchers
+// one CTA per SM: a CTA owns all 512 TMEM columns, so a second resident CTA would only block in tcgen05.alloc
+static int c5_smem_bytes(size_t need) { return (int)(need > 120 * 1024 ? need : 120 * 1024); }
+
+static int c5_grid(int64_t B) {
+    int dev = 0, sms = NGP_SM_COUNT;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t tiles = ngp_div_up(B, C5_ROWS);
+    return (int)(tiles < sms ? tiles : sms);
+}
+
+int c5_field_color_forward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                           const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                           const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                           float *sigma, float *rgb, void *masks, int64_t M, cudaStream_t stream) {
+    const int smem = c5_smem_bytes(sizeof(C5FwdSmem));
+    if (cudaFuncSetAttribute(k_cfield5_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+        ngp_set_error("ngp_field_color_forward: cannot reserve %d B of shared memory", smem);
+        return NGP_ERR_CUDA;
+    }
+    C5FwdParams P;
+    P.x = xyzs; P.dirs = dirs; P.table = embeddings; P.bound = bound; P.align_corners = align_corners;
+    P.sigma = sigma; P.rgb = rgb; P.masks = (uint64_t *)masks; P.B = M;
+    k_cfield5_forward<<<c5_grid(M), C5_THREADS, smem, stream>>>(P, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
+    NGP_CHECK_LAUNCH("ngp_field_color_forward (tcgen05)");
+    return NGP_OK;
+}
+
+int c5_field_color_backward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                            const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                            const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                            const float *sigma, const float *rgb, const void *masks, const float *grad_sigma,
+                            const float *grad_rgb, float *grad_xyzs, float *grad_dirs, int64_t M, cudaStream_t stream) {
+    const int smem = c5_smem_bytes(sizeof(C5BwdSmem));
+    if (cudaFuncSetAttribute(k_cfield5_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+        ngp_set_error("ngp_field_color_backward: cannot reserve %d B of shared memory", smem);
+        return NGP_ERR_CUDA;
+    }
+    C5BwdParams P;
+    P.x = xyzs; P.dirs = dirs; P.table = embeddings; P.bound = bound; P.align_corners = align_corners;
+    P.sigma = sigma; P.rgb = rgb; P.masks = (const uint64_t *)masks; P.grad_sigma = grad_sigma; P.grad_rgb = grad_rgb;
+    P.grad_x = grad_xyzs; P.grad_d = grad_dirs; P.B = M;
+    k_cfield5_backward<<<c5_grid(M), C5_THREADS, smem, stream>>>(P, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
+    NGP_CHECK_LAUNCH("ngp_field_color_backward (tcgen05)");
+    return NGP_OK;
+}

@@ -269,6 +269,19 @@ k_render_field_backward(const float *__restrict__ x, const float *__restrict__ d
 }
 
 // ------------------------------------------------------------------------------------------------ C ABI
+// default implementation: the warp-specialised tcgen05 kernels of cfield5.cu; NGP_B200_FIELD_IMPL=mma selects the
+// mma.sync kernels above (kept as the independent fp32 cross-check)
+int ngp_field_impl_tc5();
+int c5_field_color_forward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                           const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                           const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                           float *sigma, float *rgb, void *masks, int64_t M, cudaStream_t stream);
+int c5_field_color_backward(const float *xyzs, const float *dirs, float bound, const float *embeddings,
+                            const int32_t *offsets, float S, uint32_t H, uint32_t gridtype, int align_corners,
+                            const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1, const float *Wc2,
+                            const float *sigma, const float *rgb, const void *masks, const float *grad_sigma,
+                            const float *grad_rgb, float *grad_xyzs, float *grad_dirs, int64_t M, cudaStream_t stream);
+
 template <typename K>
 static int rf_launch_cfg(K kernel, int64_t B, int *grid) {
     const int smem = (int)sizeof(RenderFieldSmem);
@@ -294,6 +307,9 @@ extern "C" int ngp_field_color_forward(const float *xyzs, const float *dirs, flo
                 "ngp_field_color_forward: null pointer");
     NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_forward: bad bound / M");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_forward: embeddings must be 16-byte aligned");
+    if (ngp_field_impl_tc5())
+        return c5_field_color_forward(xyzs, dirs, bound, embeddings, offsets, S, H, gridtype, align_corners, Ws0, Ws1, Wc0,
+                                      Wc1, Wc2, sigma, rgb, masks, M, (cudaStream_t)stream);
     int grid = 1;
     int rc = rf_launch_cfg(k_render_field_forward, M, &grid);
     if (rc) return rc;
@@ -316,6 +332,10 @@ extern "C" int ngp_field_color_backward(const float *xyzs, const float *dirs, fl
                 NGP_ERR_ARG, "ngp_field_color_backward: null pointer");
     NGP_REQUIRE(bound > 0.0f && M >= 0, NGP_ERR_ARG, "ngp_field_color_backward: bad bound / M");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_color_backward: embeddings must be 16-byte aligned");
+    if (ngp_field_impl_tc5())
+        return c5_field_color_backward(xyzs, dirs, bound, embeddings, offsets, S, H, gridtype, align_corners, Ws0, Ws1, Wc0,
+                                       Wc1, Wc2, sigma, rgb, masks, grad_sigma, grad_rgb, grad_xyzs, grad_dirs, M,
+                                       (cudaStream_t)stream);
     int grid = 1;
     int rc = rf_launch_cfg(k_render_field_backward, M, &grid);
     if (rc) return rc;
