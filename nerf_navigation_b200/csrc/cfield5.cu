@@ -69,63 +69,126 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
     }
 }
 
+// Chain warps: the five epilogues of a tile, alternating between the two slots step by step so that one slot's epilogue
+// runs while the other slot's next layer is on the tensor core.  No state is carried between steps (per-row inputs are
+// re-read from global memory before the barrier wait, outputs are written as soon as they exist), so each step's code
+// exists once with the slot as a run-time index.  d_full completes 5 times per tile: wait k of tile `it` has parity
+// (5 it + k) & 1.
 template <bool MASK>
 __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem, int warp, int lane) {
     const int q = warp & 3, row = 32 * q + lane;
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
-    uint32_t pd[2] = {0u, 0u};
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
     for (int64_t it = 0;; ++it) {
-        bool any = false;
+        const int64_t tile0 = blockIdx.x + (int64_t)gridDim.x * (2 * it);
+        const int n_act = tile0 >= ntiles ? 0 : (tile0 + gridDim.x >= ntiles ? 1 : 2);
+        if (n_act == 0) break;
+        const uint32_t par = (uint32_t)(5 * it);
+#define C5_SLOT_VARS                                                                            \
+        const uint32_t lane_addr = lane_base + s * C5_SLOT_COLS;                                \
+        const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready); \
+        const int64_t b = (tile0 + (int64_t)gridDim.x * s) * C5_ROWS + row;                     \
+        const bool inb = b < P.B;
+        // ---- sigma hidden
 #pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
-            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
-            if (tile >= ntiles) break;
-            any = true;
-            const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
-            const int64_t b = tile * C5_ROWS + row;
-            const bool inb = b < P.B;
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
+            tc5::mbar_wait_wd(bar_d, (par + 0u) & 1u);
+            tc5::fence_after_sync();
+            const uint64_t m = c5_relu_to_a<MASK>(lane_addr);
+            c5_chain_arrive(bar_a);
+            if (MASK && inb) P.masks[b * 3] = m;
+        }
+        // ---- sigma-net output o (column 0 = log sigma, 1..15 = geo_feat) -> colour input [SH(d) | 0, geo_feat]
+#pragma unroll 1
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
             float dir[3];
 #pragma unroll
             for (int a = 0; a < 3; ++a) dir[a] = inb ? __ldg(P.dirs + b * 3 + a) : 0.0f;
-            float log_sigma, logit[3];
-            uint64_t mask[3];
-            c5_chain_forward_tile<MASK>(lane_addr, dir, tc5::smem_u32(&S.bars[s].d_full), tc5::smem_u32(&S.bars[s].a_ready), pd[s],
-                                  log_sigma, logit, mask);
+            tc5::mbar_wait_wd(bar_d, (par + 1u) & 1u);
+            tc5::fence_after_sync();
+            float o[16];
+            c5_get16(lane_addr, 0, o);
+            const float log_sigma = o[0];
+            o[0] = 0.0f;
+            c5_put16(lane_addr, 16, o);
+            float sh[16];
+            ngp_sh4(dir[0], dir[1], dir[2], sh);
+            c5_put16(lane_addr, 0, sh);
+            c5_chain_arrive(bar_a);
+            if (inb) P.sigma[b] = expf(log_sigma);  // trunc_exp forward (activation.py:9-11)
+        }
+        // ---- colour hidden 1, 2
+#pragma unroll 1
+        for (int k = 0; k < 2; ++k) {
+#pragma unroll 1
+            for (int s = 0; s < n_act; ++s) {
+                C5_SLOT_VARS
+                tc5::mbar_wait_wd(bar_d, (par + 2u + (uint32_t)k) & 1u);
+                tc5::fence_after_sync();
+                const uint64_t m = c5_relu_to_a<MASK>(lane_addr);
+                c5_chain_arrive(bar_a);
+                if (MASK && inb) P.masks[b * 3 + 1 + k] = m;
+            }
+        }
+        // ---- colour logits
+#pragma unroll 1
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
+            (void)bar_a;
+            tc5::mbar_wait_wd(bar_d, (par + 4u) & 1u);
+            tc5::fence_after_sync();
+            uint32_t r[4];
+            tc5::tmem_ld4_nowait(lane_addr + C5_D, r);
+            tc5::tmem_ld_wait();
             tc5::fence_before_sync();
             tc5::mbar_arrive(tc5::smem_u32(&S.bars[s].t_free));
             if (inb) {
-                P.sigma[b] = expf(log_sigma);  // trunc_exp forward (activation.py:9-11)
 #pragma unroll
-                for (int c = 0; c < 3; ++c) P.rgb[b * 3 + c] = 1.0f / (1.0f + expf(-logit[c]));
-                if (MASK) {
-                    P.masks[b * 3] = mask[0];
-                    P.masks[b * 3 + 1] = mask[1];
-                    P.masks[b * 3 + 2] = mask[2];
-                }
+                for (int c = 0; c < 3; ++c) P.rgb[b * 3 + c] = 1.0f / (1.0f + expf(-__uint_as_float(r[c])));
             }
         }
-        if (!any) break;
     }
 }
 
-__device__ __forceinline__ void c5_forward_mma(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem) {
-    const C5FwdAddrs W = c5_fwd_addrs(S.w);
+// MMA thread of slot s: the five layers of each tile.  a_ready completes 4 times per tile.
+__device__ __forceinline__ void c5_forward_mma(C5FwdSmem &S, const C5FwdParams &P, uint32_t tmem, int s) {
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
-    uint32_t pa[2] = {0u, 0u};
+    const uint32_t t = tmem + s * C5_SLOT_COLS;
+    const uint32_t bar_ff = tc5::smem_u32(&S.bars[s].f_full), bar_fe = tc5::smem_u32(&S.bars[s].f_empty),
+                   bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready),
+                   bar_t = tc5::smem_u32(&S.bars[s].t_free);
+    const uint32_t s0h = tc5::smem_u32(S.w.s0[0]), s0l = tc5::smem_u32(S.w.s0[1]), s1h = tc5::smem_u32(S.w.s1[0]),
+                   s1l = tc5::smem_u32(S.w.s1[1]), c0h = tc5::smem_u32(S.w.c0[0]), c0l = tc5::smem_u32(S.w.c0[1]),
+                   c1h = tc5::smem_u32(S.w.c1[0]), c1l = tc5::smem_u32(S.w.c1[1]), c2h = tc5::smem_u32(S.w.c2[0]),
+                   c2l = tc5::smem_u32(S.w.c2[1]);
     for (int64_t it = 0;; ++it) {
-        bool any = false;
-#pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
-            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
-            if (tile >= ntiles) break;
-            any = true;
-            tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].f_full), (uint32_t)(it & 1));
-            if (it > 0) tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].t_free), (uint32_t)((it - 1) & 1));
-            tc5::fence_after_sync();
-            c5_mma_forward_tile(tmem + s * C5_SLOT_COLS, W, tc5::smem_u32(&S.bars[s].f_empty),
-                                tc5::smem_u32(&S.bars[s].d_full), tc5::smem_u32(&S.bars[s].a_ready), pa[s]);
-        }
-        if (!any) break;
+        const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+        if (tile >= ntiles) break;
+        const uint32_t pa = (uint32_t)(4 * it);
+        tc5::mbar_wait_wd(bar_ff, (uint32_t)(it & 1));
+        if (it > 0) tc5::mbar_wait_wd(bar_t, (uint32_t)((it - 1) & 1));
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 32>(t + C5_D, t + C5_FHI, t + C5_FLO, s0h, s0l);   // sigma L1: features -> 64
+        tc5::mma_commit(bar_fe);
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, s1h, s1l);   // sigma L2: 64 -> 16
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 32>(t + C5_D, t + C5_HHI, t + C5_HLO, c0h, c0l);   // colour L1: [SH | o] (32) -> 64
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c1h, c1l);   // colour L2: 64 -> 64
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c2h, c2l);   // colour L3: 64 -> 3 (16)
+        tc5::mma_commit(bar_d);
     }
 }
 
@@ -165,7 +228,7 @@ k_cfield5_forward(C5FwdParams P, const int32_t *__restrict__ offsets, float S_, 
         if (P.masks) c5_forward_chain<true>(S, P, tmem, warp, lane);
         else c5_forward_chain<false>(S, P, tmem, warp, lane);
     } else {
-        if (lane == 0) c5_forward_mma(S, P, tmem);
+        if (lane == 0) c5_forward_mma(S, P, tmem, warp - C5_MMA_WARP);
         __syncwarp();
     }
     tc5::fence_before_sync();
@@ -200,123 +263,134 @@ struct C5BwdParams {
     int64_t B;
 };
 
-// chain: the MLP chain backwards for one tile; leaves dFeat in the accumulator (MMA thread commits g_full)
+// Chain warps, backward: five A-operand steps per tile, alternating between the slots like the forward.  d_full completes
+// 4 times per tile (parity of wait k = k & 1), the fifth product signals the gather warps (g_full).
 __device__ __forceinline__ void c5_backward_chain(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem, int warp, int lane) {
     const int q = warp & 3, row = 32 * q + lane;
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
     const float e_lo = expf(-15.0f), e_hi = expf(15.0f);
-    uint32_t pd[2] = {0u, 0u};
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    const unsigned long long *masks = reinterpret_cast<const unsigned long long *>(P.masks);
     for (int64_t it = 0;; ++it) {
-        bool any = false;
+        const int64_t tile0 = blockIdx.x + (int64_t)gridDim.x * (2 * it);
+        const int n_act = tile0 >= ntiles ? 0 : (tile0 + gridDim.x >= ntiles ? 1 : 2);
+        if (n_act == 0) break;
+        // ---- dRGB = dL/drgb .* sigmoid'
 #pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
-            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
-            if (tile >= ntiles) break;
-            any = true;
-            const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
-            const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready);
-            const int64_t b = tile * C5_ROWS + row;
-            const bool inb = b < P.B;
-            float dir[3] = {0.0f, 0.0f, 0.0f}, go0 = 0.0f;
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
+            (void)bar_d;
             float a0[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) a0[i] = 0.0f;
-            uint64_t m_sig = 0, m_c1 = 0, m_c2 = 0;
             if (inb) {
-                go0 = __ldg(P.grad_sigma + b) * fminf(fmaxf(__ldg(P.sigma + b), e_lo), e_hi);  // trunc_exp backward (activation.py:13-17)
 #pragma unroll
                 for (int c = 0; c < 3; ++c) {
                     const float cv = __ldg(P.rgb + b * 3 + c);
-                    a0[c] = __ldg(P.grad_rgb + b * 3 + c) * cv * (1.0f - cv);  // sigmoid'
-                    dir[c] = __ldg(P.dirs + b * 3 + c);
+                    a0[c] = __ldg(P.grad_rgb + b * 3 + c) * cv * (1.0f - cv);
                 }
-                m_sig = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3);
-                m_c1 = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3 + 1);
-                m_c2 = __ldg(reinterpret_cast<const unsigned long long *>(P.masks) + b * 3 + 2);
             }
-            // the slot is free once the gather warps have taken the previous tile's dFeat
+            // the slot is free once the gather warps have taken the previous tile's feature gradients
             if (it > 0) tc5::mbar_wait_wd(tc5::smem_u32(&S.bars[s].t_free), (uint32_t)((it - 1) & 1));
             tc5::fence_after_sync();
-            c5_put16(lane_addr, 0, a0);  // dRGB (K = 8 of these 16 columns are read)
-            c5_chain_arrive(bar_a);
-            // dHc2 .* relu'
-            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
-            tc5::fence_after_sync();
-            c5_mask_to_a(lane_addr, m_c2);
-            c5_chain_arrive(bar_a);
-            // dHc1 .* relu'
-            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
-            tc5::fence_after_sync();
-            c5_mask_to_a(lane_addr, m_c1);
-            c5_chain_arrive(bar_a);
-            // dIn = [dSH 16 | dO 16]: SH backward to the direction; dO (+ the sigma gradient on column 0) goes on
-            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
-            tc5::fence_after_sync();
-            {
-                float dsh[16], dout[16];
-                c5_get16(lane_addr, 0, dsh);
-                c5_get16(lane_addr, 16, dout);
-                dout[0] += go0;  // its colour weight is zero, so the product left 0 there
-                c5_put16(lane_addr, 0, dout);
-                c5_chain_arrive(bar_a);
-                if (P.grad_d) {
-                    float jx[16], jy[16], jz[16];
-                    ngp_sh4_jac(dir[0], dir[1], dir[2], jx, jy, jz);
-                    float g0 = 0.0f, g1 = 0.0f, g2 = 0.0f;
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        g0 = fmaf(dsh[i], jx[i], g0);
-                        g1 = fmaf(dsh[i], jy[i], g1);
-                        g2 = fmaf(dsh[i], jz[i], g2);
-                    }
-                    if (inb) {
-                        P.grad_d[b * 3] = g0;
-                        P.grad_d[b * 3 + 1] = g1;
-                        P.grad_d[b * 3 + 2] = g2;
-                    }
-                }
-            }
-            // dHs .* relu'
-            tc5::mbar_wait_wd(bar_d, pd[s]); pd[s] ^= 1u;
-            tc5::fence_after_sync();
-            c5_mask_to_a(lane_addr, m_sig);
+            c5_put16(lane_addr, 0, a0);  // K = 8 of these 16 columns are read
             c5_chain_arrive(bar_a);
         }
-        if (!any) break;
+        // ---- dHc2 .* relu', dHc1 .* relu'
+#pragma unroll 1
+        for (int k = 0; k < 2; ++k) {
+#pragma unroll 1
+            for (int s = 0; s < n_act; ++s) {
+                C5_SLOT_VARS
+                const uint64_t m = inb ? __ldg(masks + b * 3 + 2 - k) : 0ull;
+                tc5::mbar_wait_wd(bar_d, (uint32_t)k & 1u);
+                tc5::fence_after_sync();
+                c5_mask_to_a(lane_addr, m);
+                c5_chain_arrive(bar_a);
+            }
+        }
+        // ---- dIn = [dSH 16 | dO 16]: dO (+ the sigma gradient on column 0) goes on; SH backward to the direction
+#pragma unroll 1
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
+            float dir[3] = {0.0f, 0.0f, 0.0f}, go0 = 0.0f;
+            if (inb) {
+                go0 = __ldg(P.grad_sigma + b) * fminf(fmaxf(__ldg(P.sigma + b), e_lo), e_hi);  // trunc_exp backward (activation.py:13-17)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) dir[c] = __ldg(P.dirs + b * 3 + c);
+            }
+            tc5::mbar_wait_wd(bar_d, 0u);
+            tc5::fence_after_sync();
+            float dout[16], dsh[16];
+            c5_get16(lane_addr, 16, dout);
+            c5_get16(lane_addr, 0, dsh);
+            dout[0] += go0;  // its colour weight is zero, so the product left 0 there
+            c5_put16(lane_addr, 0, dout);
+            c5_chain_arrive(bar_a);
+            if (P.grad_d) {
+                float jx[16], jy[16], jz[16];
+                ngp_sh4_jac(dir[0], dir[1], dir[2], jx, jy, jz);
+                float g0 = 0.0f, g1 = 0.0f, g2 = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    g0 = fmaf(dsh[i], jx[i], g0);
+                    g1 = fmaf(dsh[i], jy[i], g1);
+                    g2 = fmaf(dsh[i], jz[i], g2);
+                }
+                if (inb) {
+                    P.grad_d[b * 3] = g0;
+                    P.grad_d[b * 3 + 1] = g1;
+                    P.grad_d[b * 3 + 2] = g2;
+                }
+            }
+        }
+        // ---- dHs .* relu'
+#pragma unroll 1
+        for (int s = 0; s < n_act; ++s) {
+            C5_SLOT_VARS
+            const uint64_t m = inb ? __ldg(masks + b * 3) : 0ull;
+            tc5::mbar_wait_wd(bar_d, 1u);
+            tc5::fence_after_sync();
+            c5_mask_to_a(lane_addr, m);
+            c5_chain_arrive(bar_a);
+        }
     }
 }
 
-__device__ __forceinline__ void c5_backward_mma(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem) {
-    uint32_t W[5][2];
-#pragma unroll
-    for (int p = 0; p < 2; ++p) {
-        W[0][p] = tc5::smem_u32(S.w.c2[p]);
-        W[1][p] = tc5::smem_u32(S.w.c1[p]);
-        W[2][p] = tc5::smem_u32(S.w.c0[p]);
-        W[3][p] = tc5::smem_u32(S.w.s1[p]);
-        W[4][p] = tc5::smem_u32(S.w.s0[p]);
-    }
-    const int NN[5] = {64, 64, 32, 64, 32}, KK[5] = {8, 64, 64, 16, 64};
+// MMA thread of slot s, backward.  a_ready completes 5 times per tile.
+__device__ __forceinline__ void c5_backward_mma(C5BwdSmem &S, const C5BwdParams &P, uint32_t tmem, int s) {
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
-    uint32_t pa[2] = {0u, 0u};
+    const uint32_t t = tmem + s * C5_SLOT_COLS;
+    const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready),
+                   bar_g = tc5::smem_u32(&S.bars[s].g_full);
+    const uint32_t c2h = tc5::smem_u32(S.w.c2[0]), c2l = tc5::smem_u32(S.w.c2[1]), c1h = tc5::smem_u32(S.w.c1[0]),
+                   c1l = tc5::smem_u32(S.w.c1[1]), c0h = tc5::smem_u32(S.w.c0[0]), c0l = tc5::smem_u32(S.w.c0[1]),
+                   s1h = tc5::smem_u32(S.w.s1[0]), s1l = tc5::smem_u32(S.w.s1[1]), s0h = tc5::smem_u32(S.w.s0[0]),
+                   s0l = tc5::smem_u32(S.w.s0[1]);
     for (int64_t it = 0;; ++it) {
-        bool any = false;
-#pragma unroll 1
-        for (int s = 0; s < 2; ++s) {
-            const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
-            if (tile >= ntiles) break;
-            any = true;
-            const uint32_t t = tmem + s * C5_SLOT_COLS;
-            const uint32_t bar_a = tc5::smem_u32(&S.bars[s].a_ready);
-#pragma unroll
-            for (int l = 0; l < 5; ++l) {
-                tc5::mbar_wait_wd(bar_a, pa[s]); pa[s] ^= 1u;
-                tc5::fence_after_sync();
-                c5_issue_layer(t + C5_D, t + C5_HHI, t + C5_HLO, W[l][0], W[l][1], NN[l], KK[l]);
-                tc5::mma_commit(tc5::smem_u32(l < 4 ? &S.bars[s].d_full : &S.bars[s].g_full));
-            }
-        }
-        if (!any) break;
+        const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
+        if (tile >= ntiles) break;
+        const uint32_t pa = (uint32_t)(5 * it);
+        tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 8>(t + C5_D, t + C5_HHI, t + C5_HLO, c2h, c2l);    // dHc2 = dRGB W_c2
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c1h, c1l);   // dHc1 = dHc2m W_c1
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<32, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c0h, c0l);   // dIn = dHc1m W_c0
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 16>(t + C5_D, t + C5_HHI, t + C5_HLO, s1h, s1l);   // dHs = dO W_s1
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 4u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<32, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, s0h, s0l);   // dFeat = dHsm W_s0
+        tc5::mma_commit(bar_g);
     }
 }
 
@@ -394,7 +468,7 @@ k_cfield5_backward(C5BwdParams P, const int32_t *__restrict__ offsets, float S_,
     } else if (warp < C5_MMA_WARP) {
         c5_backward_chain(S, P, tmem, warp, lane);
     } else {
-        if (lane == 0) c5_backward_mma(S, P, tmem);
+        if (lane == 0) c5_backward_mma(S, P, tmem, warp - C5_MMA_WARP);
         __syncwarp();
     }
     tc5::fence_before_sync();

@@ -13,7 +13,9 @@
 //     split to (hi, lo) and tcgen05.st it back as the next layer's A operand.  Activations never touch shared memory or
 //     registers of another thread; the LSU pipe carries only the table gathers.
 //   * two tile slots (2 x 256 TMEM columns) are in flight per SM so the gathers of one tile overlap the MLP chain of the
-//     other; roles hand tiles to each other through mbarriers (tcgen05.commit for MMA completion).
+//     other; each slot has its own MMA-issuing thread and the chain warps alternate between the slots layer by layer
+//     (slot 1's epilogue runs while slot 0's next layer is on the tensor core); roles hand tiles to each other through
+//     mbarriers (tcgen05.commit for MMA completion).
 #pragma once
 #include "fieldcore.cuh"
 #include "sh.cuh"
@@ -22,8 +24,8 @@
 #define C5_ROWS 128
 #define C5_GATHER_WARPS 8                       // two slots x four lane quadrants
 #define C5_CHAIN_WARP0 C5_GATHER_WARPS          // warps 8..11
-#define C5_MMA_WARP (C5_GATHER_WARPS + 4)       // warp 12
-#define C5_THREADS ((C5_MMA_WARP + 1) * 32)     // 416
+#define C5_MMA_WARP (C5_GATHER_WARPS + 4)       // warps 12, 13: one MMA-issuing thread per slot
+#define C5_THREADS ((C5_MMA_WARP + 2) * 32)     // 448
 #define C5_SLOT_COLS 256
 // TMEM column map of a slot
 #define C5_D 0        // 64: accumulator
@@ -59,15 +61,15 @@ __device__ __forceinline__ void c5_stage_tile(float *hi, float *lo, int N, int K
 
 // D[128 x N] = A[128 x K] * W[N x K]^T with A = (a_hi, a_lo) in TMEM and W = (w_hi, w_lo) tiles in shared memory;
 // 3xTF32, small terms first (the order fq_mma3 uses).  One thread.
-__device__ __forceinline__ void c5_issue_layer(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t w_hi, uint32_t w_lo,
-                                               int N, int K) {
+template <int N, int K>
+__device__ __forceinline__ void c5_issue_layer(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t w_hi, uint32_t w_lo) {
     const uint32_t idesc = tc5::idesc_tf32(C5_ROWS, N, tc5::MAJOR_K, tc5::MAJOR_K);
     const int ks_n = K >> 3;
-#pragma unroll 1
+#pragma unroll
     for (int ks = 0; ks < ks_n; ++ks) tc5::mma_tf32_ts(d, a_lo + ks * 8, tc5::tf32_kmajor_desc(w_hi, N, ks), idesc, ks > 0);
-#pragma unroll 1
+#pragma unroll
     for (int ks = 0; ks < ks_n; ++ks) tc5::mma_tf32_ts(d, a_hi + ks * 8, tc5::tf32_kmajor_desc(w_lo, N, ks), idesc, true);
-#pragma unroll 1
+#pragma unroll
     for (int ks = 0; ks < ks_n; ++ks) tc5::mma_tf32_ts(d, a_hi + ks * 8, tc5::tf32_kmajor_desc(w_hi, N, ks), idesc, true);
 }
 
@@ -234,92 +236,3 @@ __device__ __forceinline__ void c5_stage_forward_weights(C5FwdWeights &w, const 
     c5_stage_tile(w.c2[0], w.c2[1], 16, 64, [&](int n, int k) { return n < 3 ? Wc2[n * FQ_HID + k] : 0.0f; });
 }
 
-// the MMA thread's program for one forward tile of slot `s` (tmem = slot base, lane 0)
-struct C5FwdAddrs {
-    uint32_t s0[2], s1[2], c0[2], c1[2], c2[2];
-};
-__device__ __forceinline__ C5FwdAddrs c5_fwd_addrs(const C5FwdWeights &w) {
-    C5FwdAddrs a;
-#pragma unroll
-    for (int p = 0; p < 2; ++p) {
-        a.s0[p] = tc5::smem_u32(w.s0[p]);
-        a.s1[p] = tc5::smem_u32(w.s1[p]);
-        a.c0[p] = tc5::smem_u32(w.c0[p]);
-        a.c1[p] = tc5::smem_u32(w.c1[p]);
-        a.c2[p] = tc5::smem_u32(w.c2[p]);
-    }
-    return a;
-}
-
-// Issue the five layers of a forward tile.  `pa` = parity of the slot's a_ready barrier (updated).
-__device__ __forceinline__ void c5_mma_forward_tile(uint32_t tmem, const C5FwdAddrs &W, uint32_t bar_f_empty,
-                                                    uint32_t bar_d_full, uint32_t bar_a_ready, uint32_t &pa) {
-    // sigma L1: features -> 64
-    c5_issue_layer(tmem + C5_D, tmem + C5_FHI, tmem + C5_FLO, W.s0[0], W.s0[1], 64, 32);
-    tc5::mma_commit(bar_f_empty);
-    tc5::mma_commit(bar_d_full);
-    // sigma L2: 64 -> 16
-    tc5::mbar_wait_wd(bar_a_ready, pa); pa ^= 1u;
-    tc5::fence_after_sync();
-    c5_issue_layer(tmem + C5_D, tmem + C5_HHI, tmem + C5_HLO, W.s1[0], W.s1[1], 16, 64);
-    tc5::mma_commit(bar_d_full);
-    // colour L1: [SH | o] (32) -> 64
-    tc5::mbar_wait_wd(bar_a_ready, pa); pa ^= 1u;
-    tc5::fence_after_sync();
-    c5_issue_layer(tmem + C5_D, tmem + C5_HHI, tmem + C5_HLO, W.c0[0], W.c0[1], 64, 32);
-    tc5::mma_commit(bar_d_full);
-    // colour L2: 64 -> 64
-    tc5::mbar_wait_wd(bar_a_ready, pa); pa ^= 1u;
-    tc5::fence_after_sync();
-    c5_issue_layer(tmem + C5_D, tmem + C5_HHI, tmem + C5_HLO, W.c1[0], W.c1[1], 64, 64);
-    tc5::mma_commit(bar_d_full);
-    // colour L3: 64 -> 3 (16)
-    tc5::mbar_wait_wd(bar_a_ready, pa); pa ^= 1u;
-    tc5::fence_after_sync();
-    c5_issue_layer(tmem + C5_D, tmem + C5_HHI, tmem + C5_HLO, W.c2[0], W.c2[1], 16, 64);
-    tc5::mma_commit(bar_d_full);
-}
-
-// The chain warps' program for one forward tile: returns log sigma and the colour logits of the thread's row, and the ReLU
-// sign masks.  `pd` = parity of the slot's d_full barrier (updated).  The caller releases the slot (t_free) afterwards.
-template <bool MASK>
-__device__ __forceinline__ void c5_chain_forward_tile(uint32_t lane_addr, const float (&dir)[3], uint32_t bar_d_full,
-                                                      uint32_t bar_a_ready, uint32_t &pd, float &log_sigma,
-                                                      float (&logit)[3], uint64_t (&mask)[3]) {
-    // sigma hidden
-    tc5::mbar_wait_wd(bar_d_full, pd); pd ^= 1u;
-    tc5::fence_after_sync();
-    mask[0] = c5_relu_to_a<MASK>(lane_addr);
-    c5_chain_arrive(bar_a_ready);
-    // sigma-net output o (column 0 = log sigma, 1..15 = geo_feat) -> colour input [SH(d) | 0, geo_feat]
-    tc5::mbar_wait_wd(bar_d_full, pd); pd ^= 1u;
-    tc5::fence_after_sync();
-    {
-        float o[16];
-        c5_get16(lane_addr, 0, o);
-        log_sigma = o[0];
-        o[0] = 0.0f;
-        float sh[16];
-        ngp_sh4(dir[0], dir[1], dir[2], sh);
-        c5_put16(lane_addr, 0, sh);
-        c5_put16(lane_addr, 16, o);
-    }
-    c5_chain_arrive(bar_a_ready);
-    // colour hidden 1, 2
-    tc5::mbar_wait_wd(bar_d_full, pd); pd ^= 1u;
-    tc5::fence_after_sync();
-    mask[1] = c5_relu_to_a<MASK>(lane_addr);
-    c5_chain_arrive(bar_a_ready);
-    tc5::mbar_wait_wd(bar_d_full, pd); pd ^= 1u;
-    tc5::fence_after_sync();
-    mask[2] = c5_relu_to_a<MASK>(lane_addr);
-    c5_chain_arrive(bar_a_ready);
-    // colour logits
-    tc5::mbar_wait_wd(bar_d_full, pd); pd ^= 1u;
-    tc5::fence_after_sync();
-    {
-        float o[16];
-        c5_get16(lane_addr, 0, o);
-        logit[0] = o[0]; logit[1] = o[1]; logit[2] = o[2];
-    }
-}
