@@ -7,6 +7,9 @@
  * the reference's torch extensions; each declaration cites the reference interface it replaces
  * (paths relative to the reference root).  The reference launches on the legacy default stream without a
  * device guard; here the caller selects the device (cudaSetDevice / torch.cuda.device) and passes a stream.
+ * THE CURRENT DEVICE IS PART OF THE CONTRACT: kernels launch on it, so every buffer must live on it.  Each entry
+ * point verifies this for its first device pointer (cudaPointerGetAttributes) and fails with NGP_ERR_ARG instead of
+ * launching on the wrong GPU; host pointers are rejected the same way.  ngp_set_device_check(0) removes the check.
  *
  * Conventions: all pointers are device pointers unless named *_host; float = fp32; `table_dtype`
  * 0 = fp32, 1 = fp16.  Row-major, contiguous.  B/N/M are element counts.
@@ -34,6 +37,9 @@ typedef void *ngp_stream_t; /* cudaStream_t */
 const char *ngp_last_error(void);
 /* ABI version, bumped on signature changes */
 int ngp_abi_version(void);
+/* device-contract check described above: on != 0 enables (default; env NGP_B200_CHECK_DEVICE=0 disables at start),
+ * on < 0 only queries.  Returns the previous setting. */
+int ngp_set_device_check(int on);
 
 /* ---- hash-grid encoder: gridencoder/src/gridencoder.h:12-13, bindings.cpp:5-8 ------------------------- */
 
@@ -60,10 +66,11 @@ int ngp_grid_encode_backward_input(const void *grad, int grad_layout, const floa
 
 /* grid_encode_backward, table part (gridencoder.cu:227-314, 448-466): grad_embeddings [rows,C] fp32 is
  * OVERWRITTEN (no pre-zeroing needed) with a deterministic sorted segmented reduction (no float atomics).
+ * total_rows = embeddings.shape[0] (= offsets[L]; a host scalar, so nothing is read back from the device).
  * workspace: ngp_grid_backward_table_workspace_bytes(B,D,L) bytes of device scratch. */
 int64_t ngp_grid_backward_table_workspace_bytes(int64_t B, int D, int L);
 int ngp_grid_encode_backward_table(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
-                                   const int32_t *offsets, const int32_t *offsets_host, float *grad_embeddings,
+                                   const int32_t *offsets, int64_t total_rows, float *grad_embeddings,
                                    int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
                                    int align_corners, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
 
@@ -71,7 +78,7 @@ int ngp_grid_encode_backward_table(const void *grad, int grad_layout, int grad_d
  * bit-reproducible, no workspace, skips (point, level) pairs whose upstream gradient is exactly zero.  Opt-in
  * (gridencoder.table_grad.DETERMINISTIC = False); grad_embeddings is overwritten. */
 int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
-                                          const int32_t *offsets, const int32_t *offsets_host, float *grad_embeddings,
+                                          const int32_t *offsets, int64_t total_rows, float *grad_embeddings,
                                           int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
                                           int align_corners, ngp_stream_t stream);
 

@@ -25,12 +25,13 @@ _SIGNATURES = {
     "ngp_grid_encode_forward": ([P, P, I, P, P, I, I64, I, I, I, F, U32, I, P, U32, I, P, P], I),
     "ngp_grid_encode_backward_input": ([P, I, P, P, I, P, P, I64, I, I, I, F, U32, U32, I, P], I),
     "ngp_grid_backward_table_workspace_bytes": ([I64, I, I], I64),
-    "ngp_grid_encode_backward_table": ([P, I, I, P, P, P, P, I64, I, I, I, F, U32, U32, I, P, I64, P], I),
+    "ngp_grid_encode_backward_table": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P, I64, P], I),
     "ngp_linear_small": ([P, P, P, I64, I, I, I, P], I),
-    "ngp_grid_encode_backward_table_atomic": ([P, I, I, P, P, P, P, I64, I, I, I, F, U32, U32, I, P], I),
+    "ngp_grid_encode_backward_table_atomic": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P], I),
     "ngp_field_query_forward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, I64, P], I),
     "ngp_field_query_value_grad": ([P, F, P, P, F, U32, U32, I, P, P, P, P, F, F, P, P, P, I64, P], I),
     "ngp_set_field_impl": ([I], I),
+    "ngp_set_device_check": ([I], I),
     "ngp_field_color_forward": ([P, P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, P, I64, P], I),
     "ngp_field_color_backward": ([P, P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, P, P, P, P, P, I64, P], I),
     "ngp_near_far_from_aabb": ([P, P, P, I64, F, P, P, P], I),

@@ -61,6 +61,7 @@ k_adam_step(float *__restrict__ p, const float *__restrict__ g, float *__restric
 extern "C" int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float *ema, int64_t n,
                              float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
                              float ema_decay, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(param, "ngp_adam_step");
     if (n == 0) return NGP_OK;
     NGP_REQUIRE(param && grad && exp_avg && exp_avg_sq, NGP_ERR_ARG, "ngp_adam_step: null pointer");
     NGP_REQUIRE(n >= 0 && step >= 1, NGP_ERR_ARG, "ngp_adam_step: bad n / step (step counts from 1)");

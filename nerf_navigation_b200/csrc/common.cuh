@@ -28,6 +28,15 @@ void ngp_set_error(const char *fmt, ...);
         }                                                                               \
     } while (0)
 
+// The caller's CURRENT device is part of the contract (include/ngp_b200.h): every entry point checks that its first
+// device pointer lives on it (one cudaPointerGetAttributes, ~1 us; ngp_set_device_check(0) switches it off).
+int ngp_device_mismatch(const void *p, const char *fn);
+#define NGP_REQUIRE_DEVICE(p, fn)                      \
+    do {                                               \
+        const int rc__ = ngp_device_mismatch((p), (fn)); \
+        if (rc__) return rc__;                         \
+    } while (0)
+
 static inline int64_t ngp_div_up(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // ---------------------------------------------------------------------------------------------

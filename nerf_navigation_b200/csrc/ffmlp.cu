@@ -189,6 +189,7 @@ static int ff_sm_count() {
 extern "C" int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int input_dim, int output_dim,
                                  int hidden_dim, int num_layers, int activation, int output_activation,
                                  void *forward_buffer, void *outputs, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(inputs, "ngp_ffmlp_forward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && weights && outputs, NGP_ERR_ARG, "ngp_ffmlp_forward: null pointer");
     int rc = ff_check(B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, "ngp_ffmlp_forward");
@@ -441,6 +442,7 @@ extern "C" int ngp_ffmlp_backward(const void *grad, const void *inputs, const vo
                                   int activation, int output_activation, int calc_grad_inputs, void *backward_buffer,
                                   void *grad_inputs, void *grad_weights, void *workspace, int64_t workspace_bytes,
                                   ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad, "ngp_ffmlp_backward");
     NGP_REQUIRE(grad && inputs && weights && forward_buffer, NGP_ERR_ARG, "ngp_ffmlp_backward: null pointer");
     NGP_REQUIRE(!calc_grad_inputs || grad_inputs, NGP_ERR_ARG, "ngp_ffmlp_backward: calc_grad_inputs needs grad_inputs");
     int rc = ff_check(B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, "ngp_ffmlp_backward");

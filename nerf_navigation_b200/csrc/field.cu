@@ -302,6 +302,7 @@ extern "C" int ngp_field_query_forward(const float *x, float bound, const float 
                                        float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                        const float *W1, float *sigma, float *geo, uint64_t *relu_mask, int64_t B,
                                        ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(x, "ngp_field_query_forward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma, NGP_ERR_ARG, "ngp_field_query_forward: null pointer");
     NGP_REQUIRE(bound > 0.0f, NGP_ERR_ARG, "ngp_field_query_forward: bound must be > 0");
@@ -318,6 +319,7 @@ extern "C" int ngp_field_query_backward(const float *x, float bound, const float
                                         const float *W1, const float *sigma, const uint64_t *relu_mask,
                                         const float *grad_sigma, const float *grad_geo, float *grad_x, int64_t B,
                                         ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(x, "ngp_field_query_backward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma && relu_mask && grad_sigma && grad_x, NGP_ERR_ARG,
                 "ngp_field_query_backward: null pointer");

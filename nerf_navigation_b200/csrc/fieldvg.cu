@@ -307,6 +307,7 @@ extern "C" int ngp_field_query_value_grad(const float *x, float bound, const flo
                                           float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                           const float *W1, const float *coef_a, const float *coef_b, float a0, float b0,
                                           float *sigma, float *geo, float *grad_x, int64_t B, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(x, "ngp_field_query_value_grad");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma && grad_x, NGP_ERR_ARG,
                 "ngp_field_query_value_grad: null pointer");

@@ -6,6 +6,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 // ---------------------------------------------------------------- error state (one TU owns it)
@@ -17,7 +19,39 @@ void ngp_set_error(const char *fmt, ...) {
     va_end(ap);
 }
 extern "C" const char *ngp_last_error(void) { return g_err; }
-extern "C" int ngp_abi_version(void) { return 1; }
+extern "C" int ngp_abi_version(void) { return 2; }
+
+// device contract check (common.cuh): -1 = read NGP_B200_CHECK_DEVICE on first use (default on)
+static int g_device_check = -1;
+extern "C" int ngp_set_device_check(int on) {
+    const int prev = g_device_check < 0 ? 1 : g_device_check;
+    if (on >= 0) g_device_check = on ? 1 : 0;
+    return prev;
+}
+int ngp_device_mismatch(const void *p, const char *fn) {
+    if (g_device_check < 0) {
+        const char *e = getenv("NGP_B200_CHECK_DEVICE");
+        g_device_check = (e && e[0] == '0') ? 0 : 1;
+    }
+    if (!g_device_check || !p) return NGP_OK;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return NGP_OK;
+    }
+    if (a.type != cudaMemoryTypeDevice && a.type != cudaMemoryTypeManaged) {
+        ngp_set_error("%s: expected a device pointer (got host / unregistered memory)", fn);
+        return NGP_ERR_ARG;
+    }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (a.type == cudaMemoryTypeDevice && a.device != dev) {
+        ngp_set_error("%s: buffers live on device %d but the current device is %d (select the device before the call)", fn,
+                      a.device, dev);
+        return NGP_ERR_ARG;
+    }
+    return NGP_OK;
+}
 
 #define GRID_MAX_L 32
 #define GRID_THREADS 256
@@ -28,6 +62,7 @@ __global__ void k_level_scales(float *scales, int L, float S, uint32_t H) {
 }
 
 extern "C" int ngp_grid_level_scales(float *scales, int L, float S, uint32_t H, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(scales, "ngp_grid_level_scales");
     NGP_REQUIRE(scales && L > 0 && L <= GRID_MAX_L, NGP_ERR_ARG, "ngp_grid_level_scales: bad arguments");
     k_level_scales<<<1, GRID_MAX_L, 0, (cudaStream_t)stream>>>(scales, L, S, H);
     NGP_CHECK_LAUNCH("ngp_grid_level_scales");
@@ -253,6 +288,7 @@ extern "C" int ngp_grid_encode_forward(const float *inputs, const void *embeddin
                                        const int32_t *offsets, void *outputs, int out_layout, int64_t B, int D, int C,
                                        int L, float S, uint32_t H, int calc_grad_inputs, void *dy_dx, uint32_t gridtype,
                                        int align_corners, uint32_t *indices, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(inputs, "ngp_grid_encode_forward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && embeddings && offsets && outputs, NGP_ERR_ARG, "ngp_grid_encode_forward: null pointer");
     NGP_REQUIRE(L > 0 && L <= GRID_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_forward: L must be in [1,%d]", GRID_MAX_L);
@@ -303,6 +339,7 @@ extern "C" int ngp_grid_encode_backward_input(const void *grad, int grad_layout,
                                               const void *embeddings, int table_dtype, const int32_t *offsets,
                                               float *grad_inputs, int64_t B, int D, int C, int L, float S, uint32_t H,
                                               uint32_t gridtype, int align_corners, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad, "ngp_grid_encode_backward_input");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(grad && inputs && embeddings && offsets && grad_inputs, NGP_ERR_ARG,
                 "ngp_grid_encode_backward_input: null pointer");

@@ -99,6 +99,7 @@ k_linear_small(const float *__restrict__ X, const float *__restrict__ W, float *
 // W is always nn.Linear.weight [n_out, n_in], row-major.
 extern "C" int ngp_linear_small(const float *X, const float *W, float *Y, int64_t M, int n_out, int n_in, int transpose_w,
                                 ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(X, "ngp_linear_small");
     NGP_REQUIRE(n_out >= 1 && n_out <= LIN_MAX && n_in >= 1 && n_in <= LIN_MAX && M >= 0, NGP_ERR_UNSUPPORTED,
                 "ngp_linear_small: needs 1 <= n_out, n_in <= 64 (got %d, %d)", n_out, n_in);
     if (M == 0) return NGP_OK;

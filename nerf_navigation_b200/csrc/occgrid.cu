@@ -66,6 +66,7 @@ k_occ_update(float *__restrict__ grid, const float *__restrict__ sigma, int64_t 
 extern "C" int ngp_occ_grid_positions(int cascade, uint32_t G, float bound, float jitter, uint32_t seed, float *xyz,
                                       ngp_stream_t stream) {
     NGP_REQUIRE(xyz, NGP_ERR_ARG, "ngp_occ_grid_positions: null pointer");
+    NGP_REQUIRE_DEVICE(xyz, "ngp_occ_grid_positions");
     NGP_REQUIRE(G >= 2 && G <= 1024 && (G & (G - 1)) == 0 && cascade >= 0 && cascade < 8 && bound > 0.0f, NGP_ERR_ARG,
                 "ngp_occ_grid_positions: G must be a power of two in [2, 1024], cascade in [0, 8)");
     const uint32_t n = G * G * G;
@@ -79,6 +80,7 @@ extern "C" int64_t ngp_occ_grid_update_blocks(int64_t n) { return ngp_div_up(n, 
 
 extern "C" int ngp_occ_grid_update(float *grid, const float *sigma, int64_t n, float decay, float density_scale,
                                    float *block_sums, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grid, "ngp_occ_grid_update");
     if (n == 0) return NGP_OK;
     NGP_REQUIRE(grid && sigma && block_sums, NGP_ERR_ARG, "ngp_occ_grid_update: null pointer");
     k_occ_update<<<(unsigned)ngp_div_up(n, OCC_THREADS), OCC_THREADS, 0, (cudaStream_t)stream>>>(grid, sigma, n, decay,

@@ -47,6 +47,7 @@ k_probe_gather(const T *__restrict__ buf, uint32_t rows, int iters, int pattern,
 
 extern "C" int ngp_probe_gather(const void *buf, int64_t buf_bytes, int elem_bytes, int iters, int pattern,
                                 int blocks, uint32_t *sink, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(buf, "ngp_probe_gather");
     NGP_REQUIRE(buf && sink && buf_bytes > 0 && iters > 0 && blocks > 0, NGP_ERR_ARG, "ngp_probe_gather: bad argument");
     const uint32_t rows = (uint32_t)(buf_bytes / elem_bytes);
     cudaStream_t st = (cudaStream_t)stream;

@@ -26,6 +26,7 @@ k_near_far(const float *__restrict__ rays_o, const float *__restrict__ rays_d, c
 
 extern "C" int ngp_near_far_from_aabb(const float *rays_o, const float *rays_d, const float *aabb, int64_t N,
                                       float min_near, float *nears, float *fars, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_near_far_from_aabb");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && aabb && nears && fars, NGP_ERR_ARG, "ngp_near_far_from_aabb: null pointer");
     k_near_far<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(rays_o, rays_d, aabb, N,
@@ -49,6 +50,7 @@ __global__ void k_morton3D_invert(const int32_t *__restrict__ indices, int64_t N
     coords[n * 3 + 2] = (int32_t)ngp_morton_compact(v >> 2);
 }
 extern "C" int ngp_morton3D(const int32_t *coords, int64_t N, int32_t *indices, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(coords, "ngp_morton3D");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D: null pointer");
     k_morton3D<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(coords, N, indices);
@@ -56,6 +58,7 @@ extern "C" int ngp_morton3D(const int32_t *coords, int64_t N, int32_t *indices, 
     return NGP_OK;
 }
 extern "C" int ngp_morton3D_invert(const int32_t *indices, int64_t N, int32_t *coords, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(indices, "ngp_morton3D_invert");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(coords && indices, NGP_ERR_ARG, "ngp_morton3D_invert: null pointer");
     k_morton3D_invert<<<(unsigned)ngp_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(indices, N, coords);
@@ -82,6 +85,7 @@ __global__ void k_packbits(const float *__restrict__ grid, int64_t N, float thre
     bitfield[n] = (uint8_t)bits;
 }
 extern "C" int ngp_packbits(const float *grid, int64_t N, float thresh, uint8_t *bitfield, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grid, "ngp_packbits");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(grid && bitfield, NGP_ERR_ARG, "ngp_packbits: null pointer");
     NGP_REQUIRE(((uintptr_t)grid & 15) == 0, NGP_ERR_ARG, "ngp_packbits: grid must be 16-byte aligned");
@@ -361,6 +365,7 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
                                     const float *nears, const float *fars, float *xyzs, float *dirs, float *deltas,
                                     int32_t *rays, int32_t *counter, uint32_t perturb, void *workspace,
                                     int64_t workspace_bytes, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_march_rays_train");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && grid && nears && fars && rays && counter, NGP_ERR_ARG,
                 "ngp_march_rays_train: null pointer");
@@ -440,6 +445,7 @@ extern "C" int ngp_march_rays_train_backward(const float *grad_xyzs, const float
                                              const int32_t *rays, float bound, uint32_t max_steps, uint32_t perturb,
                                              int64_t N, int64_t M, float *grad_rays_o, float *grad_rays_d,
                                              ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad_xyzs, "ngp_march_rays_train_backward");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && nears && rays && grad_rays_o && grad_rays_d, NGP_ERR_ARG,
                 "ngp_march_rays_train_backward: null pointer");
@@ -515,6 +521,7 @@ k_composite_train_bwd(const float *__restrict__ grad_ws, const float *__restrict
 extern "C" int ngp_composite_rays_train_forward(const float *sigmas, const float *rgbs, const float *deltas,
                                                 const int32_t *rays, int64_t M, int64_t N, float *weights_sum,
                                                 float *depth, float *image, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(sigmas, "ngp_composite_rays_train_forward");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays && weights_sum && depth && image, NGP_ERR_ARG, "ngp_composite_rays_train_forward: null pointer");
     NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas), NGP_ERR_ARG, "ngp_composite_rays_train_forward: null samples");
@@ -529,6 +536,7 @@ extern "C" int ngp_composite_rays_train_backward(const float *grad_weights_sum, 
                                                  const int32_t *rays, const float *weights_sum, const float *image,
                                                  int64_t M, int64_t N, float *grad_sigmas, float *grad_rgbs,
                                                  ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad_weights_sum, "ngp_composite_rays_train_backward");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(grad_weights_sum && grad_image && rays && weights_sum && image, NGP_ERR_ARG,
                 "ngp_composite_rays_train_backward: null pointer");
@@ -607,6 +615,7 @@ extern "C" int ngp_march_rays(int64_t n_alive, uint32_t n_step, const int32_t *r
                               uint32_t C, uint32_t H, const uint8_t *grid, const float *nears, const float *fars,
                               float *xyzs, float *dirs, float *deltas, uint32_t perturb, ngp_stream_t stream) {
     if (n_alive == 0) return NGP_OK;
+    NGP_REQUIRE_DEVICE(rays_alive, "ngp_march_rays");
     (void)nears;
     NGP_REQUIRE(rays_alive && rays_t && rays_o && rays_d && grid && fars && xyzs && dirs && deltas, NGP_ERR_ARG,
                 "ngp_march_rays: null pointer");
@@ -622,6 +631,7 @@ extern "C" int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *ray
                                   const float *sigmas, const float *rgbs, const float *deltas, float *weights_sum,
                                   float *depth, float *image, ngp_stream_t stream) {
     if (n_alive == 0) return NGP_OK;
+    NGP_REQUIRE_DEVICE(rays_alive, "ngp_composite_rays");
     NGP_REQUIRE(rays_alive && rays_t && sigmas && rgbs && deltas && weights_sum && depth && image, NGP_ERR_ARG,
                 "ngp_composite_rays: null pointer");
     k_composite_rays<<<(unsigned)ngp_div_up(n_alive, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(

@@ -251,6 +251,7 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
                                      const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
                                      const float *bg_color, int bg_stride, float *image, float *depth,
                                      float *weights_sum, void *workspace, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_render_rays_infer");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && aabb && grid && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && image &&
                     depth && workspace,

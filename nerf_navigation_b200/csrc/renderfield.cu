@@ -302,6 +302,7 @@ extern "C" int ngp_field_color_forward(const float *xyzs, const float *dirs, flo
                                        int align_corners, const float *Ws0, const float *Ws1, const float *Wc0,
                                        const float *Wc1, const float *Wc2, float *sigma, float *rgb, void *masks,
                                        int64_t M, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(xyzs, "ngp_field_color_forward");
     if (M == 0) return NGP_OK;
     NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb, NGP_ERR_ARG,
                 "ngp_field_color_forward: null pointer");
@@ -326,6 +327,7 @@ extern "C" int ngp_field_color_backward(const float *xyzs, const float *dirs, fl
                                         const float *Wc1, const float *Wc2, const float *sigma, const float *rgb,
                                         const void *masks, const float *grad_sigma, const float *grad_rgb,
                                         float *grad_xyzs, float *grad_dirs, int64_t M, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(xyzs, "ngp_field_color_backward");
     if (M == 0) return NGP_OK;
     NGP_REQUIRE(xyzs && dirs && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && sigma && rgb && masks &&
                     grad_sigma && grad_rgb && grad_xyzs,

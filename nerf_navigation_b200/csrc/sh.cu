@@ -51,6 +51,7 @@ k_sh_backward(const float *__restrict__ grad, const float *__restrict__ inputs, 
 
 extern "C" int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_t B, int D, int degree,
                                      int calc_grad_inputs, float *dy_dx, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(inputs, "ngp_sh_encode_forward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(inputs && outputs, NGP_ERR_ARG, "ngp_sh_encode_forward: null pointer");
     NGP_REQUIRE(D == 3, NGP_ERR_UNSUPPORTED, "SHEncoder: input_dim must be 3 (got %d)", D);
@@ -63,6 +64,7 @@ extern "C" int ngp_sh_encode_forward(const float *inputs, float *outputs, int64_
 
 extern "C" int ngp_sh_encode_backward(const float *grad, const float *inputs, int64_t B, int D, int degree,
                                       float *grad_inputs, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad, "ngp_sh_encode_backward");
     if (B == 0) return NGP_OK;
     NGP_REQUIRE(grad && inputs && grad_inputs, NGP_ERR_ARG, "ngp_sh_encode_backward: null pointer");
     NGP_REQUIRE(D == 3, NGP_ERR_UNSUPPORTED, "SHEncoder: input_dim must be 3 (got %d)", D);

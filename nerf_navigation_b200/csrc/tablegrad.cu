@@ -313,18 +313,19 @@ static int tg_launch_atomic(int C, const void *grad, int grad_layout, const floa
 }
 
 extern "C" int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
-                                                     const int32_t *offsets, const int32_t *offsets_host,
+                                                     const int32_t *offsets, int64_t total_rows_,
                                                      float *grad_embeddings, int64_t B, int D, int C, int L, float S,
                                                      uint32_t H, uint32_t gridtype, int align_corners,
                                                      ngp_stream_t stream) {
-    NGP_REQUIRE(grad && inputs && offsets && offsets_host && grad_embeddings, NGP_ERR_ARG,
+    NGP_REQUIRE_DEVICE(grad, "ngp_grid_encode_backward_table_atomic");
+    NGP_REQUIRE(grad && inputs && offsets && total_rows_ > 0 && total_rows_ < (1ll << 32) && grad_embeddings, NGP_ERR_ARG,
                 "ngp_grid_encode_backward_table_atomic: null pointer");
     NGP_REQUIRE(L > 0 && L <= TG_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_backward_table_atomic: L out of range");
     NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
     NGP_REQUIRE(((uintptr_t)grad_embeddings & 15u) == 0, NGP_ERR_ARG,
                 "ngp_grid_encode_backward_table_atomic: grad_embeddings must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    cudaError_t e = cudaMemsetAsync(grad_embeddings, 0, (size_t)offsets_host[L] * C * sizeof(float), st);
+    cudaError_t e = cudaMemsetAsync(grad_embeddings, 0, (size_t)total_rows_ * C * sizeof(float), st);
     NGP_REQUIRE(e == cudaSuccess, NGP_ERR_CUDA, "ngp_grid_encode_backward_table_atomic: memset: %s", cudaGetErrorString(e));
     if (B == 0) return NGP_OK;
     int rc;
@@ -379,16 +380,17 @@ static int tg_launch_reduce(int C, const uint32_t *keys, const uint32_t *ids, in
 }
 
 extern "C" int ngp_grid_encode_backward_table(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
-                                              const int32_t *offsets, const int32_t *offsets_host,
+                                              const int32_t *offsets, int64_t total_rows_,
                                               float *grad_embeddings, int64_t B, int D, int C, int L, float S,
                                               uint32_t H, uint32_t gridtype, int align_corners, void *workspace,
                                               int64_t workspace_bytes, ngp_stream_t stream) {
-    NGP_REQUIRE(grad && inputs && offsets && offsets_host && grad_embeddings, NGP_ERR_ARG,
+    NGP_REQUIRE_DEVICE(grad, "ngp_grid_encode_backward_table");
+    NGP_REQUIRE(grad && inputs && offsets && total_rows_ > 0 && total_rows_ < (1ll << 32) && grad_embeddings, NGP_ERR_ARG,
                 "ngp_grid_encode_backward_table: null pointer");
     NGP_REQUIRE(L > 0 && L <= TG_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_backward_table: L out of range");
     NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
     cudaStream_t st = (cudaStream_t)stream;
-    const uint32_t total_rows = (uint32_t)offsets_host[L];
+    const uint32_t total_rows = (uint32_t)total_rows_;
     cudaError_t e = cudaMemsetAsync(grad_embeddings, 0, (size_t)total_rows * C * sizeof(float), st);
     NGP_REQUIRE(e == cudaSuccess, NGP_ERR_CUDA, "ngp_grid_encode_backward_table: memset: %s", cudaGetErrorString(e));
     if (B == 0) return NGP_OK;

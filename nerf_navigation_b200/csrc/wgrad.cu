@@ -124,6 +124,7 @@ extern "C" int64_t ngp_linear_wgrad_workspace_bytes(int64_t M) {
 
 extern "C" int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, void *workspace,
                                 int64_t workspace_bytes, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(dY, "ngp_linear_wgrad");
     NGP_REQUIRE(dY && X && dW, NGP_ERR_ARG, "ngp_linear_wgrad: null pointer");
     NGP_REQUIRE(n_out >= 1 && n_out <= WG_MAXN && n_in >= 1 && n_in <= WG_MAXN && M >= 0, NGP_ERR_UNSUPPORTED,
                 "ngp_linear_wgrad: needs 1 <= n_out, n_in <= 64 (got %d, %d)", n_out, n_in);

@@ -9,18 +9,6 @@ from .. import _lib
 
 DETERMINISTIC = True
 
-_offsets_host_cache = {}
-
-
-def _offsets_host(offsets):
-    key = (offsets.data_ptr(), offsets.shape[0])
-    hit = _offsets_host_cache.get(key)
-    if hit is None:
-        hit = offsets.cpu().contiguous()
-        _offsets_host_cache[key] = hit
-    return hit
-
-
 def grid_backward_table(grad, inputs, embeddings, offsets, dims, align_corners, grad_layout=1):
     """grad [B, L*C] (layout 1) or [L,B,C] (layout 0), same dtype as embeddings -> grad_embeddings like embeddings."""
     B, D, C, L, S, H, gridtype = dims
@@ -29,15 +17,14 @@ def grid_backward_table(grad, inputs, embeddings, offsets, dims, align_corners, 
         out = torch.empty(embeddings.shape, dtype=torch.float32, device=inputs.device)
         _lib.check(L_.ngp_grid_encode_backward_table_atomic(
             _lib.ptr(grad), grad_layout, 0 if grad.dtype == torch.float32 else 1, _lib.ptr(inputs), _lib.ptr(offsets),
-            _offsets_host(offsets).data_ptr(), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.stream()),
+            int(embeddings.shape[0]), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.stream()),
             "grid_encode_backward(table, atomic)")
         return out if embeddings.dtype == torch.float32 else out.to(embeddings.dtype)
     ws_bytes = L_.ngp_grid_backward_table_workspace_bytes(B, D, L)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=inputs.device)
     out = torch.empty(embeddings.shape, dtype=torch.float32, device=inputs.device)
-    oh = _offsets_host(offsets)
     _lib.check(L_.ngp_grid_encode_backward_table(
         _lib.ptr(grad), grad_layout, 0 if grad.dtype == torch.float32 else 1, _lib.ptr(inputs), _lib.ptr(offsets),
-        oh.data_ptr(), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.ptr(ws), ws_bytes,
+        int(embeddings.shape[0]), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.ptr(ws), ws_bytes,
         _lib.stream()), "grid_encode_backward(table)")
     return out if embeddings.dtype == torch.float32 else out.to(embeddings.dtype)

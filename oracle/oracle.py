@@ -143,6 +143,37 @@ def sh_encode(dirs, degree=4, calc_grad_inputs=False):
     return out, dy
 
 
+def field_color(x, d, bound, table, offsets, scales, Ws, Wc, grad_sigma=None, grad_rgb=None):
+    """NeRFNetwork.forward(x, d) (network.py:95-124) and its backward to (x, d): density() restated by orc_field_query,
+    SH(4) by orc_sh_encode (shencoder.cu:44-70 and its Jacobian :131-298), then the colour net 31-64-64-3 + sigmoid
+    (network.py:113-122) and the chain rule through it in float64 numpy.  Ws = [W0, W1] sigma net, Wc = [W0, W1, W2]
+    colour net, nn.Linear layouts.  Returns dict(sigma, rgb, z=[pre-activations of the two hidden colour layers],
+    grad_x, grad_d) (gradients only when grad_sigma / grad_rgb are given)."""
+    x = _f32(x); d = _f32(d)
+    B = x.shape[0]
+    want_grad = grad_sigma is not None or grad_rgb is not None
+    sigma, geo, _ = field_query(x, bound, table, offsets, scales, Ws[0], Ws[1], None)
+    sh, dsh = sh_encode(d, 4, calc_grad_inputs=want_grad)
+    h0 = np.concatenate([sh, geo], -1).astype(np.float64)
+    W0, W1, W2 = (np.asarray(w, np.float64) for w in Wc)
+    z1 = h0 @ W0.T; h1 = np.maximum(z1, 0)
+    z2 = h1 @ W1.T; h2 = np.maximum(z2, 0)
+    z3 = h2 @ W2.T
+    rgb = 1.0 / (1.0 + np.exp(-z3))
+    out = dict(sigma=sigma, rgb=rgb, z=[z1, z2])
+    if want_grad:
+        gs = np.zeros(B, np.float32) if grad_sigma is None else _f32(grad_sigma)
+        gr = np.zeros((B, 3), np.float64) if grad_rgb is None else np.asarray(grad_rgb, np.float64)
+        dz3 = gr * rgb * (1.0 - rgb)
+        dz2 = (dz3 @ W2) * (z2 > 0)
+        dz1 = (dz2 @ W1) * (z1 > 0)
+        dh0 = dz1 @ W0
+        out["grad_d"] = np.einsum("bk,bak->ba", dh0[:, :16], dsh.astype(np.float64))
+        _, _, gx = field_query(x, bound, table, offsets, scales, Ws[0], Ws[1], gs, dh0[:, 16:].astype(np.float32))
+        out["grad_x"] = gx
+    return out
+
+
 # ---------------------------------------------------------------- ray ops
 def near_far_from_aabb(rays_o, rays_d, aabb, min_near=0.2):
     """raymarching.cu:93-147."""

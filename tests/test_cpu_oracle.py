@@ -97,6 +97,42 @@ def test_field_query_vs_torch_autograd(oracle):
     assert rel_err(gx, ref_gx) < 1e-5
 
 
+def test_field_color_backward_vs_torch_autograd(oracle):
+    """oracle.field_color (the checker of the fused colour-field backward) == torch autograd through the same chain:
+    grid oracle features -> sigma net -> [SH | geo_feat] -> colour net -> sigmoid, d entering through a torch
+    transcription of the degree-4 SH polynomials' first rows checked against orc_sh_encode's own Jacobian."""
+    cfg = hashgrid_config(); W0, W1 = sigma_net_weights()
+    rng = np.random.default_rng(9)
+    Wc = [rng.uniform(-1, 1, s).astype(np.float32) / np.sqrt(s[1]) for s in ((64, 31), (64, 64), (3, 64))]
+    sc = oracle.level_scales(16, cfg["per_level_scale"], 16)
+    n = 200
+    x = rng.uniform(-1.9, 1.9, (n, 3)).astype(np.float32)
+    d = rng.standard_normal((n, 3)).astype(np.float32); d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    gs = rng.standard_normal(n).astype(np.float32); gr = rng.standard_normal((n, 3)).astype(np.float32)
+    got = oracle.field_color(x, d, 2.0, cfg["table"], cfg["offsets"], sc, [W0, W1], Wc, gs, gr)
+    out, dy, _ = oracle.grid_encode_forward((x + 2.0) / 4.0, cfg["table"], cfg["offsets"], sc, True)
+    sh, dsh = oracle.sh_encode(d, 4, True)
+    feat = torch.from_numpy(np.ascontiguousarray(out.transpose(1, 0, 2).reshape(n, 32))).double().requires_grad_()
+    sht = torch.from_numpy(sh).double().requires_grad_()
+    t = lambda a: torch.from_numpy(a).double()
+    o = torch.relu(feat @ t(W0).T) @ t(W1).T
+    sig = torch.exp(o[:, 0])
+    h = torch.cat([sht, o[:, 1:]], -1)
+    h = torch.relu(h @ t(Wc[0]).T); h = torch.relu(h @ t(Wc[1]).T)
+    rgb = torch.sigmoid(h @ t(Wc[2]).T)
+    ((sig * t(gs)).sum() + (rgb * t(gr)).sum()).backward()
+    ref_gx = np.einsum("blc,bldc->bd", feat.grad.numpy().reshape(n, 16, 2), dy.astype(np.float64)) / 4.0
+    ref_gd = np.einsum("bk,bak->ba", sht.grad.numpy(), dsh.astype(np.float64))
+    assert rel_err(got["sigma"], sig.detach().numpy()) < 1e-5 and rel_err(got["rgb"], rgb.detach().numpy()) < 1e-6
+    assert rel_err(got["grad_x"], ref_gx) < 1e-5 and rel_err(got["grad_d"], ref_gd) < 1e-6
+    # the SH Jacobian itself: central differences of orc_sh_encode in float64-accurate steps
+    eps = 1e-3
+    for a in range(3):
+        dp, dm = d.copy(), d.copy(); dp[:, a] += eps; dm[:, a] -= eps
+        fd = (oracle.sh_encode(dp, 4)[0].astype(np.float64) - oracle.sh_encode(dm, 4)[0]) / (2 * eps)
+        assert np.abs(fd - dsh[:, a]).max() < 2e-3
+
+
 def test_morton_packbits_pcg_known_answers(oracle):
     assert oracle.morton3D(np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [3, 3, 3], [1023, 1023, 1023]], np.int32)).tolist() \
         == [1, 2, 4, 63, (1 << 30) - 1]

@@ -3,7 +3,7 @@ import numpy as np
 import pytest
 import torch
 
-from util import hashgrid_config, sigma_net_weights, rel_err
+from util import hashgrid_config, sigma_net_weights, rel_err, rel_err_cols
 
 pytestmark = pytest.mark.gpu
 
@@ -45,6 +45,9 @@ def test_field_query_vs_oracle(ngp, oracle, B, with_geo):
     assert rel_err(sigma, rs) < 1e-5
     assert rel_err(geo, rg) < 1e-5
     assert rel_err(gx, rgx) < 1e-5
+    if B > 10:
+        # every geo_feat channel / gradient axis against its OWN scale (a small channel cannot hide behind a large one)
+        assert rel_err_cols(geo, rg) < 1e-5 and rel_err_cols(gx, rgx) < 1e-5
     if B > 10:
         assert sigma[2] == 1.0 and np.all(gx[2] == 0.0)
 

@@ -208,6 +208,45 @@ def test_fused_forward_xd_vs_oracle(model, oracle, ngp):
     assert rel_err(rgb.cpu().numpy(), ref_rgb) < 1e-5
 
 
+@pytest.mark.parametrize("impl", ["tc5", "mma"])
+def test_fused_backward_xd_vs_oracle(model, oracle, ngp, impl):
+    """k_cfield5_backward / k_render_field_backward (dL/dx, dL/dd of the fused sample kernel) directly against the CPU
+    oracle chain: orc_field_query backward + orc_sh_encode Jacobian + the colour-MLP chain rule in float64
+    (oracle.field_color).  1e-5 on every sample except ones the oracle itself names as a ReLU tie: a hidden
+    pre-activation within 1e-5 of zero relative to the layer's scale, whose sign two fp32 evaluation orders may disagree on."""
+    model.eval()
+    n = 6000
+    x, d = _sample_points(n, 23)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    w_s = torch.randn(n, device="cuda", generator=g)
+    w_c = torch.randn(n, 3, device="cuda", generator=g)
+    prev = ngp.lib().ngp_set_field_impl(1 if impl == "tc5" else 0)
+    try:
+        xa, da = x.clone().requires_grad_(), d.clone().requires_grad_()
+        sigma, rgb = model(xa, da)
+        torch.autograd.backward([sigma, rgb], [w_s, w_c])
+        torch.cuda.synchronize()
+    finally:
+        ngp.lib().ngp_set_field_impl(prev)
+    enc = model.encoder
+    s = torch.empty(16, device="cuda")
+    ngp.check(ngp.lib().ngp_grid_level_scales(s.data_ptr(), 16, float(np.log2(enc.per_level_scale)), 16, ngp.stream()))
+    Ws = [l.weight.detach().cpu().numpy() for l in model.sigma_net]
+    Wc = [l.weight.detach().cpu().numpy() for l in model.color_net]
+    ref = oracle.field_color(x.cpu().numpy(), d.cpu().numpy(), 2.0, enc.embeddings.detach().cpu().numpy(),
+                             enc.offsets.cpu().numpy(), s.cpu().numpy(), Ws, Wc, w_s.cpu().numpy(), w_c.cpu().numpy())
+    assert rel_err(sigma.detach().cpu().numpy(), ref["sigma"]) < 1e-5
+    assert rel_err(rgb.detach().cpu().numpy(), ref["rgb"]) < 1e-5
+    tie = np.zeros(n, bool)
+    for z in ref["z"]:
+        tie |= (np.abs(z) < 1e-5 * np.abs(z).max()).any(-1)
+    for ours, want in ((xa.grad, ref["grad_x"]), (da.grad, ref["grad_d"])):
+        err = np.abs(ours.cpu().numpy().astype(np.float64) - want).max(-1) / np.abs(want).max()
+        bad = err > 1e-5
+        assert not (bad & ~tie).any(), (impl, float(err[~tie].max()), int(bad.sum()))
+    assert tie.sum() < n // 100
+
+
 def test_cfg1_frequency_network_vs_reference_golden():
     """BASELINE config 1 through the host mirror ON THE GPU (NeRFNetwork(frequency), cuda_ray=False, render staged ->
     run -> density / masked color) against tests/golden/cfg1.npz, which scripts/make_golden.py produced by importing the

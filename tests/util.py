@@ -33,6 +33,28 @@ def rel_err(a, b, floor=1e-30):
     return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), floor))
 
 
+def rel_err_cols(a, b, axis=-1, floor=1e-30):
+    """Worst per-column relative error: max over columns c of max|a[..., c] - b[..., c]| / max|b[..., c]|.  The global
+    rel_err lets a channel 100x smaller than the largest one hide a wrong value; this normalises every column (geo_feat
+    channel, dy_dx component, table-gradient level ...) by its own scale."""
+    a = np.moveaxis(np.asarray(a, np.float64), axis, -1).reshape(-1, np.shape(a)[axis])
+    b = np.moveaxis(np.asarray(b, np.float64), axis, -1).reshape(-1, np.shape(b)[axis])
+    num = np.max(np.abs(a - b), axis=0)
+    den = np.maximum(np.max(np.abs(b), axis=0), floor)
+    return float(np.max(num / den))
+
+
+def level_rel_err(a, b, offsets, floor=1e-30):
+    """Worst per-level relative error of two [rows, C] tables (levels delimited by `offsets`)."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    worst = 0.0
+    for l in range(len(offsets) - 1):
+        lo, hi = int(offsets[l]), int(offsets[l + 1])
+        den = max(float(np.max(np.abs(b[lo:hi]))), floor)
+        worst = max(worst, float(np.max(np.abs(a[lo:hi] - b[lo:hi]))) / den)
+    return worst
+
+
 def load_ref(name):
     """Reference CUDA extension built by oracle/build_ref.py, or None."""
     from oracle import build_ref
