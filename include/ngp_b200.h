@@ -189,16 +189,18 @@ int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, fl
  * compact alive rays } -> image + (1 - weights_sum) * bg, clamp(depth - near, 0) / (far - near).  Per-sample data never
  * reach HBM.  rays_o/rays_d [N,3]; aabb [6]; grid = density_bitfield u8 [C*Hgrid^3/8]; field arguments as in
  * ngp_field_color_forward; bg_color NULL (= 1), 3 floats (bg_stride 0) or [N,3] (bg_stride 3).  Outputs image [N,3],
- * depth [N], weights_sum [N] (may be NULL).  workspace: ngp_render_rays_infer_workspace_bytes() bytes, 8-byte aligned;
- * after the call its second u64 holds the number of samples evaluated.  dt_gamma/max_steps as in march_rays; a ray takes
- * at most max_steps samples; no perturbation. */
+ * depth [N], weights_sum [N] (may be NULL), counts i32 [N] (may be NULL): the number of samples composited for each ray —
+ * the integer output of the path (= what march_rays / composite_rays process for the ray before it dies).
+ * workspace: ngp_render_rays_infer_workspace_bytes() bytes, 8-byte aligned; after the call its second u64 holds the number
+ * of samples evaluated.  dt_gamma/max_steps as in march_rays; a ray takes at most max_steps samples; no perturbation.
+ * Implementation: the warp-specialised tcgen05 kernel (csrc/render5.cu) unless ngp_set_field_impl(0) selected mma.sync. */
 int64_t ngp_render_rays_infer_workspace_bytes(void);
 int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
                           const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
                           const float *embeddings, const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
                           int align_corners, const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1,
                           const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
-                          float *depth, float *weights_sum, void *workspace, ngp_stream_t stream);
+                          float *depth, float *weights_sum, int32_t *counts, void *workspace, ngp_stream_t stream);
 
 /* ---- training-step tail: torch.optim.Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:126) + EMA (nerf/utils.py:814) - */
 

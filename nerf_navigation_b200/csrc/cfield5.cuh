@@ -112,7 +112,7 @@ __device__ __noinline__ uint64_t c5_relu_to_a(uint32_t lane_addr) {
     return m;
 }
 // accumulator (64 columns) .* mask -> A operand
-__device__ __noinline__ void c5_mask_to_a(uint32_t lane_addr, uint64_t m) {
+static __device__ __noinline__ void c5_mask_to_a(uint32_t lane_addr, uint64_t m) {
 #pragma unroll 1
     for (int c = 0; c < 4; ++c) {
         float v[16];

@@ -34,6 +34,7 @@ struct MarchCfg {
     float bound, dt_gamma, dt_min, dt_max, rH, Hf;
     uint32_t C, H, H3;
     int h_pow2;
+    int lvl_dt;   // dt_gamma == 0: the (then constant) mip level of dt = dt_min, raymarching.cu:51-56; -1 otherwise
     const uint8_t *grid;
 };
 
@@ -50,6 +51,12 @@ __host__ __device__ __forceinline__ MarchCfg ngp_march_cfg(const uint8_t *grid, 
     c.H = H;
     c.H3 = H * H * H;
     c.h_pow2 = (H & (H - 1)) == 0;
+    c.lvl_dt = -1;
+    if (dt_gamma == 0.0f) {   // clamp(t * 0, dt_min, dt_max) = dt_min for every finite t
+        int e;
+        frexpf(c.dt_min * c.Hf * 0.5f, &e);
+        c.lvl_dt = e < 0 ? 0 : (e > (int)C - 1 ? (int)C - 1 : e);
+    }
     c.grid = grid;
     return c;
 }
@@ -96,6 +103,77 @@ __device__ __forceinline__ bool ngp_march_probe(const MarchRay &r, const MarchCf
     const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;
     tt = t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
     return false;
+}
+
+// The probe in two halves, for marchers that keep several rays' occupancy loads in flight per thread (render5.cu): the
+// bit address of the cell that holds the sample at t0, then — only for an empty cell, after the load came back — the voxel
+// exit.  Every expression is the one ngp_march_probe evaluates (the position is recomputed from (o, d, t0), the cell
+// coordinates are decoded from the Morton index), so both forms give the same bits.
+__device__ __forceinline__ uint32_t ngp_march_cell(const MarchRay &r, const MarchCfg &c, float t0, float &dt) {
+    const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
+    const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
+    const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
+    dt = ngp_clampf(t0 * c.dt_gamma, c.dt_min, c.dt_max);
+    const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+    const int level = max(ngp_mip_level(mx, c.C), ngp_mip_level(dt * c.Hf * 0.5f, c.C));
+    const float mip_rbound = 1.0f / fminf((float)(1 << level), c.bound);
+    const int nx = ngp_cell_coord(x, mip_rbound, c);
+    const int ny = ngp_cell_coord(y, mip_rbound, c);
+    const int nz = ngp_cell_coord(z, mip_rbound, c);
+    return (uint32_t)level * c.H3 + ngp_morton3D((uint32_t)nx, (uint32_t)ny, (uint32_t)nz);
+}
+// frexpf exponent of a finite v >= 0 from its bit pattern (zero / subnormal give a negative value, clamped to 0 like the
+// negative exponents frexpf returns for them)
+__device__ __forceinline__ int ngp_mip_level_bits(float v, uint32_t C) {
+    const int e = (int)((__float_as_uint(v) >> 23) & 0xffu) - 126;
+    return min((int)C - 1, max(0, e));
+}
+// The same cell address with the level returned separately, the level of the position taken from the exponent bits and —
+// when dt_gamma == 0 — dt and its level taken from the configuration: identical values, fewer instructions (render5.cu).
+__device__ __forceinline__ uint32_t ngp_march_cell_fast(const MarchRay &r, const MarchCfg &c, float t0, float &dt, int &level) {
+    const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
+    const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
+    const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
+    int lvl_dt = c.lvl_dt;
+    if (lvl_dt < 0) {
+        dt = ngp_clampf(t0 * c.dt_gamma, c.dt_min, c.dt_max);
+        lvl_dt = ngp_mip_level(dt * c.Hf * 0.5f, c.C);
+    } else {
+        dt = c.dt_min;
+    }
+    const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
+    level = max(ngp_mip_level_bits(mx, c.C), lvl_dt);
+    const float mip_rbound = 1.0f / fminf((float)(1 << level), c.bound);
+    const int nx = ngp_cell_coord(x, mip_rbound, c);
+    const int ny = ngp_cell_coord(y, mip_rbound, c);
+    const int nz = ngp_cell_coord(z, mip_rbound, c);
+    return (uint32_t)level * c.H3 + ngp_morton3D((uint32_t)nx, (uint32_t)ny, (uint32_t)nz);
+}
+// r.rdx/rdy/rdz must be set
+__device__ __forceinline__ float ngp_march_exit_fast(const MarchRay &r, const MarchCfg &c, float t0, uint32_t index, int level) {
+    const uint32_t m = index - (uint32_t)level * c.H3;
+    const int nx = (int)ngp_morton_compact(m), ny = (int)ngp_morton_compact(m >> 1), nz = (int)ngp_morton_compact(m >> 2);
+    const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
+    const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
+    const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
+    const float mip_bound = fminf((float)(1 << level), c.bound);
+    const float tx = fmaf(fmaf(((float)nx + 0.5f + 0.5f * copysignf(1.0f, r.dx)) * c.rH, 2.0f, -1.0f), mip_bound, -x) * r.rdx;
+    const float ty = fmaf(fmaf(((float)ny + 0.5f + 0.5f * copysignf(1.0f, r.dy)) * c.rH, 2.0f, -1.0f), mip_bound, -y) * r.rdy;
+    const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;
+    return t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
+}
+// r.rdx/rdy/rdz must be set
+__device__ __forceinline__ float ngp_march_exit(const MarchRay &r, const MarchCfg &c, float t0, uint32_t index) {
+    const uint32_t level = index / c.H3, m = index - level * c.H3;
+    const int nx = (int)ngp_morton_compact(m), ny = (int)ngp_morton_compact(m >> 1), nz = (int)ngp_morton_compact(m >> 2);
+    const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
+    const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
+    const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
+    const float mip_bound = fminf((float)(1 << level), c.bound);
+    const float tx = fmaf(fmaf(((float)nx + 0.5f + 0.5f * copysignf(1.0f, r.dx)) * c.rH, 2.0f, -1.0f), mip_bound, -x) * r.rdx;
+    const float ty = fmaf(fmaf(((float)ny + 0.5f + 0.5f * copysignf(1.0f, r.dy)) * c.rH, 2.0f, -1.0f), mip_bound, -y) * r.rdy;
+    const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;
+    return t0 + fmaxf(0.0f, fminf(tx, fminf(ty, tz)));
 }
 
 // One step of the parameter sequence of a ray: t_{k+1} = t_k + clamp(t_k dt_gamma, dt_min, dt_max).  Both branches of the

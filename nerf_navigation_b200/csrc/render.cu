@@ -52,12 +52,15 @@ struct RenderRaysParams {
     const float *table;
     int align_corners;
     float *image, *depth, *weights_sum;
+    int32_t *counts;               // optional: samples composited per ray
     unsigned long long *counter;
     unsigned long long *nsamples;  // optional statistics: total samples evaluated
 };
 
 // write the finished ray of `slot` (renderer.py:371-374: image + (1 - ws) * bg; clamp(depth - near, 0) / (far - near))
-__device__ __forceinline__ void ri_finish(const RenderRaysSmem &S, const RenderRaysParams &P, int slot, int64_t id) {
+__device__ __forceinline__ void ri_finish(const RenderRaysSmem &S, const RenderRaysParams &P, int slot, int64_t id,
+                                          uint32_t ncomp) {
+    if (P.counts) P.counts[id] = (int32_t)ncomp;
     const float ws = S.ws[slot], om = 1.0f - ws;
     const float *bg = P.bg ? P.bg + (int64_t)P.bg_stride * id : nullptr;
     const float b0 = bg ? __ldg(bg) : 1.0f, b1 = bg ? __ldg(bg + 1) : 1.0f, b2 = bg ? __ldg(bg + 2) : 1.0f;
@@ -76,6 +79,7 @@ __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams
     int64_t id = -1;                          // -1: slot wants a ray; -2: no rays left
     int cnt = 0, head = 0;                    // FIFO fill / read position
     uint32_t marched = 0;                     // samples queued so far for this ray (<= max_steps)
+    uint32_t ncomp = 0;                       // samples composited so far for this ray
     bool mend = false;                        // the march of this ray is over (t >= far or sample cap)
     unsigned rot = 0;
     unsigned long long evaluated = 0;
@@ -108,7 +112,7 @@ __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams
                         S.dx[slot] = d[0]; S.dy[slot] = d[1]; S.dz[slot] = d[2];
                         S.t[slot] = near; S.near[slot] = near; S.far[slot] = far;
                         S.ws[slot] = 0.0f; S.depth[slot] = 0.0f; S.r[slot] = 0.0f; S.g[slot] = 0.0f; S.b[slot] = 0.0f;
-                        cnt = 0; head = 0; marched = 0; mend = false;
+                        cnt = 0; head = 0; marched = 0; ncomp = 0; mend = false;
                     } else {
                         id = -2;
                     }
@@ -140,7 +144,7 @@ __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams
             }
             // ---- A3: rays whose march is over and whose queue is drained are done
             if (id >= 0 && mend && cnt == 0) {
-                ri_finish(S, P, slot, id);
+                ri_finish(S, P, slot, id, ncomp);
                 id = -1;
             }
 
@@ -214,8 +218,9 @@ __device__ __forceinline__ void ri_run(RenderRaysSmem &S, const RenderRaysParams
             head = (head + 1) % RI_FIFO;
             --cnt;
             ++evaluated;
+            ++ncomp;
             if ((double)T < 1e-4) {   // :880 (the sample that saw T < 1e-4 is still accumulated); queued samples are dropped
-                ri_finish(S, P, slot, id);
+                ri_finish(S, P, slot, id, ncomp);
                 id = -1;
                 cnt = 0;
             }
@@ -244,13 +249,23 @@ k_render_rays_infer(RenderRaysParams P, MarchCfg cfg, const int32_t *__restrict_
 
 extern "C" int64_t ngp_render_rays_infer_workspace_bytes(void) { return 16; }
 
+// default implementation: the warp-specialised tcgen05 kernel of render5.cu; NGP_B200_FIELD_IMPL=mma / ngp_set_field_impl(0)
+// selects the mma.sync kernel above (kept as the independent cross-check)
+int ngp_field_impl_tc5();
+int r5_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                         const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
+                         const float *embeddings, const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
+                         int align_corners, const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1,
+                         const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
+                         float *depth, float *weights_sum, int32_t *counts, void *workspace, cudaStream_t stream);
+
 extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
                                      const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
                                      uint32_t Hgrid, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
                                      uint32_t gridtype, int align_corners, const float *Ws0, const float *Ws1,
                                      const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
                                      const float *bg_color, int bg_stride, float *image, float *depth,
-                                     float *weights_sum, void *workspace, ngp_stream_t stream) {
+                                     float *weights_sum, int32_t *counts, void *workspace, ngp_stream_t stream) {
     NGP_REQUIRE_DEVICE(rays_o, "ngp_render_rays_infer");
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays_o && rays_d && aabb && grid && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && image &&
@@ -261,6 +276,14 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
     NGP_REQUIRE(bg_stride == 0 || bg_stride == 3, NGP_ERR_ARG, "ngp_render_rays_infer: bg_stride must be 0 or 3");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0 && ((uintptr_t)workspace & 7u) == 0, NGP_ERR_ARG,
                 "ngp_render_rays_infer: embeddings must be 16-byte aligned, workspace 8-byte aligned");
+    if (cudaMemsetAsync(workspace, 0, 16, (cudaStream_t)stream) != cudaSuccess) {
+        ngp_set_error("ngp_render_rays_infer: workspace memset failed");
+        return NGP_ERR_CUDA;
+    }
+    if (ngp_field_impl_tc5())
+        return r5_render_rays_infer(rays_o, rays_d, N, aabb, min_near, grid, bound, dt_gamma, max_steps, C, Hgrid, embeddings,
+                                    offsets, S, H, gridtype, align_corners, Ws0, Ws1, Wc0, Wc1, Wc2, density_scale, bg_color,
+                                    bg_stride, image, depth, weights_sum, counts, workspace, (cudaStream_t)stream);
     const int smem = (int)sizeof(RenderRaysSmem);
     if (cudaFuncSetAttribute(k_render_rays_infer, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         ngp_set_error("ngp_render_rays_infer: cannot reserve %d B of shared memory", smem);
@@ -269,15 +292,11 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
     int dev = 0, sms = NGP_SM_COUNT;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (cudaMemsetAsync(workspace, 0, 16, (cudaStream_t)stream) != cudaSuccess) {
-        ngp_set_error("ngp_render_rays_infer: workspace memset failed");
-        return NGP_ERR_CUDA;
-    }
     RenderRaysParams P;
     P.rays_o = rays_o; P.rays_d = rays_d; P.aabb = aabb; P.bg = bg_color; P.N = N; P.bg_stride = bg_stride;
     P.min_near = min_near; P.density_scale = density_scale; P.bound = bound; P.max_steps = max_steps;
     P.table = embeddings; P.align_corners = align_corners;
-    P.image = image; P.depth = depth; P.weights_sum = weights_sum;
+    P.image = image; P.depth = depth; P.weights_sum = weights_sum; P.counts = counts;
     P.counter = (unsigned long long *)workspace;
     P.nsamples = (unsigned long long *)workspace + 1;
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);

@@ -1,0 +1,640 @@
+// render5.cu — fused inference renderer on the Blackwell tensor-core path: the whole eval branch of
+// NeRFRenderer.run_cuda (nerf/renderer.py:325-374: near/far -> loop { march_rays (raymarching.cu:706-814) ->
+// self(xyzs, dirs) (network.py:95-124) -> composite_rays (:828-913) -> compaction } -> bg / depth post) as ONE persistent,
+// warp-specialised kernel.  Same tcgen05 field core as cfield5.cu (128-sample tiles, A operands and accumulators in TMEM,
+// 3xTF32), fed by marcher warps instead of a sample array:
+//
+//   marcher warps (4)  own R5_NR ray slots in shared memory (6 per lane): they fetch rays (one warp-aggregated atomic per
+//                      refill), compute near/far, march each ray into a small per-slot FIFO of (t, dt) samples (one
+//                      voxel step per slot per pass, three slots' occupancy loads in flight per lane), build the row list
+//                      of the next tile from the FIFO heads of rays that have no sample in flight (ballot compaction, 32
+//                      rows per warp), and write finished pixels;
+//   gather warps (8)   thread = tile row: hash-grid encode of the row's sample -> features straight into TMEM;
+//   MMA threads (2)    the five layers of a tile as tcgen05.mma kind::tf32 (one thread per TMEM slot);
+//   chain warps (4)    the epilogues (ReLU / SH / split to hi, lo) and, after the last layer, the compositing step of the
+//                      row's ray (raymarching.cu:860-893) on the ray's accumulators in shared memory.
+//
+// A ray has at most ONE sample in flight, so compositing is in ray order with exact early termination (no speculative
+// samples); tiles stay full because there are more ray slots (768) than rows in flight (4 tile buffers x 128).  Roles hand
+// tiles over through mbarriers; the end of the work is a pair of zero-row tiles.  Per-sample positions, sigma and rgb
+// never reach HBM: 24 B in and 20 B (+4 B count) out per RAY.  Differences from the reference loop are those of render.cu
+// (documented there): t is the marcher's own abscissa, at most max_steps samples per ray, no perturb.
+#include <float.h>
+
+#include "cfield5.cuh"
+#include "march.cuh"
+
+#define R5_MARCH_WARP0 (C5_MMA_WARP + 2)                       // warps 14 .. 17
+#define R5_MARCH_WARPS 4
+#define R5_THREADS ((R5_MARCH_WARP0 + R5_MARCH_WARPS) * 32)    // 576 (<= 112 registers per thread)
+#ifndef R5_PER_LANE
+#define R5_PER_LANE 6                                          // ray slots per marcher lane
+#endif
+#define R5_PER_WARP (32 * R5_PER_LANE)
+#define R5_NR (R5_MARCH_WARPS * R5_PER_WARP)                   // 768 ray slots per CTA
+#define R5_PART (C5_ROWS / R5_MARCH_WARPS)                     // tile rows built by one marcher warp (32)
+#define R5_FIFO 4                                              // queued samples per ray slot
+#define R5_TBUF 4                                              // tile row buffers (tile n: buffer n & 3, TMEM slot n & 1)
+#ifndef R5_ILP
+#define R5_ILP 3                                               // ray slots a marcher lane steps concurrently
+#endif
+#define R5_INVALID 0xffffffffu
+// ray-slot status (written by the marcher when idle, by the chain thread while the sample is in flight)
+#define R5_IDLE 0u
+#define R5_BUSY 1u
+#define R5_DEAD 2u   // composited with T < 1e-4: the ray is over
+
+// marcher-private state word: samples queued so far (20 bits) | FIFO fill (3) | FIFO head (2) | march ended (1)
+#define R5_MS_MARCHED(m) ((m) & 0xfffffu)
+#define R5_MS_CNT(m) (((m) >> 20) & 7u)
+#define R5_MS_HEAD(m) (((m) >> 23) & 3u)
+#define R5_MS_END(m) (((m) >> 25) & 1u)
+#define R5_MS_PACK(marched, cnt, head, end) ((marched) | ((cnt) << 20) | ((head) << 23) | ((end) << 25))
+
+struct R5Tile {
+    float x[C5_ROWS], y[C5_ROWS], z[C5_ROWS];        // sample position (the marcher's clamped o + t d)
+    float dx[C5_ROWS], dy[C5_ROWS], dz[C5_ROWS];     // view direction
+    float tn[C5_ROWS], dt[C5_ROWS];                  // t + dt and dt of the sample
+    float lsig[C5_ROWS];                             // log sigma (chain step 2 -> step 5)
+    uint32_t slot[C5_ROWS];                          // ray slot of the row, R5_INVALID for an unused row
+    int nrows[R5_MARCH_WARPS];
+};
+
+struct R5Rays {
+    float ox[R5_NR], oy[R5_NR], oz[R5_NR], dx[R5_NR], dy[R5_NR], dz[R5_NR];
+    float rdx[R5_NR], rdy[R5_NR], rdz[R5_NR];        // 1 / d (raymarching.cu:338)
+    float near[R5_NR], far[R5_NR], t[R5_NR];
+    int id[R5_NR];                                   // ray index; -1: slot wants a ray; -2: no rays left
+    uint32_t mstate[R5_NR];
+    float qt[R5_FIFO][R5_NR], qdt[R5_FIFO][R5_NR];
+    float ws[R5_NR], depth[R5_NR], r[R5_NR], g[R5_NR], b[R5_NR];
+    uint32_t ncomp[R5_NR];                           // samples composited for the ray
+    uint32_t status[R5_NR];
+};
+
+struct R5Bars {
+    uint64_t rows_full[R5_TBUF];   // 128 marcher threads: the tile's rows are in the buffer
+    uint64_t rows_free[R5_TBUF];   // 128 chain threads: the tile has been composited, the buffer may be rewritten
+};
+
+struct __align__(128) R5Smem {
+    C5FwdWeights w;
+    FqLevel lv[FQ_L];
+    C5Bars bars[2];
+    R5Bars tb;
+    uint32_t tmem;
+    int all_safe;
+    int chain_two[2];              // chain warps: does the current group take two tiles (double-buffered by group parity)
+    R5Tile tile[R5_TBUF];
+    R5Rays rays;
+};
+
+struct R5Params {
+    const float *rays_o, *rays_d, *aabb, *bg;
+    int64_t N;
+    int bg_stride;
+    float min_near, density_scale, bound;
+    uint32_t max_steps;
+    const float *table;
+    int align_corners;
+    float *image, *depth, *weights_sum;
+    int32_t *counts;
+    unsigned long long *counter;
+    unsigned long long *nsamples;
+};
+
+__device__ __forceinline__ uint32_t r5_ld_status(const uint32_t *p) { return *(const volatile uint32_t *)p; }
+__device__ __forceinline__ void r5_st_status(uint32_t *p, uint32_t v) { *(volatile uint32_t *)p = v; }
+
+__device__ __forceinline__ bool r5_tile_end(const R5Tile &T) {
+    int n = 0;
+#pragma unroll
+    for (int w = 0; w < R5_MARCH_WARPS; ++w) n += T.nrows[w];
+    return n == 0;
+}
+
+// ------------------------------------------------------------------------------------------------ marcher warps
+// renderer.py:371-374: image + (1 - ws) * bg; clamp(depth - near, 0) / (far - near)
+__device__ __forceinline__ void r5_finish(const R5Rays &R, const R5Params &P, int slot, int64_t id) {
+    const float ws = R.ws[slot], om = 1.0f - ws;
+    const float *bg = P.bg ? P.bg + (int64_t)P.bg_stride * id : nullptr;
+    const float b0 = bg ? __ldg(bg) : 1.0f, b1 = bg ? __ldg(bg + 1) : 1.0f, b2 = bg ? __ldg(bg + 2) : 1.0f;
+    P.image[id * 3] = __fadd_rn(R.r[slot], __fmul_rn(om, b0));
+    P.image[id * 3 + 1] = __fadd_rn(R.g[slot], __fmul_rn(om, b1));
+    P.image[id * 3 + 2] = __fadd_rn(R.b[slot], __fmul_rn(om, b2));
+    const float near = R.near[slot], far = R.far[slot];
+    P.depth[id] = __fdiv_rn(fmaxf(R.depth[slot] - near, 0.0f), far - near);
+    if (P.weights_sum) P.weights_sum[id] = ws;
+    if (P.counts) P.counts[id] = (int32_t)R.ncomp[slot];
+}
+
+// initialise slot `slot` with ray `nid`
+__device__ __forceinline__ void r5_load_ray(R5Rays &R, const R5Params &P, int slot, int64_t nid) {
+    const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
+    const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
+    float near, far;
+    ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
+    R.ox[slot] = o[0]; R.oy[slot] = o[1]; R.oz[slot] = o[2];
+    R.dx[slot] = d[0]; R.dy[slot] = d[1]; R.dz[slot] = d[2];
+    R.rdx[slot] = 1.0f / d[0]; R.rdy[slot] = 1.0f / d[1]; R.rdz[slot] = 1.0f / d[2];
+    R.t[slot] = near; R.near[slot] = near; R.far[slot] = far;
+    R.ws[slot] = 0.0f; R.depth[slot] = 0.0f; R.r[slot] = 0.0f; R.g[slot] = 0.0f; R.b[slot] = 0.0f;
+    R.ncomp[slot] = 0u;
+    R.mstate[slot] = 0u;
+    R.id[slot] = (int)nid;
+}
+
+__device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const MarchCfg &cfg, int w, int lane) {
+    R5Rays &R = S.rays;
+    const int slot0 = w * R5_PER_WARP + lane;
+    const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll 1
+    for (int j = 0; j < R5_PER_LANE; ++j) {
+        const int slot = slot0 + 32 * j;
+        R.id[slot] = -1;
+        R.mstate[slot] = 0u;
+        r5_st_status(&R.status[slot], R5_IDLE);
+    }
+    bool rays_left = true;
+    unsigned long long evaluated = 0;
+    int64_t n = 0;                                  // next tile to build
+    int rot = 0;
+    unsigned needs = (1u << R5_PER_LANE) - 1u;      // bit j: slot j of this lane wants a ray
+    for (;;) {
+        // ---- refill the slots that want a ray: one atomic per warp
+        if (!rays_left) needs = 0u;
+        if (__any_sync(0xffffffffu, needs != 0u)) {
+            const int mine = __popc(needs);
+            int pre = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, pre, o);
+                if (lane >= o) pre += v;
+            }
+            const int total = __shfl_sync(0xffffffffu, pre, 31);
+            unsigned long long base = 0;
+            if (lane == 31) base = atomicAdd(P.counter, (unsigned long long)total);
+            base = __shfl_sync(0xffffffffu, base, 31);
+            int64_t nid = (int64_t)base + pre - mine;
+            while (needs) {
+                const int j = __ffs(needs) - 1;
+                needs &= needs - 1u;
+                const int slot = slot0 + 32 * j;
+                if (nid < P.N) {
+                    r5_load_ray(R, P, slot, nid);
+                    ++nid;
+                } else {
+                    R.id[slot] = -2;
+                    rays_left = false;
+                }
+            }
+        }
+        // ---- one marcher step for every slot whose queue has room, R5_ILP slots at a time so that a lane keeps R5_ILP
+        // occupancy loads in flight (the step is a dependent chain per ray: position -> cell -> bit -> next t); then classify
+        unsigned elig = 0u;       // bit j: idle ray with a queued sample
+        unsigned retire = 0u;     // bit j: the ray of slot j is over (dead, or marched to the end and drained)
+        bool pending = false;     // some slot may still become eligible without a tile being built
+        bool worked = false;      // this pass marched something
+#pragma unroll 1
+        for (int g = 0; g < R5_PER_LANE / R5_ILP; ++g) {
+            float tq[R5_ILP];
+            uint32_t cell[R5_ILP], ms[R5_ILP], st[R5_ILP], byte[R5_ILP];
+            int lvl[R5_ILP];
+            bool act[R5_ILP], live[R5_ILP];
+#pragma unroll
+            for (int k = 0; k < R5_ILP; ++k) {
+                const int slot = slot0 + 32 * (g * R5_ILP + k);
+                live[k] = R.id[slot] >= 0;
+                st[k] = r5_ld_status(&R.status[slot]);
+                ms[k] = R.mstate[slot];
+                act[k] = live[k] && st[k] != R5_DEAD && !R5_MS_END(ms[k]) && R5_MS_CNT(ms[k]) < R5_FIFO;
+                tq[k] = 0.0f;
+                cell[k] = 0u;
+                lvl[k] = 0;
+                if (act[k]) {
+                    tq[k] = R.t[slot];
+                    if (!(tq[k] < R.far[slot]) || R5_MS_MARCHED(ms[k]) >= P.max_steps) {   // raymarching.cu:730
+                        ms[k] |= 1u << 25;
+                        R.mstate[slot] = ms[k];
+                        act[k] = false;
+                    } else {
+                        MarchRay r;
+                        r.ox = R.ox[slot]; r.oy = R.oy[slot]; r.oz = R.oz[slot];
+                        r.dx = R.dx[slot]; r.dy = R.dy[slot]; r.dz = R.dz[slot];
+                        float dt;
+                        cell[k] = ngp_march_cell_fast(r, cfg, tq[k], dt, lvl[k]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < R5_ILP; ++k) byte[k] = act[k] ? (uint32_t)__ldg(cfg.grid + (cell[k] >> 3)) : 0u;
+#pragma unroll
+            for (int k = 0; k < R5_ILP; ++k) {
+                const int j = g * R5_ILP + k;
+                const int slot = slot0 + 32 * j;
+                if (act[k]) {
+                    worked = true;
+                    uint32_t cnt = R5_MS_CNT(ms[k]), marched = R5_MS_MARCHED(ms[k]);
+                    const uint32_t head = R5_MS_HEAD(ms[k]);
+                    float tc = tq[k];
+                    if ((byte[k] >> (cell[k] & 7u)) & 1u) {
+                        const float dt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(tc * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+                        const uint32_t wpos = (head + cnt) % R5_FIFO;
+                        R.qt[wpos][slot] = tc;
+                        R.qdt[wpos][slot] = dt;
+                        tc += dt;
+                        ++cnt;
+                        ++marched;
+                    } else {
+                        MarchRay r;
+                        r.ox = R.ox[slot]; r.oy = R.oy[slot]; r.oz = R.oz[slot];
+                        r.dx = R.dx[slot]; r.dy = R.dy[slot]; r.dz = R.dz[slot];
+                        r.rdx = R.rdx[slot]; r.rdy = R.rdy[slot]; r.rdz = R.rdz[slot];
+                        const float tt = ngp_march_exit_fast(r, cfg, tc, cell[k], lvl[k]);
+                        if (cfg.lvl_dt >= 0) {   // dt_gamma == 0: the recurrence of ngp_march_advance is t += dt_min
+                            do {
+                                tc += cfg.dt_min;
+                            } while (tc < tt);
+                        } else {
+                            do {
+                                tc = ngp_march_advance(tc, cfg);
+                            } while (tc < tt);
+                        }
+                    }
+                    R.t[slot] = tc;
+                    ms[k] = R5_MS_PACK(marched, cnt, head, 0u);
+                    R.mstate[slot] = ms[k];
+                }
+                if (live[k]) {
+                    const uint32_t cnt = R5_MS_CNT(ms[k]);
+                    if (st[k] == R5_IDLE && cnt > 0u) elig |= 1u << j;
+                    else if (st[k] == R5_DEAD || (st[k] == R5_IDLE && R5_MS_END(ms[k]))) retire |= 1u << j;   // cnt == 0 here
+                    else pending = true;   // in flight (comes back) or still marching
+                }
+            }
+        }
+        // ---- retire finished rays (their slots want a new ray at the top of the next pass)
+        needs = 0u;
+        if (retire) pending = true;        // the slot is refilled (or runs out of rays) next pass
+        while (retire) {
+            const int j = __ffs(retire) - 1;
+            retire &= retire - 1u;
+            const int slot = slot0 + 32 * j;
+            __threadfence_block();         // the chain thread wrote the accumulators before the status
+            r5_finish(R, P, slot, R.id[slot]);
+            evaluated += R.ncomp[slot];
+            R.id[slot] = -1;
+            r5_st_status(&R.status[slot], R5_IDLE);
+            needs |= 1u << j;
+        }
+        if (!rays_left && needs) {         // nothing to refill with: the slots are out of the game
+            unsigned m = needs;
+            while (m) {
+                const int j = __ffs(m) - 1;
+                m &= m - 1u;
+                R.id[slot0 + 32 * j] = -2;
+            }
+            needs = 0u;
+        }
+        int E = __popc(elig);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+        const bool any_pending = __any_sync(0xffffffffu, pending);
+        const bool any_worked = __any_sync(0xffffffffu, worked);
+        if (E < R5_PART && any_pending) {
+            if (!any_worked) __nanosleep(200);   // waiting for rays in flight: leave the issue slots to the other roles
+            continue;
+        }
+        // ---- build this warp's part of tile n (all eligible slots if fewer than R5_PART: nothing else can come)
+        const int b = (int)(n & (R5_TBUF - 1));
+        if (n >= R5_TBUF) {
+            uint32_t ok = 0;
+            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> 2) - 1) & 1));
+            if (!__shfl_sync(0xffffffffu, ok, 0)) {           // buffer still in use: keep marching
+                if (!any_worked) __nanosleep(200);
+                continue;
+            }
+        }
+        R5Tile &T = S.tile[b];
+        int nrows = 0;
+#pragma unroll 1
+        for (int jj = 0; jj < R5_PER_LANE && nrows < R5_PART; ++jj) {
+            int j = jj + rot;
+            if (j >= R5_PER_LANE) j -= R5_PER_LANE;
+            const bool e = (elig >> j) & 1u;
+            const unsigned m = __ballot_sync(0xffffffffu, e);
+            const int row = nrows + __popc(m & lt_mask);
+            if (e && row < R5_PART) {
+                const int slot = slot0 + 32 * j;
+                const uint32_t ms = R.mstate[slot];
+                const uint32_t head = R5_MS_HEAD(ms);
+                const float st = R.qt[head][slot], sdt = R.qdt[head][slot];
+                R.mstate[slot] = R5_MS_PACK(R5_MS_MARCHED(ms), R5_MS_CNT(ms) - 1u, (head + 1u) % R5_FIFO, R5_MS_END(ms));
+                const float dxv = R.dx[slot], dyv = R.dy[slot], dzv = R.dz[slot];
+                const int tr = w * R5_PART + row;
+                T.x[tr] = ngp_clampf(fmaf(st, dxv, R.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
+                T.y[tr] = ngp_clampf(fmaf(st, dyv, R.oy[slot]), -P.bound, P.bound);
+                T.z[tr] = ngp_clampf(fmaf(st, dzv, R.oz[slot]), -P.bound, P.bound);
+                T.dx[tr] = dxv; T.dy[tr] = dyv; T.dz[tr] = dzv;
+                T.tn[tr] = st + sdt;
+                T.dt[tr] = sdt;
+                T.slot[tr] = (uint32_t)slot;
+                r5_st_status(&R.status[slot], R5_BUSY);
+            }
+            nrows = min(R5_PART, nrows + __popc(m));
+        }
+        rot = rot + 5 >= R5_PER_LANE ? rot + 5 - R5_PER_LANE : rot + 5;
+        for (int row = nrows + lane; row < R5_PART; row += 32) T.slot[w * R5_PART + row] = R5_INVALID;
+        if (lane == 0) T.nrows[w] = nrows;
+        tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b]));
+        ++n;
+        if (nrows == 0) {
+            // this part is empty for good (every slot is out of rays).  The work ends with the first tile whose other parts
+            // are empty too; one more empty tile follows so that the roles of both TMEM slots see an end.
+            tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> 2) & 1));
+            if (r5_tile_end(T)) {
+                const int b2 = (int)(n & (R5_TBUF - 1));
+                if (n >= R5_TBUF) tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> 2) - 1) & 1));
+                R5Tile &T2 = S.tile[b2];
+                for (int row = lane; row < R5_PART; row += 32) T2.slot[w * R5_PART + row] = R5_INVALID;
+                if (lane == 0) T2.nrows[w] = 0;
+                tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b2]));
+                break;
+            }
+        }
+    }
+    if (P.nsamples) {
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) evaluated += __shfl_xor_sync(0xffffffffu, evaluated, o2);
+        if (lane == 0 && evaluated) atomicAdd(P.nsamples, evaluated);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ gather warps
+template <bool SAFE>
+__device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
+    const int s = warp >> 2, q = warp & 3, row = 32 * q + lane;
+    const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
+    const uint32_t bar_full = tc5::smem_u32(&S.bars[s].f_full), bar_empty = tc5::smem_u32(&S.bars[s].f_empty);
+    const float den = 2.0f * P.bound;
+    for (int64_t it = 0;; ++it) {
+        const int64_t n = 2 * it + s;
+        const int b = (int)(n & (R5_TBUF - 1));
+        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> 2) & 1));
+        const R5Tile &T = S.tile[b];
+        if (r5_tile_end(T)) break;
+        bool valid = T.slot[row] != R5_INVALID;
+        float x01[3];
+        x01[0] = __fdiv_rn((valid ? T.x[row] : 0.0f) + P.bound, den);   // grid.py:144
+        x01[1] = __fdiv_rn((valid ? T.y[row] : 0.0f) + P.bound, den);
+        x01[2] = __fdiv_rn((valid ? T.z[row] : 0.0f) + P.bound, den);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) valid = valid && !(x01[a] < 0.0f || x01[a] > 1.0f);
+        if (!valid) x01[0] = x01[1] = x01[2] = 0.5f;
+#pragma unroll 1
+        for (int lp = 0; lp < 8; ++lp) {
+            float feat[4];
+            c5_encode_pair<SAFE>(P.table, S.lv, lp, x01, valid, P.align_corners, feat);
+            if (lp == 0) {
+                if (it > 0) tc5::mbar_wait_wd(bar_empty, (uint32_t)((it - 1) & 1));
+                tc5::fence_after_sync();
+            }
+            c5_put_features(lane_addr, lp, feat);
+        }
+        tc5::tmem_st_wait();
+        tc5::fence_before_sync();
+        tc5::mbar_arrive(bar_full);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ MMA threads
+__device__ __forceinline__ void r5_mma(R5Smem &S, uint32_t tmem, int s) {
+    const uint32_t t = tmem + s * C5_SLOT_COLS;
+    const uint32_t bar_ff = tc5::smem_u32(&S.bars[s].f_full), bar_fe = tc5::smem_u32(&S.bars[s].f_empty),
+                   bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready),
+                   bar_t = tc5::smem_u32(&S.bars[s].t_free);
+    const uint32_t s0h = tc5::smem_u32(S.w.s0[0]), s0l = tc5::smem_u32(S.w.s0[1]), s1h = tc5::smem_u32(S.w.s1[0]),
+                   s1l = tc5::smem_u32(S.w.s1[1]), c0h = tc5::smem_u32(S.w.c0[0]), c0l = tc5::smem_u32(S.w.c0[1]),
+                   c1h = tc5::smem_u32(S.w.c1[0]), c1l = tc5::smem_u32(S.w.c1[1]), c2h = tc5::smem_u32(S.w.c2[0]),
+                   c2l = tc5::smem_u32(S.w.c2[1]);
+    for (int64_t it = 0;; ++it) {
+        const int64_t n = 2 * it + s;
+        const int b = (int)(n & (R5_TBUF - 1));
+        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> 2) & 1));
+        if (r5_tile_end(S.tile[b])) break;
+        const uint32_t pa = (uint32_t)(4 * it);
+        tc5::mbar_wait_wd(bar_ff, (uint32_t)(it & 1));
+        if (it > 0) tc5::mbar_wait_wd(bar_t, (uint32_t)((it - 1) & 1));
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 32>(t + C5_D, t + C5_FHI, t + C5_FLO, s0h, s0l);   // sigma L1: features -> 64
+        tc5::mma_commit(bar_fe);
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, s1h, s1l);   // sigma L2: 64 -> 16
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 32>(t + C5_D, t + C5_HHI, t + C5_HLO, c0h, c0l);   // colour L1: [SH | o] (32) -> 64
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<64, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c1h, c1l);   // colour L2: 64 -> 64
+        tc5::mma_commit(bar_d);
+        tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u);
+        tc5::fence_after_sync();
+        c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c2h, c2l);   // colour L3: 64 -> 3 (16)
+        tc5::mma_commit(bar_d);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ chain warps
+// Tiles are taken in order, two at a time when the second one's rows are already there (its epilogues then run while the
+// first tile's next layer is on the tensor core, as in cfield5.cu), otherwise one — waiting for a tile that the marchers
+// can only build once THIS tile's rays have been composited would deadlock.  d_full of a TMEM slot completes 5 times per
+// tile: wait k of the slot's tile number `it` has parity (5 it + k) & 1.
+__device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
+    const int q = warp & 3, row = 32 * q + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    R5Rays &R = S.rays;
+    int64_t n0 = 0;
+    uint32_t group = 0;
+    for (;;) {
+        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[n0 & (R5_TBUF - 1)]), (uint32_t)((n0 >> 2) & 1));
+        if (r5_tile_end(S.tile[n0 & (R5_TBUF - 1)])) break;
+        // one decision for the four chain warps (they hand the same tiles to the MMA threads step by step, so taking a tile
+        // in one warp and not in another would deadlock): the first chain warp tests, the others read its verdict
+        if (warp == C5_CHAIN_WARP0 && lane == 0) {
+            const int64_t n1 = n0 + 1;
+            bool ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_full[n1 & (R5_TBUF - 1)]), (uint32_t)((n1 >> 2) & 1));
+            if (ok && r5_tile_end(S.tile[n1 & (R5_TBUF - 1)])) ok = false;
+            S.chain_two[group & 1] = ok ? 1 : 0;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int n_act = S.chain_two[group & 1] ? 2 : 1;
+        ++group;
+#define R5_TILE_VARS                                                                                \
+        const int64_t n = n0 + i;                                                                   \
+        const int s = (int)(n & 1);                                                                 \
+        R5Tile &T = S.tile[n & (R5_TBUF - 1)];                                                      \
+        const uint32_t par = (uint32_t)(5 * (n >> 1));                                              \
+        const uint32_t lane_addr = lane_base + s * C5_SLOT_COLS;                                    \
+        const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready);
+        // ---- sigma hidden
+#pragma unroll 1
+        for (int i = 0; i < n_act; ++i) {
+            R5_TILE_VARS
+            (void)T;
+            tc5::mbar_wait_wd(bar_d, (par + 0u) & 1u);
+            tc5::fence_after_sync();
+            c5_relu_to_a<false>(lane_addr);
+            c5_chain_arrive(bar_a);
+        }
+        // ---- sigma-net output o (column 0 = log sigma, 1..15 = geo_feat) -> colour input [SH(d) | 0, geo_feat]
+#pragma unroll 1
+        for (int i = 0; i < n_act; ++i) {
+            R5_TILE_VARS
+            const float dir[3] = {T.dx[row], T.dy[row], T.dz[row]};
+            tc5::mbar_wait_wd(bar_d, (par + 1u) & 1u);
+            tc5::fence_after_sync();
+            float o[16];
+            c5_get16(lane_addr, 0, o);
+            T.lsig[row] = o[0];
+            o[0] = 0.0f;
+            c5_put16(lane_addr, 16, o);
+            float sh[16];
+            ngp_sh4(dir[0], dir[1], dir[2], sh);
+            c5_put16(lane_addr, 0, sh);
+            c5_chain_arrive(bar_a);
+        }
+        // ---- colour hidden 1, 2
+#pragma unroll 1
+        for (int k = 0; k < 2; ++k) {
+#pragma unroll 1
+            for (int i = 0; i < n_act; ++i) {
+                R5_TILE_VARS
+                (void)T;
+                tc5::mbar_wait_wd(bar_d, (par + 2u + (uint32_t)k) & 1u);
+                tc5::fence_after_sync();
+                c5_relu_to_a<false>(lane_addr);
+                c5_chain_arrive(bar_a);
+            }
+        }
+        // ---- colour logits -> sigmoid, and the compositing step of the row's ray (raymarching.cu:860-893)
+#pragma unroll 1
+        for (int i = 0; i < n_act; ++i) {
+            R5_TILE_VARS
+            (void)bar_a;
+            const uint32_t slot = T.slot[row];
+            const float tn = T.tn[row], sdt = T.dt[row], lsig = T.lsig[row];
+            tc5::mbar_wait_wd(bar_d, (par + 4u) & 1u);
+            tc5::fence_after_sync();
+            uint32_t lg[4];
+            tc5::tmem_ld4_nowait(lane_addr + C5_D, lg);
+            tc5::tmem_ld_wait();
+            tc5::fence_before_sync();
+            tc5::mbar_arrive(tc5::smem_u32(&S.bars[s].t_free));
+            if (slot != R5_INVALID) {
+                const float sigma = expf(lsig) * P.density_scale;   // trunc_exp fwd; renderer.py:355
+                const float cr = 1.0f / (1.0f + expf(-__uint_as_float(lg[0])));
+                const float cg = 1.0f / (1.0f + expf(-__uint_as_float(lg[1])));
+                const float cb = 1.0f / (1.0f + expf(-__uint_as_float(lg[2])));
+                const float ws = R.ws[slot];
+                const float alpha = 1.0f - __expf(-sigma * sdt);
+                const float Tr = 1.0f - ws;
+                const float wgt = alpha * Tr;
+                R.ws[slot] = ws + wgt;
+                R.depth[slot] = fmaf(wgt, tn, R.depth[slot]);
+                R.r[slot] = fmaf(wgt, cr, R.r[slot]);
+                R.g[slot] = fmaf(wgt, cg, R.g[slot]);
+                R.b[slot] = fmaf(wgt, cb, R.b[slot]);
+                R.ncomp[slot] += 1u;
+                __threadfence_block();
+                // :880 — the sample that saw T < 1e-4 is still accumulated, then the ray is over
+                r5_st_status(&R.status[slot], (double)Tr < 1e-4 ? R5_DEAD : R5_IDLE);
+            }
+            tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_free[n & (R5_TBUF - 1)]));
+        }
+        n0 += n_act;
+    }
+}
+
+__global__ void __launch_bounds__(R5_THREADS, 1)
+k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offsets, float S_, uint32_t H, uint32_t gridtype,
+                     const float *__restrict__ Ws0, const float *__restrict__ Ws1, const float *__restrict__ Wc0,
+                     const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
+    extern __shared__ __align__(128) unsigned char r5_smem_raw[];
+    R5Smem &S = *reinterpret_cast<R5Smem *>(r5_smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
+    c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].f_full), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].f_empty), 1);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].d_full), 1);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].a_ready), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].t_free), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].g_full), 1);
+        }
+        for (int b = 0; b < R5_TBUF; ++b) {
+            tc5::mbar_init(tc5::smem_u32(&S.tb.rows_full[b]), R5_MARCH_WARPS * 32);
+            tc5::mbar_init(tc5::smem_u32(&S.tb.rows_free[b]), 128);
+        }
+        tc5::fence_mbar_init();
+    }
+    if (warp == C5_MMA_WARP) tc5::tmem_alloc(tc5::smem_u32(&S.tmem), 512);
+    tc5::fence_async_smem();
+    tc5::fence_before_sync();
+    __syncthreads();
+    tc5::fence_after_sync();
+    const uint32_t tmem = S.tmem;
+
+    if (warp < C5_GATHER_WARPS) {
+        if (S.all_safe) r5_gather<true>(S, P, tmem, warp, lane);
+        else r5_gather<false>(S, P, tmem, warp, lane);
+    } else if (warp < C5_MMA_WARP) {
+        r5_chain(S, P, tmem, warp, lane);
+    } else if (warp < R5_MARCH_WARP0) {
+        if (lane == 0) r5_mma(S, tmem, warp - C5_MMA_WARP);
+        __syncwarp();
+    } else {
+        r5_marcher(S, P, cfg, warp - R5_MARCH_WARP0, lane);
+    }
+    tc5::fence_before_sync();
+    __syncthreads();
+    if (warp == C5_MMA_WARP) tc5::tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------------ launcher (render.cu)
+int r5_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                         const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
+                         const float *embeddings, const int32_t *offsets, float S, uint32_t H, uint32_t gridtype,
+                         int align_corners, const float *Ws0, const float *Ws1, const float *Wc0, const float *Wc1,
+                         const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
+                         float *depth, float *weights_sum, int32_t *counts, void *workspace, cudaStream_t stream) {
+    NGP_REQUIRE(N < (1ll << 31) && max_steps < (1u << 20), NGP_ERR_UNSUPPORTED,
+                "ngp_render_rays_infer (tcgen05): N must be < 2^31 and max_steps < 2^20");
+    const int smem = (int)sizeof(R5Smem);
+    if (cudaFuncSetAttribute(k_render5_rays_infer, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+        ngp_set_error("ngp_render_rays_infer: cannot reserve %d B of shared memory", smem);
+        return NGP_ERR_CUDA;
+    }
+    int dev = 0, sms = NGP_SM_COUNT;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    R5Params P;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.aabb = aabb; P.bg = bg_color; P.N = N; P.bg_stride = bg_stride;
+    P.min_near = min_near; P.density_scale = density_scale; P.bound = bound; P.max_steps = max_steps;
+    P.table = embeddings; P.align_corners = align_corners;
+    P.image = image; P.depth = depth; P.weights_sum = weights_sum; P.counts = counts;
+    P.counter = (unsigned long long *)workspace;
+    P.nsamples = (unsigned long long *)workspace + 1;
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
+    // one CTA per SM (a CTA owns all 512 TMEM columns); small batches use fewer CTAs so that tiles still fill
+    const int64_t want = ngp_div_up(N, R5_NR / 2);
+    const int nblocks = (int)(want < sms ? want : sms);
+    k_render5_rays_infer<<<nblocks, R5_THREADS, smem, stream>>>(P, cfg, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
+    NGP_CHECK_LAUNCH("ngp_render_rays_infer (tcgen05)");
+    return NGP_OK;
+}

@@ -134,10 +134,12 @@ def field_color(model, x, d):
 
 
 @torch.no_grad()
-def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, max_steps=1024, return_stats=False):
+def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, max_steps=1024, return_stats=False,
+                      return_counts=False):
     """Fused eval branch of NeRFRenderer.run_cuda (renderer.py:325-374): near/far, the alive-ray loop of march_rays ->
     forward(x, d) -> composite_rays, and the background / depth post-processing in ONE kernel (csrc/render.cu).
-    rays_o, rays_d [N,3] -> image [N,3], depth [N], weights_sum [N] (already post-processed like run_cuda's results)."""
+    rays_o, rays_d [N,3] -> image [N,3], depth [N], weights_sum [N] (already post-processed like run_cuda's results);
+    return_stats appends the workspace (its second i64 = samples evaluated), return_counts the per-ray int32 sample counts."""
     _lib.require_cuda(rays_o, rays_d, model.density_bitfield)
     rays_o = rays_o.contiguous().float()
     rays_d = rays_d.contiguous().float()
@@ -157,6 +159,7 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
         else:
             bg, stride = bg.expand(N, 3).contiguous(), 3
     work = torch.empty(2, device=dev, dtype=torch.int64)
+    counts = torch.empty(N, device=dev, dtype=torch.int32) if return_counts else None
     ws = [w.detach().contiguous() for w in (model.sigma_net[0].weight, model.sigma_net[1].weight, model.color_net[0].weight,
                                             model.color_net[1].weight, model.color_net[2].weight)]
     with torch.cuda.device(dev):
@@ -166,10 +169,13 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
             int(model.grid_size), _lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets),
             float(np.log2(enc.per_level_scale)), int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners),
             *[_lib.ptr(w) for w in ws], float(model.density_scale), _lib.ptr(bg), stride, _lib.ptr(image),
-            _lib.ptr(depth), _lib.ptr(wsum), _lib.ptr(work), _lib.stream()), "render_rays_infer")
+            _lib.ptr(depth), _lib.ptr(wsum), _lib.ptr(counts), _lib.ptr(work), _lib.stream()), "render_rays_infer")
+    out = (image, depth, wsum)
     if return_stats:
-        return image, depth, wsum, work
-    return image, depth, wsum
+        out = out + (work,)
+    if return_counts:
+        out = out + (counts,)
+    return out
 
 
 class HostFieldQuery:

@@ -161,27 +161,53 @@ def _sample_points(n, seed):
     return x, d
 
 
+def _relu_tie_samples(model, x, d, tol=1e-5):
+    """Samples with a hidden pre-activation within `tol` (relative to the layer's largest) of zero, computed with plain
+    torch matmuls on the unfused encoder outputs: the sign of such a unit — hence the sample's gradient — can differ between
+    two fp32 evaluation orders.  They are named and excluded from the 1e-5 gradient bar (and counted)."""
+    with torch.no_grad():
+        feat = model.encoder(x, bound=model.bound)
+        z0 = feat @ model.sigma_net[0].weight.t()
+        o = torch.relu(z0) @ model.sigma_net[1].weight.t()
+        cin = torch.cat([model.encoder_dir(d), o[:, 1:]], -1)
+        z1 = cin @ model.color_net[0].weight.t()
+        z2 = torch.relu(z1) @ model.color_net[1].weight.t()
+        tie = torch.zeros(x.shape[0], dtype=torch.bool, device=x.device)
+        for z in (z0, z1, z2):
+            tie |= (z.abs() < tol * z.abs().max()).any(-1)
+    return tie
+
+
+@pytest.mark.parametrize("impl", ["tc5", "mma"])
 @pytest.mark.parametrize("n", [1, 191, 5000, 40001])
-def test_fused_forward_xd_equals_unfused(model, n):
-    """Fused sample kernel (encode + sigma MLP + SH + colour MLP, csrc/renderfield.cu) == the unfused path
-    (GridEncoder / nn.Linear / SHEncoder kernels, themselves pinned to the oracle + reference CUDA build): values and
-    the gradients w.r.t. sample positions and view directions (1e-5 bar for the fp32 path)."""
+def test_fused_forward_xd_equals_unfused(model, ngp, n, impl):
+    """Fused sample kernels (encode + sigma MLP + SH + colour MLP: tcgen05 csrc/cfield5.cu, mma.sync csrc/renderfield.cu)
+    == the unfused path (GridEncoder / nn.Linear / SHEncoder kernels, themselves pinned to the oracle + reference CUDA
+    build): values and the gradients w.r.t. sample positions and view directions (1e-5 bar for the fp32 path; samples
+    with a ReLU pre-activation at a tie are named by _relu_tie_samples and excluded from the gradient bar)."""
     model.eval()
     x, d = _sample_points(n, n)
     w_s = torch.randn(n, device="cuda"); w_c = torch.randn(n, 3, device="cuda")
     outs = []
-    for fused in (True, False):
-        model.fused_eval = fused
-        xa, da = x.clone().requires_grad_(), d.clone().requires_grad_()
-        sigma, rgb = model(xa, da)
-        ((sigma * w_s).sum() + (rgb * w_c).sum()).backward()
-        outs.append((sigma.detach(), rgb.detach(), xa.grad.clone(), da.grad.clone()))
-    model.fused_eval = True
+    prev = ngp.lib().ngp_set_field_impl(1 if impl == "tc5" else 0)
+    try:
+        for fused in (True, False):
+            model.fused_eval = fused
+            xa, da = x.clone().requires_grad_(), d.clone().requires_grad_()
+            sigma, rgb = model(xa, da)
+            ((sigma * w_s).sum() + (rgb * w_c).sum()).backward()
+            outs.append((sigma.detach(), rgb.detach(), xa.grad.clone(), da.grad.clone()))
+    finally:
+        model.fused_eval = True
+        ngp.lib().ngp_set_field_impl(prev)
     (s1, c1, gx1, gd1), (s0, c0, gx0, gd0) = outs
     assert rel_err(s1.cpu().numpy(), s0.cpu().numpy()) < 1e-5
     assert rel_err(c1.cpu().numpy(), c0.cpu().numpy()) < 1e-5
-    assert rel_err(gx1.cpu().numpy(), gx0.cpu().numpy()) < 1e-5
-    assert rel_err(gd1.cpu().numpy(), gd0.cpu().numpy()) < 1e-5
+    keep = (~_relu_tie_samples(model, x, d)).cpu().numpy()
+    assert keep.mean() > 0.99
+    for a, b in ((gx1, gx0), (gd1, gd0)):
+        err = (a - b).abs().amax(-1).cpu().numpy() / float(b.abs().max())
+        assert err[keep].max(initial=0.0) < 1e-5, (impl, float(err[keep].max(initial=0.0)), int((err > 1e-5).sum()))
 
 
 def test_fused_forward_xd_vs_oracle(model, oracle, ngp):
