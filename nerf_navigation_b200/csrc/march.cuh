@@ -128,9 +128,20 @@ __device__ __forceinline__ int ngp_mip_level_bits(float v, uint32_t C) {
     const int e = (int)((__float_as_uint(v) >> 23) & 0xffu) - 126;
     return min((int)C - 1, max(0, e));
 }
-// The same cell address with the level returned separately, the level of the position taken from the exponent bits and —
-// when dt_gamma == 0 — dt and its level taken from the configuration: identical values, fewer instructions (render5.cu).
-__device__ __forceinline__ uint32_t ngp_march_cell_fast(const MarchRay &r, const MarchCfg &c, float t0, float &dt, int &level) {
+// fp64 form of the cell coordinate for grids whose H is not a power of two, out of line so that the common fp32 form
+// does not carry its (predicated-off) double-precision instructions
+static __device__ __noinline__ float ngp_cell_coord_f64(float u, uint32_t H) { return (float)(0.5 * (double)u * (double)H); }
+__device__ __forceinline__ int ngp_cell_coord_fast(float p, float mip_rbound, const MarchCfg &c) {
+    const float u = fmaf(p, mip_rbound, 1.0f);
+    const float v = c.h_pow2 ? 0.5f * u * c.Hf : ngp_cell_coord_f64(u, c.H);
+    return (int)ngp_clampf(v, 0.0f, c.Hf - 1.0f);
+}
+// The same cell address with fewer instructions (render5.cu): the level of the position from the exponent bits; dt and its
+// level from the configuration when dt_gamma == 0; min(2^level, bound) and its reciprocal from tables filled with the
+// expressions above (mipb[l] = fminf((float)(1 << l), bound), miprb[l] = 1.0f / mipb[l]); the cell coordinates are also
+// returned packed (nx | ny << 10 | nz << 20) so that the exit needs no Morton decode.  Identical values.
+__device__ __forceinline__ uint32_t ngp_march_cell_fast(const MarchRay &r, const MarchCfg &c, const float *miprb, float t0,
+                                                        float &dt, int &level, uint32_t &nxyz) {
     const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
     const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
     const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
@@ -143,20 +154,21 @@ __device__ __forceinline__ uint32_t ngp_march_cell_fast(const MarchRay &r, const
     }
     const float mx = fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)));
     level = max(ngp_mip_level_bits(mx, c.C), lvl_dt);
-    const float mip_rbound = 1.0f / fminf((float)(1 << level), c.bound);
-    const int nx = ngp_cell_coord(x, mip_rbound, c);
-    const int ny = ngp_cell_coord(y, mip_rbound, c);
-    const int nz = ngp_cell_coord(z, mip_rbound, c);
+    const float mip_rbound = miprb[level];
+    const int nx = ngp_cell_coord_fast(x, mip_rbound, c);
+    const int ny = ngp_cell_coord_fast(y, mip_rbound, c);
+    const int nz = ngp_cell_coord_fast(z, mip_rbound, c);
+    nxyz = (uint32_t)nx | ((uint32_t)ny << 10) | ((uint32_t)nz << 20);
     return (uint32_t)level * c.H3 + ngp_morton3D((uint32_t)nx, (uint32_t)ny, (uint32_t)nz);
 }
 // r.rdx/rdy/rdz must be set
-__device__ __forceinline__ float ngp_march_exit_fast(const MarchRay &r, const MarchCfg &c, float t0, uint32_t index, int level) {
-    const uint32_t m = index - (uint32_t)level * c.H3;
-    const int nx = (int)ngp_morton_compact(m), ny = (int)ngp_morton_compact(m >> 1), nz = (int)ngp_morton_compact(m >> 2);
+__device__ __forceinline__ float ngp_march_exit_fast(const MarchRay &r, const MarchCfg &c, const float *mipb, float t0,
+                                                     uint32_t nxyz, int level) {
+    const int nx = (int)(nxyz & 1023u), ny = (int)((nxyz >> 10) & 1023u), nz = (int)(nxyz >> 20);
     const float x = ngp_clampf(fmaf(t0, r.dx, r.ox), -c.bound, c.bound);
     const float y = ngp_clampf(fmaf(t0, r.dy, r.oy), -c.bound, c.bound);
     const float z = ngp_clampf(fmaf(t0, r.dz, r.oz), -c.bound, c.bound);
-    const float mip_bound = fminf((float)(1 << level), c.bound);
+    const float mip_bound = mipb[level];
     const float tx = fmaf(fmaf(((float)nx + 0.5f + 0.5f * copysignf(1.0f, r.dx)) * c.rH, 2.0f, -1.0f), mip_bound, -x) * r.rdx;
     const float ty = fmaf(fmaf(((float)ny + 0.5f + 0.5f * copysignf(1.0f, r.dy)) * c.rH, 2.0f, -1.0f), mip_bound, -y) * r.rdy;
     const float tz = fmaf(fmaf(((float)nz + 0.5f + 0.5f * copysignf(1.0f, r.dz)) * c.rH, 2.0f, -1.0f), mip_bound, -z) * r.rdz;

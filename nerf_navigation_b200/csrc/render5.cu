@@ -84,6 +84,8 @@ struct __align__(128) R5Smem {
     R5Bars tb;
     uint32_t tmem;
     int all_safe;
+    float mipb[8], miprb[8];       // min(2^level, bound) and its reciprocal (raymarching.cu:376-377)
+    uint16_t mlist[R5_MARCH_WARPS][R5_PER_WARP];   // marcher warps: slots that want a step this pass
     int chain_two[2];              // chain warps: does the current group take two tiles (double-buffered by group parity)
     R5Tile tile[R5_TBUF];
     R5Rays rays;
@@ -115,7 +117,7 @@ __device__ __forceinline__ bool r5_tile_end(const R5Tile &T) {
 
 // ------------------------------------------------------------------------------------------------ marcher warps
 // renderer.py:371-374: image + (1 - ws) * bg; clamp(depth - near, 0) / (far - near)
-__device__ __forceinline__ void r5_finish(const R5Rays &R, const R5Params &P, int slot, int64_t id) {
+static __device__ __noinline__ void r5_finish(const R5Rays &R, const R5Params &P, int slot, int64_t id) {
     const float ws = R.ws[slot], om = 1.0f - ws;
     const float *bg = P.bg ? P.bg + (int64_t)P.bg_stride * id : nullptr;
     const float b0 = bg ? __ldg(bg) : 1.0f, b1 = bg ? __ldg(bg + 1) : 1.0f, b2 = bg ? __ldg(bg + 2) : 1.0f;
@@ -129,7 +131,7 @@ __device__ __forceinline__ void r5_finish(const R5Rays &R, const R5Params &P, in
 }
 
 // initialise slot `slot` with ray `nid`
-__device__ __forceinline__ void r5_load_ray(R5Rays &R, const R5Params &P, int slot, int64_t nid) {
+static __device__ __noinline__ void r5_load_ray(R5Rays &R, const R5Params &P, int slot, int64_t nid) {
     const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
     const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
     float near, far;
@@ -144,10 +146,20 @@ __device__ __forceinline__ void r5_load_ray(R5Rays &R, const R5Params &P, int sl
     R.id[slot] = (int)nid;
 }
 
+// One pass of a marcher warp over its R5_PER_WARP slots:
+//   1. classify every slot from one read of (id, status, mstate): eligible for a tile / finished / wants marching;
+//   2. retire finished rays and refill their slots (one atomic per warp);
+//   3. if R5_PART slots are eligible (or nothing more can come) and the tile buffer is free: build the warp's part of tile n;
+//   4. march: the slots that want a step are compacted into a list (ballots) and the lanes walk the list, so every lane
+//      probes a cell no matter how the work is spread over the slots; R5_ILP list entries per lane are in flight at once
+//      (a step is a dependent chain: position -> cell -> occupancy bit -> next t).
+// All marcher state lives in shared memory, so any lane of the warp can step any of the warp's slots; the phases are
+// separated by __syncwarp().
 __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const MarchCfg &cfg, int w, int lane) {
     R5Rays &R = S.rays;
     const int slot0 = w * R5_PER_WARP + lane;
     const unsigned lt_mask = (1u << lane) - 1u;
+    uint16_t *list = S.mlist[w];
 #pragma unroll 1
     for (int j = 0; j < R5_PER_LANE; ++j) {
         const int slot = slot0 + 32 * j;
@@ -160,8 +172,9 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
     int64_t n = 0;                                  // next tile to build
     int rot = 0;
     unsigned needs = (1u << R5_PER_LANE) - 1u;      // bit j: slot j of this lane wants a ray
+    bool ended = false;
     for (;;) {
-        // ---- refill the slots that want a ray: one atomic per warp
+        // ---- 2a. refill the slots that want a ray: one atomic per warp
         if (!rays_left) needs = 0u;
         if (__any_sync(0xffffffffu, needs != 0u)) {
             const int mine = __popc(needs);
@@ -189,68 +202,172 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
                 }
             }
         }
-        // ---- one marcher step for every slot whose queue has room, R5_ILP slots at a time so that a lane keeps R5_ILP
-        // occupancy loads in flight (the step is a dependent chain per ray: position -> cell -> bit -> next t); then classify
+        // ---- 1. classify
         unsigned elig = 0u;       // bit j: idle ray with a queued sample
         unsigned retire = 0u;     // bit j: the ray of slot j is over (dead, or marched to the end and drained)
+        unsigned want = 0u;       // bit j: the ray wants a marcher step (queue has room, march not over)
         bool pending = false;     // some slot may still become eligible without a tile being built
-        bool worked = false;      // this pass marched something
-#pragma unroll 1
-        for (int g = 0; g < R5_PER_LANE / R5_ILP; ++g) {
-            float tq[R5_ILP];
-            uint32_t cell[R5_ILP], ms[R5_ILP], st[R5_ILP], byte[R5_ILP];
-            int lvl[R5_ILP];
-            bool act[R5_ILP], live[R5_ILP];
+        {
+            int id[R5_PER_LANE];
+            uint32_t st[R5_PER_LANE], ms[R5_PER_LANE];
 #pragma unroll
-            for (int k = 0; k < R5_ILP; ++k) {
-                const int slot = slot0 + 32 * (g * R5_ILP + k);
-                live[k] = R.id[slot] >= 0;
-                st[k] = r5_ld_status(&R.status[slot]);
-                ms[k] = R.mstate[slot];
-                act[k] = live[k] && st[k] != R5_DEAD && !R5_MS_END(ms[k]) && R5_MS_CNT(ms[k]) < R5_FIFO;
-                tq[k] = 0.0f;
-                cell[k] = 0u;
-                lvl[k] = 0;
-                if (act[k]) {
-                    tq[k] = R.t[slot];
-                    if (!(tq[k] < R.far[slot]) || R5_MS_MARCHED(ms[k]) >= P.max_steps) {   // raymarching.cu:730
-                        ms[k] |= 1u << 25;
-                        R.mstate[slot] = ms[k];
-                        act[k] = false;
-                    } else {
-                        MarchRay r;
-                        r.ox = R.ox[slot]; r.oy = R.oy[slot]; r.oz = R.oz[slot];
-                        r.dx = R.dx[slot]; r.dy = R.dy[slot]; r.dz = R.dz[slot];
-                        float dt;
-                        cell[k] = ngp_march_cell_fast(r, cfg, tq[k], dt, lvl[k]);
-                    }
-                }
+            for (int j = 0; j < R5_PER_LANE; ++j) {
+                const int slot = slot0 + 32 * j;
+                id[j] = R.id[slot];
+                st[j] = r5_ld_status(&R.status[slot]);
+                ms[j] = R.mstate[slot];
             }
 #pragma unroll
-            for (int k = 0; k < R5_ILP; ++k) byte[k] = act[k] ? (uint32_t)__ldg(cfg.grid + (cell[k] >> 3)) : 0u;
+            for (int j = 0; j < R5_PER_LANE; ++j) {
+                if (id[j] < 0) continue;
+                const uint32_t cnt = R5_MS_CNT(ms[j]);
+                const bool end = R5_MS_END(ms[j]) != 0u;
+                if (st[j] != R5_DEAD && !end && cnt < R5_FIFO) want |= 1u << j;
+                if (st[j] == R5_IDLE && cnt > 0u) elig |= 1u << j;
+                else if (st[j] == R5_DEAD || (st[j] == R5_IDLE && end)) retire |= 1u << j;   // cnt == 0 here
+                else pending = true;   // in flight (comes back) or still marching
+            }
+        }
+        // ---- 2b. retire finished rays (their slots are refilled at the top of the next pass)
+        if (retire) pending = true;
+        while (retire) {
+            const int j = __ffs(retire) - 1;
+            retire &= retire - 1u;
+            const int slot = slot0 + 32 * j;
+            __threadfence_block();         // the chain thread wrote the accumulators before the status
+            r5_finish(R, P, slot, R.id[slot]);
+            evaluated += R.ncomp[slot];
+            if (rays_left) {
+                R.id[slot] = -1;
+                needs |= 1u << j;
+            } else {
+                R.id[slot] = -2;
+            }
+            r5_st_status(&R.status[slot], R5_IDLE);
+        }
+        // ---- 3. build this warp's part of tile n: R5_PART eligible slots, or all of them if nothing else can come
+        int E = __popc(elig);
 #pragma unroll
-            for (int k = 0; k < R5_ILP; ++k) {
-                const int j = g * R5_ILP + k;
-                const int slot = slot0 + 32 * j;
-                if (act[k]) {
-                    worked = true;
-                    uint32_t cnt = R5_MS_CNT(ms[k]), marched = R5_MS_MARCHED(ms[k]);
-                    const uint32_t head = R5_MS_HEAD(ms[k]);
-                    float tc = tq[k];
-                    if ((byte[k] >> (cell[k] & 7u)) & 1u) {
+        for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+        const bool any_pending = __any_sync(0xffffffffu, pending);
+        const bool any_want = __any_sync(0xffffffffu, want != 0u);
+        bool build = E >= R5_PART || !any_pending;
+        const int b = (int)(n & (R5_TBUF - 1));
+        if (build && n >= R5_TBUF) {
+            uint32_t ok = 0;
+            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> 2) - 1) & 1));
+            build = __shfl_sync(0xffffffffu, ok, 0) != 0u;     // buffer still in use: keep marching
+        }
+        if (build) {
+            R5Tile &T = S.tile[b];
+            int nrows = 0;
+#pragma unroll 1
+            for (int jj = 0; jj < R5_PER_LANE && nrows < R5_PART; ++jj) {
+                int j = jj + rot;
+                if (j >= R5_PER_LANE) j -= R5_PER_LANE;
+                const bool e = (elig >> j) & 1u;
+                const unsigned m = __ballot_sync(0xffffffffu, e);
+                const int row = nrows + __popc(m & lt_mask);
+                if (e && row < R5_PART) {
+                    const int slot = slot0 + 32 * j;
+                    const uint32_t ms = R.mstate[slot];
+                    const uint32_t head = R5_MS_HEAD(ms);
+                    const float st = R.qt[head][slot], sdt = R.qdt[head][slot];
+                    R.mstate[slot] = R5_MS_PACK(R5_MS_MARCHED(ms), R5_MS_CNT(ms) - 1u, (head + 1u) % R5_FIFO, R5_MS_END(ms));
+                    if (!R5_MS_END(ms)) want |= 1u << j;      // its queue has room again
+                    const float dxv = R.dx[slot], dyv = R.dy[slot], dzv = R.dz[slot];
+                    const int tr = w * R5_PART + row;
+                    T.x[tr] = ngp_clampf(fmaf(st, dxv, R.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
+                    T.y[tr] = ngp_clampf(fmaf(st, dyv, R.oy[slot]), -P.bound, P.bound);
+                    T.z[tr] = ngp_clampf(fmaf(st, dzv, R.oz[slot]), -P.bound, P.bound);
+                    T.dx[tr] = dxv; T.dy[tr] = dyv; T.dz[tr] = dzv;
+                    T.tn[tr] = st + sdt;
+                    T.dt[tr] = sdt;
+                    T.slot[tr] = (uint32_t)slot;
+                    r5_st_status(&R.status[slot], R5_BUSY);
+                }
+                nrows = min(R5_PART, nrows + __popc(m));
+            }
+            rot = rot + 5 >= R5_PER_LANE ? rot + 5 - R5_PER_LANE : rot + 5;
+            for (int row = nrows + lane; row < R5_PART; row += 32) T.slot[w * R5_PART + row] = R5_INVALID;
+            if (lane == 0) T.nrows[w] = nrows;
+            tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b]));
+            ++n;
+            if (nrows == 0) {
+                // this part is empty for good (every slot is out of rays).  The work ends with the first tile whose other
+                // parts are empty too; one more empty tile follows so that the roles of both TMEM slots see an end.
+                tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> 2) & 1));
+                if (r5_tile_end(T)) {
+                    const int b2 = (int)(n & (R5_TBUF - 1));
+                    if (n >= R5_TBUF) tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> 2) - 1) & 1));
+                    R5Tile &T2 = S.tile[b2];
+                    for (int row = lane; row < R5_PART; row += 32) T2.slot[w * R5_PART + row] = R5_INVALID;
+                    if (lane == 0) T2.nrows[w] = 0;
+                    tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b2]));
+                    ended = true;
+                }
+            }
+        } else if (!any_want) {
+            __nanosleep(200);   // nothing to march, nothing to build: rays are in flight — leave the issue slots to the others
+        }
+        if (ended) break;
+        // ---- 4. march: compact the slots that want a step, then walk the list
+        int nlist = 0;
+#pragma unroll
+        for (int j = 0; j < R5_PER_LANE; ++j) {
+            const bool wj = (want >> j) & 1u;
+            const unsigned m = __ballot_sync(0xffffffffu, wj);
+            if (wj) list[nlist + __popc(m & lt_mask)] = (uint16_t)(slot0 + 32 * j);
+            nlist += __popc(m);
+        }
+        __syncwarp();
+        // rolled software pipeline (one copy of the step in the instruction cache): the occupancy load of list entry i + 32 is
+        // issued before entry i is finished, so a lane has two loads in flight across the loop
+        {
+            bool have = false;
+            int slotA = 0, lvlA = 0;
+            float tqA = 0.0f;
+            uint32_t cellA = 0u, nxyzA = 0u, msA = 0u, byteA = 0u;
+#pragma unroll 1
+            for (int i = lane; have || i < nlist; i += 32) {
+                bool haveB = false;
+                int slotB = 0, lvlB = 0;
+                float tqB = 0.0f;
+                uint32_t cellB = 0u, nxyzB = 0u, msB = 0u, byteB = 0u;
+                if (i < nlist) {
+                    slotB = (int)list[i];
+                    msB = R.mstate[slotB];
+                    tqB = R.t[slotB];
+                    if (!(tqB < R.far[slotB]) || R5_MS_MARCHED(msB) >= P.max_steps) {   // raymarching.cu:730
+                        R.mstate[slotB] = msB | (1u << 25);
+                    } else {
+                        MarchRay r;
+                        r.ox = R.ox[slotB]; r.oy = R.oy[slotB]; r.oz = R.oz[slotB];
+                        r.dx = R.dx[slotB]; r.dy = R.dy[slotB]; r.dz = R.dz[slotB];
+                        float dt;
+                        cellB = ngp_march_cell_fast(r, cfg, S.miprb, tqB, dt, lvlB, nxyzB);
+                        byteB = (uint32_t)__ldg(cfg.grid + (cellB >> 3));
+                        haveB = true;
+                    }
+                }
+                if (have) {
+                    uint32_t cnt = R5_MS_CNT(msA), marched = R5_MS_MARCHED(msA);
+                    const uint32_t head = R5_MS_HEAD(msA);
+                    float tc = tqA;
+                    if ((byteA >> (cellA & 7u)) & 1u) {
                         const float dt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(tc * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
                         const uint32_t wpos = (head + cnt) % R5_FIFO;
-                        R.qt[wpos][slot] = tc;
-                        R.qdt[wpos][slot] = dt;
+                        R.qt[wpos][slotA] = tc;
+                        R.qdt[wpos][slotA] = dt;
                         tc += dt;
                         ++cnt;
                         ++marched;
                     } else {
                         MarchRay r;
-                        r.ox = R.ox[slot]; r.oy = R.oy[slot]; r.oz = R.oz[slot];
-                        r.dx = R.dx[slot]; r.dy = R.dy[slot]; r.dz = R.dz[slot];
-                        r.rdx = R.rdx[slot]; r.rdy = R.rdy[slot]; r.rdz = R.rdz[slot];
-                        const float tt = ngp_march_exit_fast(r, cfg, tc, cell[k], lvl[k]);
+                        r.ox = R.ox[slotA]; r.oy = R.oy[slotA]; r.oz = R.oz[slotA];
+                        r.dx = R.dx[slotA]; r.dy = R.dy[slotA]; r.dz = R.dz[slotA];
+                        r.rdx = R.rdx[slotA]; r.rdy = R.rdy[slotA]; r.rdz = R.rdz[slotA];
+                        const float tt = ngp_march_exit_fast(r, cfg, S.mipb, tc, nxyzA, lvlA);
                         if (cfg.lvl_dt >= 0) {   // dt_gamma == 0: the recurrence of ngp_march_advance is t += dt_min
                             do {
                                 tc += cfg.dt_min;
@@ -261,107 +378,13 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
                             } while (tc < tt);
                         }
                     }
-                    R.t[slot] = tc;
-                    ms[k] = R5_MS_PACK(marched, cnt, head, 0u);
-                    R.mstate[slot] = ms[k];
+                    R.t[slotA] = tc;
+                    R.mstate[slotA] = R5_MS_PACK(marched, cnt, head, 0u);
                 }
-                if (live[k]) {
-                    const uint32_t cnt = R5_MS_CNT(ms[k]);
-                    if (st[k] == R5_IDLE && cnt > 0u) elig |= 1u << j;
-                    else if (st[k] == R5_DEAD || (st[k] == R5_IDLE && R5_MS_END(ms[k]))) retire |= 1u << j;   // cnt == 0 here
-                    else pending = true;   // in flight (comes back) or still marching
-                }
+                have = haveB; slotA = slotB; lvlA = lvlB; tqA = tqB; cellA = cellB; nxyzA = nxyzB; msA = msB; byteA = byteB;
             }
         }
-        // ---- retire finished rays (their slots want a new ray at the top of the next pass)
-        needs = 0u;
-        if (retire) pending = true;        // the slot is refilled (or runs out of rays) next pass
-        while (retire) {
-            const int j = __ffs(retire) - 1;
-            retire &= retire - 1u;
-            const int slot = slot0 + 32 * j;
-            __threadfence_block();         // the chain thread wrote the accumulators before the status
-            r5_finish(R, P, slot, R.id[slot]);
-            evaluated += R.ncomp[slot];
-            R.id[slot] = -1;
-            r5_st_status(&R.status[slot], R5_IDLE);
-            needs |= 1u << j;
-        }
-        if (!rays_left && needs) {         // nothing to refill with: the slots are out of the game
-            unsigned m = needs;
-            while (m) {
-                const int j = __ffs(m) - 1;
-                m &= m - 1u;
-                R.id[slot0 + 32 * j] = -2;
-            }
-            needs = 0u;
-        }
-        int E = __popc(elig);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
-        const bool any_pending = __any_sync(0xffffffffu, pending);
-        const bool any_worked = __any_sync(0xffffffffu, worked);
-        if (E < R5_PART && any_pending) {
-            if (!any_worked) __nanosleep(200);   // waiting for rays in flight: leave the issue slots to the other roles
-            continue;
-        }
-        // ---- build this warp's part of tile n (all eligible slots if fewer than R5_PART: nothing else can come)
-        const int b = (int)(n & (R5_TBUF - 1));
-        if (n >= R5_TBUF) {
-            uint32_t ok = 0;
-            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> 2) - 1) & 1));
-            if (!__shfl_sync(0xffffffffu, ok, 0)) {           // buffer still in use: keep marching
-                if (!any_worked) __nanosleep(200);
-                continue;
-            }
-        }
-        R5Tile &T = S.tile[b];
-        int nrows = 0;
-#pragma unroll 1
-        for (int jj = 0; jj < R5_PER_LANE && nrows < R5_PART; ++jj) {
-            int j = jj + rot;
-            if (j >= R5_PER_LANE) j -= R5_PER_LANE;
-            const bool e = (elig >> j) & 1u;
-            const unsigned m = __ballot_sync(0xffffffffu, e);
-            const int row = nrows + __popc(m & lt_mask);
-            if (e && row < R5_PART) {
-                const int slot = slot0 + 32 * j;
-                const uint32_t ms = R.mstate[slot];
-                const uint32_t head = R5_MS_HEAD(ms);
-                const float st = R.qt[head][slot], sdt = R.qdt[head][slot];
-                R.mstate[slot] = R5_MS_PACK(R5_MS_MARCHED(ms), R5_MS_CNT(ms) - 1u, (head + 1u) % R5_FIFO, R5_MS_END(ms));
-                const float dxv = R.dx[slot], dyv = R.dy[slot], dzv = R.dz[slot];
-                const int tr = w * R5_PART + row;
-                T.x[tr] = ngp_clampf(fmaf(st, dxv, R.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
-                T.y[tr] = ngp_clampf(fmaf(st, dyv, R.oy[slot]), -P.bound, P.bound);
-                T.z[tr] = ngp_clampf(fmaf(st, dzv, R.oz[slot]), -P.bound, P.bound);
-                T.dx[tr] = dxv; T.dy[tr] = dyv; T.dz[tr] = dzv;
-                T.tn[tr] = st + sdt;
-                T.dt[tr] = sdt;
-                T.slot[tr] = (uint32_t)slot;
-                r5_st_status(&R.status[slot], R5_BUSY);
-            }
-            nrows = min(R5_PART, nrows + __popc(m));
-        }
-        rot = rot + 5 >= R5_PER_LANE ? rot + 5 - R5_PER_LANE : rot + 5;
-        for (int row = nrows + lane; row < R5_PART; row += 32) T.slot[w * R5_PART + row] = R5_INVALID;
-        if (lane == 0) T.nrows[w] = nrows;
-        tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b]));
-        ++n;
-        if (nrows == 0) {
-            // this part is empty for good (every slot is out of rays).  The work ends with the first tile whose other parts
-            // are empty too; one more empty tile follows so that the roles of both TMEM slots see an end.
-            tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> 2) & 1));
-            if (r5_tile_end(T)) {
-                const int b2 = (int)(n & (R5_TBUF - 1));
-                if (n >= R5_TBUF) tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> 2) - 1) & 1));
-                R5Tile &T2 = S.tile[b2];
-                for (int row = lane; row < R5_PART; row += 32) T2.slot[w * R5_PART + row] = R5_INVALID;
-                if (lane == 0) T2.nrows[w] = 0;
-                tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b2]));
-                break;
-            }
-        }
+        __syncwarp();
     }
     if (P.nsamples) {
 #pragma unroll
@@ -582,6 +605,10 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
             tc5::mbar_init(tc5::smem_u32(&S.tb.rows_free[b]), 128);
         }
         tc5::fence_mbar_init();
+    }
+    if (tid < 8) {
+        S.mipb[tid] = fminf((float)(1 << tid), cfg.bound);
+        S.miprb[tid] = 1.0f / S.mipb[tid];
     }
     if (warp == C5_MMA_WARP) tc5::tmem_alloc(tc5::smem_u32(&S.tmem), 512);
     tc5::fence_async_smem();

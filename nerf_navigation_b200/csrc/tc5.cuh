@@ -109,9 +109,9 @@ __device__ __forceinline__ bool mbar_try(uint32_t bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-// wait with a watchdog: a protocol bug traps after ~2 s instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
-    if (mbar_try(bar, parity)) return;
+// wait with a watchdog: a protocol bug traps after ~2 s instead of hanging the GPU.  The spin loop is out of line so that
+// the many wait sites of the warp-specialised kernels cost two instructions each in the instruction cache.
+static __device__ __noinline__ void mbar_spin_wd(uint32_t bar, uint32_t parity) {
     const long long t0 = clock64();
     while (!mbar_try(bar, parity)) {
         if (clock64() - t0 > 4000000000ll) {
@@ -119,6 +119,9 @@ __device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
             __trap();
         }
     }
+}
+__device__ __forceinline__ void mbar_wait_wd(uint32_t bar, uint32_t parity) {
+    if (!mbar_try(bar, parity)) mbar_spin_wd(bar, parity);
 }
 
 // instruction descriptor for kind::tf32: tf32 A/B (fp32 containers, low 13 mantissa bits ignored), fp32 accumulate
