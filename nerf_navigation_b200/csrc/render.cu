@@ -247,7 +247,7 @@ k_render_rays_infer(RenderRaysParams P, MarchCfg cfg, const int32_t *__restrict_
     else ri_run<false>(S, P, cfg);
 }
 
-extern "C" int64_t ngp_render_rays_infer_workspace_bytes(void) { return 16; }
+extern "C" int64_t ngp_render_rays_infer_workspace_bytes(void) { return 16 + 24 * 8; }   // counter, samples, 24 dev statistics
 
 // default implementation: the warp-specialised tcgen05 kernel of render5.cu; NGP_B200_FIELD_IMPL=mma / ngp_set_field_impl(0)
 // selects the mma.sync kernel above (kept as the independent cross-check)
@@ -276,7 +276,7 @@ extern "C" int ngp_render_rays_infer(const float *rays_o, const float *rays_d, i
     NGP_REQUIRE(bg_stride == 0 || bg_stride == 3, NGP_ERR_ARG, "ngp_render_rays_infer: bg_stride must be 0 or 3");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0 && ((uintptr_t)workspace & 7u) == 0, NGP_ERR_ARG,
                 "ngp_render_rays_infer: embeddings must be 16-byte aligned, workspace 8-byte aligned");
-    if (cudaMemsetAsync(workspace, 0, 16, (cudaStream_t)stream) != cudaSuccess) {
+    if (cudaMemsetAsync(workspace, 0, 16 + 24 * 8, (cudaStream_t)stream) != cudaSuccess) {
         ngp_set_error("ngp_render_rays_infer: workspace memset failed");
         return NGP_ERR_CUDA;
     }

@@ -24,25 +24,35 @@
 #include "cfield5.cuh"
 #include "march.cuh"
 
-#define R5_MARCH_WARP0 (C5_MMA_WARP + 2)                       // warps 14 .. 17
-#define R5_MARCH_WARPS 4
-#define R5_THREADS ((R5_MARCH_WARP0 + R5_MARCH_WARPS) * 32)    // 576 (<= 112 registers per thread)
+#define R5_MARCH_WARP0 (C5_MMA_WARP + 2)                       // warps 14 .. 21
+#ifndef R5_MARCH_WARPS
+#define R5_MARCH_WARPS 8
+#endif
+#define R5_THREADS ((R5_MARCH_WARP0 + R5_MARCH_WARPS) * 32)    // 704 (80 registers per thread)
 #ifndef R5_PER_LANE
-#define R5_PER_LANE 6                                          // ray slots per marcher lane
+#define R5_PER_LANE (24 / R5_MARCH_WARPS)                      // ray slots per marcher lane (768 slots per CTA)
 #endif
 #define R5_PER_WARP (32 * R5_PER_LANE)
 #define R5_NR (R5_MARCH_WARPS * R5_PER_WARP)                   // 768 ray slots per CTA
 #define R5_PART (C5_ROWS / R5_MARCH_WARPS)                     // tile rows built by one marcher warp (32)
 #define R5_FIFO 4                                              // queued samples per ray slot
-#define R5_TBUF 4                                              // tile row buffers (tile n: buffer n & 3, TMEM slot n & 1)
-#ifndef R5_ILP
-#define R5_ILP 3                                               // ray slots a marcher lane steps concurrently
+#ifndef R5_TBUF_LOG2
+#define R5_TBUF_LOG2 3
+#endif
+#define R5_TBUF (1 << R5_TBUF_LOG2)                             // tile row buffers (tile n: buffer n % R5_TBUF, TMEM slot n & 1)
+#ifndef R5_INFLIGHT
+#define R5_INFLIGHT 2                                          // samples of one ray that may be in flight (in consecutive tiles)
+#endif
+#ifndef R5_BUDGET
+#define R5_BUDGET 2                                            // marcher steps a ray may take per pass
 #endif
 #define R5_INVALID 0xffffffffu
 // ray-slot status (written by the marcher when idle, by the chain thread while the sample is in flight)
+// ray-slot status word: bits 0-1 = samples in flight (the marcher adds one per issued sample, the chain thread takes it off
+// after compositing: shared-memory atomics), bit 2 = the ray saw T < 1e-4 and is over (later samples are not composited)
 #define R5_IDLE 0u
-#define R5_BUSY 1u
-#define R5_DEAD 2u   // composited with T < 1e-4: the ray is over
+#define R5_DEAD 4u
+#define R5_NFLY(st) ((st) & 3u)
 
 // marcher-private state word: samples queued so far (20 bits) | FIFO fill (3) | FIFO head (2) | march ended (1)
 #define R5_MS_MARCHED(m) ((m) & 0xfffffu)
@@ -50,6 +60,33 @@
 #define R5_MS_HEAD(m) (((m) >> 23) & 3u)
 #define R5_MS_END(m) (((m) >> 25) & 1u)
 #define R5_MS_PACK(marched, cnt, head, end) ((marched) | ((cnt) << 20) | ((head) << 23) | ((end) << 25))
+
+// -DR5_STATS=1: per-role cycle accounting (dev aid, scripts/check_r5.py prints it): every wait is timed with clock64 by
+// lane 0 of the warp and summed into workspace[2 + index]
+#ifndef R5_STATS
+#define R5_STATS 0
+#endif
+#if R5_STATS
+#define R5_STAT_DECL long long stat_[24] = {0}
+#define R5_WAIT(bar, par, idx)                       \
+    do {                                             \
+        const long long t0_ = clock64();             \
+        tc5::mbar_wait_wd((bar), (par));             \
+        stat_[idx] += clock64() - t0_;               \
+    } while (0)
+#define R5_STAT_ADD(idx, v) stat_[idx] += (long long)(v)
+#define R5_STAT_FLUSH(P, lane)                                                                       \
+    do {                                                                                             \
+        if ((lane) == 0)                                                                             \
+            for (int q_ = 0; q_ < 24; ++q_)                                                          \
+                if (stat_[q_]) atomicAdd((P).counter + 2 + q_, (unsigned long long)stat_[q_]);       \
+    } while (0)
+#else
+#define R5_STAT_DECL
+#define R5_WAIT(bar, par, idx) tc5::mbar_wait_wd((bar), (par))
+#define R5_STAT_ADD(idx, v)
+#define R5_STAT_FLUSH(P, lane)
+#endif
 
 struct R5Tile {
     float x[C5_ROWS], y[C5_ROWS], z[C5_ROWS];        // sample position (the marcher's clamped o + t d)
@@ -173,7 +210,10 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
     int rot = 0;
     unsigned needs = (1u << R5_PER_LANE) - 1u;      // bit j: slot j of this lane wants a ray
     bool ended = false;
+    R5_STAT_DECL;
+    R5_STAT_ADD(17, -clock64());
     for (;;) {
+        R5_STAT_ADD(13, 1);
         // ---- 2a. refill the slots that want a ray: one atomic per warp
         if (!rays_left) needs = 0u;
         if (__any_sync(0xffffffffu, needs != 0u)) {
@@ -222,9 +262,11 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
                 if (id[j] < 0) continue;
                 const uint32_t cnt = R5_MS_CNT(ms[j]);
                 const bool end = R5_MS_END(ms[j]) != 0u;
-                if (st[j] != R5_DEAD && !end && cnt < R5_FIFO) want |= 1u << j;
-                if (st[j] == R5_IDLE && cnt > 0u) elig |= 1u << j;
-                else if (st[j] == R5_DEAD || (st[j] == R5_IDLE && end)) retire |= 1u << j;   // cnt == 0 here
+                const bool dead = (st[j] & R5_DEAD) != 0u;
+                const uint32_t fly = R5_NFLY(st[j]);
+                if (!dead && !end && cnt < R5_FIFO) want |= 1u << j;
+                if (!dead && fly < R5_INFLIGHT && cnt > 0u) elig |= 1u << j;
+                else if (fly == 0u && (dead || (end && cnt == 0u))) retire |= 1u << j;
                 else pending = true;   // in flight (comes back) or still marching
             }
         }
@@ -252,11 +294,14 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
         const bool any_pending = __any_sync(0xffffffffu, pending);
         const bool any_want = __any_sync(0xffffffffu, want != 0u);
         bool build = E >= R5_PART || !any_pending;
+        if (!build) R5_STAT_ADD(15, 1);
+        R5_STAT_ADD(20, E);
         const int b = (int)(n & (R5_TBUF - 1));
         if (build && n >= R5_TBUF) {
             uint32_t ok = 0;
-            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> 2) - 1) & 1));
+            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> R5_TBUF_LOG2) - 1) & 1));
             build = __shfl_sync(0xffffffffu, ok, 0) != 0u;     // buffer still in use: keep marching
+            if (!build) R5_STAT_ADD(16, 1);
         }
         if (build) {
             R5Tile &T = S.tile[b];
@@ -284,22 +329,24 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
                     T.tn[tr] = st + sdt;
                     T.dt[tr] = sdt;
                     T.slot[tr] = (uint32_t)slot;
-                    r5_st_status(&R.status[slot], R5_BUSY);
+                    atomicAdd(&R.status[slot], 1u);
                 }
                 nrows = min(R5_PART, nrows + __popc(m));
             }
-            rot = rot + 5 >= R5_PER_LANE ? rot + 5 - R5_PER_LANE : rot + 5;
+            rot = rot + 1 >= R5_PER_LANE ? 0 : rot + 1;
             for (int row = nrows + lane; row < R5_PART; row += 32) T.slot[w * R5_PART + row] = R5_INVALID;
             if (lane == 0) T.nrows[w] = nrows;
             tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b]));
             ++n;
+            R5_STAT_ADD(14, 1);
+            R5_STAT_ADD(21, nrows);
             if (nrows == 0) {
                 // this part is empty for good (every slot is out of rays).  The work ends with the first tile whose other
                 // parts are empty too; one more empty tile follows so that the roles of both TMEM slots see an end.
-                tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> 2) & 1));
+                R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> R5_TBUF_LOG2) & 1), 18);
                 if (r5_tile_end(T)) {
                     const int b2 = (int)(n & (R5_TBUF - 1));
-                    if (n >= R5_TBUF) tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> 2) - 1) & 1));
+                    if (n >= R5_TBUF) tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> R5_TBUF_LOG2) - 1) & 1));
                     R5Tile &T2 = S.tile[b2];
                     for (int row = lane; row < R5_PART; row += 32) T2.slot[w * R5_PART + row] = R5_INVALID;
                     if (lane == 0) T2.nrows[w] = 0;
@@ -320,68 +367,88 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
             if (wj) list[nlist + __popc(m & lt_mask)] = (uint16_t)(slot0 + 32 * j);
             nlist += __popc(m);
         }
+        R5_STAT_ADD(19, nlist);
         __syncwarp();
-        // rolled software pipeline (one copy of the step in the instruction cache): the occupancy load of list entry i + 32 is
-        // issued before entry i is finished, so a lane has two loads in flight across the loop
+        // Each lane walks its share of the list (entries lane, lane + 32, ...) with TWO rays in hand, alternating between them
+        // every iteration: while the occupancy load of one is in flight the other's step is finished and its next load
+        // issued (rolled: one copy of the step in the instruction cache).  A ray keeps its chain for up to R5_BUDGET steps
+        // or until its queue is full, so a pass moves a ray through several empty voxels and the per-pass bookkeeping
+        // (classification, compaction, tile building) is paid once per several steps.
         {
-            bool have = false;
-            int slotA = 0, lvlA = 0;
-            float tqA = 0.0f;
-            uint32_t cellA = 0u, nxyzA = 0u, msA = 0u, byteA = 0u;
+            int i = lane;
+            bool haveA = false, haveB = false;
+            int slotA = 0, lvlA = 0, stepsA = 0, slotB = 0, lvlB = 0, stepsB = 0;
+            float tA = 0.0f, tB = 0.0f;
+            uint32_t cellA = 0u, nxyzA = 0u, msA = 0u, byteA = 0u, cellB = 0u, nxyzB = 0u, msB = 0u, byteB = 0u;
 #pragma unroll 1
-            for (int i = lane; have || i < nlist; i += 32) {
-                bool haveB = false;
-                int slotB = 0, lvlB = 0;
-                float tqB = 0.0f;
-                uint32_t cellB = 0u, nxyzB = 0u, msB = 0u, byteB = 0u;
-                if (i < nlist) {
-                    slotB = (int)list[i];
-                    msB = R.mstate[slotB];
-                    tqB = R.t[slotB];
-                    if (!(tqB < R.far[slotB]) || R5_MS_MARCHED(msB) >= P.max_steps) {   // raymarching.cu:730
-                        R.mstate[slotB] = msB | (1u << 25);
-                    } else {
-                        MarchRay r;
-                        r.ox = R.ox[slotB]; r.oy = R.oy[slotB]; r.oz = R.oz[slotB];
-                        r.dx = R.dx[slotB]; r.dy = R.dy[slotB]; r.dz = R.dz[slotB];
-                        float dt;
-                        cellB = ngp_march_cell_fast(r, cfg, S.miprb, tqB, dt, lvlB, nxyzB);
-                        byteB = (uint32_t)__ldg(cfg.grid + (cellB >> 3));
-                        haveB = true;
-                    }
-                }
-                if (have) {
-                    uint32_t cnt = R5_MS_CNT(msA), marched = R5_MS_MARCHED(msA);
-                    const uint32_t head = R5_MS_HEAD(msA);
-                    float tc = tqA;
+            for (;;) {
+                if (haveA) {   // finish the step whose load was issued two iterations ago
                     if ((byteA >> (cellA & 7u)) & 1u) {
-                        const float dt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(tc * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
-                        const uint32_t wpos = (head + cnt) % R5_FIFO;
-                        R.qt[wpos][slotA] = tc;
+                        const float dt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(tA * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+                        const uint32_t wpos = (R5_MS_HEAD(msA) + R5_MS_CNT(msA)) % R5_FIFO;
+                        R.qt[wpos][slotA] = tA;
                         R.qdt[wpos][slotA] = dt;
-                        tc += dt;
-                        ++cnt;
-                        ++marched;
+                        tA += dt;
+                        msA += (1u << 20) + 1u;   // one more queued, one more marched
                     } else {
                         MarchRay r;
                         r.ox = R.ox[slotA]; r.oy = R.oy[slotA]; r.oz = R.oz[slotA];
                         r.dx = R.dx[slotA]; r.dy = R.dy[slotA]; r.dz = R.dz[slotA];
                         r.rdx = R.rdx[slotA]; r.rdy = R.rdy[slotA]; r.rdz = R.rdz[slotA];
-                        const float tt = ngp_march_exit_fast(r, cfg, S.mipb, tc, nxyzA, lvlA);
+                        const float tt = ngp_march_exit_fast(r, cfg, S.mipb, tA, nxyzA, lvlA);
                         if (cfg.lvl_dt >= 0) {   // dt_gamma == 0: the recurrence of ngp_march_advance is t += dt_min
                             do {
-                                tc += cfg.dt_min;
-                            } while (tc < tt);
+                                tA += cfg.dt_min;
+                            } while (tA < tt);
                         } else {
                             do {
-                                tc = ngp_march_advance(tc, cfg);
-                            } while (tc < tt);
+                                tA = ngp_march_advance(tA, cfg);
+                            } while (tA < tt);
                         }
                     }
-                    R.t[slotA] = tc;
-                    R.mstate[slotA] = R5_MS_PACK(marched, cnt, head, 0u);
+                    --stepsA;
+                    bool go = stepsA > 0 && R5_MS_CNT(msA) < R5_FIFO;
+                    if (go && (!(tA < R.far[slotA]) || R5_MS_MARCHED(msA) >= P.max_steps)) {   // raymarching.cu:730
+                        msA |= 1u << 25;
+                        go = false;
+                    }
+                    if (!go) {
+                        R.t[slotA] = tA;
+                        R.mstate[slotA] = msA;
+                        haveA = false;
+                    }
                 }
-                have = haveB; slotA = slotB; lvlA = lvlB; tqA = tqB; cellA = cellB; nxyzA = nxyzB; msA = msB; byteA = byteB;
+                if (!haveA && i < nlist) {   // take the next list entry
+                    slotA = (int)list[i];
+                    i += 32;
+                    msA = R.mstate[slotA];
+                    tA = R.t[slotA];
+                    stepsA = R5_BUDGET;
+                    if (!(tA < R.far[slotA]) || R5_MS_MARCHED(msA) >= P.max_steps) R.mstate[slotA] = msA | (1u << 25);
+                    else haveA = true;
+                }
+                if (haveA) {                 // issue the occupancy load of the ray's current cell
+                    MarchRay r;
+                    r.ox = R.ox[slotA]; r.oy = R.oy[slotA]; r.oz = R.oz[slotA];
+                    r.dx = R.dx[slotA]; r.dy = R.dy[slotA]; r.dz = R.dz[slotA];
+                    float dt;
+                    cellA = ngp_march_cell_fast(r, cfg, S.miprb, tA, dt, lvlA, nxyzA);
+                    byteA = (uint32_t)__ldg(cfg.grid + (cellA >> 3));
+                }
+                if (!haveA && !haveB && i >= nlist) break;
+                // swap the two chains — unless the other one is idle and there is nothing left to give it (then this lane
+                // keeps stepping its one ray instead of spending every other iteration on an empty chain)
+                if (haveB || i < nlist) {
+                    { const bool h = haveA; haveA = haveB; haveB = h; }
+                    { const int v = slotA; slotA = slotB; slotB = v; }
+                    { const int v = lvlA; lvlA = lvlB; lvlB = v; }
+                    { const int v = stepsA; stepsA = stepsB; stepsB = v; }
+                    { const float v = tA; tA = tB; tB = v; }
+                    { const uint32_t v = cellA; cellA = cellB; cellB = v; }
+                    { const uint32_t v = nxyzA; nxyzA = nxyzB; nxyzB = v; }
+                    { const uint32_t v = msA; msA = msB; msB = v; }
+                    { const uint32_t v = byteA; byteA = byteB; byteB = v; }
+                }
             }
         }
         __syncwarp();
@@ -391,6 +458,8 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
         for (int o2 = 16; o2 > 0; o2 >>= 1) evaluated += __shfl_xor_sync(0xffffffffu, evaluated, o2);
         if (lane == 0 && evaluated) atomicAdd(P.nsamples, evaluated);
     }
+    R5_STAT_ADD(17, clock64());
+    R5_STAT_FLUSH(P, lane);
 }
 
 // ------------------------------------------------------------------------------------------------ gather warps
@@ -400,10 +469,12 @@ __device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t
     const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
     const uint32_t bar_full = tc5::smem_u32(&S.bars[s].f_full), bar_empty = tc5::smem_u32(&S.bars[s].f_empty);
     const float den = 2.0f * P.bound;
+    R5_STAT_DECL;
+    R5_STAT_ADD(2, -clock64());
     for (int64_t it = 0;; ++it) {
         const int64_t n = 2 * it + s;
         const int b = (int)(n & (R5_TBUF - 1));
-        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> 2) & 1));
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> R5_TBUF_LOG2) & 1), 0);
         const R5Tile &T = S.tile[b];
         if (r5_tile_end(T)) break;
         bool valid = T.slot[row] != R5_INVALID;
@@ -419,7 +490,7 @@ __device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t
             float feat[4];
             c5_encode_pair<SAFE>(P.table, S.lv, lp, x01, valid, P.align_corners, feat);
             if (lp == 0) {
-                if (it > 0) tc5::mbar_wait_wd(bar_empty, (uint32_t)((it - 1) & 1));
+                if (it > 0) R5_WAIT(bar_empty, (uint32_t)((it - 1) & 1), 1);
                 tc5::fence_after_sync();
             }
             c5_put_features(lane_addr, lp, feat);
@@ -428,10 +499,14 @@ __device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t
         tc5::fence_before_sync();
         tc5::mbar_arrive(bar_full);
     }
+    R5_STAT_ADD(2, clock64());
+    R5_STAT_FLUSH(P, lane);
 }
 
 // ------------------------------------------------------------------------------------------------ MMA threads
-__device__ __forceinline__ void r5_mma(R5Smem &S, uint32_t tmem, int s) {
+__device__ __forceinline__ void r5_mma(R5Smem &S, const R5Params &P, uint32_t tmem, int s) {
+    R5_STAT_DECL;
+    R5_STAT_ADD(7, -clock64());
     const uint32_t t = tmem + s * C5_SLOT_COLS;
     const uint32_t bar_ff = tc5::smem_u32(&S.bars[s].f_full), bar_fe = tc5::smem_u32(&S.bars[s].f_empty),
                    bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready),
@@ -443,32 +518,34 @@ __device__ __forceinline__ void r5_mma(R5Smem &S, uint32_t tmem, int s) {
     for (int64_t it = 0;; ++it) {
         const int64_t n = 2 * it + s;
         const int b = (int)(n & (R5_TBUF - 1));
-        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> 2) & 1));
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> R5_TBUF_LOG2) & 1), 3);
         if (r5_tile_end(S.tile[b])) break;
         const uint32_t pa = (uint32_t)(4 * it);
-        tc5::mbar_wait_wd(bar_ff, (uint32_t)(it & 1));
-        if (it > 0) tc5::mbar_wait_wd(bar_t, (uint32_t)((it - 1) & 1));
+        R5_WAIT(bar_ff, (uint32_t)(it & 1), 4);
+        if (it > 0) R5_WAIT(bar_t, (uint32_t)((it - 1) & 1), 5);
         tc5::fence_after_sync();
         c5_issue_layer<64, 32>(t + C5_D, t + C5_FHI, t + C5_FLO, s0h, s0l);   // sigma L1: features -> 64
         tc5::mma_commit(bar_fe);
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u);
+        R5_WAIT(bar_a, (pa + 0u) & 1u, 6);
         tc5::fence_after_sync();
         c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, s1h, s1l);   // sigma L2: 64 -> 16
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u);
+        R5_WAIT(bar_a, (pa + 1u) & 1u, 6);
         tc5::fence_after_sync();
         c5_issue_layer<64, 32>(t + C5_D, t + C5_HHI, t + C5_HLO, c0h, c0l);   // colour L1: [SH | o] (32) -> 64
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u);
+        R5_WAIT(bar_a, (pa + 2u) & 1u, 6);
         tc5::fence_after_sync();
         c5_issue_layer<64, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c1h, c1l);   // colour L2: 64 -> 64
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u);
+        R5_WAIT(bar_a, (pa + 3u) & 1u, 6);
         tc5::fence_after_sync();
         c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c2h, c2l);   // colour L3: 64 -> 3 (16)
         tc5::mma_commit(bar_d);
     }
+    R5_STAT_ADD(7, clock64());
+    R5_STAT_FLUSH(P, 0);
 }
 
 // ------------------------------------------------------------------------------------------------ chain warps
@@ -482,20 +559,24 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
     R5Rays &R = S.rays;
     int64_t n0 = 0;
     uint32_t group = 0;
+    R5_STAT_DECL;
+    R5_STAT_ADD(10, -clock64());
     for (;;) {
-        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_full[n0 & (R5_TBUF - 1)]), (uint32_t)((n0 >> 2) & 1));
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[n0 & (R5_TBUF - 1)]), (uint32_t)((n0 >> R5_TBUF_LOG2) & 1), 8);
         if (r5_tile_end(S.tile[n0 & (R5_TBUF - 1)])) break;
         // one decision for the four chain warps (they hand the same tiles to the MMA threads step by step, so taking a tile
         // in one warp and not in another would deadlock): the first chain warp tests, the others read its verdict
         if (warp == C5_CHAIN_WARP0 && lane == 0) {
             const int64_t n1 = n0 + 1;
-            bool ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_full[n1 & (R5_TBUF - 1)]), (uint32_t)((n1 >> 2) & 1));
+            bool ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_full[n1 & (R5_TBUF - 1)]), (uint32_t)((n1 >> R5_TBUF_LOG2) & 1));
             if (ok && r5_tile_end(S.tile[n1 & (R5_TBUF - 1)])) ok = false;
             S.chain_two[group & 1] = ok ? 1 : 0;
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
         const int n_act = S.chain_two[group & 1] ? 2 : 1;
         ++group;
+        R5_STAT_ADD(12, 1);
+        R5_STAT_ADD(11, n_act - 1);
 #define R5_TILE_VARS                                                                                \
         const int64_t n = n0 + i;                                                                   \
         const int s = (int)(n & 1);                                                                 \
@@ -508,7 +589,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
         for (int i = 0; i < n_act; ++i) {
             R5_TILE_VARS
             (void)T;
-            tc5::mbar_wait_wd(bar_d, (par + 0u) & 1u);
+            R5_WAIT(bar_d, (par + 0u) & 1u, 9);
             tc5::fence_after_sync();
             c5_relu_to_a<false>(lane_addr);
             c5_chain_arrive(bar_a);
@@ -518,7 +599,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
         for (int i = 0; i < n_act; ++i) {
             R5_TILE_VARS
             const float dir[3] = {T.dx[row], T.dy[row], T.dz[row]};
-            tc5::mbar_wait_wd(bar_d, (par + 1u) & 1u);
+            R5_WAIT(bar_d, (par + 1u) & 1u, 9);
             tc5::fence_after_sync();
             float o[16];
             c5_get16(lane_addr, 0, o);
@@ -537,7 +618,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
             for (int i = 0; i < n_act; ++i) {
                 R5_TILE_VARS
                 (void)T;
-                tc5::mbar_wait_wd(bar_d, (par + 2u + (uint32_t)k) & 1u);
+                R5_WAIT(bar_d, (par + 2u + (uint32_t)k) & 1u, 9);
                 tc5::fence_after_sync();
                 c5_relu_to_a<false>(lane_addr);
                 c5_chain_arrive(bar_a);
@@ -550,7 +631,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
             (void)bar_a;
             const uint32_t slot = T.slot[row];
             const float tn = T.tn[row], sdt = T.dt[row], lsig = T.lsig[row];
-            tc5::mbar_wait_wd(bar_d, (par + 4u) & 1u);
+            R5_WAIT(bar_d, (par + 4u) & 1u, 9);
             tc5::fence_after_sync();
             uint32_t lg[4];
             tc5::tmem_ld4_nowait(lane_addr + C5_D, lg);
@@ -558,28 +639,37 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
             tc5::fence_before_sync();
             tc5::mbar_arrive(tc5::smem_u32(&S.bars[s].t_free));
             if (slot != R5_INVALID) {
-                const float sigma = expf(lsig) * P.density_scale;   // trunc_exp fwd; renderer.py:355
-                const float cr = 1.0f / (1.0f + expf(-__uint_as_float(lg[0])));
-                const float cg = 1.0f / (1.0f + expf(-__uint_as_float(lg[1])));
-                const float cb = 1.0f / (1.0f + expf(-__uint_as_float(lg[2])));
-                const float ws = R.ws[slot];
-                const float alpha = 1.0f - __expf(-sigma * sdt);
-                const float Tr = 1.0f - ws;
-                const float wgt = alpha * Tr;
-                R.ws[slot] = ws + wgt;
-                R.depth[slot] = fmaf(wgt, tn, R.depth[slot]);
-                R.r[slot] = fmaf(wgt, cr, R.r[slot]);
-                R.g[slot] = fmaf(wgt, cg, R.g[slot]);
-                R.b[slot] = fmaf(wgt, cb, R.b[slot]);
-                R.ncomp[slot] += 1u;
+                bool dead = (r5_ld_status(&R.status[slot]) & R5_DEAD) != 0u;   // an earlier sample of the ray ended it
+                if (!dead) {
+                    const float sigma = expf(lsig) * P.density_scale;   // trunc_exp fwd; renderer.py:355
+                    const float cr = 1.0f / (1.0f + expf(-__uint_as_float(lg[0])));
+                    const float cg = 1.0f / (1.0f + expf(-__uint_as_float(lg[1])));
+                    const float cb = 1.0f / (1.0f + expf(-__uint_as_float(lg[2])));
+                    const float ws = R.ws[slot];
+                    const float alpha = 1.0f - __expf(-sigma * sdt);
+                    const float Tr = 1.0f - ws;
+                    const float wgt = alpha * Tr;
+                    R.ws[slot] = ws + wgt;
+                    R.depth[slot] = fmaf(wgt, tn, R.depth[slot]);
+                    R.r[slot] = fmaf(wgt, cr, R.r[slot]);
+                    R.g[slot] = fmaf(wgt, cg, R.g[slot]);
+                    R.b[slot] = fmaf(wgt, cb, R.b[slot]);
+                    R.ncomp[slot] += 1u;
+                    dead = (double)Tr < 1e-4;   // :880 — the sample that saw T < 1e-4 is still accumulated, then the ray is over
+                }
                 __threadfence_block();
-                // :880 — the sample that saw T < 1e-4 is still accumulated, then the ray is over
-                r5_st_status(&R.status[slot], (double)Tr < 1e-4 ? R5_DEAD : R5_IDLE);
+                if (dead) atomicOr(&R.status[slot], R5_DEAD);
+                atomicAdd(&R.status[slot], 0xffffffffu);   // one sample fewer in flight (after the flag: the marcher retires at 0)
             }
+            // the two samples a ray may have in flight sit in consecutive tiles and in the same 32-row band (its marcher
+            // warp's rows), i.e. this warp composites both, one after the other: order and visibility between its lanes
+            __syncwarp();
             tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_free[n & (R5_TBUF - 1)]));
         }
         n0 += n_act;
     }
+    R5_STAT_ADD(10, clock64());
+    R5_STAT_FLUSH(P, lane);
 }
 
 __global__ void __launch_bounds__(R5_THREADS, 1)
@@ -623,7 +713,7 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
     } else if (warp < C5_MMA_WARP) {
         r5_chain(S, P, tmem, warp, lane);
     } else if (warp < R5_MARCH_WARP0) {
-        if (lane == 0) r5_mma(S, tmem, warp - C5_MMA_WARP);
+        if (lane == 0) r5_mma(S, P, tmem, warp - C5_MMA_WARP);
         __syncwarp();
     } else {
         r5_marcher(S, P, cfg, warp - R5_MARCH_WARP0, lane);

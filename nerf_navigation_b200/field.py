@@ -158,7 +158,7 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
             bg = bg.reshape(3).contiguous()
         else:
             bg, stride = bg.expand(N, 3).contiguous(), 3
-    work = torch.empty(2, device=dev, dtype=torch.int64)
+    work = torch.empty(_lib.lib().ngp_render_rays_infer_workspace_bytes() // 8, device=dev, dtype=torch.int64)
     counts = torch.empty(N, device=dev, dtype=torch.int32) if return_counts else None
     ws = [w.detach().contiguous() for w in (model.sigma_net[0].weight, model.sigma_net[1].weight, model.color_net[0].weight,
                                             model.color_net[1].weight, model.color_net[2].weight)]

@@ -59,6 +59,19 @@ def main():
         ns = int(out[3][1])
         print(f"impl {'tc5' if impl else 'mma'}: {ms:.2f} ms for {nn} rays, {ns} samples -> {ns / ms / 1e6:.3f} Gsamples/s, "
               f"{nn / ms / 1e3:.2f} Mrays/s", flush=True)
+        st = out[3][2:].cpu().numpy().astype(float)
+        if impl == 1 and st.any():   # -DR5_STATS=1 build: cycle accounting per role (lane 0 of every warp, summed over the grid)
+            names = {0: "gather wait rows_full", 1: "gather wait f_empty", 2: "gather total", 3: "mma wait rows_full",
+                     4: "mma wait f_full", 5: "mma wait t_free", 6: "mma wait a_ready", 7: "mma total", 8: "chain wait rows_full",
+                     9: "chain wait d_full", 10: "chain total", 11: "chain groups of 2", 12: "chain groups", 13: "marcher passes",
+                     14: "marcher builds", 15: "marcher passes E < part", 16: "marcher passes buffer busy", 17: "marcher total",
+                     18: "marcher end wait", 19: "marcher list entries", 20: "marcher sum E", 21: "marcher rows built"}
+            tot = {0: 2, 1: 2, 3: 7, 4: 7, 5: 7, 6: 7, 8: 10, 9: 10, 18: 17}
+            for k, nm in names.items():
+                extra = f"  ({100 * st[k] / st[tot[k]]:.1f} % of role time)" if k in tot and st[tot[k]] else ""
+                print(f"   stat {nm:28s} {st[k]:.4g}{extra}")
+            print(f"   per build: passes {st[13] / max(st[14], 1):.2f}  list entries {st[19] / max(st[14], 1):.1f}  rows {st[21] / max(st[14], 1):.1f}"
+                  f"   cycles per pass {st[17] / max(st[13], 1):.0f}")
     L.ngp_set_field_impl(1)
 
 

