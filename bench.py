@@ -38,7 +38,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--points", type=int, default=1 << 22, help="points per GPU per step")
-    ap.add_argument("--cpu-points", type=int, default=1 << 18, help="points per CPU-baseline step")
+    ap.add_argument("--cpu-points", type=int, default=None, help="points per CPU step (default: 2^18 for the cpu_baseline leg; "
+                    "--impl reference uses the full --points when the run fits in ~4 min)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-estimator", action="store_true")
     ap.add_argument("--hypotheses", type=int, default=256)
@@ -50,9 +51,15 @@ def parse():
     ap.add_argument("--render-steps", type=int, default=1)
     ap.add_argument("--e2e-chunk", type=int, default=1 << 20, help="points per pipelined chunk of the host-fed query")
     ap.add_argument("--no-train", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-CUDA-build leg (oracle/_ref)")
+    ap.add_argument("--no-ffmlp", action="store_true")
     ap.add_argument("--train-steps", type=int, default=20)
     ap.add_argument("--train-rays", type=int, default=4096, help="config 5: rays per GPU per optimiser step")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.cpu_points_forced = a.cpu_points is not None
+    if a.cpu_points is None:
+        a.cpu_points = 1 << 18
+    return a
 
 
 def ncu_traffic(kernel):
@@ -170,21 +177,31 @@ def run_reference(args):
     if rank != 0:
         return
     cfg1 = None if args.no_config1 else cpu_config1()
-    step, cores = cpu_field_setup(args.cpu_points)
+    # points per step: the GPU arm's own 4,194,304 when the whole run fits in ~4 minutes on this host, else the largest
+    # power-of-two fraction that does (the metric is per sample, so a bounded sample measures the same rate)
+    probe_step, cores = cpu_field_setup(1 << 18)
+    probe_step()
+    t0 = time.perf_counter(); probe_step(); rate = (1 << 18) / (time.perf_counter() - t0)
+    points = args.points
+    while points > (1 << 18) and points / rate * (args.steps + max(args.warmup, 1)) > 240.0:
+        points >>= 1
+    if args.cpu_points_forced:
+        points = args.cpu_points
+    step, cores = cpu_field_setup(points)
     for _ in range(max(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = time.perf_counter() - t0
-    val = args.cpu_points * args.steps / dt / 1e6
-    sample = f"{args.cpu_points} of {args.points} uniform points per step, fwd + dL/dx bwd"
+    val = points * args.steps / dt / 1e6
+    sample = f"{points} of {args.points} uniform points per step, fwd + dL/dx bwd"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "points_per_step": args.cpu_points, "levels": 16, "feats": 2,
-                   "log2_table": 19, "mlp": "32-64-16", "bound": BOUND},
+        "config": {"workload": WORKLOAD, "points_per_gpu": args.points, "points_per_step": points, "levels": 16, "feats": 2,
+                   "log2_table": 19, "mlp": "32-64-16", "bound": BOUND, "points": "uniform[-1,1]^3"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -442,6 +459,15 @@ def run_b200(args):
         e5.record()
         barrier()
         t_est = e4.elapsed_time(e5) / 1e3 / args.estimator_steps
+        with torch.no_grad():   # samples per ray of the scene (one chunk of hypotheses), for the roofline fraction
+            from nerf_navigation_b200 import closures as _cl, raymarching as _rm
+            _ro, _rd = _cl.rays_from_poses(eposes[:8], epix, BE.INTR, BE.W)
+            _ro, _rd = _ro.reshape(-1, 3).contiguous(), _rd.reshape(-1, 3).contiguous()
+            _n, _f = _rm.near_far_from_aabb(_ro, _rd, emodel.aabb_train, emodel.min_near)
+            _x = _rm.march_rays_train(_ro, _rd, emodel.bound, emodel.density_bitfield, emodel.cascade, emodel.grid_size,
+                                      _n, _f, None, -1, False, -1, True, 0, 1024)[0]
+            est_spr = _x.shape[0] / _ro.shape[0]
+            del _ro, _rd, _n, _f, _x
         del emodel
 
     # ---- BASELINE config 4: full-frame cuda_ray render, 800x800 x `frames` poses on an orbit, inference path through the
@@ -475,7 +501,7 @@ def run_b200(args):
         del rmodel, rays
 
     # ---- BASELINE config 5: training step, 4096 rays per GPU (weak scaling), table + MLP gradient all-reduce over NCCL
-    t_trn, trn_loss = 0.0, (0.0, 0.0)
+    t_trn, trn_loss, trn_parity = 0.0, (0.0, 0.0), None
     if not args.no_train:
         sys.path.insert(0, os.path.join(ROOT, "scripts"))
         import bench_train as BT
@@ -508,6 +534,7 @@ def run_b200(args):
             table_grad.DETERMINISTIC = True
         trn_bytes = sum(p.numel() for p in tmodel.parameters() if p.requires_grad) * 4
         del tmodel, topt
+        trn_parity = BT.parity(dev, args.train_rays, rank, world) if world > 1 else None
 
     if world > 1:
         tt = torch.tensor([t_dev, t_e2e, 0.0 if args.no_estimator else t_est, t_ren, t_trn], device=dev, dtype=torch.float64)
@@ -523,8 +550,8 @@ def run_b200(args):
                "unit": "rays/s", "ms_per_step": t_est * 1e3, "hypotheses": args.hypotheses, "rays_per_hypothesis": 4096,
                "scaling": "strong", "sharding": "pose hypotheses by rank, replicated field, no collective",
                "scene": "synthetic stonehenge occupancy (128^3 x 2 cascades), random-init field, ~75 samples/ray",
-               "path": "near_far -> march_rays_train -> fused field+colour kernel -> composite_rays_train, and backward",
-               "reference_cuda_build_same_box": "profiles/r1_reference_cuda_build.json (scripts/bench_ref_cuda.py)"}
+               "path": "near_far -> march_rays_train -> fused tcgen05 field+colour kernels (csrc/cfield5.cu) -> composite_rays_train, and backward",
+               "samples_per_ray": est_spr, "reference_cuda_build_same_box": "ref_cuda_build / estimator_vs_ref_cuda in this line"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -544,6 +571,15 @@ def run_b200(args):
     torch.cuda.synchronize()
     probe_ms = min(a.elapsed_time(b) for a, b in pe)
     gather_peak = pb_blocks * 256 * pb_iters * 8 * 8 / (probe_ms / 1e3) / 1e9
+    probe0 = lambda: ngp.check(L.ngp_probe_gather(probe_buf.data_ptr(), probe_buf.numel() * 4, 8, pb_iters, 0, pb_blocks,
+                                                  sink.data_ptr(), st))
+    for _ in range(3):
+        probe0()
+    pe0 = [(ev(), ev()) for _ in range(5)]
+    for a, b in pe0:
+        a.record(); probe0(); b.record()
+    torch.cuda.synchronize()
+    random8_peak = pb_blocks * 256 * pb_iters * 8 * 8 / (min(a.elapsed_time(b) for a, b in pe0) / 1e3) / 1e9
     del probe_buf
 
     peaks, peak_kind = measured_peaks()
@@ -551,6 +587,17 @@ def run_b200(args):
     e2e_val = world * B * e2e_steps / t_e2e / 1e6
     dom, dom_ms = ("k_field_backward", bwd_ms) if bwd_ms >= fwd_ms else ("k_field_forward", fwd_ms)
     achieved = B * BYTES_PER_POINT_PASS / (dom_ms / 1e3) / 1e9
+    traffic = ncu_traffic(dom)
+    # the kernel of this bench that sits lowest against the same roofline (not the longest one of the headline leg)
+    fracs = {"k_field_forward": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak,
+             "k_field_backward": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}
+    if not args.no_render and t_ren > 0:
+        fracs["k_render5_rays_infer"] = ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak
+    if not args.no_estimator:
+        fracs["estimator step (k_cfield5_forward + k_cfield5_backward + marcher / compositor)"] = \
+            args.hypotheses * 4096 * est_spr * 2 * BYTES_PER_POINT_PASS / t_est / 1e9 / world / gather_peak
+    low = min(fracs, key=fracs.get)
+    lowest = {"kernel": low, "frac": fracs[low], "all": fracs}
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -571,13 +618,18 @@ def run_b200(args):
         "single_pass": {"value": world * B * args.steps / t_vg / 1e6, "unit": UNIT,
                         "what": "ngp_field_query_value_grad: the same sigma + dL/dx in ONE kernel (rank-0 time), "
                                 "1280 B of table gathers per point instead of 2048"},
-        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                     "frac": achieved / peaks["hbm_gbs"], "traffic": ncu_traffic(dom), "peak_source": peak_kind,
-                     "traffic_note": "DRAM bytes per launch from the committed ncu --set full capture at the same size: ~0.4 GB of "
-                                     "point/output streaming against 4.3 GB of algorithmic (L2-served) gather bytes; the "
-                                     "same capture shows the L1 data pipe at 90-92 % of its wavefront slots",
-                     "note": "algorithmic bytes = 1024 B of table gathers per point per pass; gathers are served by L2 "
-                             "(table resident), so the binding limit is L1/L2 request rate, not HBM"},
+        "roofline": {"bound": "l2_gather", "kernel": dom, "achieved": achieved, "peak": gather_peak, "unit": "GB/s",
+                     "frac": achieved / gather_peak, "traffic": traffic,
+                     "peak_source": "ngp_probe_gather live on this GPU: 8-byte hashed-cell corner gathers from a 48 MiB "
+                                    "L2-resident buffer (the kernels' own access shape); MEASURED_PEAKS.json has no L2 figure",
+                     "peak_random8B": random8_peak,
+                     "hbm_peak": peaks["hbm_gbs"], "hbm_peak_source": peak_kind,
+                     "hbm_frac": (traffic / (dom_ms / 1e3) / 1e9 / peaks["hbm_gbs"]) if traffic else None,
+                     "note": "algorithmic bytes = 1024 B of table gathers per point per pass, served by L2 (table resident): the "
+                             "binding limit is the L1->L2 request rate, not HBM (DRAM traffic per launch = `traffic`, ~1.07x the "
+                             "minimal point/output streaming, a few % of the HBM peak).  The peak is a PATTERN ceiling for "
+                             "arrival-ordered uniform points: spatially clustered batches exceed it (locality.clustered)",
+                     "lowest": lowest},
         "l2_gather_roofline": {
             "peak": gather_peak, "unit": "GB/s useful", "how": "ngp_probe_gather live: 8-byte hashed-cell corner gathers "
             "from a 48 MiB L2-resident buffer, all SMs (the binding unit is one L1-miss sector per clock per SM)",
@@ -591,7 +643,8 @@ def run_b200(args):
     if not args.no_train:
         out["train"] = {"metric": "training step (config 5)", "rays_per_gpu": args.train_rays, "ms_per_step": t_trn * 1e3,
                         "steps_per_s": 1.0 / t_trn, "rays_per_s": world * args.train_rays / t_trn, "scaling": "weak",
-                        "loss_first": trn_loss[0], "loss_last": trn_loss[1],
+                        "loss_first": trn_loss[0], "loss_last": trn_loss[1], "parity": trn_parity,
+                        "train_parity": None if trn_parity is None else trn_parity["train_parity"],
                         "collective": "none (1 GPU)" if world == 1 else f"NCCL all-reduce (sum) of {trn_bytes} gradient bytes per step, 1/world folded into the Adam kernel",
                         "path": "march_rays_train -> GridEncoder/SH kernels + torch Linear -> composite_rays_train; "
                                 "backward incl. deterministic table gradient; fused Adam + EMA",
@@ -600,14 +653,13 @@ def run_b200(args):
                                                       "reference (not bit-reproducible), rank-0 time"}}
     if not args.no_render:
         nrays = args.frames * 800 * 800
-        # per-sample bounds of the fused kernel: 1024 B of L2 gathers (same unit as the field query) and 1368 mma.sync
-        # m16n8k8 TF32 per 16 samples (456 products x 3 for the 3xTF32 split)
+        # per-sample bound of the fused kernel: 1024 B of L2 gathers (same unit as the field query)
         out["render"] = {
             "metric": "full-frame render (config 4)", "frames": args.frames, "rays": nrays, "ms_per_step": t_ren * 1e3,
             "ms_per_frame": t_ren * 1e3 / args.frames, "frames_per_s": args.frames / t_ren, "rays_per_s": nrays / t_ren,
             "samples": ren_samples, "samples_per_ray": ren_samples / nrays, "samples_per_s": ren_samples / t_ren,
             "scaling": "strong", "sharding": "frames by rank, replicated field + bitfield, no collective",
-            "path": "ngp_render_rays_infer: near/far + march + field + colour + composite + post in one persistent kernel",
+            "path": "ngp_render_rays_infer: near/far + march + field + colour + composite + post in one persistent warp-specialised tcgen05 kernel (csrc/render5.cu)",
             "gpu_launches": args.render_steps * ((ren_frames + args.frames_per_step - 1) // args.frames_per_step),
             "l2_gather": {"achieved": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world, "peak": gather_peak,
                           "unit": "GB/s useful per GPU",
@@ -625,6 +677,36 @@ def run_b200(args):
                                "sample": f"{reps} x {args.cpu_points} of the {B} points, fwd + dL/dx bwd, C/OpenMP oracle"}
         if cfg1 is not None:
             out["cpu_baseline"]["config1"] = cfg1
+    # ---- strong-scaling legs as top-level keys (the headline `value` is weak scaling of independent points): whole-job
+    # throughput at this N, so that value(N) / value(1) / N is the efficiency of each leg
+    out["estimator_rays_per_s"] = None if est is None else est["value"]
+    out["render_frames_per_s"] = None if args.no_render else out["render"]["frames_per_s"]
+    out["train_rays_per_s"] = None if args.no_train else out["train"]["rays_per_s"]
+    out["strong_scaling"] = {"estimator_rays_per_s": out["estimator_rays_per_s"], "render_frames_per_s": out["render_frames_per_s"],
+                             "what": "fixed total work (256 hypotheses x 4096 rays; 64 frames) split over n_gpus ranks, no collective; "
+                                     "efficiency = value(N) / (N x value(1))"}
+    if world == 1:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import bench_legs as BL
+        if not args.no_ref_cuda:
+            try:
+                out["ref_cuda_build"] = BL.ref_cuda_build_leg(dev)
+                rc = out["ref_cuda_build"]
+                if "cfg3_estimator_cuda_ray_train" in rc:
+                    out["estimator_vs_ref_cuda"] = {
+                        "cuda_ray_train_fwd_bwd": rc["cfg3_estimator_cuda_ray_train"]["ours_vs_ref_fwd_bwd"],
+                        "cuda_ray_train_fwd": rc["cfg3_estimator_cuda_ray_train"]["ours_vs_ref_fwd"],
+                        "run_512_fwd_bwd_to_rays": rc["cfg1_shape_run_512_fwd_bwd_to_rays"]["ours_vs_ref"],
+                        "what": "ours / reference CUDA build, rays/s, same box and run; first = the cuda_ray train branch (ours "
+                                "back-propagates to the rays, the reference to its parameters: it has no pose gradient there), last = "
+                                "the reference-shaped run() with 512 samples per ray, gradient to the rays on both sides"}
+            except Exception as e:   # a reported baseline must not take the bench line down
+                out["ref_cuda_build"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        if not args.no_ffmlp:
+            try:
+                out["ffmlp"] = BL.ffmlp_leg(dev, peaks["hbm_gbs"])
+            except Exception as e:
+                out["ffmlp"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

@@ -204,12 +204,14 @@ int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, c
 
 /* ---- training-step tail: torch.optim.Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:126) + EMA (nerf/utils.py:814) - */
 
-/* One fused pass over a parameter tensor: g *= grad_scale (all-reduce mean / GradScaler), Adam moments and update with
- * torch's single-tensor arithmetic, optional EMA shadow update (ema may be NULL).  step counts from 1.  All pointers
+/* One fused pass over a parameter tensor: g *= grad_scale (all-reduce mean), Adam moments and update with torch's
+ * single-tensor arithmetic, optional EMA shadow update (ema may be NULL; ema_decay is the decay of THIS update).  step
+ * counts from 1.  torch.amp.GradScaler (nerf/utils.py:784-791): amp_scale (device float, may be NULL) is the loss scale the
+ * gradients are divided by; found_inf (device float, may be NULL) non-zero skips the step entirely.  All array pointers
  * 16-byte aligned, n fp32 elements. */
 int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float *ema, int64_t n, float lr,
                   float beta1, float beta2, float eps, int64_t step, float grad_scale, float ema_decay,
-                  ngp_stream_t stream);
+                  const float *amp_scale, const float *found_inf, ngp_stream_t stream);
 
 /* Weight gradient of a bias-free Linear of the field MLPs (nn.Linear backward inside Trainer.train_step,
  * nerf/network.py:33-68): dW [n_out, n_in] = dY^T X with dY [M, n_out], X [M, n_in] row-major fp32, n_out, n_in <= 64.
@@ -235,6 +237,26 @@ int ngp_occ_grid_positions(int cascade, uint32_t G, float bound, float jitter, u
 int64_t ngp_occ_grid_update_blocks(int64_t n);
 int ngp_occ_grid_update(float *grid, const float *sigma, int64_t n, float decay, float density_scale, float *block_sums,
                         ngp_stream_t stream);
+
+/* Partial refresh of update_extra_state (renderer.py:488-517), one cascade: N uniformly random cells + N cells drawn with
+ * replacement from the occupied ones (grid_cas [G^3] > 0; ordered, reproducible compaction) -> cell_idx i32 [2N] (Morton
+ * index; -1 where nothing is occupied) and their jittered query positions xyz [2N,3].  workspace:
+ * ngp_occ_grid_partial_workspace_bytes(G) bytes.  Then, with sigma [2N] = density(xyz):
+ * ngp_occ_grid_scatter_update: tmp [n] (scratch) = -1, tmp[cell] = max of the queries that hit it (x density_scale),
+ * grid = max(grid * decay, tmp) where both >= 0 (renderer.py:519-520), block_sums as in ngp_occ_grid_update. */
+int64_t ngp_occ_grid_partial_workspace_bytes(uint32_t G);
+int ngp_occ_grid_partial_select(const float *grid_cas, int cascade, uint32_t G, float bound, float jitter, uint32_t seed,
+                                uint32_t N, void *workspace, int32_t *cell_idx, float *xyz, ngp_stream_t stream);
+int ngp_occ_grid_scatter_update(float *grid_cas, const int32_t *cell_idx, const float *sigma, uint32_t nq, int64_t n,
+                                float decay, float density_scale, float *tmp, float *block_sums, ngp_stream_t stream);
+/* NeRFRenderer.mark_untrained_grid (renderer.py:381-444): grid [C, G^3] cells that none of the B cam2world poses [B,4,4]
+ * (intrinsics fx, fy, cx, cy) sees are set to -1. */
+int ngp_occ_grid_mark_untrained(const float *poses, int B, float fx, float fy, float cx, float cy, uint32_t C, uint32_t G,
+                                float bound, float *grid, ngp_stream_t stream);
+/* The planner's A* occupancy (nav/quad_plot.py:64-83): xyz [side^3, 3] = meshgrid('ij') of torch.linspace(lo, hi, side)
+ * per axis (lo_host / hi_host: 3 HOST floats each); out u8 [(side/k)^3] = MaxPool3d(k)(sigma [side^3]) > thresh. */
+int ngp_lattice_positions(const float *lo_host, const float *hi_host, uint32_t side, float *xyz, ngp_stream_t stream);
+int ngp_maxpool_threshold(const float *sigma, uint32_t side, uint32_t k, float thresh, uint8_t *out, ngp_stream_t stream);
 
 /* ---- spherical harmonics: shencoder/src/shencoder.h:10,13 (degree <= 4) ----------------------------------------- */
 

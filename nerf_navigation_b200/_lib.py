@@ -48,12 +48,18 @@ _SIGNATURES = {
     "ngp_render_rays_infer_workspace_bytes": ([], I64),
     "ngp_render_rays_infer": ([P, P, I64, P, F, P, F, F, U32, U32, U32, P, P, F, U32, U32, I, P, P, P, P, P, F, P, I, P, P,
                               P, P, P, P], I),
-    "ngp_adam_step": ([P, P, P, P, P, I64, F, F, F, F, I64, F, F, P], I),
+    "ngp_adam_step": ([P, P, P, P, P, I64, F, F, F, F, I64, F, F, P, P, P], I),
     "ngp_linear_wgrad_workspace_bytes": ([I64], I64),
     "ngp_linear_wgrad": ([P, P, P, I64, I, I, P, I64, P], I),
     "ngp_occ_grid_positions": ([I, U32, F, F, U32, P, P], I),
     "ngp_occ_grid_update_blocks": ([I64], I64),
     "ngp_occ_grid_update": ([P, P, I64, F, F, P, P], I),
+    "ngp_occ_grid_partial_workspace_bytes": ([U32], I64),
+    "ngp_occ_grid_partial_select": ([P, I, U32, F, F, U32, U32, P, P, P, P], I),
+    "ngp_occ_grid_scatter_update": ([P, P, P, U32, I64, F, F, P, P, P], I),
+    "ngp_occ_grid_mark_untrained": ([P, I, F, F, F, F, U32, U32, F, P, P], I),
+    "ngp_lattice_positions": ([P, P, U32, P, P], I),
+    "ngp_maxpool_threshold": ([P, U32, U32, F, P, P], I),
     "ngp_sh_encode_forward": ([P, P, I64, I, I, I, P, P], I),
     "ngp_sh_encode_backward": ([P, P, I64, I, I, P, P], I),
     "ngp_ffmlp_forward": ([P, P, I64, I, I, I, I, I, I, P, P, P], I),

@@ -85,8 +85,23 @@ def make_density_fn(model, rot=NAV_ROT, single_pass=True):
 def astar_occupancy(density_fn, side=100, kernel_size=5, thresh=0.3, lo=(-1.0, -1.0, -1.0), hi=(1.0, 1.0, 1.0),
                     device="cuda"):
     """The planner's A* occupancy grid (nav/quad_plot.py:64-83): density at a side^3 lattice over [lo, hi], max-pooled by
-    kernel_size^3, thresholded -> bool [side//k]^3.  One fused field query of side^3 points (10^6 at the defaults)."""
-    axes = [torch.linspace(l, h, side, device=device) for l, h in zip(lo, hi)]
-    coods = torch.stack(torch.meshgrid(*axes, indexing="ij"), dim=-1)
-    sigma = density_fn(coods)
-    return torch.nn.functional.max_pool3d(sigma[None, None], kernel_size)[0, 0] > thresh
+    kernel_size^3, thresholded -> bool [side//k]^3.  Three launches: lattice positions (torch.linspace's arithmetic, meshgrid
+    'ij' order) -> the density closure (one fused field query of side^3 points, 10^6 at the defaults) -> max-pool + threshold
+    (csrc/occgrid.cu)."""
+    import ctypes
+
+    from . import _lib
+    dev = torch.device(device)
+    L = _lib.lib()
+    xyz = torch.empty(side, side, side, 3, device=dev)
+    f3 = ctypes.c_float * 3
+    g = side // kernel_size
+    out = torch.empty(g, g, g, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(L.ngp_lattice_positions(ctypes.cast(f3(*[float(v) for v in lo]), ctypes.c_void_p),
+                                           ctypes.cast(f3(*[float(v) for v in hi]), ctypes.c_void_p), side, _lib.ptr(xyz),
+                                           _lib.stream()), "lattice_positions")
+        sigma = density_fn(xyz).float().contiguous()
+        _lib.check(L.ngp_maxpool_threshold(_lib.ptr(sigma), side, kernel_size, float(thresh), _lib.ptr(out), _lib.stream()),
+                   "maxpool_threshold")
+    return out.bool()

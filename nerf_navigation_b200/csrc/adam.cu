@@ -4,7 +4,10 @@
 // nerf/utils.py:814-815).  torch's single-tensor Adam arithmetic is followed operation by operation:
 //     m = lerp(m, g, 1 - b1);  v = b2 v + (1 - b2) g g;  p -= (lr / (1 - b1^t)) * m / (sqrt(v) / sqrt(1 - b2^t) + eps)
 // One pass over the hash table (12.66 M fp32 parameters): 16 B read + 12 B written per parameter (+ 8 B with the EMA),
-// HBM-bound; the all-reduce's 1/world (or GradScaler's 1/scale) is folded into `grad_scale` so the mean needs no pass.
+// HBM-bound; the all-reduce's 1/world is folded into `grad_scale` so the mean needs no pass.  torch.amp.GradScaler
+// semantics (nerf/utils.py:784-791 scaler.step / scaler.update): `amp_scale` (device, the loss scale: gradients are divided
+// by it) and `found_inf` (device, non-zero = some gradient was inf / nan: the step is skipped, moments and EMA untouched)
+// are read by the kernel, so a skipped step needs no host round trip.
 #include "common.cuh"
 
 #define ADAM_THREADS 256
@@ -25,7 +28,10 @@ __device__ __forceinline__ void adam_one(float &p, float g, float &m, float &v, 
 
 __global__ void __launch_bounds__(ADAM_THREADS)
 k_adam_step(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v,
-            float *__restrict__ ema, int64_t n, AdamScalars s) {
+            float *__restrict__ ema, int64_t n, AdamScalars s, const float *__restrict__ amp_scale,
+            const float *__restrict__ found_inf) {
+    if (found_inf && *found_inf != 0.0f) return;           // GradScaler: skip the whole step
+    if (amp_scale) s.grad_scale = __fdiv_rn(s.grad_scale, *amp_scale);
     const int64_t n4 = n >> 2;
     const int64_t stride = (int64_t)gridDim.x * ADAM_THREADS;
     for (int64_t i = (int64_t)blockIdx.x * ADAM_THREADS + threadIdx.x; i < n4; i += stride) {
@@ -60,7 +66,7 @@ k_adam_step(float *__restrict__ p, const float *__restrict__ g, float *__restric
 
 extern "C" int ngp_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, float *ema, int64_t n,
                              float lr, float beta1, float beta2, float eps, int64_t step, float grad_scale,
-                             float ema_decay, ngp_stream_t stream) {
+                             float ema_decay, const float *amp_scale, const float *found_inf, ngp_stream_t stream) {
     NGP_REQUIRE_DEVICE(param, "ngp_adam_step");
     if (n == 0) return NGP_OK;
     NGP_REQUIRE(param && grad && exp_avg && exp_avg_sq, NGP_ERR_ARG, "ngp_adam_step: null pointer");
@@ -79,7 +85,8 @@ extern "C" int ngp_adam_step(float *param, const float *grad, float *exp_avg, fl
     const int64_t want = ngp_div_up(ngp_div_up(n, 4) > 0 ? ngp_div_up(n, 4) : 1, ADAM_THREADS);
     const int64_t cap = (int64_t)sms * 8;
     const int blocks = (int)(want < cap ? want : cap);
-    k_adam_step<<<blocks, ADAM_THREADS, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, ema, n, s);
+    k_adam_step<<<blocks, ADAM_THREADS, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, ema, n, s, amp_scale,
+                                                                   found_inf);
     NGP_CHECK_LAUNCH("ngp_adam_step");
     return NGP_OK;
 }

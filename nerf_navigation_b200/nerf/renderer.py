@@ -1,11 +1,18 @@
-"""NeRFRenderer — host-side mirror of the reference's nerf/renderer.py:61-575 (same ctor kwargs, buffers, kwargs contract of
-run / run_cuda / render / update_extra_state), on top of the B200 ray kernels in ..raymarching.
+"""NeRFRenderer for the B200 kernels — the kept API of the reference's nerf/renderer.py:61-575 (constructor kwargs, buffers
+`aabb_train / aabb_infer / density_grid / density_bitfield / step_counter`, and the kwargs contracts of `run`, `run_cuda`,
+`render`, `update_extra_state`, `mark_untrained_grid`), organised around what runs on the GPU:
 
-Kept semantics: `run` = uniform sampler through density()/color() (renderer.py:125-254); `run_cuda` train branch =
-near_far -> march_rays_train -> field -> composite_rays_train (:282-323), eval branch = the alive-ray loop of
-march_rays / field / composite_rays (:325-374); `render` = dispatcher + max_ray_batch staging (:542-575);
-`update_extra_state` = occupancy-grid refresh + packbits (:446-539).  `sample_pdf` (:13-48) supports upsample_steps > 0.
-Out of scope: bg_radius > 0 background sphere, plot_pointcloud, mark_untrained_grid's camera culling is kept (pure torch).
+* cuda_ray = True, eval: ONE persistent kernel renders the rays (`field.render_rays_infer`, csrc/render5.cu) — the
+  reference's alive-ray loop of march_rays / forward / composite_rays with a host sync per iteration (:325-374) is kept as
+  `_render_eval_loop` for the cases the kernel does not cover (perturb, other network shapes);
+* cuda_ray = True, train: near/far -> march_rays_train -> fused field (+ colour) -> composite_rays_train (:282-323), all
+  differentiable to the rays (the estimator's pose gradient) and to the parameters;
+* cuda_ray = False: the uniform (+ importance) sampler in torch over density() / color() (:125-254), whose density() is
+  the fused field query;
+* occupancy upkeep (`update_extra_state` :446-539, `mark_untrained_grid` :381-444): cell positions, the draw of the cells to
+  refresh, the EMA-max / mean and the frustum test are kernels (csrc/occgrid.cu); the densities come from density().
+
+Out of scope: the background model (bg_radius > 0) and plot_pointcloud (trimesh viewer).
 """
 import math
 
@@ -13,32 +20,29 @@ import numpy as np
 import torch
 import torch.nn as nn
 
-from .. import raymarching
+from .. import _lib, raymarching
 
 
 def sample_pdf(bins, weights, n_samples, det=False):
-    """Inverse-CDF sampling of `n_samples` depths per ray from piecewise-constant `weights` (renderer.py:13-48)."""
-    weights = weights + 1e-5
-    pdf = weights / torch.sum(weights, -1, keepdim=True)
-    cdf = torch.cumsum(pdf, -1)
-    cdf = torch.cat([torch.zeros_like(cdf[..., :1]), cdf], -1)
+    """Draw `n_samples` depths per ray from the piecewise-constant density `weights` [B, T-1] over `bins` [B, T] by
+    inverting its CDF (renderer.py:13-48; `det` = evenly spaced quantiles instead of uniform noise)."""
+    pdf = weights + 1e-5
+    pdf = pdf / pdf.sum(-1, keepdim=True)
+    cdf = torch.nn.functional.pad(pdf.cumsum(-1), (1, 0))                       # [B, T], starts at 0
+    shape = (*cdf.shape[:-1], n_samples)
     if det:
-        u = torch.linspace(0.5 / n_samples, 1.0 - 0.5 / n_samples, steps=n_samples, device=weights.device)
-        u = u.expand(list(cdf.shape[:-1]) + [n_samples])
+        u = torch.linspace(0.5 / n_samples, 1.0 - 0.5 / n_samples, n_samples, device=cdf.device).expand(shape)
     else:
-        u = torch.rand(list(cdf.shape[:-1]) + [n_samples], device=weights.device)
+        u = torch.rand(shape, device=cdf.device)
     u = u.contiguous()
-    inds = torch.searchsorted(cdf, u, right=True)
-    below = torch.max(torch.zeros_like(inds - 1), inds - 1)
-    above = torch.min((cdf.shape[-1] - 1) * torch.ones_like(inds), inds)
-    inds_g = torch.stack([below, above], -1)
-    matched_shape = [inds_g.shape[0], inds_g.shape[1], cdf.shape[-1]]
-    cdf_g = torch.gather(cdf.unsqueeze(1).expand(matched_shape), 2, inds_g)
-    bins_g = torch.gather(bins.unsqueeze(1).expand(matched_shape), 2, inds_g)
-    denom = cdf_g[..., 1] - cdf_g[..., 0]
-    denom = torch.where(denom < 1e-5, torch.ones_like(denom), denom)
-    t = (u - cdf_g[..., 0]) / denom
-    return bins_g[..., 0] + t * (bins_g[..., 1] - bins_g[..., 0])
+    hi = torch.searchsorted(cdf, u, right=True)
+    lo = (hi - 1).clamp_min(0)
+    hi = hi.clamp_max(cdf.shape[-1] - 1)
+    c0, c1 = cdf.gather(-1, lo), cdf.gather(-1, hi)
+    b0, b1 = bins.gather(-1, lo), bins.gather(-1, hi)
+    width = c1 - c0
+    width = torch.where(width < 1e-5, torch.ones_like(width), width)            # empty bin: take its left edge
+    return b0 + (u - c0) / width * (b1 - b0)
 
 
 class NeRFRenderer(nn.Module):
@@ -51,17 +55,17 @@ class NeRFRenderer(nn.Module):
         self.min_near = min_near
         self.density_thresh = density_thresh
         self.bg_radius = bg_radius
-        aabb_train = torch.FloatTensor([-bound, -bound, -bound, bound, bound, bound])
-        self.register_buffer("aabb_train", aabb_train)
-        self.register_buffer("aabb_infer", aabb_train.clone())
+        box = torch.tensor([-bound] * 3 + [bound] * 3, dtype=torch.float32)
+        self.register_buffer("aabb_train", box)
+        self.register_buffer("aabb_infer", box.clone())
         self.cuda_ray = cuda_ray
         if cuda_ray:
-            self.register_buffer("density_grid", torch.zeros([self.cascade, self.grid_size ** 3]))
-            self.register_buffer("density_bitfield",
-                                 torch.zeros(self.cascade * self.grid_size ** 3 // 8, dtype=torch.uint8))
+            cells = self.grid_size ** 3
+            self.register_buffer("density_grid", torch.zeros(self.cascade, cells))
+            self.register_buffer("density_bitfield", torch.zeros(self.cascade * cells // 8, dtype=torch.uint8))
+            self.register_buffer("step_counter", torch.zeros(16, 2, dtype=torch.int32))   # last 16 (samples, rays) counts
             self.mean_density = 0
             self.iter_density = 0
-            self.register_buffer("step_counter", torch.zeros(16, 2, dtype=torch.int32))
             self.mean_count = 0
             self.local_step = 0
 
@@ -74,11 +78,71 @@ class NeRFRenderer(nn.Module):
     def color(self, x, d, mask=None, **kwargs):
         raise NotImplementedError()
 
+    def reset_extra_state(self):
+        if self.cuda_ray:
+            self.density_grid.zero_()
+            self.step_counter.zero_()
+            self.mean_density = self.iter_density = self.mean_count = self.local_step = 0
+
+    def _box(self):
+        return self.aabb_train if self.training else self.aabb_infer
+
+    # ------------------------------------------------------------------ cuda_ray = False: sampler in torch
+    def _weights(self, z, last_gap, sigma):
+        """Alpha-compositing weights of the samples at depths z [N, T] (renderer.py:206-210); gaps, weights."""
+        gaps = torch.cat([z[:, 1:] - z[:, :-1], last_gap.expand(z.shape[0], 1)], -1)
+        alpha = 1 - torch.exp(-gaps * self.density_scale * sigma)
+        through = torch.cat([torch.ones_like(alpha[:, :1]), 1 - alpha + 1e-15], -1).cumprod(-1)[:, :-1]
+        return gaps, alpha * through
+
+    def _points(self, rays_o, rays_d, z, box):
+        p = rays_o[:, None, :] + rays_d[:, None, :] * z[..., None]
+        return torch.min(torch.max(p, box[:3]), box[3:])
+
+    def run(self, rays_o, rays_d, num_steps=128, upsample_steps=128, bg_color=None, perturb=False, **kwargs):
+        lead = rays_o.shape[:-1]
+        rays_o = rays_o.contiguous().view(-1, 3)
+        rays_d = rays_d.contiguous().view(-1, 3)
+        N = rays_o.shape[0]
+        box = self._box()
+        with torch.no_grad():
+            near, far = raymarching.near_far_from_aabb(rays_o, rays_d, box, self.min_near)
+        near, far = near[:, None], far[:, None]
+        span = far - near
+        gap = span / num_steps
+        z = near + span * torch.linspace(0.0, 1.0, num_steps, device=rays_o.device)[None, :].expand(N, num_steps)
+        if perturb:
+            z = z + (torch.rand_like(z) - 0.5) * gap
+        pts = self._points(rays_o, rays_d, z, box)
+        field = {k: v.view(N, num_steps, -1) for k, v in self.density(pts.reshape(-1, 3)).items()}
+        if upsample_steps > 0:   # importance samples where the coarse pass puts its weight, merged in depth order
+            with torch.no_grad():
+                gaps, w = self._weights(z, gap, field["sigma"].squeeze(-1))
+                mids = z[:, :-1] + 0.5 * gaps[:, :-1]
+                z_new = sample_pdf(mids, w[:, 1:-1], upsample_steps, det=not self.training).detach()
+                pts_new = self._points(rays_o, rays_d, z_new, box)
+            extra = {k: v.view(N, upsample_steps, -1) for k, v in self.density(pts_new.reshape(-1, 3)).items()}
+            z, order = torch.cat([z, z_new], 1).sort(1)
+            pts = torch.cat([pts, pts_new], 1).gather(1, order[..., None].expand(-1, -1, 3))
+            for k in field:
+                both = torch.cat([field[k], extra[k]], 1)
+                field[k] = both.gather(1, order[..., None].expand_as(both))
+        _, w = self._weights(z, gap, field["sigma"].squeeze(-1))
+        flat = {k: v.reshape(-1, v.shape[-1]) for k, v in field.items()}
+        dirs = rays_d[:, None, :].expand_as(pts).reshape(-1, 3)
+        rgb = self.color(pts.reshape(-1, 3), dirs, mask=(w > 1e-4).reshape(-1), **flat).view(N, -1, 3)
+        opacity = w.sum(-1)
+        depth = (w * ((z - near) / span).clamp(0, 1)).sum(-1)
+        image = (w[..., None] * rgb).sum(-2) + (1 - opacity)[:, None] * (1 if bg_color is None else bg_color)
+        return {"depth": depth.view(*lead), "image": image.view(*lead, 3), "weights_sum": opacity}
+
+    # ------------------------------------------------------------------ cuda_ray = True: occupancy-grid marcher
     def _fused_render_supported(self, rays_o, rays_d, perturb):
         """The fused inference renderer covers nav's model (NeRFNetwork: 16x2 hash grid, 64-wide torch MLPs, SH 4) with a
-        frozen field, fp32, no perturbation; anything else takes the op-by-op loop below."""
-        if perturb or not getattr(self, "fused_eval", False) or not getattr(self, "fused_render", True) or torch.is_grad_enabled() and (
-                rays_o.requires_grad or rays_d.requires_grad):
+        frozen field, fp32, no perturbation; anything else takes the op-by-op loop."""
+        if perturb or not getattr(self, "fused_eval", False) or not getattr(self, "fused_render", True):
+            return False
+        if torch.is_grad_enabled() and (rays_o.requires_grad or rays_d.requires_grad):
             return False
         try:
             from ..field import fused_color_supported
@@ -87,233 +151,176 @@ class NeRFRenderer(nn.Module):
         except AttributeError:
             return False
 
-    def reset_extra_state(self):
-        if not self.cuda_ray:
-            return
-        self.density_grid.zero_()
-        self.mean_density = 0
-        self.iter_density = 0
-        self.step_counter.zero_()
-        self.mean_count = 0
-        self.local_step = 0
+    def _finish(self, image, depth, opacity, near, far, bg_color):
+        return image + (1 - opacity)[:, None] * bg_color, torch.clamp(depth - near, min=0) / (far - near)
 
-    # ------------------------------------------------------------------ torch sampler (cuda_ray=False)
-    def _alpha_weights(self, z_vals, sample_dist, sigma):
-        deltas = z_vals[..., 1:] - z_vals[..., :-1]
-        deltas = torch.cat([deltas, sample_dist * torch.ones_like(deltas[..., :1])], dim=-1)
-        alphas = 1 - torch.exp(-deltas * self.density_scale * sigma)
-        alphas_shifted = torch.cat([torch.ones_like(alphas[..., :1]), 1 - alphas + 1e-15], dim=-1)
-        return deltas, alphas * torch.cumprod(alphas_shifted, dim=-1)[..., :-1]
+    def _render_train(self, rays_o, rays_d, near, far, bg_color, perturb, force_all_rays, dt_gamma, max_steps):
+        counter = self.step_counter[self.local_step % 16]
+        counter.zero_()
+        self.local_step += 1
+        xyzs, dirs, deltas, rays = raymarching.march_rays_train(
+            rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, near, far, counter,
+            self.mean_count, perturb, 128, force_all_rays, dt_gamma, max_steps)
+        sigma, rgb = self(xyzs, dirs)
+        opacity, depth, image = raymarching.composite_rays_train(self.density_scale * sigma, rgb, deltas, rays)
+        return (*self._finish(image, depth, opacity, near, far, bg_color), opacity)
 
-    def run(self, rays_o, rays_d, num_steps=128, upsample_steps=128, bg_color=None, perturb=False, **kwargs):
-        prefix = rays_o.shape[:-1]
-        rays_o = rays_o.contiguous().view(-1, 3)
-        rays_d = rays_d.contiguous().view(-1, 3)
-        N = rays_o.shape[0]
-        device = rays_o.device
-        aabb = self.aabb_train if self.training else self.aabb_infer
-        with torch.no_grad():
-            nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, aabb, self.min_near)
-        nears = nears.unsqueeze(-1)
-        fars = fars.unsqueeze(-1)
-        z_vals = torch.linspace(0.0, 1.0, num_steps, device=device).unsqueeze(0).expand((N, num_steps))
-        z_vals = nears + (fars - nears) * z_vals
-        sample_dist = (fars - nears) / num_steps
-        if perturb:
-            z_vals = z_vals + (torch.rand(z_vals.shape, device=device) - 0.5) * sample_dist
-        xyzs = rays_o.unsqueeze(-2) + rays_d.unsqueeze(-2) * z_vals.unsqueeze(-1)
-        xyzs = torch.min(torch.max(xyzs, aabb[:3]), aabb[3:])
-        density_outputs = self.density(xyzs.reshape(-1, 3))
-        for k, v in density_outputs.items():
-            density_outputs[k] = v.view(N, num_steps, -1)
-        if upsample_steps > 0:
-            with torch.no_grad():
-                deltas, weights = self._alpha_weights(z_vals, sample_dist, density_outputs["sigma"].squeeze(-1))
-                z_vals_mid = z_vals[..., :-1] + 0.5 * deltas[..., :-1]
-                new_z_vals = sample_pdf(z_vals_mid, weights[:, 1:-1], upsample_steps, det=not self.training).detach()
-                new_xyzs = rays_o.unsqueeze(-2) + rays_d.unsqueeze(-2) * new_z_vals.unsqueeze(-1)
-                new_xyzs = torch.min(torch.max(new_xyzs, aabb[:3]), aabb[3:])
-            new_density_outputs = self.density(new_xyzs.reshape(-1, 3))
-            for k, v in new_density_outputs.items():
-                new_density_outputs[k] = v.view(N, upsample_steps, -1)
-            z_vals = torch.cat([z_vals, new_z_vals], dim=1)
-            z_vals, z_index = torch.sort(z_vals, dim=1)
-            xyzs = torch.cat([xyzs, new_xyzs], dim=1)
-            xyzs = torch.gather(xyzs, dim=1, index=z_index.unsqueeze(-1).expand_as(xyzs))
-            for k in density_outputs:
-                tmp = torch.cat([density_outputs[k], new_density_outputs[k]], dim=1)
-                density_outputs[k] = torch.gather(tmp, dim=1, index=z_index.unsqueeze(-1).expand_as(tmp))
-        _, weights = self._alpha_weights(z_vals, sample_dist, density_outputs["sigma"].squeeze(-1))
-        dirs = rays_d.view(-1, 1, 3).expand_as(xyzs)
-        for k, v in density_outputs.items():
-            density_outputs[k] = v.view(-1, v.shape[-1])
-        mask = weights > 1e-4
-        rgbs = self.color(xyzs.reshape(-1, 3), dirs.reshape(-1, 3), mask=mask.reshape(-1), **density_outputs)
-        rgbs = rgbs.view(N, -1, 3)
-        weights_sum = weights.sum(dim=-1)
-        ori_z_vals = ((z_vals - nears) / (fars - nears)).clamp(0, 1)
-        depth = torch.sum(weights * ori_z_vals, dim=-1)
-        image = torch.sum(weights.unsqueeze(-1) * rgbs, dim=-2)
-        if bg_color is None:
-            bg_color = 1
-        image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
-        return {"depth": depth.view(*prefix), "image": image.view(*prefix, 3), "weights_sum": weights_sum}
+    def _render_eval_loop(self, rays_o, rays_d, near, far, bg_color, perturb, dt_gamma, max_steps):
+        N, dev = rays_o.shape[0], rays_o.device
+        opacity = torch.zeros(N, device=dev)
+        depth = torch.zeros(N, device=dev)
+        image = torch.zeros(N, 3, device=dev)
+        alive = torch.arange(N, dtype=torch.int32, device=dev)
+        t = near.clone()
+        done = 0
+        while done < max_steps and alive.shape[0] > 0:
+            n_alive = alive.shape[0]
+            chunk = max(min(N // n_alive, 8), 1)          # more samples per round as rays die
+            xyzs, dirs, deltas = raymarching.march_rays(n_alive, chunk, alive, t, rays_o, rays_d, self.bound,
+                                                        self.density_bitfield, self.cascade, self.grid_size, near, far, 128,
+                                                        perturb, dt_gamma, max_steps)
+            sigma, rgb = self(xyzs, dirs)
+            raymarching.composite_rays(n_alive, chunk, alive, t, self.density_scale * sigma, rgb, deltas, opacity, depth, image)
+            alive = raymarching.compact_alive(alive)
+            done += chunk
+        return (*self._finish(image, depth, opacity, near, far, bg_color), opacity)
 
-    # ------------------------------------------------------------------ occupancy-grid ray marcher (cuda_ray=True)
     def run_cuda(self, rays_o, rays_d, dt_gamma=0, bg_color=None, perturb=False, force_all_rays=False, max_steps=1024,
                  **kwargs):
-        prefix = rays_o.shape[:-1]
+        lead = rays_o.shape[:-1]
         rays_o = rays_o.contiguous().view(-1, 3)
         rays_d = rays_d.contiguous().view(-1, 3)
-        N = rays_o.shape[0]
-        device = rays_o.device
-        aabb = self.aabb_train if self.training else self.aabb_infer
-        with torch.no_grad():
-            nears, fars = raymarching.near_far_from_aabb(rays_o, rays_d, aabb, self.min_near)
-        if bg_color is None:
-            bg_color = 1
-        results = {}
-        if self.training:
-            counter = self.step_counter[self.local_step % 16]
-            counter.zero_()
-            self.local_step += 1
-            xyzs, dirs, deltas, rays = raymarching.march_rays_train(
-                rays_o, rays_d, self.bound, self.density_bitfield, self.cascade, self.grid_size, nears, fars, counter,
-                self.mean_count, perturb, 128, force_all_rays, dt_gamma, max_steps)
-            sigmas, rgbs = self(xyzs, dirs)
-            sigmas = self.density_scale * sigmas
-            weights_sum, depth, image = raymarching.composite_rays_train(sigmas, rgbs, deltas, rays)
-            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
-            depth = torch.clamp(depth - nears, min=0) / (fars - nears)
-            results["weights_sum"] = weights_sum
-        elif self._fused_render_supported(rays_o, rays_d, perturb):
-            # one persistent kernel for the whole alive-ray loop + post-processing (csrc/render.cu)
+        box = self._box()
+        bg = 1 if bg_color is None else bg_color
+        out = {}
+        if not self.training and self._fused_render_supported(rays_o, rays_d, perturb):
             from ..field import render_rays_infer
-            image, depth, weights_sum = render_rays_infer(self, rays_o, rays_d, aabb, bg_color, dt_gamma, max_steps)
+            image, depth, _ = render_rays_infer(self, rays_o, rays_d, box, bg, dt_gamma, max_steps)
         else:
-            weights_sum = torch.zeros(N, dtype=torch.float32, device=device)
-            depth = torch.zeros(N, dtype=torch.float32, device=device)
-            image = torch.zeros(N, 3, dtype=torch.float32, device=device)
-            rays_alive = torch.arange(N, dtype=torch.int32, device=device)
-            rays_t = nears.clone()
-            step = 0
-            while step < max_steps:
-                n_alive = rays_alive.shape[0]
-                if n_alive <= 0:
-                    break
-                n_step = max(min(N // n_alive, 8), 1)
-                xyzs, dirs, deltas = raymarching.march_rays(
-                    n_alive, n_step, rays_alive, rays_t, rays_o, rays_d, self.bound, self.density_bitfield, self.cascade,
-                    self.grid_size, nears, fars, 128, perturb, dt_gamma, max_steps)
-                sigmas, rgbs = self(xyzs, dirs)
-                sigmas = self.density_scale * sigmas
-                raymarching.composite_rays(n_alive, n_step, rays_alive, rays_t, sigmas, rgbs, deltas, weights_sum, depth,
-                                           image)
-                rays_alive = raymarching.compact_alive(rays_alive)
-                step += n_step
-            image = image + (1 - weights_sum).unsqueeze(-1) * bg_color
-            depth = torch.clamp(depth - nears, min=0) / (fars - nears)
-        results["depth"] = depth.view(*prefix)
-        results["image"] = image.view(*prefix, 3)
-        return results
+            with torch.no_grad():
+                near, far = raymarching.near_far_from_aabb(rays_o, rays_d, box, self.min_near)
+            if self.training:
+                image, depth, out["weights_sum"] = self._render_train(rays_o, rays_d, near, far, bg, perturb, force_all_rays,
+                                                                      dt_gamma, max_steps)
+            else:
+                image, depth, _ = self._render_eval_loop(rays_o, rays_d, near, far, bg, perturb, dt_gamma, max_steps)
+        out["depth"] = depth.view(*lead)
+        out["image"] = image.view(*lead, 3)
+        return out
+
+    # ------------------------------------------------------------------ occupancy upkeep
+    @torch.no_grad()
+    def mark_untrained_grid(self, poses, intrinsic, S=64):
+        """Cells no training camera sees get density -1: never refreshed, never occupied (renderer.py:381-444).  poses
+        [B,4,4] cam2world (tensor or ndarray), intrinsic (fx, fy, cx, cy).  One kernel over all cells and cameras."""
+        if not self.cuda_ray:
+            return
+        if isinstance(poses, np.ndarray):
+            poses = torch.from_numpy(poses)
+        grid = self.density_grid
+        if not grid.is_cuda:
+            raise RuntimeError("mark_untrained_grid: the occupancy grid must be on a CUDA device (no CPU path)")
+        poses = poses.to(device=grid.device, dtype=torch.float32).contiguous()
+        fx, fy, cx, cy = (float(v) for v in intrinsic)
+        with torch.cuda.device(grid.device):
+            _lib.check(_lib.lib().ngp_occ_grid_mark_untrained(_lib.ptr(poses), poses.shape[0], fx, fy, cx, cy, self.cascade,
+                                                              self.grid_size, float(self.bound), _lib.ptr(grid),
+                                                              _lib.stream()), "mark_untrained_grid")
+
+    def _refresh_seed(self):
+        return (int(self.iter_density) * 2654435761 + 12345) & 0xFFFFFFFF
+
+    @torch.no_grad()
+    def _refresh_full(self, decay, sums, jitter=1.0):
+        """Every cell of every cascade (the first 16 refreshes, renderer.py:457-486)."""
+        L = _lib.lib()
+        cells = self.grid_size ** 3
+        xyz = torch.empty(cells, 3, device=self.density_grid.device)
+        for cas in range(self.cascade):
+            _lib.check(L.ngp_occ_grid_positions(cas, self.grid_size, float(self.bound), float(jitter), self._refresh_seed(),
+                                                _lib.ptr(xyz), _lib.stream()), "occ_grid_positions")
+            sigma = self.density(xyz)["sigma"].reshape(-1).float().contiguous()
+            _lib.check(L.ngp_occ_grid_update(self.density_grid[cas].data_ptr(), _lib.ptr(sigma), cells, float(decay),
+                                             float(self.density_scale), sums[cas].data_ptr(), _lib.stream()), "occ_grid_update")
+
+    @torch.no_grad()
+    def _refresh_partial(self, decay, sums, jitter=1.0):
+        """A quarter of the cells at random plus as many draws from the occupied ones, per cascade (renderer.py:488-517);
+        returns the drawn cell indices [cascade, 2N] (for inspection / tests)."""
+        L = _lib.lib()
+        dev = self.density_grid.device
+        cells = self.grid_size ** 3
+        N = cells // 4
+        work = torch.empty(L.ngp_occ_grid_partial_workspace_bytes(self.grid_size), dtype=torch.uint8, device=dev)
+        picked = torch.empty(self.cascade, 2 * N, dtype=torch.int32, device=dev)
+        xyz = torch.empty(2 * N, 3, device=dev)
+        tmp = torch.empty(cells, device=dev)
+        for cas in range(self.cascade):
+            _lib.check(L.ngp_occ_grid_partial_select(self.density_grid[cas].data_ptr(), cas, self.grid_size, float(self.bound),
+                                                     float(jitter), self._refresh_seed(), N, _lib.ptr(work),
+                                                     picked[cas].data_ptr(), _lib.ptr(xyz), _lib.stream()), "occ_grid_partial_select")
+            sigma = self.density(xyz)["sigma"].reshape(-1).float().contiguous()
+            _lib.check(L.ngp_occ_grid_scatter_update(self.density_grid[cas].data_ptr(), picked[cas].data_ptr(), _lib.ptr(sigma),
+                                                     2 * N, cells, float(decay), float(self.density_scale), _lib.ptr(tmp),
+                                                     sums[cas].data_ptr(), _lib.stream()), "occ_grid_scatter_update")
+        return picked
 
     @torch.no_grad()
     def update_extra_state(self, decay=0.95, S=128):
-        """Occupancy refresh, renderer.py:446-539: full sweep for the first 16 calls, then 1/4 random + 1/4 occupied
-        cells per cascade; grid <- max(grid*decay, sigma); thresh = min(mean, density_thresh); packbits."""
+        """Refresh the occupancy grid and its bitfield (renderer.py:446-539): grid <- max(grid * decay, density) on the
+        queried cells (all of them for the first 16 calls, then the partial draw), threshold min(mean density,
+        density_thresh), pack the bits; then fold the marcher's sample counters into mean_count."""
         if not self.cuda_ray:
             return
-        dev = self.density_bitfield.device
-        G = self.grid_size
-        tmp_grid = -torch.ones_like(self.density_grid)
-
-        def query(cas, coords):
-            xyzs = 2 * coords.float() / (G - 1) - 1
-            bound = min(2 ** cas, self.bound)
-            half = bound / G
-            cas_xyzs = xyzs * (bound - half)
-            cas_xyzs += (torch.rand_like(cas_xyzs) * 2 - 1) * half
-            sig = self.density(cas_xyzs)["sigma"].reshape(-1).detach()
-            return sig * self.density_scale
-
-        if self.iter_density < 16 and getattr(self, "fused_occ_sweep", True) and self.density_grid.is_cuda:
-            return self._update_extra_state_sweep(decay)
-        if self.iter_density < 16:
-            ar = torch.arange(G, dtype=torch.int32, device=dev)
-            for xs in ar.split(S):
-                for ys in ar.split(S):
-                    for zs in ar.split(S):
-                        xx, yy, zz = torch.meshgrid(xs, ys, zs, indexing="ij")
-                        coords = torch.stack([xx.reshape(-1), yy.reshape(-1), zz.reshape(-1)], dim=-1)
-                        indices = raymarching.morton3D(coords).long()
-                        for cas in range(self.cascade):
-                            tmp_grid[cas, indices] = query(cas, coords)
-        else:
-            N = G ** 3 // 4
-            for cas in range(self.cascade):
-                coords = torch.randint(0, G, (N, 3), device=dev)
-                indices = raymarching.morton3D(coords).long()
-                occ_indices = torch.nonzero(self.density_grid[cas] > 0).squeeze(-1)
-                rand_mask = torch.randint(0, occ_indices.shape[0], [N], dtype=torch.long, device=dev)
-                occ_indices = occ_indices[rand_mask]
-                occ_coords = raymarching.morton3D_invert(occ_indices)
-                indices = torch.cat([indices, occ_indices], dim=0)
-                coords = torch.cat([coords, occ_coords], dim=0)
-                tmp_grid[cas, indices] = query(cas, coords)
-        valid = (self.density_grid >= 0) & (tmp_grid >= 0)
-        self.density_grid[valid] = torch.maximum(self.density_grid[valid] * decay, tmp_grid[valid])
-        self.mean_density = torch.mean(self.density_grid.clamp(min=0)).item()
+        if not self.density_grid.is_cuda:
+            raise RuntimeError("update_extra_state: the occupancy grid must be on a CUDA device (no CPU path)")
+        L = _lib.lib()
+        cells = self.grid_size ** 3
+        sums = torch.empty(self.cascade, L.ngp_occ_grid_update_blocks(cells), device=self.density_grid.device)
+        with torch.cuda.device(self.density_grid.device):
+            if self.iter_density < 16:
+                self._refresh_full(decay, sums)
+            else:
+                self._refresh_partial(decay, sums)
+        self.mean_density = float(sums.double().sum().item() / (self.cascade * cells))
         self.iter_density += 1
-        density_thresh = min(self.mean_density, self.density_thresh)
-        self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
-        total_step = min(16, self.local_step)
-        if total_step > 0:
-            self.mean_count = int(self.step_counter[:total_step, 0].sum().item() / total_step)
+        self.density_bitfield = raymarching.packbits(self.density_grid, min(self.mean_density, self.density_thresh),
+                                                     self.density_bitfield)
+        recent = min(16, self.local_step)
+        if recent > 0:
+            self.mean_count = int(self.step_counter[:recent, 0].sum().item() / recent)
         self.local_step = 0
 
+    # kept name of the round-1 entry point (bench / tests call it to force a full sweep without jitter)
     @torch.no_grad()
     def _update_extra_state_sweep(self, decay, jitter=1.0):
-        """Full-sweep branch of update_extra_state (renderer.py:457-486, 519-539) on the occupancy kernels (csrc/occgrid.cu):
-        positions in Morton order -> density() (the fused field query) -> EMA-max + mean partials -> packbits."""
-        from .. import _lib
-        L = _lib.lib()
-        G, n = self.grid_size, self.grid_size ** 3
-        dev = self.density_grid.device
-        xyz = torch.empty(n, 3, device=dev)
-        nblk = L.ngp_occ_grid_update_blocks(n)
-        sums = torch.empty(self.cascade, nblk, device=dev)
-        seed = (int(self.iter_density) * 2654435761 + 12345) & 0xFFFFFFFF
-        with torch.cuda.device(dev):
-            for cas in range(self.cascade):
-                _lib.check(L.ngp_occ_grid_positions(cas, G, float(self.bound), float(jitter), seed, _lib.ptr(xyz), _lib.stream()),
-                           "occ_grid_positions")
-                sigma = self.density(xyz)["sigma"].reshape(-1).float().contiguous()
-                _lib.check(L.ngp_occ_grid_update(self.density_grid[cas].data_ptr(), _lib.ptr(sigma), n, float(decay),
-                                                 float(self.density_scale), sums[cas].data_ptr(), _lib.stream()), "occ_grid_update")
-        self.mean_density = float(sums.double().sum().item() / (self.cascade * n))
+        cells = self.grid_size ** 3
+        sums = torch.empty(self.cascade, _lib.lib().ngp_occ_grid_update_blocks(cells), device=self.density_grid.device)
+        with torch.cuda.device(self.density_grid.device):
+            self._refresh_full(decay, sums, jitter)
+        self.mean_density = float(sums.double().sum().item() / (self.cascade * cells))
         self.iter_density += 1
-        density_thresh = min(self.mean_density, self.density_thresh)
-        self.density_bitfield = raymarching.packbits(self.density_grid, density_thresh, self.density_bitfield)
-        total_step = min(16, self.local_step)
-        if total_step > 0:
-            self.mean_count = int(self.step_counter[:total_step, 0].sum().item() / total_step)
+        self.density_bitfield = raymarching.packbits(self.density_grid, min(self.mean_density, self.density_thresh),
+                                                     self.density_bitfield)
+        recent = min(16, self.local_step)
+        if recent > 0:
+            self.mean_count = int(self.step_counter[:recent, 0].sum().item() / recent)
         self.local_step = 0
 
+    # ------------------------------------------------------------------ dispatcher
     def render(self, rays_o, rays_d, staged=False, max_ray_batch=4096, **kwargs):
-        """renderer.py:542-575.  rays_o, rays_d: [B, N, 3] -> {'image': [B, N, 3], 'depth': [B, N]}."""
-        _run = self.run_cuda if self.cuda_ray else self.run
+        """rays_o, rays_d [B, N, 3] -> {'image': [B, N, 3], 'depth': [B, N]} (renderer.py:542-575).  The torch sampler is
+        run in batches of max_ray_batch rays when `staged` (its per-sample tensors are large); the marcher never is."""
+        if self.cuda_ray:
+            return self.run_cuda(rays_o, rays_d, **kwargs)
+        if not staged:
+            return self.run(rays_o, rays_d, **kwargs)
         B, N = rays_o.shape[:2]
-        device = rays_o.device
-        if staged and not self.cuda_ray:
-            depth = torch.empty((B, N), device=device)
-            image = torch.empty((B, N, 3), device=device)
-            for b in range(B):
-                head = 0
-                while head < N:
-                    tail = min(head + max_ray_batch, N)
-                    r = _run(rays_o[b:b + 1, head:tail], rays_d[b:b + 1, head:tail], **kwargs)
-                    depth[b:b + 1, head:tail] = r["depth"]
-                    image[b:b + 1, head:tail] = r["image"]
-                    head += max_ray_batch
-            return {"depth": depth, "image": image}
-        return _run(rays_o, rays_d, **kwargs)
+        depth = torch.empty(B, N, device=rays_o.device)
+        image = torch.empty(B, N, 3, device=rays_o.device)
+        for b in range(B):
+            for a in range(0, N, max_ray_batch):
+                part = self.run(rays_o[b:b + 1, a:a + max_ray_batch], rays_d[b:b + 1, a:a + max_ray_batch], **kwargs)
+                depth[b:b + 1, a:a + max_ray_batch] = part["depth"]
+                image[b:b + 1, a:a + max_ray_batch] = part["image"]
+        return {"depth": depth, "image": image}

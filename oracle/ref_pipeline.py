@@ -163,3 +163,77 @@ def ref_render_train(field, rays_o, rays_d, bitfield, C, H, aabb, min_near, bg_c
     sigmas, rgbs = field(xyzs, dirs)
     ws, depth, image = _RefComposite.apply(sigmas, rgbs, deltas, rays)
     return image + (1 - ws).unsqueeze(-1) * bg_color, xyzs.shape[0]
+
+
+def ref_run(field, rays_o, rays_d, aabb, min_near, num_steps=512, bg_color=1.0, density_scale=1.0):
+    """renderer.py:125-254 with upsample_steps = 0, perturb = False: the cuda_ray=False sampler the pose estimator uses
+    under `simulate.py -O` — uniform depths between the AABB hits, density() on every sample, colour on the samples with
+    weight > 1e-4 (network.py:163-191), alpha compositing in torch.  Its autograd reaches rays_o / rays_d through the
+    reference's CUDA GridEncoder (dy_dx) and SHEncoder: the like-for-like comparator for a photometric loss fwd + bwd to
+    the pose."""
+    N = rays_o.shape[0]
+    dev = rays_o.device
+    nears = torch.empty(N, device=dev); fars = torch.empty(N, device=dev)
+    with torch.no_grad():
+        ext("raymarching").near_far_from_aabb(rays_o.detach().contiguous(), rays_d.detach().contiguous(), aabb, N, min_near, nears, fars)
+    nears = nears.unsqueeze(-1); fars = fars.unsqueeze(-1)
+    z = torch.linspace(0.0, 1.0, num_steps, device=dev).unsqueeze(0).expand(N, num_steps)
+    z = nears + (fars - nears) * z
+    sample_dist = (fars - nears) / num_steps
+    xyzs = rays_o.unsqueeze(-2) + rays_d.unsqueeze(-2) * z.unsqueeze(-1)
+    xyzs = torch.min(torch.max(xyzs, aabb[:3]), aabb[3:])
+    sigma, geo = field.density(xyzs.reshape(-1, 3))
+    sigma = sigma.view(N, num_steps)
+    deltas = torch.cat([z[..., 1:] - z[..., :-1], sample_dist * torch.ones_like(z[..., :1])], dim=-1)
+    alphas = 1 - torch.exp(-deltas * density_scale * sigma)
+    shifted = torch.cat([torch.ones_like(alphas[..., :1]), 1 - alphas + 1e-15], dim=-1)
+    weights = alphas * torch.cumprod(shifted, dim=-1)[..., :-1]
+    mask = (weights > 1e-4).reshape(-1)
+    dirs = rays_d.view(-1, 1, 3).expand_as(xyzs).reshape(-1, 3)
+    rgbs = torch.zeros(N * num_steps, 3, device=dev)
+    if mask.any():
+        h = torch.cat([_RefSH.apply(dirs[mask], 4, dirs.requires_grad), geo[mask]], dim=-1)
+        for i, w in enumerate(field.color_w):
+            h = F.linear(h, w)
+            if i != len(field.color_w) - 1:
+                h = F.relu(h, inplace=True)
+        rgbs[mask] = torch.sigmoid(h)
+    rgbs = rgbs.view(N, num_steps, 3)
+    ws = weights.sum(-1)
+    depth = (weights * ((z - nears) / (fars - nears)).clamp(0, 1)).sum(-1)
+    image = (weights.unsqueeze(-1) * rgbs).sum(-2) + (1 - ws).unsqueeze(-1) * bg_color
+    return image, depth
+
+
+@torch.no_grad()
+def ref_render_infer(field, rays_o, rays_d, bitfield, C, H, aabb, min_near, bg_color=1.0, max_steps=1024, density_scale=1.0):
+    """renderer.py:325-374 (eval branch): the alive-ray loop of march_rays -> forward(x, d) -> composite_rays with the
+    host-side compaction (one device->host sync per iteration for the alive count).  Returns image, depth, samples evaluated."""
+    N = rays_o.shape[0]
+    dev = rays_o.device
+    R = ext("raymarching")
+    nears = torch.empty(N, device=dev); fars = torch.empty(N, device=dev)
+    R.near_far_from_aabb(rays_o, rays_d, aabb, N, min_near, nears, fars)
+    ws = torch.zeros(N, device=dev); depth = torch.zeros(N, device=dev); image = torch.zeros(N, 3, device=dev)
+    alive = torch.arange(N, dtype=torch.int32, device=dev)
+    rays_t = nears.clone()
+    step, evaluated = 0, 0
+    while step < max_steps:
+        n_alive = alive.shape[0]
+        if n_alive <= 0:
+            break
+        n_step = max(min(N // n_alive, 8), 1)
+        M = n_alive * n_step
+        M += 128 - (M % 128)
+        xyzs = torch.zeros(M, 3, device=dev); dirs = torch.zeros(M, 3, device=dev); deltas = torch.zeros(M, 2, device=dev)
+        R.march_rays(n_alive, n_step, alive, rays_t, rays_o, rays_d, field.bound, 0.0, max_steps, C, H, bitfield, nears, fars,
+                     xyzs, dirs, deltas, 0)
+        sigmas, rgbs = field(xyzs, dirs)
+        sigmas = density_scale * sigmas
+        R.composite_rays(n_alive, n_step, alive, rays_t, sigmas.contiguous(), rgbs.contiguous(), deltas, ws, depth, image)
+        alive = alive[alive >= 0]
+        evaluated += M
+        step += n_step
+    image = image + (1 - ws).unsqueeze(-1) * bg_color
+    depth = torch.clamp(depth - nears, min=0) / (fars - nears)
+    return image, depth, evaluated

@@ -43,6 +43,43 @@ def step(model, opt, ro, rd, target, world):
                                max_steps=1024)
 
 
+def parity(dev, rays, rank, world, steps=3):
+    """SURVEY §8(d) config 5 on hardware: `steps` optimiser steps with the gradients averaged over the ranks (each rank its own
+    rays) against a single-process run of the same steps on the CONCATENATED batch (every rank computes it: the inputs are
+    seeded).  perturb = False and force_all_rays so that a ray takes the same samples in both runs.  Compared: the reduced
+    gradient of the first step (well conditioned: 1e-5 of the tensor's largest entry) and the parameters after the last
+    step.  Adam with eps = 1e-15 turns a gradient into +-lr whatever its size, so a parameter whose gradient is at the
+    rounding level of the sum can land on the other side; reported as the fraction of parameters within 1e-5 (of the
+    tensor's largest entry) plus the worst relative difference."""
+    kw = dict(perturb=False, force_all_rays=True, dt_gamma=0, max_steps=1024)
+    shards = [setup(dev, rays, r)[2:] for r in range(world)]
+    model_d, opt_d = setup(dev, rays, rank)[:2]
+    model_s, opt_s = setup(dev, rays, rank)[:2]
+    ro, rd, target = (torch.cat([s[i] for s in shards]) for i in range(3))
+    my = shards[rank]
+    grad_rel = 0.0
+    for it in range(steps):
+        training.train_step(model_d, opt_d, my[0], my[1], my[2], world=world, **kw)
+        training.train_step(model_s, opt_s, ro, rd, target, world=1, **kw)
+        if it == 0:
+            for a, b in zip(training.trainable(model_d), training.trainable(model_s)):
+                ga, gb = a.grad / world, b.grad
+                grad_rel = max(grad_rel, float((ga - gb).abs().max() / gb.abs().max().clamp_min(1e-30)))
+    worst, inside, total = 0.0, 0, 0
+    for a, b in zip(training.trainable(model_d), training.trainable(model_s)):
+        d = (a.detach() - b.detach()).abs() / b.detach().abs().max().clamp_min(1e-30)
+        worst = max(worst, float(d.max()))
+        inside += int((d <= 1e-5).sum()); total += d.numel()
+    ok = grad_rel < 1e-5 and inside / total > 0.999
+    if world > 1:
+        t = torch.tensor([1.0 if ok else 0.0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        ok = bool(t.item() > 0)
+    return {"train_parity": ok, "reduced_gradient_rel_err": grad_rel, "params_within_1e-5": inside / total,
+            "params_worst_rel_diff": worst, "steps": steps, "rays": world * rays,
+            "what": "rank-mean gradients / post-step parameters vs a single-process run on the concatenated batch"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rays", type=int, default=4096)

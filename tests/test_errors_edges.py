@@ -11,22 +11,27 @@ import torch
 def test_argument_validation_without_a_gpu(ngp):
     """Null pointers / unsupported shapes are rejected before any CUDA call, with a message naming the entry point."""
     L = ngp.lib()
+    prev = L.ngp_set_device_check(0)      # the host scratch pointers below are deliberate: argument checks come first here
     rc = L.ngp_near_far_from_aabb(None, None, None, 4, 0.2, None, None, None)
     assert rc == 1 and b"ngp_near_far_from_aabb" in L.ngp_last_error()
     rc = L.ngp_field_query_forward(None, 2.0, None, None, 0.5, 16, 0, 0, None, None, None, None, None, 8, None)
     assert rc != 0 and b"field_query" in L.ngp_last_error()
     rc = L.ngp_render_rays_infer(None, None, 8, None, 0.2, None, 2.0, 0.0, 1024, 2, 128, None, None, 0.5, 16, 0, 0, None, None,
-                                 None, None, None, 1.0, None, 0, None, None, None, None, None)
+                                 None, None, None, 1.0, None, 0, None, None, None, None, None, None)
     assert rc == 1 and b"ngp_render_rays_infer" in L.ngp_last_error()
     buf = (C.c_float * 64)()
     p = C.addressof(buf)
     rc = L.ngp_linear_wgrad(p, p, p, 16, 65, 64, p, 1 << 20, None)      # n_out > 64
     assert rc == 3 and b"n_out" in L.ngp_last_error()
-    rc = L.ngp_adam_step(p, p, p, p, None, 16, 1e-2, 0.9, 0.99, 1e-15, 0, 1.0, 0.0, None)   # step counts from 1
+    rc = L.ngp_adam_step(p, p, p, p, None, 16, 1e-2, 0.9, 0.99, 1e-15, 0, 1.0, 0.0, None, None, None)   # step counts from 1
     assert rc == 1 and b"step" in L.ngp_last_error()
     assert L.ngp_grid_backward_table_workspace_bytes(1000, 3, 16) > 4 * 1000 * 16 * 8 * 4
     assert L.ngp_march_rays_train_workspace_bytes(1000) >= 2 * 1000 * 4
-    assert L.ngp_render_rays_infer_workspace_bytes() == 16 and L.ngp_linear_wgrad_workspace_bytes(1 << 20) > 0
+    assert L.ngp_render_rays_infer_workspace_bytes() >= 16 and L.ngp_linear_wgrad_workspace_bytes(1 << 20) > 0
+    assert L.ngp_occ_grid_partial_workspace_bytes(128) > 4 * 128 ** 3
+    rc = L.ngp_occ_grid_mark_untrained(None, 3, 1.0, 1.0, 1.0, 1.0, 2, 128, 2.0, None, None)
+    assert rc == 1 and b"mark_untrained" in L.ngp_last_error()
+    L.ngp_set_device_check(prev)
 
 
 @pytest.mark.gpu

@@ -370,37 +370,3 @@ def test_single_pass_density_closure(model):
     assert torch.equal(outs[0][0], outs[1][0])
     assert rel_err(outs[0][1].cpu().numpy(), outs[1][1].cpu().numpy()) < 1e-5
     assert abs(outs[0][2] - outs[1][2]) <= 1e-6 * abs(outs[1][2])
-
-
-def test_occupancy_sweep_kernels_match_torch_path(model, ngp):
-    """update_extra_state full sweep on csrc/occgrid.cu == the reference-shaped torch path (renderer.py:457-486, 519-530)
-    when the jitter is switched off in both (torch.rand_like is not reproducible elsewhere); untrained cells (-1) stay."""
-    import copy
-    from unittest import mock
-    a, b = copy.deepcopy(model).eval(), copy.deepcopy(model).eval()
-    for m in (a, b):
-        m.reset_extra_state()
-        m.density_grid[0, 1000:1100] = -1.0          # "untrained" cells (mark_untrained_grid, renderer.py:381-444)
-    a.fused_occ_sweep = False
-    for it in range(2):                              # second round exercises the decay branch of the EMA-max
-        with mock.patch.object(torch, "rand_like", lambda t: torch.full_like(t, 0.5)):
-            a.update_extra_state()
-        b._update_extra_state_sweep(0.95, jitter=0.0)
-        assert torch.equal(a.density_grid, b.density_grid)
-        assert abs(a.mean_density - b.mean_density) <= 1e-6 * abs(a.mean_density)
-        assert (a.density_bitfield != b.density_bitfield).sum() <= 2       # a cell sitting exactly on the threshold
-    assert (b.density_grid[0, 1000:1100] == -1).all() and a.iter_density == b.iter_density == 2
-    # jittered positions: inside their cell, in Morton order
-    xyz = torch.empty(128 ** 3, 3, device="cuda")
-    ngp.check(ngp.lib().ngp_occ_grid_positions(1, 128, 2.0, 1.0, 7, xyz.data_ptr(), ngp.stream()))
-    ctr = torch.empty_like(xyz)
-    ngp.check(ngp.lib().ngp_occ_grid_positions(1, 128, 2.0, 0.0, 7, ctr.data_ptr(), ngp.stream()))
-    from nerf_navigation_b200 import raymarching as rm
-    coords = rm.morton3D_invert(torch.arange(128 ** 3, dtype=torch.int32, device="cuda"))
-    want = (2 * coords.float() / 127 - 1) * (2.0 - 2.0 / 128)
-    assert torch.equal(ctr, want)
-    dev = (xyz - ctr).abs()
-    assert dev.max() <= 2.0 / 128 and dev.mean() > 0.3 * 2.0 / 128 and abs(float((xyz - ctr).mean())) < 1e-4
-    # the default (jittered) sweep runs through update_extra_state
-    c = copy.deepcopy(model).eval(); c.reset_extra_state(); c.update_extra_state()
-    assert c.iter_density == 1 and c.mean_density > 0 and c.density_bitfield.any()

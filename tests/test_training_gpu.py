@@ -23,16 +23,44 @@ def test_fused_adam_matches_torch_adam(n):
     for step in range(6):
         g = torch.randn(n, device="cuda") * (10.0 ** (step - 3))
         pa.grad = g.clone() * 4.0          # as if 4 ranks' gradients had been summed
-        oa.grad_scale = 0.25
+        oa.grad_mult = 0.25
         pb.grad = g.clone()
         oa.step(); ob.step()
-        shadow = shadow - (1 - 0.95) * (shadow - pb.detach())       # torch_ema update (nerf/utils.py:814)
+        decay = min(0.95, (1 + (step + 1)) / (10 + (step + 1)))     # torch_ema, use_num_updates=True (the reference's default)
+        shadow = shadow - (1 - decay) * (shadow - pb.detach())      # torch_ema update (nerf/utils.py:814)
     assert rel_err(pa.detach().cpu().numpy(), pb.detach().cpu().numpy()) < 1e-6
     sa, sb = oa.state[pa], ob.state[pb]
     assert rel_err(sa["exp_avg"].cpu().numpy(), sb["exp_avg"].cpu().numpy()) < 1e-6
     assert rel_err(sa["exp_avg_sq"].cpu().numpy(), sb["exp_avg_sq"].cpu().numpy()) < 1e-6
     assert rel_err(oa.ema_shadow(pa).cpu().numpy(), shadow.cpu().numpy()) < 1e-6
     assert sa["step"] == 6
+
+
+def test_fused_adam_under_grad_scaler():
+    """The reference's fp16 recipe (nerf/utils.py:784-791): scaler.scale(loss).backward(); scaler.step(opt); scaler.update().
+    FusedAdam takes GradScaler's device-side scale / found_inf like torch's fused optimisers: finite gradients are unscaled
+    inside the kernel (== torch.optim.Adam under the same scaler), an inf gradient skips the step — parameters, moments,
+    step count and EMA untouched — and the scaler backs off."""
+    from nerf_navigation_b200.optim import FusedAdam
+    torch.manual_seed(3)
+    p0 = torch.randn(5000, device="cuda")
+    pa = torch.nn.Parameter(p0.clone()); pb = torch.nn.Parameter(p0.clone())
+    oa = FusedAdam([pa], lr=1e-2, betas=(0.9, 0.99), eps=1e-15, ema_decay=0.95)
+    ob = torch.optim.Adam([pb], lr=1e-2, betas=(0.9, 0.99), eps=1e-15)
+    sa = torch.amp.GradScaler("cuda", init_scale=1024.0); sb = torch.amp.GradScaler("cuda", init_scale=1024.0)
+    w = torch.randn(5000, device="cuda")
+    for step in range(5):
+        for p, o, sc in ((pa, oa, sa), (pb, ob, sb)):
+            o.zero_grad()
+            loss = ((p * w) ** 2).sum() * (float("inf") if step == 2 else 1.0)
+            sc.scale(loss).backward()
+            sc.step(o)
+            sc.update()
+        if step == 2:   # the overflow step changed nothing and halved the scale
+            assert oa.state[pa]["step"] == 2 and sa.get_scale() == 512.0 and sb.get_scale() == 512.0
+    assert rel_err(pa.detach().cpu().numpy(), pb.detach().cpu().numpy()) < 1e-6
+    assert oa.state[pa]["step"] == 4 and int(ob.state[pb]["step"]) == 4 and oa.ema_updates == 4
+    assert torch.isfinite(pa).all() and torch.isfinite(oa.ema_shadow(pa)).all()
 
 
 @pytest.fixture(scope="module")
