@@ -84,11 +84,12 @@ def mark_untrained(grid, poses, intrinsic, G, bound):
 
 
 def linspace(lo, hi, n):
-    """torch.linspace in float32: start + i step for the first half, end - (n - 1 - i) step for the second."""
+    """torch.linspace in float32: start + i step for the first half, end - (n - 1 - i) step for the second, each a fused
+    multiply-add on the GPU (one rounding: evaluated here in float64, where the product and sum are exact, then rounded)."""
     lo, hi = np.float32(lo), np.float32(hi)
-    step = np.float32((hi - lo) / np.float32(n - 1))
-    i = np.arange(n)
-    return np.where(i < n // 2, lo + step * i.astype(np.float32), hi - step * (n - 1 - i).astype(np.float32)).astype(np.float32)
+    step = np.float64(np.float32((hi - lo) / np.float32(n - 1)))
+    i = np.arange(n).astype(np.float64)
+    return np.where(i < n // 2, np.float64(lo) + step * i, np.float64(hi) - step * (n - 1 - i)).astype(np.float32)
 
 
 def astar_lattice(lo, hi, side):
