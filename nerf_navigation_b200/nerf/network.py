@@ -80,11 +80,25 @@ class NeRFNetwork(NeRFRenderer):
     def density(self, x):
         """network.py:126-143 -> {'sigma': [...], 'geo_feat': [..., 15]}."""
         if self._use_fused_density(x):
+            if x.requires_grad:
+                self._warn_eval_params()
             sigma, geo_feat = field_query(x, self.encoder, self.sigma_net[0].weight.detach(),
                                           self.sigma_net[1].weight.detach(), self.bound)
             return {"sigma": sigma, "geo_feat": geo_feat}
         h = self._sigma_mlp(self.encoder(x, bound=self.bound))
         return {"sigma": trunc_exp(h[..., 0]), "geo_feat": h[..., 1:]}
+
+    def _warn_eval_params(self):
+        """eval() mode takes the fused kernels, whose gradients reach the inputs only (the planner / estimator case:
+        simulate.py:191 calls model.eval() and differentiates w.r.t. points / poses).  The reference would ALSO fill
+        parameter gradients there; say so once instead of silently leaving them None."""
+        if (not self.training and torch.is_grad_enabled() and not getattr(self, "_eval_param_warned", False)
+                and any(p.requires_grad for p in self.parameters())):
+            import warnings
+            self._eval_param_warned = True
+            warnings.warn("NeRFNetwork in eval() mode uses the fused field kernels: gradients flow to x / d only, parameter "
+                          "gradients are not computed.  Call model.train() (or set model.fused_eval = False) to get them, or "
+                          "freeze the parameters (requires_grad_(False)) to silence this.", stacklevel=3)
 
     def _frozen(self):
         return not self.training or not torch.is_grad_enabled() or not any(p.requires_grad for p in self.parameters())
@@ -93,6 +107,8 @@ class NeRFNetwork(NeRFRenderer):
         """network.py:95-124 -> (sigma [...], color [..., 3]).  Frozen field on CUDA: one fused kernel each way."""
         if (self.fused_eval and self._frozen() and x.is_cuda and self.num_layers == 2 and hasattr(self.encoder, "embeddings")
                 and fused_color_supported(self, x, d)):
+            if x.requires_grad or d.requires_grad:
+                self._warn_eval_params()
             return field_color(self, x, d)
         dens = self.density(x)
         return dens["sigma"], self._color_mlp(d, dens["geo_feat"])

@@ -80,6 +80,64 @@ def test_run_torch_sampler_fwd_bwd_to_pose(model):
     assert rel_err(ga.cpu().numpy(), ro.grad.cpu().numpy()) < 5e-4 and rel_err(gb.cpu().numpy(), rd.grad.cpu().numpy()) < 5e-4
 
 
+def test_ray_gradient_bar_is_the_fp32_floor(model, ngp):
+    """The pose gradient (dL/d rays_o, dL/d rays_d of the photometric loss, 512 samples per ray) against a FLOAT64 oracle, on
+    a 64-ray subset (32,768 samples): util.run_f64 evaluates the reference's definition of the field — sample depths,
+    box clipping, grid cells and interpolation weights taken at the fp32 positions the reference itself computes
+    (gridencoder.cu:134-138), everything after that exact — with torch autograd in double.  Three fp32 evaluations are
+    measured against it: ours (fused kernels), the unfused op kernels, and the reference's own CUDA build driven as its
+    Python does (oracle/ref_pipeline.ref_run, when oracle/_ref is in the tree).  Asserted: ours meets north_star's 1e-5
+    against fp64, and is not further from it than 1.5x the reference build / the unfused path.  (The looser 5e-4 bars of the
+    fused-vs-unfused and golden comparisons in this file are between TWO fp32 evaluation orders over 4x as many rays, where
+    a ReLU or cell-face tie moves one sample's gradient by a whole term: this test is the pinned statement.)"""
+    from util import run_f64, load_ref
+    model.eval()
+    n = 64
+    o, d = orbit_rays(n, 9)
+    ro32, rd32 = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    tgt = torch.rand(n, 3, device="cuda")
+    from nerf_navigation_b200 import raymarching as rm
+    near, far = rm.near_far_from_aabb(ro32, rd32, model.aabb_infer, model.min_near)
+    s = torch.empty(16, device="cuda")
+    ngp.check(ngp.lib().ngp_grid_level_scales(s.data_ptr(), 16, float(np.log2(model.encoder.per_level_scale)), 16, ngp.stream()))
+    a, b = ro32.double().requires_grad_(), rd32.double().requires_grad_()
+    img64 = run_f64(model, a, b, near, far, s.cpu().numpy().astype(np.float64))
+    ((img64 - tgt.double()) ** 2).mean().backward()
+    g64 = torch.cat([a.grad, b.grad], -1)
+
+    def grad32(render):
+        x, y = ro32.clone().requires_grad_(), rd32.clone().requires_grad_()
+        img = render(x, y)
+        ((img - tgt) ** 2).mean().backward()
+        return torch.cat([x.grad, y.grad], -1).double(), img.detach()
+
+    def dist(g):
+        return float((g - g64).abs().max() / g64.abs().max())
+
+    kw = dict(staged=True, bg_color=1.0, perturb=False, num_steps=512, upsample_steps=0, max_ray_batch=4096)
+    model.cuda_ray = False
+    try:
+        g_ours, img_ours = grad32(lambda x, y: model.render(x[None], y[None], **kw)["image"][0])
+        model.fused_eval = False
+        g_unf, _ = grad32(lambda x, y: model.render(x[None], y[None], **kw)["image"][0])
+    finally:
+        model.fused_eval = True
+        model.cuda_ray = True
+    assert rel_err(img_ours.cpu().numpy(), img64.detach().cpu().numpy()) < 1e-5          # the VALUES meet the fp32 bar
+    e_ours, e_unf = dist(g_ours), dist(g_unf)
+    others = [e_unf]
+    if load_ref("gridencoder") is not None and load_ref("shencoder") is not None and load_ref("raymarching") is not None:
+        from oracle import ref_pipeline as RP
+        field = RP.RefField(model.encoder.embeddings.detach(), model.encoder.offsets, model.encoder.per_level_scale,
+                            [l.weight.detach() for l in model.sigma_net], [l.weight.detach() for l in model.color_net], 2.0)
+        g_ref, _ = grad32(lambda x, y: RP.ref_run(field, x, y, model.aabb_infer, model.min_near, num_steps=512)[0])
+        others.append(dist(g_ref))
+    print(f"ray-gradient distance from fp64: ours {e_ours:.2e}, unfused {e_unf:.2e}" +
+          (f", reference CUDA build {others[-1]:.2e}" if len(others) > 1 else ""))
+    assert e_ours < 1e-5
+    assert e_ours <= 1.5 * max(others) + 2e-6
+
+
 def test_run_cuda_train_and_eval_agree(model):
     """Same rays through the training branch (march_rays_train + composite_rays_train) and the inference loop
     (march_rays / composite_rays): identical samples => images agree to fp32 rounding."""
