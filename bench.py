@@ -450,12 +450,13 @@ def run_b200(args):
         emodel, eposes, epix, etarget, ekw = BE.setup(dev, args.hypotheses, 4096)
         lo, hi = shard_range(args.hypotheses, rank, world)
         eposes = eposes[lo:hi]
-        BE.step(emodel, eposes, epix, etarget, ekw, 32)
+        estates = emodel.estimator_states[lo:hi].contiguous()
+        BE.step_states(emodel, estates, epix, etarget, ekw)
         barrier()
         e4, e5 = ev(), ev()
         e4.record()
         for _ in range(args.estimator_steps):
-            BE.step(emodel, eposes, epix, etarget, ekw, 32)
+            elosses, egrads = BE.step_states(emodel, estates, epix, etarget, ekw)
         e5.record()
         barrier()
         t_est = e4.elapsed_time(e5) / 1e3 / args.estimator_steps
@@ -546,11 +547,14 @@ def run_b200(args):
         dist.all_reduce(cnt)
         ren_samples = int(cnt.item())
     if not args.no_estimator:
-        est = {"metric": "estimator rays/s (photometric loss fwd + bwd to pose)", "value": args.hypotheses * 4096 / t_est,
+        est = {"metric": "estimator rays/s (photometric loss fwd + bwd to the 12-state)", "value": args.hypotheses * 4096 / t_est,
                "unit": "rays/s", "ms_per_step": t_est * 1e3, "hypotheses": args.hypotheses, "rays_per_hypothesis": 4096,
                "scaling": "strong", "sharding": "pose hypotheses by rank, replicated field, no collective",
                "scene": "synthetic stonehenge occupancy (128^3 x 2 cascades), random-init field, ~75 samples/ray",
-               "path": "near_far -> march_rays_train -> fused tcgen05 field+colour kernels (csrc/cfield5.cu) -> composite_rays_train, and backward",
+               "path": "12-states -> poses -> rays of the sampled pixels (one kernel) -> near_far -> march_rays_train -> fused tcgen05 field+colour "
+                       "kernels (csrc/cfield5.cu) -> composite_rays_train -> per-hypothesis MSE, and backward to the 12-states; all "
+                       "hypotheses of the rank in ONE launch chain (no Python loop over chunks)",
+               "loss_gt_hypothesis": float(elosses[0]) if rank == 0 else None, "grad_state_abs_mean": float(egrads.abs().mean()),
                "samples_per_ray": est_spr, "reference_cuda_build_same_box": "ref_cuda_build / estimator_vs_ref_cuda in this line"}
     if rank != 0:
         if world > 1:

@@ -183,6 +183,18 @@ int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *rays_alive, fl
                        const float *rgbs, const float *deltas, float *weights_sum, float *depth, float *image,
                        ngp_stream_t stream);
 
+/* ---- pose -> rays closure of the estimator: get_rays (nerf/utils.py:52-116) at the sampled pixels only, for a batch of
+ * hypotheses (nav/estimator_helpers.py:311-314 builds all H*W rays of one pose and indexes ~1k of them) ------------------- */
+
+/* poses [P,4,4] cam2world (row-major), pix i64 [R] flat pixel indices (j * W + i) shared by the hypotheses, pinhole
+ * (fx, fy, cx, cy) -> rays_o, rays_d [P*R, 3] (hypothesis-major): dir = ((i + .5 - cx) / fx, (j + .5 - cy) / fy, 1) / |.|,
+ * rays_d = R dir, rays_o = t.  Backward: grad_poses [P,4,4] (row 3 = 0) from grad_o / grad_d [P*R,3] (either may be NULL),
+ * one fixed-order reduction over the R rays of each hypothesis. */
+int ngp_pose_rays_forward(const float *poses, const int64_t *pix, int P, int R, int W, float fx, float fy, float cx, float cy,
+                          float *rays_o, float *rays_d, ngp_stream_t stream);
+int ngp_pose_rays_backward(const float *grad_o, const float *grad_d, const int64_t *pix, int P, int R, int W, float fx, float fy,
+                           float cx, float cy, float *grad_poses, ngp_stream_t stream);
+
 /* ---- fused inference renderer: NeRFRenderer.run_cuda eval branch, nerf/renderer.py:325-374 ----------------------- */
 
 /* One persistent kernel for: near_far_from_aabb -> loop { march_rays -> NeRFNetwork.forward(x, d) -> composite_rays ->

@@ -45,6 +45,8 @@ _SIGNATURES = {
     "ngp_composite_rays_train_backward": ([P, P, P, P, P, P, P, P, I64, I64, P, P, P], I),
     "ngp_march_rays": ([I64, U32, P, P, P, P, F, F, U32, U32, U32, P, P, P, P, P, P, U32, P], I),
     "ngp_composite_rays": ([I64, U32, P, P, P, P, P, P, P, P, P], I),
+    "ngp_pose_rays_forward": ([P, P, I, I, I, F, F, F, F, P, P, P], I),
+    "ngp_pose_rays_backward": ([P, P, P, I, I, I, F, F, F, F, P, P], I),
     "ngp_render_rays_infer_workspace_bytes": ([], I64),
     "ngp_render_rays_infer": ([P, P, I64, P, F, P, F, F, U32, U32, U32, P, P, F, U32, U32, I, P, P, P, P, P, F, P, I, P, P,
                               P, P, P, P], I),

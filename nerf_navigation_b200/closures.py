@@ -7,12 +7,50 @@ rays_d = dir @ R^T, rays_o = t (cam2world pose [R|t]); loss = mse(render(rays).i
 Everything is differentiable w.r.t. the poses through the march_rays_train pose-gradient extension (cuda_ray=True) or
 the torch sampler (cuda_ray=False).
 """
+import math
+
 import torch
+
+
+class _pose_rays(torch.autograd.Function):
+    """rays_from_poses on the GPU: one kernel forward, one per-hypothesis reduction backward (csrc/rays.cu)."""
+
+    @staticmethod
+    def forward(ctx, poses, pix, intrinsics, W):
+        from . import _lib
+        P, R = poses.shape[0], pix.shape[0]
+        poses = poses.contiguous().float()
+        pix = pix.contiguous().long()
+        rays_o = torch.empty(P, R, 3, device=poses.device)
+        rays_d = torch.empty(P, R, 3, device=poses.device)
+        fx, fy, cx, cy = (float(v) for v in intrinsics)
+        with torch.cuda.device(poses.device):
+            _lib.check(_lib.lib().ngp_pose_rays_forward(_lib.ptr(poses), _lib.ptr(pix), P, R, int(W), fx, fy, cx, cy,
+                                                        _lib.ptr(rays_o), _lib.ptr(rays_d), _lib.stream()), "pose_rays_forward")
+        ctx.save_for_backward(pix)
+        ctx.cfg = (P, R, int(W), fx, fy, cx, cy)
+        return rays_o, rays_d
+
+    @staticmethod
+    def backward(ctx, grad_o, grad_d):
+        from . import _lib
+        (pix,) = ctx.saved_tensors
+        P, R, W, fx, fy, cx, cy = ctx.cfg
+        go = None if grad_o is None else grad_o.contiguous().float()
+        gd = None if grad_d is None else grad_d.contiguous().float()
+        grad_poses = torch.empty(P, 4, 4, device=pix.device)
+        with torch.cuda.device(pix.device):
+            _lib.check(_lib.lib().ngp_pose_rays_backward(_lib.ptr(go), _lib.ptr(gd), _lib.ptr(pix), P, R, W, fx, fy, cx, cy,
+                                                         _lib.ptr(grad_poses), _lib.stream()), "pose_rays_backward")
+        return grad_poses, None, None, None
 
 
 def rays_from_poses(poses, pix, intrinsics, W):
     """poses [P,4,4] cam2world, pix [R] int64 flat pixel indices (row-major, j*W+i) shared by all hypotheses
-    -> rays_o, rays_d [P,R,3]."""
+    -> rays_o, rays_d [P,R,3].  CUDA tensors take the fused kernels (forward + per-hypothesis gradient reduction); the
+    torch formulation below is the CPU / reference-shaped form (and the one the golden vectors pin)."""
+    if poses.is_cuda and poses.dtype == torch.float32:
+        return _pose_rays.apply(poses, pix, tuple(intrinsics), W)
     fx, fy, cx, cy = intrinsics
     i = (pix % W).to(poses.dtype) + 0.5
     j = torch.div(pix, W, rounding_mode="floor").to(poses.dtype) + 0.5
@@ -21,6 +59,68 @@ def rays_from_poses(poses, pix, intrinsics, W):
     rays_d = d.unsqueeze(0) @ poses[:, :3, :3].transpose(-1, -2)
     rays_o = poses[:, None, :3, 3].expand_as(rays_d)
     return rays_o, rays_d
+
+
+def rotvec_to_matrix(v):
+    """Rodrigues' formula as nav/math_utils.py:159-174 writes it: axis = v / (1e-10 + |v|) (so v = 0 gives the identity and
+    a zero gradient), R = I + sin(a) K + (1 - cos(a)) K K.  v [..., 3] -> [..., 3, 3]."""
+    angle = torch.norm(v, dim=-1, keepdim=True)
+    k = v / (1e-10 + angle)
+    zero = torch.zeros_like(k[..., 0])
+    K = torch.stack([torch.stack([zero, -k[..., 2], k[..., 1]], -1),
+                     torch.stack([k[..., 2], zero, -k[..., 0]], -1),
+                     torch.stack([-k[..., 1], k[..., 0], zero], -1)], -2)
+    a = angle[..., None]
+    return torch.eye(3, dtype=v.dtype, device=v.device) + torch.sin(a) * K + (1 - torch.cos(a)) * (K @ K)
+
+
+def state_to_pose(states):
+    """The estimator's 12-state (position 3, velocity 3, rotation vector 3, angular velocity 3) -> the cam2world pose the
+    renderer sees (nav/estimator_helpers.py:293-327 measurement_fn): R = vec_to_rot_matrix(state[6:9]); the camera looks
+    along the body y axis, hence rot_x(pi/2) @ R; then Blender -> NGP axes (nav/math_utils.py:26-38): flip_yz @ rot @ neg_yz
+    and flip_yz @ position.  states [P,12] -> poses [P,4,4], differentiable (dL/d(12-state) by autograd: velocity and
+    angular velocity take no gradient from the measurement)."""
+    dt, dev = states.dtype, states.device
+    half_pi = torch.tensor(math.pi / 2, dtype=torch.float32)           # the reference evaluates cos / sin of a float32 pi / 2
+    c, s = float(torch.cos(half_pi)), float(torch.sin(half_pi))
+    rot_x = torch.tensor([[1.0, 0.0, 0.0], [0.0, c, -s], [0.0, s, c]], dtype=dt, device=dev)
+    flip_yz = torch.tensor([[0.0, 1.0, 0.0], [0.0, 0.0, 1.0], [1.0, 0.0, 0.0]], dtype=dt, device=dev)
+    neg_yz = torch.tensor([[1.0, 0.0, 0.0], [0.0, -1.0, 0.0], [0.0, 0.0, -1.0]], dtype=dt, device=dev)
+    R = rotvec_to_matrix(states[:, 6:9])
+    rot = flip_yz @ (rot_x @ R) @ neg_yz
+    trans = states[:, :3] @ flip_yz.t()
+    top = torch.cat([rot, trans[..., None]], -1)
+    bottom = torch.tensor([0.0, 0.0, 0.0, 1.0], dtype=dt, device=dev).expand(states.shape[0], 1, 4)
+    return torch.cat([top, bottom], -2)
+
+
+def pose_to_state(pose, velocity=None, angular_velocity=None):
+    """Inverse of state_to_pose for one cam2world pose [4,4] (rotation angle in (0, pi)): the 12-state whose measurement
+    sees that pose — used to seed hypothesis batches from a camera pose."""
+    dt = pose.dtype
+    half_pi = torch.tensor(math.pi / 2, dtype=torch.float32)
+    c, s = float(torch.cos(half_pi)), float(torch.sin(half_pi))
+    rot_x = torch.tensor([[1.0, 0.0, 0.0], [0.0, c, -s], [0.0, s, c]], dtype=dt)
+    flip_yz = torch.tensor([[0.0, 1.0, 0.0], [0.0, 0.0, 1.0], [1.0, 0.0, 0.0]], dtype=dt)
+    neg_yz = torch.tensor([[1.0, 0.0, 0.0], [0.0, -1.0, 0.0], [0.0, 0.0, -1.0]], dtype=dt)
+    pose = pose.detach().cpu()
+    R = rot_x.t() @ flip_yz.t() @ pose[:3, :3] @ neg_yz          # neg_yz is its own inverse
+    angle = torch.acos(((torch.trace(R) - 1) / 2).clamp(-1, 1))
+    axis = torch.stack([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]]) / (2 * torch.sin(angle)).clamp_min(1e-12)
+    z3 = torch.zeros(3, dtype=dt)
+    return torch.cat([flip_yz.t() @ pose[:3, 3], z3 if velocity is None else velocity, angle * axis,
+                      z3 if angular_velocity is None else angular_velocity])
+
+
+def measurement_loss(model, states, pix, target, intrinsics, W, start_states=None, sig_inv=None, **render_kwargs):
+    """measurement_fn for a batch of state hypotheses [P,12]: mse(render(rays(state_to_pose(state))), target) per hypothesis
+    (+ the Mahalanobis process term delta^T sig_inv delta when start_states / sig_inv are given).  Returns losses [P];
+    .sum().backward() gives dL_p / d state_p for every hypothesis in one pass."""
+    loss = photometric_loss(model, state_to_pose(states), pix, target, intrinsics, W, **render_kwargs)
+    if start_states is not None and sig_inv is not None:
+        delta = states - start_states
+        loss = loss + torch.einsum("pi,ij,pj->p", delta, sig_inv, delta)
+    return loss
 
 
 def photometric_loss(model, poses, pix, target, intrinsics, W, **render_kwargs):

@@ -639,3 +639,92 @@ extern "C" int ngp_composite_rays(int64_t n_alive, uint32_t n_step, int32_t *ray
     NGP_CHECK_LAUNCH("ngp_composite_rays");
     return NGP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ pose -> rays closure
+// The estimator's measurement (nav/estimator_helpers.py:293-327) builds ALL H*W rays of one pose with get_rays
+// (nerf/utils.py:52-116) and then indexes the ~1k sampled pixels; here only the sampled pixels' rays are generated, for a
+// batch of pose hypotheses at once, with the same conventions: pixel centres at +0.5, camera-space direction
+// ((i - cx) / fx, (j - cy) / fy, 1) normalised, rays_d = dir @ R^T, rays_o = t (pose = cam2world [R | t]).
+//   k_pose_rays_fwd: one thread per (hypothesis, pixel);
+//   k_pose_rays_bwd: dL/d(pose) = [sum_r grad_d (x) dir_r | sum_r grad_o]: one CTA per hypothesis, fixed-order tree over its
+//       rays (deterministic), so the estimator step has no eager elementwise / matmul launches around the marcher.
+__device__ __forceinline__ void pose_pixel_dir(int64_t pix, int W, float fx, float fy, float cx, float cy, float (&d)[3]) {
+    const float i = (float)(pix % W) + 0.5f, j = (float)(pix / W) + 0.5f;
+    const float x = __fdiv_rn(i - cx, fx), y = __fdiv_rn(j - cy, fy);
+    const float n = sqrtf(fmaf(x, x, fmaf(y, y, 1.0f)));
+    d[0] = __fdiv_rn(x, n); d[1] = __fdiv_rn(y, n); d[2] = __fdiv_rn(1.0f, n);
+}
+
+__global__ void __launch_bounds__(RAY_THREADS)
+k_pose_rays_fwd(const float *__restrict__ poses, const int64_t *__restrict__ pix, int P, int R, int W, float fx, float fy,
+                float cx, float cy, float *__restrict__ rays_o, float *__restrict__ rays_d) {
+    const int64_t q = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
+    if (q >= (int64_t)P * R) return;
+    const int p = (int)(q / R), r = (int)(q - (int64_t)p * R);
+    float d[3];
+    pose_pixel_dir(pix[r], W, fx, fy, cx, cy, d);
+    const float *M = poses + (size_t)p * 16;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        rays_d[q * 3 + a] = fmaf(d[2], __ldg(M + 4 * a + 2), fmaf(d[1], __ldg(M + 4 * a + 1), d[0] * __ldg(M + 4 * a)));
+        rays_o[q * 3 + a] = __ldg(M + 4 * a + 3);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_pose_rays_bwd(const float *__restrict__ grad_o, const float *__restrict__ grad_d, const int64_t *__restrict__ pix, int R, int W,
+                float fx, float fy, float cx, float cy, float *__restrict__ grad_poses) {
+    __shared__ float part[8][12];
+    const int p = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = 0.0f;
+    for (int r = threadIdx.x; r < R; r += 256) {
+        float d[3];
+        pose_pixel_dir(pix[r], W, fx, fy, cx, cy, d);
+        const int64_t q = (int64_t)p * R + r;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float gd = grad_d ? grad_d[q * 3 + a] : 0.0f;
+            acc[4 * a + 0] = fmaf(gd, d[0], acc[4 * a + 0]);
+            acc[4 * a + 1] = fmaf(gd, d[1], acc[4 * a + 1]);
+            acc[4 * a + 2] = fmaf(gd, d[2], acc[4 * a + 2]);
+            acc[4 * a + 3] += grad_o ? grad_o[q * 3 + a] : 0.0f;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+        if (lane == 0) part[warp][k] = acc[k];
+    }
+    __syncthreads();
+    if (threadIdx.x < 16) {
+        float v = 0.0f;
+        if (threadIdx.x < 12)
+            for (int w = 0; w < 8; ++w) v += part[w][threadIdx.x];
+        grad_poses[(size_t)p * 16 + threadIdx.x] = v;      // row 3 of the pose takes no gradient
+    }
+}
+
+extern "C" int ngp_pose_rays_forward(const float *poses, const int64_t *pix, int P, int R, int W, float fx, float fy, float cx,
+                                     float cy, float *rays_o, float *rays_d, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(poses, "ngp_pose_rays_forward");
+    if ((int64_t)P * R == 0) return NGP_OK;
+    NGP_REQUIRE(poses && pix && rays_o && rays_d && P > 0 && R > 0 && W > 0, NGP_ERR_ARG, "ngp_pose_rays_forward: bad arguments");
+    k_pose_rays_fwd<<<(unsigned)ngp_div_up((int64_t)P * R, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+        poses, pix, P, R, W, fx, fy, cx, cy, rays_o, rays_d);
+    NGP_CHECK_LAUNCH("ngp_pose_rays_forward");
+    return NGP_OK;
+}
+
+extern "C" int ngp_pose_rays_backward(const float *grad_o, const float *grad_d, const int64_t *pix, int P, int R, int W, float fx,
+                                      float fy, float cx, float cy, float *grad_poses, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad_poses, "ngp_pose_rays_backward");
+    if (P == 0) return NGP_OK;
+    NGP_REQUIRE((grad_o || grad_d) && pix && grad_poses && P > 0 && R >= 0 && W > 0, NGP_ERR_ARG,
+                "ngp_pose_rays_backward: bad arguments");
+    k_pose_rays_bwd<<<P, 256, 0, (cudaStream_t)stream>>>(grad_o, grad_d, pix, R, W, fx, fy, cx, cy, grad_poses);
+    NGP_CHECK_LAUNCH("ngp_pose_rays_backward");
+    return NGP_OK;
+}

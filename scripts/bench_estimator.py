@@ -29,6 +29,14 @@ def setup(dev, hyp, rays, seed=0):
     gt = closures.look_at_pose((1.2, 0.0, 0.4))
     poses = closures.perturb_poses(gt, hyp, generator=g).to(dev)
     pix = torch.randint(0, H * W, (rays,), generator=g).to(dev)
+    # the same hypotheses in the estimator's own coordinates: 12-states around the state that sees `gt`
+    # (position +- 0.02 m, rotation vector +- 0.02 rad: SURVEY §8d config 3)
+    st0 = closures.pose_to_state(gt)
+    noise = torch.zeros(hyp, 12)
+    noise[:, 0:3] = torch.randn(hyp, 3, generator=g) * 0.02
+    noise[:, 6:9] = torch.randn(hyp, 3, generator=g) * 0.02
+    noise[0] = 0
+    model.estimator_states = (st0[None, :] + noise).to(dev)
     kw = dict(bg_color=1.0, perturb=False, dt_gamma=0, max_steps=1024, force_all_rays=True)
     with torch.no_grad():
         ro, rd = closures.rays_from_poses(poses[:1], pix, INTR, W)
@@ -48,6 +56,16 @@ def step(model, poses, pix, target, kw, chunk):
         losses[a:a + chunk] = l.detach()
         grads[a:a + chunk] = p.grad
     return losses, grads
+
+
+def step_states(model, states, pix, target, kw):
+    """The estimator step as nav/ runs it, for ALL hypotheses in one launch chain: 12-states -> poses (closures.state_to_pose)
+    -> rays of the sampled pixels (one kernel) -> march_rays_train -> fused field + colour -> composite -> per-hypothesis MSE
+    -> backward to the states.  Returns losses [P], dL_p / d state_p [P,12]."""
+    s = states.detach().requires_grad_(True)
+    l = closures.measurement_loss(model, s, pix, target, INTR, W, **kw)
+    l.sum().backward()
+    return l.detach(), s.grad
 
 
 def run(dev, hyp=256, rays=4096, chunk=16, steps=3, warmup=1):

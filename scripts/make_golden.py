@@ -54,8 +54,42 @@ def install_stubs():
     sys.path.insert(0, REF)
 
 
+def pose_algebra():
+    """nav/estimator_helpers.py:293-327 measurement_fn, the pose part: state[6:9] -> vec_to_rot_matrix (nav/math_utils.py:159-174)
+    -> rot_x(pi/2) @ R -> nerf_matrix_to_ngp_torch (math_utils.py:26-38) -> 4x4 cam2world handed to get_rays; plus the
+    gradient of a fixed linear functional of the pose w.r.t. the 12-state (autograd through the reference's own code)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_math_utils", os.path.join(REF, "nav", "math_utils.py"))
+    M = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(M)
+    gen = torch.Generator().manual_seed(11)
+    states = torch.randn(8, 12, generator=gen)
+    states[:, 6:9] *= 0.7
+    states[0, 6:9] = 0.0                        # zero rotation vector: the 1e-10 guard of vec_to_rot_matrix
+    states[1, 6:9] = torch.tensor([1e-6, 0.0, 0.0])
+    Wf = torch.randn(4, 4, generator=gen)
+    poses, grads = [], []
+    for st in states:
+        st = st.clone().requires_grad_(True)
+        R = M.vec_to_rot_matrix(st[6:9])
+        rot = M.rot_x(torch.tensor(np.pi / 2)) @ R[:3, :3]
+        pose, trans = M.nerf_matrix_to_ngp_torch(rot, st[:3])
+        new_pose = torch.eye(4)
+        new_pose[:3, :3] = pose
+        new_pose[:3, 3] = trans
+        (new_pose * Wf).sum().backward()
+        poses.append(new_pose.detach().numpy())
+        grads.append(st.grad.numpy())
+    np.savez(os.path.join(OUT, "pose_algebra.npz"), states=states.numpy(), poses=np.stack(poses), functional=Wf.numpy(),
+             grad_states=np.stack(grads))
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--pose-only" in sys.argv:
+        install_stubs()
+        pose_algebra()
+        return
     install_stubs()
     torch.set_num_threads(max(1, os.cpu_count() or 1))
 
@@ -113,6 +147,9 @@ def main():
     wts = torch.rand(7, 32, generator=gen)
     smp = R.sample_pdf(bins, wts, 48, det=True)
     np.savez(os.path.join(OUT, "sample_pdf.npz"), bins=bins.numpy(), weights=wts.numpy(), samples=smp.numpy())
+
+    # ---------------------------------------------------------------- estimator pose algebra (12-state -> NGP pose)
+    pose_algebra()
 
     # ---------------------------------------------------------------- config 1
     import encoding as E

@@ -116,3 +116,18 @@ def test_hashgrid_torch_transcription_vs_oracle(oracle):
     ref, _, _ = oracle.grid_encode_forward(x, cfg["table"], cfg["offsets"], sc)       # [L, B, C]
     out = C1.hashgrid_encode(torch.from_numpy(x), torch.from_numpy(cfg["table"]), cfg["offsets"], sc)
     assert rel_err(out.numpy().reshape(500, 16, 2).transpose(1, 0, 2), ref) < 1e-5
+
+
+def test_estimator_pose_algebra_golden():
+    """closures.state_to_pose (12-state -> NGP cam2world pose) and its gradient w.r.t. the state against the reference's own
+    vec_to_rot_matrix / rot_x / nerf_matrix_to_ngp_torch chain (nav/estimator_helpers.py:293-327, nav/math_utils.py:26-38,
+    159-174), incl. the zero rotation vector."""
+    from nerf_navigation_b200 import closures
+    g = np.load(os.path.join(GOLD, "pose_algebra.npz"))
+    states = torch.from_numpy(g["states"]).requires_grad_(True)
+    poses = closures.state_to_pose(states)
+    assert poses.shape == (8, 4, 4)
+    assert np.abs(poses.detach().numpy() - g["poses"]).max() < 1e-6
+    (poses * torch.from_numpy(g["functional"])).sum().backward()
+    assert np.abs(states.grad.numpy() - g["grad_states"]).max() < 1e-5 * max(1.0, np.abs(g["grad_states"]).max())
+    assert (states.grad[:, 3:6] == 0).all() and (states.grad[:, 9:] == 0).all()     # velocities take no measurement gradient

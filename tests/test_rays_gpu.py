@@ -231,3 +231,66 @@ def test_march_rays_train_pose_gradient(ngp):
     ((x2 * w1[:m]).sum() + (d2[ray_of] * w2[:m]).sum()).backward()
     assert rel_err(go.cpu().numpy(), o2.grad.cpu().numpy()) < 1e-5
     assert rel_err(gd.cpu().numpy(), d2.grad.cpu().numpy()) < 1e-5
+
+
+def test_pose_rays_kernels_vs_torch():
+    """closures.rays_from_poses on the GPU (one kernel + a per-hypothesis reduction backward) == the torch formulation that
+    the get_rays golden pins, values and the gradient w.r.t. the poses; and the full measurement (12-state -> pose -> rays ->
+    render -> mse) back-propagates to the states."""
+    from nerf_navigation_b200 import closures
+    g = torch.Generator().manual_seed(4)
+    gt = closures.look_at_pose((1.2, 0.0, 0.4))
+    poses = closures.perturb_poses(gt, 5, generator=g)
+    pix = torch.randint(0, 640000, (777,), generator=g)
+    intr = (1111.1, 1111.1, 400.0, 400.0)
+    wo, wd = torch.randn(5, 777, 3, generator=g), torch.randn(5, 777, 3, generator=g)
+    pc = poses.clone().requires_grad_(True)
+    ro_c, rd_c = closures.rays_from_poses(pc, pix, intr, 800)                 # CPU tensors: the torch formulation
+    ((ro_c * wo).sum() + (rd_c * wd).sum()).backward()
+    pg = poses.cuda().requires_grad_(True)
+    ro_g, rd_g = closures.rays_from_poses(pg, pix.cuda(), intr, 800)          # CUDA tensors: the kernels
+    ((ro_g * wo.cuda()).sum() + (rd_g * wd.cuda()).sum()).backward()
+    assert rel_err(ro_g.detach().cpu().numpy(), ro_c.detach().numpy()) == 0.0
+    assert rel_err(rd_g.detach().cpu().numpy(), rd_c.detach().numpy()) < 1e-6
+    assert rel_err(pg.grad.cpu().numpy(), pc.grad.numpy()) < 1e-5
+    assert (pg.grad[:, 3] == 0).all()
+
+
+def test_measurement_loss_backpropagates_to_states():
+    """nav/estimator_helpers.py:293-327 for a batch of state hypotheses: the hypothesis that equals the observed state has
+    (near) zero photometric loss, perturbed ones do not, and every hypothesis gets a finite gradient w.r.t. its position and
+    rotation vector (none w.r.t. its velocities)."""
+    from nerf_navigation_b200 import closures, synthetic
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    torch.manual_seed(0)
+    model = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=True, density_scale=1, min_near=0.2, density_thresh=10).cuda()
+    model.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    synthetic.install_stonehenge(model)
+    for p in model.parameters():
+        p.requires_grad_(False)
+    model.train()
+    gt = closures.look_at_pose((1.2, 0.0, 0.4))
+    st0 = closures.pose_to_state(gt)
+    assert float((closures.state_to_pose(st0[None])[0] - gt).abs().max()) < 1e-5       # round trip
+    g = torch.Generator().manual_seed(1)
+    noise = torch.zeros(6, 12)
+    noise[1:, 0:3] = torch.randn(5, 3, generator=g) * 0.02
+    noise[1:, 6:9] = torch.randn(5, 3, generator=g) * 0.02
+    states = (st0[None] + noise).cuda().requires_grad_(True)
+    pix = torch.randint(0, 640000, (1024,), generator=g).cuda()
+    intr = (1111.1, 1111.1, 400.0, 400.0)
+    kw = dict(bg_color=1.0, perturb=False, dt_gamma=0, max_steps=1024, force_all_rays=True)
+    with torch.no_grad():
+        ro, rd = closures.rays_from_poses(gt[None].cuda(), pix, intr, 800)
+        target = model.render(ro.reshape(1, -1, 3), rd.reshape(1, -1, 3), **kw)["image"].reshape(-1, 3)
+    losses = closures.measurement_loss(model, states, pix, target, intr, 800, **kw)
+    losses.sum().backward()
+    assert losses.shape == (6,) and float(losses[0]) < 1e-8 and float(losses[1:].min()) > 1e-6
+    gs = states.grad
+    assert torch.isfinite(gs).all() and (gs[:, 3:6] == 0).all() and (gs[:, 9:] == 0).all()
+    assert (gs[1:, :3].abs().sum(-1) > 0).all() and (gs[1:, 6:9].abs().sum(-1) > 0).all()
+    # the process term adds the Mahalanobis distance and its gradient
+    sig_inv = torch.eye(12, device="cuda") * 3.0
+    s2 = states.detach().clone().requires_grad_(True)
+    l2 = closures.measurement_loss(model, s2, pix, target, intr, 800, start_states=st0[None].cuda(), sig_inv=sig_inv, **kw)
+    assert torch.allclose(l2.detach() - losses.detach(), 3.0 * (noise.cuda() ** 2).sum(-1), atol=1e-7)
