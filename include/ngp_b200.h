@@ -152,6 +152,13 @@ int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t
                          uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M, const float *nears,
                          const float *fars, float *xyzs, float *dirs, float *deltas, int32_t *rays, int32_t *counter,
                          uint32_t perturb, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+/* Write-only second half of the two-call form: after ngp_march_rays_train(..., M = 0, xyzs = dirs = deltas = NULL, ...)
+ * counted the samples (counter[0]; `rays` holds (ray, offset, count)), this writes them into buffers of exactly that size
+ * without repeating the count pass.  `rays` / `workspace`: those of the count call, untouched in between. */
+int ngp_march_rays_train_write(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
+                               uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M, const float *nears,
+                               const float *fars, float *xyzs, float *dirs, float *deltas, const int32_t *rays,
+                               uint32_t perturb, const void *workspace, ngp_stream_t stream);
 
 /* EXTENSION (no reference counterpart; the reference's cuda_ray path is not differentiable w.r.t. the pose): gradient
  * of a loss w.r.t. rays_o / rays_d through the samples of ngp_march_rays_train, with the sample abscissae held constant

@@ -40,6 +40,7 @@ _SIGNATURES = {
     "ngp_packbits": ([P, I64, F, P, P], I),
     "ngp_march_rays_train_workspace_bytes": ([I64], I64),
     "ngp_march_rays_train": ([P, P, P, F, F, U32, I64, U32, U32, I64, P, P, P, P, P, P, P, U32, P, I64, P], I),
+    "ngp_march_rays_train_write": ([P, P, P, F, F, U32, I64, U32, U32, I64, P, P, P, P, P, P, U32, P, P], I),
     "ngp_march_rays_train_backward": ([P, P, P, P, P, P, P, F, U32, U32, I64, I64, P, P, P], I),
     "ngp_composite_rays_train_forward": ([P, P, P, P, I64, I64, P, P, P, P], I),
     "ngp_composite_rays_train_backward": ([P, P, P, P, P, P, P, P, I64, I64, P, P, P], I),

@@ -389,11 +389,40 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
     k_scan_tile_totals<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, N, tile_totals);
     k_scan_totals<<<1, SCAN_THREADS, 0, st>>>(tile_totals, n_tiles, counter, N);
     k_scan_write_rays<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, tile_totals, N, rays);
-    if (by_warp)
-        k_march_write_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
-    else
-        k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
+    if (M > 0) {
+        if (by_warp)
+            k_march_write_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
+        else
+            k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
+    }
     NGP_CHECK_LAUNCH("ngp_march_rays_train");
+    return NGP_OK;
+}
+
+// Second half of a two-call use: after ngp_march_rays_train(..., M = 0, ...) has counted, scanned and filled `rays` /
+// `counter` (the host reads counter[0] to size the sample buffers exactly), write the samples without marching the count
+// pass again.  `rays` and `workspace` must be the ones of that count call.
+extern "C" int ngp_march_rays_train_write(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound,
+                                          float dt_gamma, uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M,
+                                          const float *nears, const float *fars, float *xyzs, float *dirs, float *deltas,
+                                          const int32_t *rays, uint32_t perturb, const void *workspace, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_march_rays_train_write");
+    if (N == 0 || M == 0) return NGP_OK;
+    NGP_REQUIRE(rays_o && rays_d && grid && nears && fars && rays && xyzs && dirs && deltas && workspace, NGP_ERR_ARG,
+                "ngp_march_rays_train_write: null pointer");
+    NGP_REQUIRE(C >= 1 && C <= 8 && H >= 1 && H <= 1024, NGP_ERR_ARG, "ngp_march_rays_train_write: bad cascade/grid size");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int32_t *counts = (const int32_t *)workspace;
+    const int64_t n_tiles = ngp_div_up(N, SCAN_TILE);
+    const float *t_first = (const float *)(counts + N + n_tiles + 8);
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, H);
+    if (N <= MARCH_WARP_MAX_RAYS)
+        k_march_write_warp<<<(unsigned)ngp_div_up(N * 32, RAY_THREADS), RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars,
+                                                                                              perturb, rays, t_first, xyzs, dirs, deltas);
+    else
+        k_march_write<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb,
+                                                                                    rays, t_first, xyzs, dirs, deltas);
+    NGP_CHECK_LAUNCH("ngp_march_rays_train_write");
     return NGP_OK;
 }
 

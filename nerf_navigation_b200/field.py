@@ -60,10 +60,110 @@ class _field_query(Function):
         return grad_x, None, None, None, None, None, None, None, None, None
 
 
+def _host_chunks(B, chunk=1 << 20):
+    """Chunk sizes covering B points: a short first chunk (so the first kernel starts early) and a short last one (so little
+    of the last download is exposed), full chunks in between."""
+    if B <= chunk:
+        return [B] if B else []
+    head = [chunk // 4, chunk // 2]
+    if B < 2 * sum(head) + chunk:
+        return [min(chunk, B - a) for a in range(0, B, chunk)]
+    mid = B - 2 * sum(head)
+    return head + [chunk] * (mid // chunk) + ([mid % chunk] if mid % chunk else []) + head[::-1]
+
+
+_host_streams = {}
+
+
+def _streams_for(dev):
+    if dev not in _host_streams:
+        _host_streams[dev] = (torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+    return _host_streams[dev]
+
+
+class _field_query_host(Function):
+    """density() for points that live in PINNED HOST memory (the planner keeps its states on the host until the query,
+    nav/quad_plot.py:224-250): (x_host [B,3]) -> sigma [B], geo_feat [B,15] on the device; backward: dL/dx back in pinned
+    host memory.  Forward: the upload of chunk k+1 overlaps the forward kernel of chunk k; backward: the download of chunk
+    k overlaps the backward kernel of chunk k+1 (PCIe is full duplex, copies on their own streams), so the drop-in call
+    `model.density(x_pinned)` costs about max(copies, kernels) instead of their sum."""
+
+    @staticmethod
+    def forward(ctx, x, embeddings, W0, W1, offsets, bound, S, H, gridtype, align_corners):
+        dev = embeddings.device
+        _lib.require_cuda(embeddings, W0, W1, offsets)
+        embeddings = embeddings.contiguous(); W0 = W0.contiguous(); W1 = W1.contiguous()
+        B = x.shape[0]
+        need_bwd = ctx.needs_input_grad[0]
+        xd = torch.empty(B, 3, device=dev)
+        sigma = torch.empty(B, device=dev)
+        geo = torch.empty(B, 15, device=dev)
+        mask = torch.empty(B, device=dev, dtype=torch.int64) if need_bwd else None
+        s_in, _ = _streams_for(dev)
+        L = _lib.lib()
+        with torch.cuda.device(dev):
+            cur = torch.cuda.current_stream()
+            s_in.wait_stream(cur)                   # the buffers above were allocated on the current stream
+            a = 0
+            for n in _host_chunks(B):
+                with torch.cuda.stream(s_in):
+                    xd[a:a + n].copy_(x[a:a + n], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(s_in)
+                cur.wait_event(ev)
+                _lib.check(L.ngp_field_query_forward(
+                    xd[a:a + n].data_ptr(), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype,
+                    int(align_corners), _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), geo[a:a + n].data_ptr(),
+                    mask[a:a + n].data_ptr() if need_bwd else None, n, _lib.stream()), "field_query_forward")
+                a += n
+            xd.record_stream(s_in)
+        if need_bwd:
+            ctx.save_for_backward(xd, embeddings, W0, W1, offsets, sigma, mask)
+        ctx.cfg = (float(bound), S, H, gridtype, int(align_corners))
+        return sigma, geo
+
+    @staticmethod
+    def backward(ctx, grad_sigma, grad_geo):
+        xd, embeddings, W0, W1, offsets, sigma, mask = ctx.saved_tensors
+        bound, S, H, gridtype, align = ctx.cfg
+        dev = xd.device
+        B = xd.shape[0]
+        grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
+        gg = None if grad_geo is None else grad_geo.contiguous().float()
+        gxd = torch.empty(B, 3, device=dev)
+        gxh = torch.empty(B, 3, pin_memory=True)
+        _, s_out = _streams_for(dev)
+        L = _lib.lib()
+        with torch.cuda.device(dev):
+            cur = torch.cuda.current_stream()
+            a = 0
+            for n in _host_chunks(B):
+                _lib.check(L.ngp_field_query_backward(
+                    xd[a:a + n].data_ptr(), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align,
+                    _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), mask[a:a + n].data_ptr(),
+                    grad_sigma[a:a + n].data_ptr(), gg[a:a + n].data_ptr() if gg is not None else None,
+                    gxd[a:a + n].data_ptr(), n, _lib.stream()), "field_query_backward")
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(ev)
+                    gxh[a:a + n].copy_(gxd[a:a + n], non_blocking=True)
+                a += n
+            gxd.record_stream(s_out)
+            s_out.synchronize()                     # the caller reads x.grad on the host right away
+        return gxh, None, None, None, None, None, None, None, None, None
+
+
 def field_query(x, encoder, W0, W1, bound):
-    """x [..., 3] -> (sigma [...], geo_feat [..., 15])."""
+    """x [..., 3] -> (sigma [...], geo_feat [..., 15]).  x on the device, or in pinned host memory (pipelined copies)."""
     prefix = list(x.shape[:-1])
     S = float(np.log2(encoder.per_level_scale))
+    if not x.is_cuda:
+        if not x.is_pinned():
+            raise RuntimeError("expected a CUDA tensor or a PINNED host tensor (nerf_navigation_b200 has no CPU path)")
+        sigma, geo = _field_query_host.apply(x.reshape(-1, 3), encoder.embeddings, W0, W1, encoder.offsets, bound, S,
+                                             int(encoder.base_resolution), encoder.gridtype_id, encoder.align_corners)
+        return sigma.view(prefix), geo.view(prefix + [15])
     sigma, geo = _field_query.apply(x.reshape(-1, 3), encoder.embeddings, W0, W1, encoder.offsets, bound, S,
                                     int(encoder.base_resolution), encoder.gridtype_id, encoder.align_corners)
     return sigma.view(prefix), geo.view(prefix + [15])

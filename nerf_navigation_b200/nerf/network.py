@@ -56,7 +56,8 @@ class NeRFNetwork(NeRFRenderer):
         frozen = not self.training or not torch.is_grad_enabled() or not (
             self.encoder.embeddings.requires_grad or self.sigma_net[0].weight.requires_grad
             or self.sigma_net[1].weight.requires_grad)
-        return (self.fused_eval and frozen and x.is_cuda and self.num_layers == 2
+        on_gpu = x.is_cuda or (x.device.type == "cpu" and x.is_pinned() and self.encoder.embeddings.is_cuda)   # pinned host points
+        return (self.fused_eval and frozen and on_gpu and self.num_layers == 2
                 and hasattr(self.encoder, "embeddings")
                 and fused_supported(self.encoder, self.sigma_net[0].weight, self.sigma_net[1].weight, x))
 

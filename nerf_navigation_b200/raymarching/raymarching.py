@@ -122,8 +122,6 @@ class _march_rays_train(Function):
                                                   _lib.ptr(step_counter), int(perturb), _lib.ptr(ws), ws_bytes,
                                                   _lib.stream()), "march_rays_train")
                 m = int(step_counter[0].item())
-                step_counter[0] -= m  # the second call adds it back
-                step_counter[1] -= N
                 if align > 0:
                     m += align - m % align
                 M_alloc = m
@@ -132,11 +130,18 @@ class _march_rays_train(Function):
             xyzs = torch.zeros(M_alloc, 3, dtype=rays_o.dtype, device=dev)
             dirs = torch.zeros(M_alloc, 3, dtype=rays_o.dtype, device=dev)
             deltas = torch.zeros(M_alloc, 2, dtype=rays_o.dtype, device=dev)
-            _lib.check(L.ngp_march_rays_train(_lib.ptr(rays_o), _lib.ptr(rays_d), _lib.ptr(density_bitfield),
-                                              float(bound), float(dt_gamma), int(max_steps), N, int(C), int(H),
-                                              M if exact else M_alloc, _lib.ptr(nears), _lib.ptr(fars), _lib.ptr(xyzs),
-                                              _lib.ptr(dirs), _lib.ptr(deltas), _lib.ptr(rays), _lib.ptr(step_counter),
-                                              int(perturb), _lib.ptr(ws), ws_bytes, _lib.stream()), "march_rays_train")
+            if exact:   # counts, offsets and the counter are in place: only the write pass is left
+                _lib.check(L.ngp_march_rays_train_write(_lib.ptr(rays_o), _lib.ptr(rays_d), _lib.ptr(density_bitfield),
+                                                        float(bound), float(dt_gamma), int(max_steps), N, int(C), int(H), M,
+                                                        _lib.ptr(nears), _lib.ptr(fars), _lib.ptr(xyzs), _lib.ptr(dirs),
+                                                        _lib.ptr(deltas), _lib.ptr(rays), int(perturb), _lib.ptr(ws),
+                                                        _lib.stream()), "march_rays_train_write")
+            else:
+                _lib.check(L.ngp_march_rays_train(_lib.ptr(rays_o), _lib.ptr(rays_d), _lib.ptr(density_bitfield),
+                                                  float(bound), float(dt_gamma), int(max_steps), N, int(C), int(H), M_alloc,
+                                                  _lib.ptr(nears), _lib.ptr(fars), _lib.ptr(xyzs), _lib.ptr(dirs),
+                                                  _lib.ptr(deltas), _lib.ptr(rays), _lib.ptr(step_counter), int(perturb),
+                                                  _lib.ptr(ws), ws_bytes, _lib.stream()), "march_rays_train")
         if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
             ctx.save_for_backward(rays_o, rays_d, nears, deltas, rays)
             ctx.cfg = (float(bound), int(max_steps), int(perturb), N, M if exact else M_alloc)

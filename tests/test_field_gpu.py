@@ -123,3 +123,28 @@ def test_field_value_grad_vs_oracle_and_two_pass(ngp, oracle, B, mode):
     assert rel_err(gx.cpu().numpy(), rgx) < 1e-5
     if B > 10:
         assert sigma[2] == 1.0 and (gx[2] == 0).all()
+
+
+def test_density_on_pinned_host_points_matches_device_path():
+    """model.density(x) with x in PINNED HOST memory (the drop-in call, copies pipelined inside field._field_query_host):
+    sigma / geo_feat on the device and x.grad on the host equal the device-tensor path; ragged sizes around the chunk
+    schedule; a pageable host tensor is refused (no CPU path)."""
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    torch.manual_seed(0)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    for p in m.parameters():
+        p.requires_grad_(False)
+    for B in (1, 5000, (1 << 20) + 17, 3 * (1 << 20) + 5):
+        xh = (torch.rand(B, 3) * 4.2 - 2.1).pin_memory().requires_grad_(True)
+        out = m.density(xh)
+        assert out["sigma"].is_cuda and out["sigma"].shape == (B,) and out["geo_feat"].shape == (B, 15)
+        ((out["sigma"] ** 2).mean() + (out["geo_feat"] * 0.01).sum()).backward()
+        xd = xh.detach().cuda().requires_grad_(True)
+        ref = m.density(xd)
+        ((ref["sigma"] ** 2).mean() + (ref["geo_feat"] * 0.01).sum()).backward()
+        assert not xh.grad.is_cuda and xh.grad.is_pinned()
+        assert torch.equal(out["sigma"], ref["sigma"]) and torch.equal(out["geo_feat"], ref["geo_feat"])
+        assert torch.equal(xh.grad, xd.grad.cpu())
+    with pytest.raises(RuntimeError):
+        m.density(torch.rand(8, 3))
