@@ -64,20 +64,21 @@ def parse():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed `ncu --set full` capture
-    of this same workload at the same 4,194,304 points (profiles/r1_field_4m_ncu_keys.txt); None if the capture is not
-    there."""
-    p = os.path.join(ROOT, "profiles", "r1_field_4m_ncu_keys.txt")
-    if not os.path.exists(p):
-        return None
+    of this same workload at the same 4,194,304 points (profiles/r2_dfield5_4m_ncu_keys.txt for the tcgen05 kernels,
+    profiles/r1_field_4m_ncu_keys.txt for the mma.sync ones); None if the capture is not there."""
     cur, tot = None, {}
-    for line in open(p):
-        if line.startswith("----"):
-            cur = line
-        elif cur and "dram__bytes_" in line and ".sum" in line:
-            unit = line.split("[")[1].split("]")[0]
-            val = float(line.split("=")[1].strip().replace(",", ""))
-            mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
-            tot[cur] = tot.get(cur, 0.0) + val * mul
+    for name in ("r2_dfield5_4m_ncu_keys.txt", "r1_field_4m_ncu_keys.txt"):
+        p = os.path.join(ROOT, "profiles", name)
+        if not os.path.exists(p):
+            continue
+        for line in open(p):
+            if line.startswith("----"):
+                cur = line
+            elif cur and "dram__bytes_" in line and ".sum" in line:
+                unit = line.split("[")[1].split("]")[0]
+                val = float(line.split("=")[1].strip().replace(",", ""))
+                mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
+                tot[cur] = tot.get(cur, 0.0) + val * mul
     for k, v in tot.items():
         if kernel in k:
             return v
@@ -293,9 +294,24 @@ def run_b200(args):
                                              W1.data_ptr(), sigma.data_ptr(), mask.data_ptr(), gs.data_ptr(), None,
                                              gx.data_ptr(), B, st))
 
-    def step():
+    jac = torch.empty(B, 3, device=dev)
+
+    def fwd_jac():   # what density(x) launches when x requires a gradient (field._field_query.forward)
+        ngp.check(L.ngp_field_query_forward_jacobian(x.data_ptr(), BOUND, tab.data_ptr(), off.data_ptr(), S, H, 0, 0,
+                                                     W0.data_ptr(), W1.data_ptr(), sigma.data_ptr(), geo.data_ptr(),
+                                                     mask.data_ptr(), jac.data_ptr(), B, st))
+
+    def bwd_jac():   # ... and its backward for a gradient arriving through sigma (field._field_query.backward)
+        ngp.check(L.ngp_field_query_backward_jacobian(jac.data_ptr(), gs.data_ptr(), gx.data_ptr(), B, st))
+
+    def step():      # one field query: sigma, geo_feat and dL/dx for loss = mean(sigma^2) (quad_plot.py:237 collision cost)
+        fwd_jac()
+        torch.mul(sigma, 2.0 / B, out=gs)
+        bwd_jac()
+
+    def two_pass_step():   # the same result with a second table pass (the reference's structure: forward op, backward op)
         fwd()
-        torch.mul(sigma, 2.0 / B, out=gs)  # dL/dsigma of loss = mean(sigma^2)  (quad_plot.py:237 collision cost)
+        torch.mul(sigma, 2.0 / B, out=gs)
         bwd()
 
     def barrier():
@@ -310,23 +326,40 @@ def run_b200(args):
     sampler = ClockSampler(local) if rank == 0 else None
     t_begin = time.perf_counter()
     # ---- device-resident timed region: K steps, per-kernel events on the launching stream
-    e_fwd = [(ev(), ev()) for _ in range(args.steps)]
-    e_bwd = [(ev(), ev()) for _ in range(args.steps)]
+    e_fj = [(ev(), ev()) for _ in range(args.steps)]
+    e_bj = [(ev(), ev()) for _ in range(args.steps)]
     e0, e1 = ev(), ev()
     barrier()
     e0.record()
     for i in range(args.steps):
-        e_fwd[i][0].record(); fwd(); e_fwd[i][1].record()
+        e_fj[i][0].record(); fwd_jac(); e_fj[i][1].record()
         torch.mul(sigma, 2.0 / B, out=gs)
-        e_bwd[i][0].record(); bwd(); e_bwd[i][1].record()
+        e_bj[i][0].record(); bwd_jac(); e_bj[i][1].record()
     e1.record()
     barrier()
     t_dev = e0.elapsed_time(e1) / 1e3
+    fj_ms = float(np.mean([a.elapsed_time(b) for a, b in e_fj]))
+    bj_ms = float(np.mean([a.elapsed_time(b) for a, b in e_bj]))
+
+    # ---- the two-table-pass form of the same step (forward kernel, backward kernel): round 1's headline
+    for _ in range(3):
+        two_pass_step()
+    e_fwd = [(ev(), ev()) for _ in range(args.steps)]
+    e_bwd = [(ev(), ev()) for _ in range(args.steps)]
+    e2, e3 = ev(), ev()
+    barrier()
+    e2.record()
+    for i in range(args.steps):
+        e_fwd[i][0].record(); fwd(); e_fwd[i][1].record()
+        torch.mul(sigma, 2.0 / B, out=gs)
+        e_bwd[i][0].record(); bwd(); e_bwd[i][1].record()
+    e3.record()
+    barrier()
+    t_two = e2.elapsed_time(e3) / 1e3
     fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in e_fwd]))
     bwd_ms = float(np.mean([a.elapsed_time(b) for a, b in e_bwd]))
 
-    # ---- the same step as ONE kernel (csrc/fieldvg.cu: sigma and dL/dx = (2 sigma / B) dsigma/dx, corners kept in shared
-    # memory between the two halves: 1.25 table passes instead of 2)
+    # ---- the same step as ONE launch (ngp_field_query_value_grad: the upstream factor given in the affine form a + b sigma)
     def vg_step():
         ngp.check(L.ngp_field_query_value_grad(x.data_ptr(), BOUND, tab.data_ptr(), off.data_ptr(), S, H, 0, 0, W0.data_ptr(),
                                                W1.data_ptr(), None, None, 0.0, 2.0 / B, sigma.data_ptr(), geo.data_ptr(),
@@ -375,7 +408,7 @@ def run_b200(args):
                 key |= ((q[:, d] >> i) & 1) << (3 * i + d)
         xs = x_uniform[torch.argsort(key)].contiguous()
         locality = {"unit": UNIT, "clustered": timed_steps(xc), "uniform_morton_sorted": timed_steps(xs),
-                    "what": "fwd+bwd on (a) trajectory-clustered body clouds (config 2 (ii)), (b) the uniform batch handed "
+                    "what": "the headline step on (a) trajectory-clustered body clouds (config 2 (ii)), (b) the uniform batch handed "
                             "over in Morton order (8 bits/axis; sorting not timed); `value` is the uniform batch in arrival order"}
         del xc, xs, q, key
 
@@ -606,12 +639,17 @@ def run_b200(args):
     peaks, peak_kind = measured_peaks()
     value = world * B * args.steps / t_dev / 1e6
     e2e_val = world * B * e2e_steps / t_e2e_dropin / 1e6
-    dom, dom_ms = ("k_field_backward", bwd_ms) if bwd_ms >= fwd_ms else ("k_field_forward", fwd_ms)
-    achieved = B * BYTES_PER_POINT_PASS / (dom_ms / 1e3) / 1e9
+    tc5 = bool(L.ngp_set_field_impl(-1))
+    KF, KB = ("k_dfield5_forward", "k_dfield5_backward") if tc5 else ("k_field_forward", "k_field_backward")
+    KJ = "k_dfield5_value_grad" if tc5 else "k_field_forward + k_field_value_grad"
+    # dominant kernel of the headline step: the Jacobian-returning forward (one table pass per point)
+    dom, dom_ms = KJ, fj_ms
+    achieved = B * BYTES_PER_POINT_PASS * (1 if tc5 else 2.25) / (dom_ms / 1e3) / 1e9
     traffic = ncu_traffic(dom)
     # the kernel of this bench that sits lowest against the same roofline (not the longest one of the headline leg)
-    fracs = {"k_field_forward": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak,
-             "k_field_backward": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}
+    fracs = {KJ: achieved / gather_peak,
+             KF: B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak,
+             KB: B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}
     if not args.no_render and t_ren > 0:
         fracs["k_render5_rays_infer"] = ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak
     if not args.no_estimator:
@@ -625,12 +663,12 @@ def run_b200(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "points_per_gpu": B, "levels": 16, "feats": 2, "log2_table": 19,
                    "mlp": "32-64-16", "bound": BOUND, "points": "uniform[-1,1]^3", "sharding": "points by rank, replicated weights, no collective",
-                   "l2": "streams ~470 MB/step (> 126 MB L2) of points/outputs; the 48 MiB table is L2-resident by design"},
+                   "l2": "streams ~400 MB/step (> 126 MB L2) of points/outputs; the 48 MiB table is L2-resident by design"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * 12, "d2h_bytes_per_step": B * 12 + 4,
                 "steps": e2e_steps,
                 "api": "the reference-level call on host data: x = pinned host tensor; s = NeRFNetwork.density(x)['sigma']; "
-                       "(s ** 2).mean().backward(); x.grad (pinned host) + loss.item() — uploads pipelined with the forward "
-                       "kernels, downloads with the backward kernels, inside density() itself",
+                       "(s ** 2).mean().backward(); x.grad (pinned host) + loss.item() — uploads pipelined with the "
+                       "(Jacobian-returning) forward kernels, downloads with the backward kernels, inside density() itself",
                 "host_query_api": {"value": world * B * e2e_steps / t_e2e / 1e6,
                                    "api": f"field.HostFieldQuery(model)(x_pinned, (0, 2/B), None, grad_pinned, sigma_hook): chunks of "
                                           f"{args.e2e_chunk} points, H2D / single-pass value+grad kernel / D2H on 3 streams (the "
@@ -639,12 +677,20 @@ def run_b200(args):
                                  "api": "same call with dloss_dsigma as a Python callable: forward + backward kernels per chunk"},
                 "autograd_api": {"value": world * B * e2e_steps / t_e2e_autograd / 1e6,
                                  "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
-        "gpu_launches": 2 * args.steps,  # device-resident region; the e2e region launches 1 (single-pass) kernel per chunk
-        "kernels_ms": {"k_field_forward": fwd_ms, "k_field_backward": bwd_ms, "k_field_value_grad": t_vg / args.steps * 1e3},
+        "gpu_launches": 2 * args.steps,  # device-resident region: forward_jacobian + backward_jacobian per step
+        "step": "ngp_field_query_forward_jacobian (sigma, geo_feat, ReLU bits, d sigma / d x: ONE table pass) -> dL/dsigma = "
+                "2 sigma / B -> ngp_field_query_backward_jacobian (dL/dx = dL/dsigma * jac): the launches "
+                "NeRFNetwork.density(x) + backward() make for a point tensor that requires a gradient",
+        "kernels_ms": {KJ: fj_ms, "k_scale_rows3": bj_ms, KF: fwd_ms, KB: bwd_ms,
+                       "ngp_field_query_value_grad": t_vg / args.steps * 1e3},
         "locality": locality,
+        "two_pass": {"value": world * B * args.steps / t_two / 1e6, "unit": UNIT, "ms_per_step": t_two / args.steps * 1e3,
+                     "what": "the same outputs from ngp_field_query_forward + ngp_field_query_backward (two table passes, "
+                             "the reference's op structure and round 1's headline; rank-0 time); still what runs when a "
+                             "gradient arrives through geo_feat"},
         "single_pass": {"value": world * B * args.steps / t_vg / 1e6, "unit": UNIT,
-                        "what": "ngp_field_query_value_grad: the same sigma + dL/dx in ONE kernel (rank-0 time), "
-                                "1280 B of table gathers per point instead of 2048"},
+                        "what": "ngp_field_query_value_grad: sigma + dL/dx in ONE launch when the upstream gradient has the "
+                                "form a_i + b_i sigma_i (rank-0 time)"},
         "roofline": {"bound": "l2_gather", "kernel": dom, "achieved": achieved, "peak": gather_peak, "unit": "GB/s",
                      "frac": achieved / gather_peak, "traffic": traffic,
                      "peak_source": "ngp_probe_gather live on this GPU: 8-byte hashed-cell corner gathers from a 48 MiB "
@@ -652,7 +698,8 @@ def run_b200(args):
                      "peak_random8B": random8_peak,
                      "hbm_peak": peaks["hbm_gbs"], "hbm_peak_source": peak_kind,
                      "hbm_frac": (traffic / (dom_ms / 1e3) / 1e9 / peaks["hbm_gbs"]) if traffic else None,
-                     "note": "algorithmic bytes = 1024 B of table gathers per point per pass, served by L2 (table resident): the "
+                     "note": "algorithmic bytes = 1024 B of table gathers per point per table pass (the headline step makes ONE "
+                             "pass: value and Jacobian from the same corners), served by L2 (table resident): the "
                              "binding limit is the L1->L2 request rate, not HBM (DRAM traffic per launch = `traffic`, ~1.07x the "
                              "minimal point/output streaming, a few % of the HBM peak).  The peak is a PATTERN ceiling for "
                              "arrival-ordered uniform points: spatially clustered batches exceed it (locality.clustered)",
@@ -660,9 +707,10 @@ def run_b200(args):
         "l2_gather_roofline": {
             "peak": gather_peak, "unit": "GB/s useful", "how": "ngp_probe_gather live: 8-byte hashed-cell corner gathers "
             "from a 48 MiB L2-resident buffer, all SMs (the binding unit is one L1-miss sector per clock per SM)",
-            "k_field_forward": {"achieved": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9,
+            KJ: {"achieved": achieved, "frac": achieved / gather_peak},
+            KF: {"achieved": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9,
                                 "frac": B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak},
-            "k_field_backward": {"achieved": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9,
+            KB: {"achieved": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9,
                                  "frac": B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}},
         "clocks": clocks,
     }

@@ -107,6 +107,19 @@ int ngp_field_query_value_grad(const float *x, float bound, const float *embeddi
                                const float *coef_a, const float *coef_b, float a0, float b0, float *sigma, float *geo,
                                float *grad_x, int64_t B, ngp_stream_t stream);
 
+/* Density forward that also returns the Jacobian rows jac [B,3] = d sigma_i / d x_i (one table pass, csrc/dfield5.cu): what
+ * autograd's NeRFNetwork.density(x) runs when x requires a gradient (the planner's collision cost, nav/quad_plot.py:224-250,
+ * differentiates sigma w.r.t. the body-cloud points).  relu_mask (optional, u64 [B]) is what ngp_field_query_backward needs
+ * if a gradient also arrives through geo_feat; geo may be NULL. */
+int ngp_field_query_forward_jacobian(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                                     uint32_t H, uint32_t gridtype, int align_corners, const float *W0, const float *W1,
+                                     float *sigma, float *geo, uint64_t *relu_mask, float *jac, int64_t B,
+                                     ngp_stream_t stream);
+
+/* grad_x [B,3] = grad_sigma_i * jac_i: the backward of sigma after ngp_field_query_forward_jacobian (no table pass). */
+int ngp_field_query_backward_jacobian(const float *jac, const float *grad_sigma, float *grad_x, int64_t B,
+                                      ngp_stream_t stream);
+
 /* ---- fused per-sample field for the ray paths: NeRFNetwork.forward(x, d), nerf/network.py:95-124 ------------------- */
 
 /* Implementation of the fused colour-field / render kernels: 1 = warp-specialised tcgen05 (TMEM accumulators and A

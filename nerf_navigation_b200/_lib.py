@@ -30,6 +30,8 @@ _SIGNATURES = {
     "ngp_grid_encode_backward_table_atomic": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P], I),
     "ngp_field_query_forward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, I64, P], I),
     "ngp_field_query_value_grad": ([P, F, P, P, F, U32, U32, I, P, P, P, P, F, F, P, P, P, I64, P], I),
+    "ngp_field_query_forward_jacobian": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, I64, P], I),
+    "ngp_field_query_backward_jacobian": ([P, P, P, I64, P], I),
     "ngp_set_field_impl": ([I], I),
     "ngp_set_device_check": ([I], I),
     "ngp_field_color_forward": ([P, P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, P, I64, P], I),

@@ -298,6 +298,18 @@ static int fq_check(const float *embeddings, int64_t B, const char *who) {
     return NGP_OK;
 }
 
+// default implementation: the warp-specialised tcgen05 kernels of dfield5.cu; ngp_set_field_impl(0) / NGP_B200_FIELD_IMPL=mma
+// selects the mma.sync kernels above (kept as the independent fp32 cross-check).  relu_mask is opaque and its bit layout
+// belongs to the implementation that wrote it: a backward must run under the same setting as its forward.
+int ngp_field_impl_tc5();
+int d5_field_query_forward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                           uint32_t gridtype, int align_corners, const float *W0, const float *W1, float *sigma, float *geo,
+                           uint64_t *relu_mask, int64_t B, cudaStream_t stream);
+int d5_field_query_backward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                            uint32_t gridtype, int align_corners, const float *W0, const float *W1, const float *sigma,
+                            const uint64_t *relu_mask, const float *grad_sigma, const float *grad_geo, float *grad_x,
+                            int64_t B, cudaStream_t stream);
+
 extern "C" int ngp_field_query_forward(const float *x, float bound, const float *embeddings, const int32_t *offsets,
                                        float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                        const float *W1, float *sigma, float *geo, uint64_t *relu_mask, int64_t B,
@@ -308,6 +320,9 @@ extern "C" int ngp_field_query_forward(const float *x, float bound, const float 
     NGP_REQUIRE(bound > 0.0f, NGP_ERR_ARG, "ngp_field_query_forward: bound must be > 0");
     int rc = fq_check(embeddings, B, "ngp_field_query_forward");
     if (rc) return rc;
+    if (ngp_field_impl_tc5())
+        return d5_field_query_forward(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, geo, relu_mask,
+                                      B, (cudaStream_t)stream);
     k_field_forward<<<fq_grid(k_field_forward, B), FQ_THREADS, 0, (cudaStream_t)stream>>>(
         x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, geo, relu_mask, B);
     NGP_CHECK_LAUNCH("ngp_field_query_forward");
@@ -326,6 +341,9 @@ extern "C" int ngp_field_query_backward(const float *x, float bound, const float
     NGP_REQUIRE(bound > 0.0f, NGP_ERR_ARG, "ngp_field_query_backward: bound must be > 0");
     int rc = fq_check(embeddings, B, "ngp_field_query_backward");
     if (rc) return rc;
+    if (ngp_field_impl_tc5())
+        return d5_field_query_backward(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, relu_mask,
+                                       grad_sigma, grad_geo, grad_x, B, (cudaStream_t)stream);
     if (grad_geo)
         k_field_backward<true><<<fq_grid(k_field_backward<true>, B), FQ_THREADS, 0, (cudaStream_t)stream>>>(
             x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, relu_mask, grad_sigma,

@@ -303,6 +303,14 @@ k_field_value_grad(const float *__restrict__ x, float bound, const float *__rest
     else vg_tiles<false>(s, x, bound, table, align_corners, coef_a, coef_b, a0, b0, sigma, geo, grad_x, B);
 }
 
+// default implementation: the single-table-pass tcgen05 kernel of dfield5.cu; ngp_set_field_impl(0) / NGP_B200_FIELD_IMPL=mma
+// selects the mma.sync kernel above
+int ngp_field_impl_tc5();
+int d5_field_query_value_grad(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                              uint32_t gridtype, int align_corners, const float *W0, const float *W1, const float *coef_a,
+                              const float *coef_b, float a0, float b0, float *sigma, float *geo, float *grad_x,
+                              uint64_t *relu_mask, int64_t B, cudaStream_t stream);
+
 extern "C" int ngp_field_query_value_grad(const float *x, float bound, const float *embeddings, const int32_t *offsets,
                                           float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
                                           const float *W1, const float *coef_a, const float *coef_b, float a0, float b0,
@@ -313,6 +321,9 @@ extern "C" int ngp_field_query_value_grad(const float *x, float bound, const flo
                 "ngp_field_query_value_grad: null pointer");
     NGP_REQUIRE(bound > 0.0f && B >= 0, NGP_ERR_ARG, "ngp_field_query_value_grad: bad bound / B");
     NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_query_value_grad: embeddings must be 16-byte aligned");
+    if (ngp_field_impl_tc5())
+        return d5_field_query_value_grad(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, coef_a, coef_b, a0,
+                                         b0, sigma, geo, grad_x, nullptr, B, (cudaStream_t)stream);
     const int smem = (int)sizeof(FieldVGSmem);
     if (cudaFuncSetAttribute(k_field_value_grad, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         ngp_set_error("ngp_field_query_value_grad: cannot reserve %d B of shared memory", smem);
@@ -327,5 +338,48 @@ extern "C" int ngp_field_query_value_grad(const float *x, float bound, const flo
                                                                          align_corners, W0, W1, coef_a, coef_b, a0, b0, sigma,
                                                                          geo, grad_x, B);
     NGP_CHECK_LAUNCH("ngp_field_query_value_grad");
+    return NGP_OK;
+}
+
+extern "C" int ngp_field_query_forward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                                       uint32_t H, uint32_t gridtype, int align_corners, const float *W0, const float *W1,
+                                       float *sigma, float *geo, uint64_t *relu_mask, int64_t B, ngp_stream_t stream);
+
+// ---- density forward that also returns the Jacobian rows: what autograd's density(x) runs when x requires a gradient.
+// The backward of sigma = f(x_i) is then grad_sigma_i * jac_i: one streaming kernel instead of a second table pass.
+__global__ void k_scale_rows3(const float *__restrict__ jac, const float *__restrict__ gs, float *__restrict__ out, int64_t n3) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n3; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = __ldg(gs + i / 3) * __ldg(jac + i);
+}
+
+extern "C" int ngp_field_query_forward_jacobian(const float *x, float bound, const float *embeddings, const int32_t *offsets,
+                                                float S, uint32_t H, uint32_t gridtype, int align_corners, const float *W0,
+                                                const float *W1, float *sigma, float *geo, uint64_t *relu_mask, float *jac,
+                                                int64_t B, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(x, "ngp_field_query_forward_jacobian");
+    if (B == 0) return NGP_OK;
+    NGP_REQUIRE(x && embeddings && offsets && W0 && W1 && sigma && jac, NGP_ERR_ARG, "ngp_field_query_forward_jacobian: null pointer");
+    NGP_REQUIRE(bound > 0.0f && B >= 0, NGP_ERR_ARG, "ngp_field_query_forward_jacobian: bad bound / B");
+    NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0, NGP_ERR_ARG, "ngp_field_query_forward_jacobian: embeddings must be 16-byte aligned");
+    if (ngp_field_impl_tc5())
+        return d5_field_query_value_grad(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, nullptr, nullptr, 1.0f,
+                                         0.0f, sigma, geo, jac, relu_mask, B, (cudaStream_t)stream);
+    // mma.sync cross-check path: the forward kernel (sigma, geo, mask) and the single-pass kernel for the Jacobian rows
+    int rc = ngp_field_query_forward(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, sigma, geo, relu_mask, B,
+                                     stream);
+    if (rc != NGP_OK) return rc;
+    return ngp_field_query_value_grad(x, bound, embeddings, offsets, S, H, gridtype, align_corners, W0, W1, nullptr, nullptr, 1.0f,
+                                      0.0f, sigma, nullptr, jac, B, stream);
+}
+
+extern "C" int ngp_field_query_backward_jacobian(const float *jac, const float *grad_sigma, float *grad_x, int64_t B,
+                                                 ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(jac, "ngp_field_query_backward_jacobian");
+    if (B == 0) return NGP_OK;
+    NGP_REQUIRE(jac && grad_sigma && grad_x && B >= 0, NGP_ERR_ARG, "ngp_field_query_backward_jacobian: null pointer / bad B");
+    const int64_t n3 = 3 * B;
+    const int64_t blocks = ngp_div_up(n3, 256);
+    k_scale_rows3<<<(int)(blocks < 148 * 16 ? blocks : 148 * 16), 256, 0, (cudaStream_t)stream>>>(jac, grad_sigma, grad_x, n3);
+    NGP_CHECK_LAUNCH("ngp_field_query_backward_jacobian");
     return NGP_OK;
 }

@@ -4,21 +4,26 @@
 // warp-specialised kernel.  Same tcgen05 field core as cfield5.cu (128-sample tiles, A operands and accumulators in TMEM,
 // 3xTF32), fed by marcher warps instead of a sample array:
 //
-//   marcher warps (4)  own R5_NR ray slots in shared memory (6 per lane): they fetch rays (one warp-aggregated atomic per
-//                      refill), compute near/far, march each ray into a small per-slot FIFO of (t, dt) samples (one
-//                      voxel step per slot per pass, three slots' occupancy loads in flight per lane), build the row list
-//                      of the next tile from the FIFO heads of rays that have no sample in flight (ballot compaction, 32
-//                      rows per warp), and write finished pixels;
+//   marcher warps (8)  own R5_NR = 768 ray slots in shared memory (3 per lane): they fetch rays (one warp-aggregated atomic
+//                      per refill), compute near/far, march each ray into a small per-slot FIFO of (t, dt) samples (up to
+//                      R5_BUDGET voxel steps per slot per pass, the slots' occupancy loads in flight together), build
+//                      their 16 rows of the next tile from the FIFO heads of rays that have fewer than R5_INFLIGHT
+//                      samples in flight (ballot compaction), and write finished pixels;
 //   gather warps (8)   thread = tile row: hash-grid encode of the row's sample -> features straight into TMEM;
 //   MMA threads (2)    the five layers of a tile as tcgen05.mma kind::tf32 (one thread per TMEM slot);
 //   chain warps (4)    the epilogues (ReLU / SH / split to hi, lo) and, after the last layer, the compositing step of the
 //                      row's ray (raymarching.cu:860-893) on the ray's accumulators in shared memory.
 //
-// A ray has at most ONE sample in flight, so compositing is in ray order with exact early termination (no speculative
-// samples); tiles stay full because there are more ray slots (768) than rows in flight (4 tile buffers x 128).  Roles hand
-// tiles over through mbarriers; the end of the work is a pair of zero-row tiles.  Per-sample positions, sigma and rgb
-// never reach HBM: 24 B in and 20 B (+4 B count) out per RAY.  Differences from the reference loop are those of render.cu
-// (documented there): t is the marcher's own abscissa, at most max_steps samples per ray, no perturb.
+// A ray has at most R5_INFLIGHT = 2 samples in flight, always in consecutive tiles, and the chain threads composite tile
+// after tile: compositing is in ray order, and a sample that arrives after its ray fell under T < 1e-4 (status bit R5_DEAD)
+// is dropped uncounted, so early termination is exact (at most one speculative sample per ray is evaluated and thrown
+// away).  Tiles stay full because there are more ray slots (768) than rows in flight (R5_TBUF = 8 row buffers x 128).
+// Roles hand tiles over through mbarriers; the end of the work is a pair of zero-row tiles.  Per-sample positions, sigma
+// and rgb never reach HBM: 24 B in and 20 B (+4 B count) out per RAY.  Differences from the reference loop are those of
+// render.cu (documented there): t is the marcher's own abscissa, at most max_steps samples per ray, no perturb.
+// Measured decisions (R5_STATS cycle counters, ncu source page): the marcher is instruction-fetch bound, not latency
+// bound — rolled loops, out-of-line cold paths and the bit-exact fast cell/exit arithmetic of march.cuh bought more than
+// larger budgets or deeper FIFOs, which made it slower.
 #include <float.h>
 
 #include "cfield5.cuh"

@@ -20,7 +20,12 @@ def fused_supported(encoder, W0, W1, x):
 
 class _field_query(Function):
     """(x [B,3] world coords, embeddings, W0, W1) -> sigma [B], geo_feat [B,15].  Backward: dL/dx only
-    (parameter gradients go through the unfused path, see NeRFNetwork.density)."""
+    (parameter gradients go through the unfused path, see NeRFNetwork.density).
+
+    When x requires a gradient the forward is the single-table-pass kernel that also returns the Jacobian rows
+    d sigma_i / d x_i (ngp_field_query_forward_jacobian): sigma_i depends on x_i alone, so the backward of sigma is
+    grad_sigma_i * jac_i, a streaming kernel.  Only if a gradient also arrives through geo_feat does the backward run the
+    second table pass (ngp_field_query_backward, from the ReLU bits the forward saved)."""
 
     @staticmethod
     def forward(ctx, x, embeddings, W0, W1, offsets, bound, S, H, gridtype, align_corners):
@@ -31,32 +36,44 @@ class _field_query(Function):
         sigma = torch.empty(B, device=x.device, dtype=torch.float32)
         geo = torch.empty(B, 15, device=x.device, dtype=torch.float32)
         need_bwd = ctx.needs_input_grad[0]
-        mask = torch.empty(B, device=x.device, dtype=torch.int64) if need_bwd else None
+        ctx.set_materialize_grads(False)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.lib().ngp_field_query_forward(
-                _lib.ptr(x), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, int(align_corners),
-                _lib.ptr(W0), _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(geo), _lib.ptr(mask), B, _lib.stream()),
-                "field_query_forward")
-        if need_bwd:
-            ctx.save_for_backward(x, embeddings, W0, W1, offsets, sigma, mask)
+            if need_bwd:
+                mask = torch.empty(B, device=x.device, dtype=torch.int64)
+                jac = torch.empty(B, 3, device=x.device, dtype=torch.float32)
+                _lib.check(_lib.lib().ngp_field_query_forward_jacobian(
+                    _lib.ptr(x), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, int(align_corners),
+                    _lib.ptr(W0), _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(geo), _lib.ptr(mask), _lib.ptr(jac), B, _lib.stream()),
+                    "field_query_forward_jacobian")
+                ctx.save_for_backward(x, embeddings, W0, W1, offsets, sigma, mask, jac)
+            else:
+                _lib.check(_lib.lib().ngp_field_query_forward(
+                    _lib.ptr(x), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, int(align_corners),
+                    _lib.ptr(W0), _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(geo), None, B, _lib.stream()),
+                    "field_query_forward")
         ctx.cfg = (float(bound), S, H, gridtype, int(align_corners))
         return sigma, geo
 
     @staticmethod
     def backward(ctx, grad_sigma, grad_geo):
-        x, embeddings, W0, W1, offsets, sigma, mask = ctx.saved_tensors
+        x, embeddings, W0, W1, offsets, sigma, mask, jac = ctx.saved_tensors
         bound, S, H, gridtype, align = ctx.cfg
         B = x.shape[0]
-        grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
-        gg = None
-        if grad_geo is not None and ctx.needs_input_grad[0]:
-            gg = grad_geo.contiguous().float()
         grad_x = torch.empty(B, 3, device=x.device, dtype=torch.float32)
+        if grad_sigma is None and grad_geo is None:
+            return (grad_x.zero_(),) + (None,) * 9
         with torch.cuda.device(x.device):
-            _lib.check(_lib.lib().ngp_field_query_backward(
-                _lib.ptr(x), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align, _lib.ptr(W0),
-                _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(mask), _lib.ptr(grad_sigma), _lib.ptr(gg), _lib.ptr(grad_x), B,
-                _lib.stream()), "field_query_backward")
+            if grad_geo is None:
+                _lib.check(_lib.lib().ngp_field_query_backward_jacobian(
+                    _lib.ptr(jac), _lib.ptr(grad_sigma.contiguous().float()), _lib.ptr(grad_x), B, _lib.stream()),
+                    "field_query_backward_jacobian")
+            else:
+                grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
+                gg = grad_geo.contiguous().float()
+                _lib.check(_lib.lib().ngp_field_query_backward(
+                    _lib.ptr(x), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align, _lib.ptr(W0),
+                    _lib.ptr(W1), _lib.ptr(sigma), _lib.ptr(mask), _lib.ptr(grad_sigma), _lib.ptr(gg), _lib.ptr(grad_x), B,
+                    _lib.stream()), "field_query_backward")
         return grad_x, None, None, None, None, None, None, None, None, None
 
 
@@ -84,9 +101,10 @@ def _streams_for(dev):
 class _field_query_host(Function):
     """density() for points that live in PINNED HOST memory (the planner keeps its states on the host until the query,
     nav/quad_plot.py:224-250): (x_host [B,3]) -> sigma [B], geo_feat [B,15] on the device; backward: dL/dx back in pinned
-    host memory.  Forward: the upload of chunk k+1 overlaps the forward kernel of chunk k; backward: the download of chunk
-    k overlaps the backward kernel of chunk k+1 (PCIe is full duplex, copies on their own streams), so the drop-in call
-    `model.density(x_pinned)` costs about max(copies, kernels) instead of their sum."""
+    host memory.  Forward: the upload of chunk k+1 overlaps the kernel of chunk k (the Jacobian-returning forward of
+    _field_query when x requires a gradient); backward: the download of chunk k overlaps the kernel of chunk k+1 (PCIe is
+    full duplex, copies on their own streams), so the drop-in call `model.density(x_pinned)` costs about
+    max(copies, kernels) instead of their sum."""
 
     @staticmethod
     def forward(ctx, x, embeddings, W0, W1, offsets, bound, S, H, gridtype, align_corners):
@@ -95,10 +113,12 @@ class _field_query_host(Function):
         embeddings = embeddings.contiguous(); W0 = W0.contiguous(); W1 = W1.contiguous()
         B = x.shape[0]
         need_bwd = ctx.needs_input_grad[0]
+        ctx.set_materialize_grads(False)
         xd = torch.empty(B, 3, device=dev)
         sigma = torch.empty(B, device=dev)
         geo = torch.empty(B, 15, device=dev)
         mask = torch.empty(B, device=dev, dtype=torch.int64) if need_bwd else None
+        jac = torch.empty(B, 3, device=dev) if need_bwd else None
         s_in, _ = _streams_for(dev)
         L = _lib.lib()
         with torch.cuda.device(dev):
@@ -111,38 +131,51 @@ class _field_query_host(Function):
                     ev = torch.cuda.Event()
                     ev.record(s_in)
                 cur.wait_event(ev)
-                _lib.check(L.ngp_field_query_forward(
-                    xd[a:a + n].data_ptr(), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype,
-                    int(align_corners), _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), geo[a:a + n].data_ptr(),
-                    mask[a:a + n].data_ptr() if need_bwd else None, n, _lib.stream()), "field_query_forward")
+                if need_bwd:
+                    _lib.check(L.ngp_field_query_forward_jacobian(
+                        xd[a:a + n].data_ptr(), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype,
+                        int(align_corners), _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), geo[a:a + n].data_ptr(),
+                        mask[a:a + n].data_ptr(), jac[a:a + n].data_ptr(), n, _lib.stream()), "field_query_forward_jacobian")
+                else:
+                    _lib.check(L.ngp_field_query_forward(
+                        xd[a:a + n].data_ptr(), float(bound), _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype,
+                        int(align_corners), _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), geo[a:a + n].data_ptr(),
+                        None, n, _lib.stream()), "field_query_forward")
                 a += n
             xd.record_stream(s_in)
         if need_bwd:
-            ctx.save_for_backward(xd, embeddings, W0, W1, offsets, sigma, mask)
+            ctx.save_for_backward(xd, embeddings, W0, W1, offsets, sigma, mask, jac)
         ctx.cfg = (float(bound), S, H, gridtype, int(align_corners))
         return sigma, geo
 
     @staticmethod
     def backward(ctx, grad_sigma, grad_geo):
-        xd, embeddings, W0, W1, offsets, sigma, mask = ctx.saved_tensors
+        xd, embeddings, W0, W1, offsets, sigma, mask, jac = ctx.saved_tensors
         bound, S, H, gridtype, align = ctx.cfg
         dev = xd.device
         B = xd.shape[0]
+        gxh = torch.empty(B, 3, pin_memory=True)
+        if grad_sigma is None and grad_geo is None:
+            return (gxh.zero_(),) + (None,) * 9
         grad_sigma = torch.zeros_like(sigma) if grad_sigma is None else grad_sigma.contiguous().float()
         gg = None if grad_geo is None else grad_geo.contiguous().float()
         gxd = torch.empty(B, 3, device=dev)
-        gxh = torch.empty(B, 3, pin_memory=True)
         _, s_out = _streams_for(dev)
         L = _lib.lib()
         with torch.cuda.device(dev):
             cur = torch.cuda.current_stream()
             a = 0
             for n in _host_chunks(B):
-                _lib.check(L.ngp_field_query_backward(
-                    xd[a:a + n].data_ptr(), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align,
-                    _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), mask[a:a + n].data_ptr(),
-                    grad_sigma[a:a + n].data_ptr(), gg[a:a + n].data_ptr() if gg is not None else None,
-                    gxd[a:a + n].data_ptr(), n, _lib.stream()), "field_query_backward")
+                if gg is None:
+                    _lib.check(L.ngp_field_query_backward_jacobian(
+                        jac[a:a + n].data_ptr(), grad_sigma[a:a + n].data_ptr(), gxd[a:a + n].data_ptr(), n, _lib.stream()),
+                        "field_query_backward_jacobian")
+                else:
+                    _lib.check(L.ngp_field_query_backward(
+                        xd[a:a + n].data_ptr(), bound, _lib.ptr(embeddings), _lib.ptr(offsets), S, H, gridtype, align,
+                        _lib.ptr(W0), _lib.ptr(W1), sigma[a:a + n].data_ptr(), mask[a:a + n].data_ptr(),
+                        grad_sigma[a:a + n].data_ptr(), gg[a:a + n].data_ptr(), gxd[a:a + n].data_ptr(), n, _lib.stream()),
+                        "field_query_backward")
                 ev = torch.cuda.Event()
                 ev.record(cur)
                 with torch.cuda.stream(s_out):

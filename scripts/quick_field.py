@@ -34,5 +34,7 @@ def timeit(f, n=10):
     for _ in range(n): f()
     b.record(); torch.cuda.synchronize()
     return a.elapsed_time(b) / n
-tf, tb, te = timeit(fwd), timeit(bwd), timeit(enc())
-print(f"B={B} fwd {tf:.3f} ms  bwd {tb:.3f} ms  enc-only {te:.3f} ms  -> {B/(tf+tb)/1e3:.1f} Msamples/s fwd+bwd; gather GB/s fwd {B*1024/tf/1e6:.0f} bwd {B*1024/tb/1e6:.0f}")
+for impl in ((0, 1) if len(sys.argv) < 3 else (int(sys.argv[2]),)):
+  L.ngp_set_field_impl(impl)
+  tf, tb, te = timeit(fwd), timeit(bwd), timeit(enc())
+  print(f"impl={'tc5' if impl else 'mma'} B={B} fwd {tf:.3f} ms  bwd {tb:.3f} ms  enc-only {te:.3f} ms  -> {B/(tf+tb)/1e3:.1f} Msamples/s fwd+bwd; gather GB/s fwd {B*1024/tf/1e6:.0f} bwd {B*1024/tb/1e6:.0f}")

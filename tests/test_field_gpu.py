@@ -70,7 +70,8 @@ def test_host_field_query_pipeline_matches_device_path():
     xd = xh.cuda().requires_grad_(True)
     s = m.density(xd)["sigma"]
     (s ** 2).mean().backward()
-    assert torch.equal(sh, s.detach().cpu())
+    # the host query runs the single-pass value+grad kernel (mma.sync), density() the tcgen05 kernels: two 3xTF32 orders
+    assert rel_err(sh.numpy(), s.detach().cpu().numpy()) < 1e-6
     assert rel_err(gh.numpy(), xd.grad.cpu().numpy()) < 1e-6
     # ramped chunk schedule (shorter first / last chunks) covers the batch exactly, in order
     for ramp in (False, True, 3):
@@ -83,9 +84,9 @@ def test_host_field_query_pipeline_matches_device_path():
     sh2 = torch.empty(B).pin_memory(); gh2 = torch.empty(B, 3).pin_memory()
     acc = torch.zeros((), device="cuda", dtype=torch.float64)
     qr(xh, (0.0, 2.0 / B), sh2, gh2, sigma_hook=lambda sig: acc.add_((sig.double() ** 2).sum()))
-    assert torch.equal(sh2, sh)
+    assert rel_err(sh2.numpy(), sh.numpy()) < 1e-6     # single-pass kernel vs forward kernel (see above)
     assert rel_err(gh2.numpy(), gh.numpy()) < 1e-5
-    assert abs(float(acc) / B - float((s.detach().double() ** 2).mean())) < 1e-9 * max(1.0, float(acc) / B)
+    assert abs(float(acc) / B - float((s.detach().double() ** 2).mean())) < 1e-7 * max(1.0, float(acc) / B)
 
 
 @pytest.mark.parametrize("B,mode", [(1, "jac"), (191, "quad"), (4097, "coef"), (30000, "quad")])
@@ -148,3 +149,84 @@ def test_density_on_pinned_host_points_matches_device_path():
         assert torch.equal(xh.grad, xd.grad.cpu())
     with pytest.raises(RuntimeError):
         m.density(torch.rand(8, 3))
+
+
+@pytest.mark.parametrize("impl", ["tc5", "mma"])
+@pytest.mark.parametrize("B", [1, 4097, 30001])
+def test_forward_jacobian_vs_oracle_and_two_kernels(ngp, oracle, B, impl):
+    """ngp_field_query_forward_jacobian (what density(x) runs when x requires a gradient): sigma / geo_feat / the saved ReLU
+    bits equal the plain forward's, jac_i * grad_sigma_i (ngp_field_query_backward_jacobian) equals the second-table-pass
+    backward and the CPU oracle, and the saved bits drive ngp_field_query_backward when a gradient arrives through geo_feat."""
+    L = ngp.lib()
+    prev = L.ngp_set_field_impl(1 if impl == "tc5" else 0)
+    try:
+        cfg = hashgrid_config(bound=2.0, table_std=0.5)
+        W0, W1 = sigma_net_weights()
+        rng = np.random.default_rng(B)
+        x = rng.uniform(-1, 1, (B, 3)).astype(np.float32)
+        if B > 10:
+            x[1] = [2.0, -2.0, 0.0]
+            x[2] = [2.5, 0.0, 0.0]
+        gs = rng.standard_normal(B).astype(np.float32)
+        gg = rng.standard_normal((B, 15)).astype(np.float32)
+        dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        xt, tt, ot, w0, w1, gst, ggt = dev(x), dev(cfg["table"]), dev(cfg["offsets"]), dev(W0), dev(W1), dev(gs), dev(gg)
+        sigma = torch.empty(B, device="cuda"); geo = torch.empty(B, 15, device="cuda"); jac = torch.empty(B, 3, device="cuda")
+        mask = torch.empty(B, device="cuda", dtype=torch.int64); gx = torch.empty(B, 3, device="cuda")
+        ngp.check(L.ngp_field_query_forward_jacobian(xt.data_ptr(), cfg["bound"], tt.data_ptr(), ot.data_ptr(), cfg["S"], cfg["H"],
+                                                     0, 0, w0.data_ptr(), w1.data_ptr(), sigma.data_ptr(), geo.data_ptr(),
+                                                     mask.data_ptr(), jac.data_ptr(), B, ngp.stream()), "fwd_jac")
+        ngp.check(L.ngp_field_query_backward_jacobian(jac.data_ptr(), gst.data_ptr(), gx.data_ptr(), B, ngp.stream()), "bwd_jac")
+        s2, g2, gx2 = _run(ngp, cfg, W0, W1, x, gs)
+        assert np.array_equal(sigma.cpu().numpy(), s2) and np.array_equal(geo.cpu().numpy(), g2)      # same forward arithmetic
+        assert rel_err(gx.cpu().numpy(), gx2) < 1e-6
+        s16 = torch.empty(16, device="cuda")
+        ngp.check(L.ngp_grid_level_scales(s16.data_ptr(), 16, cfg["S"], cfg["H"], ngp.stream()))
+        scales = s16.cpu().numpy()
+        rs, rg, rgx = oracle.field_query(x, cfg["bound"], cfg["table"], cfg["offsets"], scales, W0, W1, gs)
+        assert rel_err(sigma.cpu().numpy(), rs) < 1e-5 and rel_err(geo.cpu().numpy(), rg) < 1e-5
+        assert rel_err(gx.cpu().numpy(), rgx) < 1e-5
+        if B > 10:
+            assert rel_err_cols(gx.cpu().numpy(), rgx) < 1e-5
+            assert sigma[2] == 1.0 and (jac[2] == 0).all()
+        # gradient through geo_feat as well: the second table pass from the bits the Jacobian forward saved
+        gx3 = torch.empty(B, 3, device="cuda")
+        ngp.check(L.ngp_field_query_backward(xt.data_ptr(), cfg["bound"], tt.data_ptr(), ot.data_ptr(), cfg["S"], cfg["H"], 0, 0,
+                                             w0.data_ptr(), w1.data_ptr(), sigma.data_ptr(), mask.data_ptr(), gst.data_ptr(),
+                                             ggt.data_ptr(), gx3.data_ptr(), B, ngp.stream()), "bwd")
+        _, _, rgx3 = oracle.field_query(x, cfg["bound"], cfg["table"], cfg["offsets"], scales, W0, W1, gs, gg)
+        assert rel_err(gx3.cpu().numpy(), rgx3) < 1e-5
+    finally:
+        L.ngp_set_field_impl(prev)
+
+
+def test_density_autograd_takes_the_jacobian_forward_and_handles_geo_gradients():
+    """model.density(x) with x.requires_grad: a loss on sigma alone (Jacobian rows, no second table pass) and a loss that also
+    uses geo_feat (second pass from the saved bits) both match the unfused GridEncoder -> Linear -> trunc_exp autograd path;
+    an unused output gives a zero gradient."""
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    torch.manual_seed(1)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    for p in m.parameters():
+        p.requires_grad_(False)
+    x = torch.rand(20011, 3, device="cuda") * 2 - 1
+    w = torch.randn(15, device="cuda")
+    for use_geo in (False, True):
+        grads = []
+        for fused in (True, False):
+            m.fused_eval = fused
+            xi = x.clone().requires_grad_(True)
+            out = m.density(xi)
+            loss = (out["sigma"] ** 2).sum() + ((out["geo_feat"] * w).sum() if use_geo else 0.0)
+            loss.backward()
+            grads.append(xi.grad.clone())
+        assert rel_err(grads[0].cpu().numpy(), grads[1].cpu().numpy()) < 1e-5, use_geo
+    m.fused_eval = True
+    xi = x.clone().requires_grad_(True)
+    out = m.density(xi)
+    (out["geo_feat"] * w).sum().backward()        # sigma unused: grad_sigma arrives as None
+    xj = x.clone().requires_grad_(True)
+    m.fused_eval = False
+    (m.density(xj)["geo_feat"] * w).sum().backward()
+    assert rel_err(xi.grad.cpu().numpy(), xj.grad.cpu().numpy()) < 1e-5
