@@ -10,13 +10,18 @@ KEYS = ['gpu__time_duration.sum', 'l1tex__data_pipe_lsu_wavefronts.avg.pct_of_pe
         'sm__warps_active.avg.pct_of_peak_sustained_active', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
         'launch__registers_per_thread', 'launch__grid_size', 'sm__inst_executed.sum',
         'l1tex__m_xbar2l1tex_read_sectors.sum', 'l1tex__m_l1tex2xbar_req_cycles_active.avg.pct_of_peak_sustained_elapsed',
-        'smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct', 'smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio']
+        'smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct', 'smsp__warp_issue_stalled_no_instruction_per_warp_active.pct',
+        'sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed', 'sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active',
+        'sm__ops_path_tensor_op_hmma_src_tf32_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed', 'sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed', 'launch__shared_mem_per_block_dynamic', 'smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio']
 out = subprocess.run(['ncu', '-i', sys.argv[1], '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr, units = rows[0], rows[1]
 for r in rows[2:]:
     print('----', r[hdr.index('Kernel Name')][:60])
     for k in KEYS:
+        cand = [h for h in hdr if h == k] or [h for h in hdr if h.endswith('.' + k)]
+        if cand:
+            k = cand[0]
         if k in hdr:
             i = hdr.index(k)
             print(f'  {k} [{units[i]}] = {r[i]}')
