@@ -186,6 +186,19 @@ static int ff_sm_count() {
     return sms;
 }
 
+// default forward: the warp-specialised multi-tile kernel of ffmlp5.cu (returns -1 if one slot does not fit in shared
+// memory); NGP_B200_FFMLP_IMPL=v1 selects the one-tile-per-CTA kernel above (the cross-check)
+int f5_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int input_dim, int num_layers, int activation,
+                     void *forward_buffer, void *outputs, cudaStream_t stream);
+static int ff_impl_v1() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("NGP_B200_FFMLP_IMPL");
+        v = (e && strcmp(e, "v1") == 0) ? 1 : 0;
+    }
+    return v;
+}
+
 extern "C" int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_t B, int input_dim, int output_dim,
                                  int hidden_dim, int num_layers, int activation, int output_activation,
                                  void *forward_buffer, void *outputs, ngp_stream_t stream) {
@@ -194,6 +207,10 @@ extern "C" int ngp_ffmlp_forward(const void *inputs, const void *weights, int64_
     NGP_REQUIRE(inputs && weights && outputs, NGP_ERR_ARG, "ngp_ffmlp_forward: null pointer");
     int rc = ff_check(B, input_dim, output_dim, hidden_dim, num_layers, activation, output_activation, "ngp_ffmlp_forward");
     if (rc) return rc;
+    if (!ff_impl_v1()) {
+        rc = f5_ffmlp_forward(inputs, weights, B, input_dim, num_layers, activation, forward_buffer, outputs, (cudaStream_t)stream);
+        if (rc != -1) return rc;
+    }
     const size_t smem = ff_forward_smem(input_dim, num_layers);
     NGP_REQUIRE(smem <= 227 * 1024, NGP_ERR_UNSUPPORTED, "ngp_ffmlp_forward: configuration needs %zu B of shared memory", smem);
     if (cudaFuncSetAttribute(k_ffmlp_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
