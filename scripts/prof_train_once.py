@@ -9,7 +9,7 @@ from nerf_navigation_b200.gridencoder import table_grad
 
 dev = torch.device("cuda", 0)
 tm, opt, ro, rd, tgt = BT.setup(dev, 4096)
-table_grad.DETERMINISTIC = False
+table_grad.DETERMINISTIC = os.environ.get("DET", "0") == "1"
 for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 2):
     BT.step(tm, opt, ro, rd, tgt, 1)
 torch.cuda.synchronize()
