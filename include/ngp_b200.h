@@ -82,6 +82,17 @@ int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int
                                           int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
                                           int align_corners, ngp_stream_t stream);
 
+/* The same gradient (gridencoder.cu:227-314), bit-reproducible WITHOUT a sort: contributions are scaled by one power of two
+ * (from max |grad| and the bound 2^D B on contributions per row, so no sum overflows), rounded to int64 and added with
+ * 64-bit integer atomics — integer addition is associative, any arrival order gives the same bits — then converted back.
+ * Resolution 2^-(61 - ceil(log2(2^D B))) of max |grad| per contribution.  workspace: 16-byte aligned,
+ * ngp_grid_backward_table_fixed_workspace_bytes(total_rows, C) = 256 + 8 total_rows C bytes; grad_embeddings is overwritten. */
+int64_t ngp_grid_backward_table_fixed_workspace_bytes(int64_t total_rows, int C);
+int ngp_grid_encode_backward_table_fixed(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
+                                         const int32_t *offsets, int64_t total_rows, float *grad_embeddings,
+                                         int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
+                                         int align_corners, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+
 /* ---- fused field query: NeRFNetwork.density(), nerf/network.py:126-143 (+ grid.py:140-156, activation.py) --- */
 
 /* sigma = exp(o[0]), geo = o[1:n_out], o = W1 relu(W0 enc((x+bound)/(2 bound))).  fp32 table + fp32 MLP,

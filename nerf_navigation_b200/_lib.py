@@ -27,6 +27,8 @@ _SIGNATURES = {
     "ngp_grid_backward_table_workspace_bytes": ([I64, I, I], I64),
     "ngp_grid_encode_backward_table": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P, I64, P], I),
     "ngp_linear_small": ([P, P, P, I64, I, I, I, P], I),
+    "ngp_grid_backward_table_fixed_workspace_bytes": ([I64, I], I64),
+    "ngp_grid_encode_backward_table_fixed": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P, I64, P], I),
     "ngp_grid_encode_backward_table_atomic": ([P, I, I, P, P, I64, P, I64, I, I, I, F, U32, U32, I, P], I),
     "ngp_field_query_forward": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, I64, P], I),
     "ngp_field_query_value_grad": ([P, F, P, P, F, U32, U32, I, P, P, P, P, F, F, P, P, P, I64, P], I),

@@ -344,6 +344,198 @@ extern "C" int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_
     return NGP_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ fixed-point atomics
+// Bit-reproducible WITHOUT a sort: float atomics depend on arrival order because float addition is not associative; integer
+// addition is.  Every contribution is scaled by one power of two (chosen from max|grad| and the row-count bound so that no
+// sum can overflow), rounded to int64 and added with 64-bit integer atomics; any arrival order gives the same 64-bit sums.
+// A last pass converts back.  Resolution: 2^-(61 - ceil(log2(2^D B))) of max|grad| per contribution (2^-40 for 3x10^5
+// samples), far below fp32's own rounding of the sum.  Same thread mapping and run pre-summing as k_tg_atomic.
+struct TgFixedHdr {
+    unsigned int max_bits;   // float bits of max |grad| (atomicMax on the bit pattern of non-negative floats)
+    int shift;               // contributions are scaled by 2^shift
+    unsigned int pad[2];
+};
+
+template <typename G>
+__global__ void __launch_bounds__(TG_THREADS) k_tg_absmax(const G *__restrict__ grad, int64_t n, TgFixedHdr *hdr) {
+    float m = 0.0f;
+    for (int64_t i = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * TG_THREADS) {
+        const float v = fabsf((float)grad[i]);
+        m = v > m ? v : m;   // NaN never wins: a NaN gradient stays NaN in the sums below anyway
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(&hdr->max_bits, __float_as_uint(m));
+}
+
+__global__ void k_tg_fixed_shift(TgFixedHdr *hdr, int count_bits) {
+    const unsigned int b = hdr->max_bits;
+    const int e = (int)((b >> 23) & 0xff) - 127;          // max < 2^(e+1)   (denormal max: e = -127, still a bound)
+    int sh = 61 - (e + 1) - count_bits;
+    hdr->shift = sh > 120 ? 120 : (sh < -120 ? -120 : sh);
+}
+
+template <typename G, int D, int C>
+__global__ void __launch_bounds__(TG_THREADS)
+k_tg_fixed(const G *__restrict__ grad, int grad_layout, const float *__restrict__ inputs, const int32_t *__restrict__ offsets,
+           int64_t B, int L, float S, uint32_t H, uint32_t gridtype, int align, const TgFixedHdr *__restrict__ hdr,
+           unsigned long long *__restrict__ acc) {
+    __shared__ LevelMeta meta[TG_MAX_L];
+    if (threadIdx.x < L) meta[threadIdx.x] = ngp_level_meta<D>(threadIdx.x, offsets, S, H, gridtype, align);
+    __syncthreads();
+    const float scale = __uint_as_float((uint32_t)(hdr->shift + 127) << 23);   // 2^shift, |shift| <= 120
+    const int64_t t = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const bool in = t < B * L;
+    const int l = in ? (int)(t / B) : 0;
+    const int64_t b = in ? t - (int64_t)l * B : 0;
+    constexpr int NC = 1 << D;
+    float gv[C];
+    bool any = false;
+    if (in) {
+        const G *g = grad_layout == 0 ? grad + ((int64_t)l * B + b) * C : grad + (b * L + l) * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            gv[c] = (float)g[c];
+            any |= gv[c] != 0.0f;
+        }
+    }
+    const LevelMeta m = meta[l];
+    uint32_t cell[D];
+    float frac[D];
+    bool live = in && any;
+    if (live) live = tg_locate<D>(inputs, b, m, align, cell, frac);
+    if (!live) {
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            cell[d] = 0xffffffffu;
+            frac[d] = 0.0f;
+        }
+    }
+    bool same_prev = lane > 0;
+    {
+        const int lp = __shfl_up_sync(0xffffffffu, l, 1);
+        const int vp = __shfl_up_sync(0xffffffffu, (int)live, 1);
+        same_prev = same_prev && lp == l && vp == (int)live;
+#pragma unroll
+        for (int d = 0; d < D; ++d) {
+            const uint32_t cp = __shfl_up_sync(0xffffffffu, cell[d], 1);
+            same_prev = same_prev && cp == cell[d];
+        }
+    }
+    const unsigned heads = __ballot_sync(0xffffffffu, !same_prev);
+    long long val[NC][C];   // the integers are what is summed, in registers too: the result cannot depend on the grouping
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        float w = 1.0f;
+#pragma unroll
+        for (int d = 0; d < D; ++d) w *= (k >> d) & 1 ? frac[d] : 1.0f - frac[d];
+#pragma unroll
+        for (int c = 0; c < C; ++c) val[k][c] = live ? __float2ll_rn(__fmul_rn(__fmul_rn(w, gv[c]), scale)) : 0ll;
+    }
+    if (__popc(heads) <= 24) {
+        const int seg = __popc(heads & (0xffffffffu >> (31 - lane)));
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int oseg = __shfl_down_sync(0xffffffffu, seg, o);
+            const bool take = lane + o < 32 && oseg == seg;
+#pragma unroll
+            for (int k = 0; k < NC; ++k)
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    const long long v = __shfl_down_sync(0xffffffffu, val[k][c], o);
+                    if (take) val[k][c] += v;
+                }
+        }
+        if (same_prev) live = false;
+    }
+    if (!live) return;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        unsigned long long *dst = acc + ((int64_t)m.row_offset + tg_row<D>(cell, k, m)) * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c)
+            if (val[k][c] != 0) atomicAdd(dst + c, (unsigned long long)val[k][c]);
+    }
+}
+
+__global__ void __launch_bounds__(TG_THREADS)
+k_tg_fixed_finish(const long long *__restrict__ acc, const TgFixedHdr *__restrict__ hdr, float *__restrict__ out, int64_t n) {
+    const double inv = __longlong_as_double((long long)(1023 - hdr->shift) << 52);   // 2^-shift
+    for (int64_t i = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * TG_THREADS)
+        out[i] = (float)((double)acc[i] * inv);
+}
+
+extern "C" int64_t ngp_grid_backward_table_fixed_workspace_bytes(int64_t total_rows, int C) {
+    return 256 + total_rows * C * 8;
+}
+
+template <typename G, int D>
+static int tg_launch_fixed(int C, const void *grad, int grad_layout, const float *inputs, const int32_t *offsets, int64_t B,
+                           int L, float S, uint32_t H, uint32_t gridtype, int align, const TgFixedHdr *hdr,
+                           unsigned long long *acc, cudaStream_t st) {
+    const unsigned grid = (unsigned)ngp_div_up(B * L, TG_THREADS);
+#define TG_FIX(CC)                                                                                                        \
+    k_tg_fixed<G, D, CC><<<grid, TG_THREADS, 0, st>>>((const G *)grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, \
+                                                      align, hdr, acc)
+    switch (C) {
+        case 1: TG_FIX(1); break;
+        case 2: TG_FIX(2); break;
+        case 4: TG_FIX(4); break;
+        case 8: TG_FIX(8); break;
+        default: ngp_set_error("GridEncoder: C must be 1, 2, 4 or 8 (got %d)", C); return NGP_ERR_UNSUPPORTED;
+    }
+#undef TG_FIX
+    return NGP_OK;
+}
+
+extern "C" int ngp_grid_encode_backward_table_fixed(const void *grad, int grad_layout, int grad_dtype, const float *inputs,
+                                                    const int32_t *offsets, int64_t total_rows_, float *grad_embeddings,
+                                                    int64_t B, int D, int C, int L, float S, uint32_t H, uint32_t gridtype,
+                                                    int align_corners, void *workspace, int64_t workspace_bytes,
+                                                    ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(grad, "ngp_grid_encode_backward_table_fixed");
+    NGP_REQUIRE(grad && inputs && offsets && total_rows_ > 0 && total_rows_ < (1ll << 32) && grad_embeddings, NGP_ERR_ARG,
+                "ngp_grid_encode_backward_table_fixed: null pointer");
+    NGP_REQUIRE(L > 0 && L <= TG_MAX_L, NGP_ERR_ARG, "ngp_grid_encode_backward_table_fixed: L out of range");
+    NGP_REQUIRE(D == 2 || D == 3, NGP_ERR_UNSUPPORTED, "GridEncoder: D must be 2 or 3 (got %d)", D);
+    NGP_REQUIRE(grad_dtype == NGP_DTYPE_F32 || grad_dtype == NGP_DTYPE_F16, NGP_ERR_UNSUPPORTED,
+                "ngp_grid_encode_backward_table_fixed: bad grad_dtype");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n_out = total_rows_ * C;
+    if (B == 0) {
+        cudaError_t e0 = cudaMemsetAsync(grad_embeddings, 0, (size_t)n_out * sizeof(float), st);
+        NGP_REQUIRE(e0 == cudaSuccess, NGP_ERR_CUDA, "ngp_grid_encode_backward_table_fixed: memset: %s", cudaGetErrorString(e0));
+        return NGP_OK;
+    }
+    NGP_REQUIRE(workspace && ((uintptr_t)workspace & 15u) == 0 &&
+                    workspace_bytes >= ngp_grid_backward_table_fixed_workspace_bytes(total_rows_, C),
+                NGP_ERR_ARG, "ngp_grid_encode_backward_table_fixed: workspace too small or misaligned");
+    TgFixedHdr *hdr = (TgFixedHdr *)workspace;
+    unsigned long long *acc = (unsigned long long *)((char *)workspace + 256);
+    cudaError_t e = cudaMemsetAsync(workspace, 0, (size_t)(256 + n_out * 8), st);
+    NGP_REQUIRE(e == cudaSuccess, NGP_ERR_CUDA, "ngp_grid_encode_backward_table_fixed: memset: %s", cudaGetErrorString(e));
+    const int64_t n_in = B * L * C;
+    const unsigned rgrid = (unsigned)(ngp_div_up(n_in, TG_THREADS) < 148 * 8 ? ngp_div_up(n_in, TG_THREADS) : 148 * 8);
+    if (grad_dtype == NGP_DTYPE_F32) k_tg_absmax<float><<<rgrid, TG_THREADS, 0, st>>>((const float *)grad, n_in, hdr);
+    else k_tg_absmax<__half><<<rgrid, TG_THREADS, 0, st>>>((const __half *)grad, n_in, hdr);
+    int count_bits = 0;   // a row receives at most 2^D contributions per point
+    while ((1ll << count_bits) < (B << D)) ++count_bits;
+    k_tg_fixed_shift<<<1, 1, 0, st>>>(hdr, count_bits);
+    int rc;
+    if (grad_dtype == NGP_DTYPE_F32)
+        rc = D == 3 ? tg_launch_fixed<float, 3>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, hdr, acc, st)
+                    : tg_launch_fixed<float, 2>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, hdr, acc, st);
+    else
+        rc = D == 3 ? tg_launch_fixed<__half, 3>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, hdr, acc, st)
+                    : tg_launch_fixed<__half, 2>(C, grad, grad_layout, inputs, offsets, B, L, S, H, gridtype, align_corners, hdr, acc, st);
+    if (rc != NGP_OK) return rc;
+    const unsigned fgrid = (unsigned)(ngp_div_up(n_out, TG_THREADS) < 148 * 16 ? ngp_div_up(n_out, TG_THREADS) : 148 * 16);
+    k_tg_fixed_finish<<<fgrid, TG_THREADS, 0, st>>>((const long long *)acc, hdr, grad_embeddings, n_out);
+    NGP_CHECK_LAUNCH("ngp_grid_encode_backward_table_fixed");
+    return NGP_OK;
+}
+
 static int tg_bits(uint32_t v) {
     int b = 0;
     while ((1ull << b) <= v) ++b;

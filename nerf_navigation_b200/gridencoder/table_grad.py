@@ -1,13 +1,16 @@
-"""Table gradient of the hash-grid encoder: deterministic sorted segmented reduction (csrc/tablegrad.cu).
-Replaces the reference's atomicAdd scatter (gridencoder.cu:227-314) behind grid.py:64-87.
+"""Table gradient of the hash-grid encoder (csrc/tablegrad.cu).  Replaces the reference's atomicAdd scatter
+(gridencoder.cu:227-314) behind grid.py:64-87.  Three methods:
 
-DETERMINISTIC = False switches to the reference's own method (float atomics, sums in arrival order: equal to the
-deterministic result up to fp32 summation order, not bit-reproducible) for throughput."""
+  DETERMINISTIC = True, METHOD = "fixed"   (default) fixed-point integer atomics: bit-reproducible, no sort
+  DETERMINISTIC = True, METHOD = "sorted"  stable sort of (row, contribution) + segmented reduction: bit-reproducible
+  DETERMINISTIC = False                    the reference's own method (float atomics, sums in arrival order: equal to the
+                                           others up to fp32 summation order, not bit-reproducible)"""
 import torch
 
 from .. import _lib
 
 DETERMINISTIC = True
+METHOD = "fixed"
 
 # training.GradBucket registers, per embeddings tensor (by data_ptr), the slice of its flat gradient bucket that the kernels
 # should write into, so the table gradient is produced in place where the all-reduce and the optimiser read it
@@ -39,6 +42,15 @@ def grid_backward_table(grad, inputs, embeddings, offsets, dims, align_corners, 
             _lib.ptr(grad), grad_layout, 0 if grad.dtype == torch.float32 else 1, _lib.ptr(inputs), _lib.ptr(offsets),
             int(embeddings.shape[0]), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.stream()),
             "grid_encode_backward(table, atomic)")
+        return out if embeddings.dtype == torch.float32 else out.to(embeddings.dtype)
+    if METHOD == "fixed":
+        ws_bytes = L_.ngp_grid_backward_table_fixed_workspace_bytes(int(embeddings.shape[0]), C)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=inputs.device)
+        out = _out_for(embeddings, inputs.device)
+        _lib.check(L_.ngp_grid_encode_backward_table_fixed(
+            _lib.ptr(grad), grad_layout, 0 if grad.dtype == torch.float32 else 1, _lib.ptr(inputs), _lib.ptr(offsets),
+            int(embeddings.shape[0]), _lib.ptr(out), B, D, C, L, S, H, gridtype, int(align_corners), _lib.ptr(ws), ws_bytes,
+            _lib.stream()), "grid_encode_backward(table, fixed-point)")
         return out if embeddings.dtype == torch.float32 else out.to(embeddings.dtype)
     ws_bytes = L_.ngp_grid_backward_table_workspace_bytes(B, D, L)
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=inputs.device)

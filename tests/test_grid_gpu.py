@@ -127,19 +127,35 @@ def _table_grad(ngp, g, x, cfg, layout=1):
     return grid_backward_table(g, x, tt, ot, (B, 3, 2, 16, cfg["S"], cfg["H"], 0), False, layout)
 
 
-def test_table_gradient_vs_oracle_and_deterministic(ngp, oracle):
+@pytest.mark.parametrize("method", ["fixed", "sorted"])
+def test_table_gradient_vs_oracle_and_deterministic(ngp, oracle, method):
+    from nerf_navigation_b200.gridencoder import table_grad
     cfg = hashgrid_config()
     B = 50000
     rng = np.random.default_rng(11)
     x = rng.uniform(0, 1, (B, 3)).astype(np.float32)
     x[7] = [1.1, 0.5, 0.5]                                  # out of range: contributes nothing
     g = rng.standard_normal((B, 32)).astype(np.float32)
+    g[100:200] *= 1e-3                                      # small contributions next to large ones
     scales = _dev_scales(ngp, cfg)
     ref = oracle.grid_backward_table(np.ascontiguousarray(g.reshape(B, 16, 2).transpose(1, 0, 2)), x, cfg["offsets"], scales, 2)
     xt, gt = torch.from_numpy(x).cuda(), torch.from_numpy(g).cuda()
-    a = _table_grad(ngp, gt, xt, cfg)
-    b = _table_grad(ngp, gt, xt, cfg)
-    assert torch.equal(a, b)                                # bit-identical run to run (no float atomics)
+    prev = table_grad.METHOD
+    try:
+        table_grad.METHOD = method
+        a = _table_grad(ngp, gt, xt, cfg)
+        b = _table_grad(ngp, gt, xt, cfg)
+        assert torch.equal(a, b)                            # bit-identical run to run (no float atomics)
+        if method == "fixed":
+            # integer sums do not depend on the order of the contributions at all: shuffle the batch
+            perm = torch.randperm(B, device="cuda")
+            c = _table_grad(ngp, gt[perm].contiguous(), xt[perm].contiguous(), cfg)
+            assert torch.equal(a, c)
+            # fp16 upstream gradient (autocast training) and the [L, B, C] layout take the same path
+            gl0 = gt.view(B, 16, 2).permute(1, 0, 2).contiguous()
+            assert torch.equal(_table_grad(ngp, gl0, xt, cfg, layout=0), a)
+    finally:
+        table_grad.METHOD = prev
     assert rel_err(a.cpu().numpy(), ref) < 1e-5
     assert level_rel_err(a.cpu().numpy(), ref, cfg["offsets"]) < 1e-5      # every level against its own largest entry
     assert (a.cpu().numpy() != 0).sum() == (ref != 0).sum()
