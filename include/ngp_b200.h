@@ -263,6 +263,18 @@ int64_t ngp_linear_wgrad_workspace_bytes(int64_t M);
 int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, void *workspace,
                      int64_t workspace_bytes, ngp_stream_t stream);
 
+/* Allocation-free variant of ngp_linear_wgrad.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same
+ * inputs, outputs and arithmetic; the per-CTA partials live in a file-scope static __device__ array of the library
+ * (4 MiB, held by every GPU that loads the library until the process exits) instead of a caller workspace.
+ * Limit: M <= 65536 samples (NGP_LINEAR_WGRAD_STATIC_MAX_M); a larger M returns NGP_ERR_UNSUPPORTED with a message.
+ * Calls no cudaMalloc / cudaFree / allocating routine.  All calls on a device share the array (it keeps the last call's
+ * contents; nothing needs clearing, every partial read is written by the same call): calls that OVERLAP on the GPU
+ * (different streams, concurrent graph replays) race — serialise them.  The first call on a device looks the array's
+ * device address up (cudaGetSymbolAddress); make one call before starting a capture. */
+#define NGP_LINEAR_WGRAD_STATIC_MAX_M 65536
+int ngp_linear_wgrad_static(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in, ngp_stream_t stream);
+
 /* Forward / input-gradient product of the same layers (csrc/linear.cu), W = nn.Linear.weight [n_out, n_in] row-major:
  * transpose_w = 0: Y [M, n_out] = X [M, n_in] W^T;  transpose_w = 1: Y [M, n_in] = X [M, n_out] W.  n_out, n_in <= 64,
  * 3xTF32 tensor-core products with fp32 accumulation (relative error ~1e-6 against an fp32 GEMM). */

@@ -58,6 +58,7 @@ _SIGNATURES = {
     "ngp_adam_step": ([P, P, P, P, P, I64, F, F, F, F, I64, F, F, P, P, P], I),
     "ngp_linear_wgrad_workspace_bytes": ([I64], I64),
     "ngp_linear_wgrad": ([P, P, P, I64, I, I, P, I64, P], I),
+    "ngp_linear_wgrad_static": ([P, P, P, I64, I, I, P], I),
     "ngp_occ_grid_positions": ([I, U32, F, F, U32, P, P], I),
     "ngp_occ_grid_update_blocks": ([I64], I64),
     "ngp_occ_grid_update": ([P, P, I64, F, F, P, P], I),

@@ -144,3 +144,64 @@ extern "C" int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int6
     NGP_CHECK_LAUNCH("ngp_linear_wgrad(reduce)");
     return NGP_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+// ngp_linear_wgrad_static: the same two kernels with the per-CTA partials in a file-scope device array instead of a
+// caller-provided workspace, for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.
+//   * limit: M <= NGP_LINEAR_WGRAD_STATIC_MAX_M = 65536 samples (256 CTAs x 64 x 64 floats = 4 MiB, held by every GPU that
+//     loads the library until the process exits); larger M is refused with NGP_ERR_UNSUPPORTED;
+//   * the array is shared by every call on a device and keeps the last call's contents.  Nothing has to start at zero:
+//     every partial the reduction reads (rows < 16 ceil(n_out / 16), all 64 columns, of the call's own CTAs) is written by
+//     the same call's first kernel.  Calls that overlap on the GPU (different streams, or graphs replayed concurrently)
+//     race on it: serialise them;
+//   * in host code `g_wgrad_static_scratch` is only a stand-in for the symbol, not a device address: the address is
+//     looked up once per device with cudaGetSymbolAddress (that device current) and cached.  The first call on a device
+//     does this lookup; make one call before starting a graph capture.
+#define WG_STATIC_MAX_M 65536
+#define WG_STATIC_BLOCKS (WG_STATIC_MAX_M / 256)
+#define WG_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) float g_wgrad_static_scratch[(size_t)WG_STATIC_BLOCKS * WG_MAXN * WG_MAXN];
+
+static float *wg_static_ptr(int dev) {
+    static float *ptrs[WG_STATIC_MAX_DEVICES] = {};
+    if (dev < 0 || dev >= WG_STATIC_MAX_DEVICES) return nullptr;
+    float *p = __atomic_load_n(&ptrs[dev], __ATOMIC_ACQUIRE);
+    if (p) return p;
+    void *sym = nullptr;   // the caller made `dev` current: the lookup returns this device's copy of the array
+    if (cudaGetSymbolAddress(&sym, g_wgrad_static_scratch) != cudaSuccess || !sym) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    __atomic_store_n(&ptrs[dev], (float *)sym, __ATOMIC_RELEASE);   // racing first calls store the same value
+    return (float *)sym;
+}
+
+extern "C" int ngp_linear_wgrad_static(const float *dY, const float *X, float *dW, int64_t M, int n_out, int n_in,
+                                       ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(dY, "ngp_linear_wgrad_static");
+    NGP_REQUIRE(dY && X && dW, NGP_ERR_ARG, "ngp_linear_wgrad_static: null pointer");
+    NGP_REQUIRE(n_out >= 1 && n_out <= WG_MAXN && n_in >= 1 && n_in <= WG_MAXN && M >= 0, NGP_ERR_UNSUPPORTED,
+                "ngp_linear_wgrad_static: needs 1 <= n_out, n_in <= 64 (got %d, %d)", n_out, n_in);
+    NGP_REQUIRE(M <= WG_STATIC_MAX_M, NGP_ERR_UNSUPPORTED,
+                "ngp_linear_wgrad_static: M = %lld exceeds the static scratch limit of %d samples; use ngp_linear_wgrad with a "
+                "caller-provided workspace", (long long)M, WG_STATIC_MAX_M);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M == 0) {
+        cudaMemsetAsync(dW, 0, (size_t)n_out * n_in * sizeof(float), st);
+        return NGP_OK;
+    }
+    int dev = 0;
+    NGP_REQUIRE(cudaGetDevice(&dev) == cudaSuccess, NGP_ERR_CUDA, "ngp_linear_wgrad_static: cudaGetDevice failed");
+    float *scratch = wg_static_ptr(dev);
+    NGP_REQUIRE(scratch != nullptr, NGP_ERR_CUDA, "ngp_linear_wgrad_static: cudaGetSymbolAddress failed on device %d", dev);
+    int blocks = wg_blocks(M);
+    if (blocks > WG_STATIC_BLOCKS) blocks = WG_STATIC_BLOCKS;   // cannot happen for M <= 65536 (>= 256 samples per CTA)
+    int64_t rows = ngp_div_up(M, blocks);
+    rows = ngp_div_up(rows, 8) * 8;
+    k_wgrad_partial<<<blocks, WG_THREADS, 0, st>>>(dY, X, M, n_out, n_in, rows, scratch);
+    NGP_CHECK_LAUNCH("ngp_linear_wgrad_static(partial)");
+    k_wgrad_reduce<<<(n_out * n_in + 255) / 256, 256, 0, st>>>(scratch, blocks, n_out, n_in, dW);
+    NGP_CHECK_LAUNCH("ngp_linear_wgrad_static(reduce)");
+    return NGP_OK;
+}
