@@ -66,7 +66,7 @@ def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed `ncu --set full` capture
     of this same workload at the same 4,194,304 points (profiles/r2_dfield5_4m_ncu_keys.txt for the tcgen05 kernels,
     profiles/r1_field_4m_ncu_keys.txt for the mma.sync ones); None if the capture is not there."""
-    cur, tot = None, {}
+    cur, tot, launches = None, {}, {}
     for name in ("r2_dfield5_4m_ncu_keys.txt", "r1_field_4m_ncu_keys.txt"):
         p = os.path.join(ROOT, "profiles", name)
         if not os.path.exists(p):
@@ -79,9 +79,11 @@ def ncu_traffic(kernel):
                 val = float(line.split("=")[1].strip().replace(",", ""))
                 mul = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(unit, 1)
                 tot[cur] = tot.get(cur, 0.0) + val * mul
+                if "dram__bytes_read" in line:                 # the capture may hold several launches of a kernel
+                    launches[cur] = launches.get(cur, 0) + 1
     for k, v in tot.items():
         if kernel in k:
-            return v
+            return v / launches[k]                             # per launch, like `achieved`
     return None
 
 
