@@ -131,6 +131,15 @@ int ngp_field_query_forward_jacobian(const float *x, float bound, const float *e
 int ngp_field_query_backward_jacobian(const float *jac, const float *grad_sigma, float *grad_x, int64_t B,
                                       ngp_stream_t stream);
 
+/* NeRFNetwork.density of the FFMLP variant, nerf/network_ff.py:76-89: h = sigma_net(encoder(x, bound)) as ONE kernel
+ * (csrc/ffmlp5.cu): the hash-grid features are rounded to fp16 (what ffmlp.py:20-24 does to the encoder output) and handed to
+ * the FFMLP layers in shared memory; the [B, 32] feature tensor never exists.  fp32 table, D=3, C=2, L=16; weights = the
+ * flat fp16 FFMLP vector [64 x 32][64 x 64]*(num_layers-1)[16 x 64]; outputs [B, 16] fp16 (column 0 = log sigma, 1..15 =
+ * geo_feat).  Inference only (no saved activations): training goes through ngp_grid_encode_forward + ngp_ffmlp_forward. */
+int ngp_field_query_ff_forward(const float *x, float bound, const float *embeddings, const int32_t *offsets, float S,
+                               uint32_t H, uint32_t gridtype, int align_corners, const void *weights, int num_layers,
+                               int activation, void *outputs, int64_t B, ngp_stream_t stream);
+
 /* ---- fused per-sample field for the ray paths: NeRFNetwork.forward(x, d), nerf/network.py:95-124 ------------------- */
 
 /* Implementation of the fused colour-field / render kernels: 1 = warp-specialised tcgen05 (TMEM accumulators and A

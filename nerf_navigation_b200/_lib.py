@@ -34,6 +34,7 @@ _SIGNATURES = {
     "ngp_field_query_value_grad": ([P, F, P, P, F, U32, U32, I, P, P, P, P, F, F, P, P, P, I64, P], I),
     "ngp_field_query_forward_jacobian": ([P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, I64, P], I),
     "ngp_field_query_backward_jacobian": ([P, P, P, I64, P], I),
+    "ngp_field_query_ff_forward": ([P, F, P, P, F, U32, U32, I, P, I, I, P, I64, P], I),
     "ngp_set_field_impl": ([I], I),
     "ngp_set_device_check": ([I], I),
     "ngp_field_color_forward": ([P, P, F, P, P, F, U32, U32, I, P, P, P, P, P, P, P, P, I64, P], I),

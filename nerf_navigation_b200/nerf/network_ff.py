@@ -4,8 +4,10 @@ colour, with the same constructor kwargs, parameter names (`encoder.embeddings`,
 `color_net.weights`) and density()/forward()/color() contracts.  The MLPs run on the tcgen05 kernels (csrc/ffmlp.cu),
 the encoders on the grid / SH kernels.  Background model (bg_radius > 0) is out of scope as in nerf/network.py.
 """
+import numpy as np
 import torch
 
+from .. import _lib
 from ..activation import trunc_exp
 from ..encoding import get_encoder
 from ..ffmlp import FFMLP
@@ -43,10 +45,35 @@ class NeRFNetwork(NeRFRenderer):
         rgb = torch.sigmoid(self.color_net(self._color_in(d, h[..., 1:])))
         return sigma, rgb
 
+    fused_eval = True  # inference density() through the fused encode -> FFMLP kernel (ngp_field_query_ff_forward)
+
+    def _sigma_net_fused(self, x):
+        """encoder + sigma_net in one kernel when nothing needs a gradient (the features never reach HBM); None otherwise."""
+        enc, net = self.encoder, self.sigma_net
+        if not (self.fused_eval and x.is_cuda and x.dtype == torch.float32 and hasattr(enc, "embeddings")
+                and not (torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())))
+                and enc.input_dim == 3 and enc.num_levels == 16 and enc.level_dim == 2 and enc.embeddings.dtype == torch.float32
+                and net.input_dim == 32 and net.hidden_dim == 64 and net.padded_output_dim == 16 and net.activation in (0, 6)
+                and not torch.is_autocast_enabled()):
+            return None
+        x = x.contiguous()
+        B = x.shape[0]
+        w = net.weights.detach()
+        w = w if w.dtype == torch.half else w.half()
+        out = torch.empty(B, 16, device=x.device, dtype=torch.half)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ngp_field_query_ff_forward(
+                _lib.ptr(x), float(self.bound), _lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets),
+                float(np.log2(enc.per_level_scale)), int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners), _lib.ptr(w),
+                net.num_layers, net.activation, _lib.ptr(out), B, _lib.stream()), "field_query_ff_forward")
+        return out[:, :net.output_dim] if net.output_dim != 16 else out
+
     def density(self, x):
         """network_ff.py:76-89 -> {'sigma', 'geo_feat'}; leading dimensions are kept."""
         prefix = x.shape[:-1]
-        h = self.sigma_net(self.encoder(x.reshape(-1, 3), bound=self.bound))
+        h = self._sigma_net_fused(x.reshape(-1, 3))
+        if h is None:
+            h = self.sigma_net(self.encoder(x.reshape(-1, 3), bound=self.bound))
         return {"sigma": trunc_exp(h[..., 0]).view(*prefix), "geo_feat": h[..., 1:].reshape(*prefix, self.geo_feat_dim)}
 
     def color(self, x, d, mask=None, geo_feat=None, **kwargs):

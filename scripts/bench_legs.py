@@ -220,4 +220,19 @@ def ffmlp_leg(dev, hbm_gbs, B=1 << 22):
             del r_bb, r_inf
         out[name] = rec
         del x, w, grad, outp, fwd, gx, gw, wsp
+    # network_ff.density (nerf/network_ff.py:76-89): hash-grid encoder -> FFMLP sigma net, as one kernel and as the two ops
+    from nerf_navigation_b200.nerf.network_ff import NeRFNetwork as NetFF
+    mff = NetFF(encoding="hashgrid", bound=2, cuda_ray=False).to(dev).eval()
+    pts = torch.rand(B, 3, device=dev) * 2 - 1
+    with torch.no_grad():
+        mff.fused_eval = True
+        t_fused = _time(lambda: mff.density(pts), 10, 3)
+        mff.fused_eval = False
+        t_two = _time(lambda: mff.density(pts), 10, 3)
+    out["network_ff_density"] = {"points": B, "fused_ms": t_fused, "fused_Msamples_per_s": B / t_fused / 1e3,
+                                 "encoder_then_ffmlp_ms": t_two, "speedup": t_two / t_fused,
+                                 "l2_gather_GBps": B * 1024 / t_fused / 1e6,
+                                 "what": "ngp_field_query_ff_forward (k_ffield5_forward: gather warps write fp16 features into the "
+                                         "FFMLP's shared-memory A tile) vs ngp_grid_encode_forward + .half() + ngp_ffmlp_forward"}
+    del mff, pts
     return out

@@ -171,3 +171,46 @@ def test_module_autograd(ngp):
     net.eval()
     with torch.no_grad():
         assert rel_err(net(x).float().cpu().numpy(), y.detach().float().cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("B,num_layers", [(1, 2), (4097, 2), (100003, 3)])
+def test_fused_encode_ffmlp_vs_unfused_and_oracle(ngp, oracle, B, num_layers):
+    """ngp_field_query_ff_forward (network_ff.density as one kernel: hash-grid features -> fp16 -> FFMLP in shared memory) ==
+    GridEncoder kernel -> .half() -> FFMLP kernel, and == the CPU oracle chain (C encoder + numpy FFMLP), 2e-3 fp16 bar; the
+    two GPU paths round the same fp32 features to fp16, so nearly every output is bit-identical."""
+    from util import hashgrid_config
+    cfg = hashgrid_config(bound=2.0, table_std=0.5)
+    rng = np.random.default_rng(B)
+    x = rng.uniform(-2, 2, (B, 3)).astype(np.float32)
+    if B > 10:
+        x[1] = [2.0, -2.0, 0.0]      # on the boundary: in range
+        x[2] = [2.5, 0.0, 0.0]       # outside: zero features -> zero outputs (no bias anywhere)
+    w = _weights(32, num_layers, B)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    xt, tt, ot, wt = dev(x), dev(cfg["table"]), dev(cfg["offsets"]), dev(w)
+    L = ngp.lib()
+    out = torch.empty(B, 16, device="cuda", dtype=torch.half)
+    ngp.check(L.ngp_field_query_ff_forward(xt.data_ptr(), cfg["bound"], tt.data_ptr(), ot.data_ptr(), cfg["S"], cfg["H"], 0, 0,
+                                           wt.data_ptr(), num_layers, 0, out.data_ptr(), B, ngp.stream()), "ff_forward")
+    # unfused: standalone encoder kernel ([B, L*C] layout), half(), FFMLP kernel
+    x01 = ((xt + cfg["bound"]) / (2 * cfg["bound"])).contiguous()
+    feat = torch.empty(B, 32, device="cuda")
+    ngp.check(L.ngp_grid_encode_forward(x01.data_ptr(), tt.data_ptr(), 0, ot.data_ptr(), feat.data_ptr(), 1, B, 3, 2, 16, cfg["S"],
+                                        cfg["H"], 0, None, 0, 0, None, ngp.stream()), "grid_forward")
+    fh = feat.half().contiguous()
+    out2 = torch.empty(B, 16, device="cuda", dtype=torch.half)
+    ngp.check(L.ngp_ffmlp_forward(fh.data_ptr(), wt.data_ptr(), B, 32, 16, 64, num_layers, 0, 6, None, out2.data_ptr(), ngp.stream()),
+              "ffmlp_forward")
+    a, b = out.float().cpu().numpy(), out2.float().cpu().numpy()
+    assert rel_err(a, b) < 2e-3
+    assert (a == b).mean() > 0.99
+    if B > 10:
+        assert np.all(a[2] == 0.0)
+    s16 = torch.empty(16, device="cuda")
+    ngp.check(L.ngp_grid_level_scales(s16.data_ptr(), 16, cfg["S"], cfg["H"], ngp.stream()))
+    n = min(B, 20000)
+    enc = oracle.grid_encode_forward(((x[:n] + cfg["bound"]) / (2 * cfg["bound"])).astype(np.float32), cfg["table"], cfg["offsets"],
+                                     s16.cpu().numpy())[0]
+    enc = np.ascontiguousarray(enc.transpose(1, 0, 2).reshape(n, 32)).astype(np.float16)
+    ro, _ = oracle.ffmlp_forward(enc, w, 32, 64, num_layers)
+    assert rel_err(a[:n], ro.astype(np.float32)) < 2e-3
