@@ -254,6 +254,28 @@ int ngp_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, c
                           const float *Wc2, float density_scale, const float *bg_color, int bg_stride, float *image,
                           float *depth, float *weights_sum, int32_t *counts, void *workspace, ngp_stream_t stream);
 
+/* The same renderer with the occupancy marching taken OUT of the persistent kernel (csrc/render5.cu, tcgen05 implementation
+ * only): marching is a chain of dependent steps that only thread-level parallelism hides, so it runs as a thread-per-ray
+ * pre-pass at full occupancy and the persistent kernel only evaluates and composites.  Same samples bit for bit, same
+ * outputs and per-ray counts as ngp_render_rays_infer; samples behind a ray's early termination are marched but never
+ * evaluated.  Two calls because the sample lists are sized by their total:
+ *   ngp_render_plan: plan_counts i32 [N] = samples on each ray (up to max_steps, before any termination), plan_ends i64 [N]
+ *     = their inclusive prefix sums (plan_ends[N-1] = total); workspace = ngp_render_plan_workspace_bytes(N) bytes;
+ *   ngp_render_rays_infer_planned: arguments of ngp_render_rays_infer + the plan + samples = scratch for 2 * total floats
+ *     (8-byte aligned; the (t, dt) lists are written by the call itself) + the renderer's workspace. */
+int64_t ngp_render_plan_workspace_bytes(int64_t N);
+int ngp_render_plan(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                    const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
+                    int32_t *plan_counts, int64_t *plan_ends, void *workspace, int64_t workspace_bytes, ngp_stream_t stream);
+int ngp_render_rays_infer_planned(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                                  const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                                  uint32_t Hgrid, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                                  uint32_t gridtype, int align_corners, const float *Ws0, const float *Ws1,
+                                  const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
+                                  const float *bg_color, int bg_stride, float *image, float *depth, float *weights_sum,
+                                  int32_t *counts, const int32_t *plan_counts, const int64_t *plan_ends, float *samples,
+                                  int64_t samples_capacity, void *workspace, ngp_stream_t stream);
+
 /* ---- training-step tail: torch.optim.Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:126) + EMA (nerf/utils.py:814) - */
 
 /* One fused pass over a parameter tensor: g *= grad_scale (all-reduce mean), Adam moments and update with torch's

@@ -26,6 +26,8 @@
 // larger budgets or deeper FIFOs, which made it slower.
 #include <float.h>
 
+#include <cub/cub.cuh>
+
 #include "cfield5.cuh"
 #include "march.cuh"
 
@@ -114,16 +116,18 @@ struct R5Rays {
     uint32_t status[R5_NR];
 };
 
-struct R5Bars {
-    uint64_t rows_full[R5_TBUF];   // 128 marcher threads: the tile's rows are in the buffer
-    uint64_t rows_free[R5_TBUF];   // 128 chain threads: the tile has been composited, the buffer may be rewritten
+template <int TB>
+struct R5BarsT {
+    uint64_t rows_full[TB];   // 128 marcher threads: the tile's rows are in the buffer
+    uint64_t rows_free[TB];   // 128 chain threads: the tile has been composited, the buffer may be rewritten
 };
 
 struct __align__(128) R5Smem {
+    static constexpr int TBUF = R5_TBUF, TBUF_LOG2 = R5_TBUF_LOG2;
     C5FwdWeights w;
     FqLevel lv[FQ_L];
     C5Bars bars[2];
-    R5Bars tb;
+    R5BarsT<R5_TBUF> tb;
     uint32_t tmem;
     int all_safe;
     float mipb[8], miprb[8];       // min(2^level, bound) and its reciprocal (raymarching.cu:376-377)
@@ -145,6 +149,10 @@ struct R5Params {
     int32_t *counts;
     unsigned long long *counter;
     unsigned long long *nsamples;
+    // pre-marched sample lists (k_render5_rays_infer_lists): samples of ray i are tdt[ends[i] - counts[i] .. ends[i])
+    const int32_t *plan_counts;
+    const long long *plan_ends;
+    const float2 *tdt;
 };
 
 __device__ __forceinline__ uint32_t r5_ld_status(const uint32_t *p) { return *(const volatile uint32_t *)p; }
@@ -159,7 +167,8 @@ __device__ __forceinline__ bool r5_tile_end(const R5Tile &T) {
 
 // ------------------------------------------------------------------------------------------------ marcher warps
 // renderer.py:371-374: image + (1 - ws) * bg; clamp(depth - near, 0) / (far - near)
-static __device__ __noinline__ void r5_finish(const R5Rays &R, const R5Params &P, int slot, int64_t id) {
+template <class RAYS>
+static __device__ __noinline__ void r5_finish(const RAYS &R, const R5Params &P, int slot, int64_t id) {
     const float ws = R.ws[slot], om = 1.0f - ws;
     const float *bg = P.bg ? P.bg + (int64_t)P.bg_stride * id : nullptr;
     const float b0 = bg ? __ldg(bg) : 1.0f, b1 = bg ? __ldg(bg + 1) : 1.0f, b2 = bg ? __ldg(bg + 2) : 1.0f;
@@ -468,8 +477,8 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
 }
 
 // ------------------------------------------------------------------------------------------------ gather warps
-template <bool SAFE>
-__device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
+template <bool SAFE, class SM>
+__device__ __forceinline__ void r5_gather(SM &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
     const int s = warp >> 2, q = warp & 3, row = 32 * q + lane;
     const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
     const uint32_t bar_full = tc5::smem_u32(&S.bars[s].f_full), bar_empty = tc5::smem_u32(&S.bars[s].f_empty);
@@ -478,8 +487,8 @@ __device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t
     R5_STAT_ADD(2, -clock64());
     for (int64_t it = 0;; ++it) {
         const int64_t n = 2 * it + s;
-        const int b = (int)(n & (R5_TBUF - 1));
-        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> R5_TBUF_LOG2) & 1), 0);
+        const int b = (int)(n & (SM::TBUF - 1));
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> SM::TBUF_LOG2) & 1), 0);
         const R5Tile &T = S.tile[b];
         if (r5_tile_end(T)) break;
         bool valid = T.slot[row] != R5_INVALID;
@@ -509,7 +518,8 @@ __device__ __forceinline__ void r5_gather(R5Smem &S, const R5Params &P, uint32_t
 }
 
 // ------------------------------------------------------------------------------------------------ MMA threads
-__device__ __forceinline__ void r5_mma(R5Smem &S, const R5Params &P, uint32_t tmem, int s) {
+template <class SM>
+__device__ __forceinline__ void r5_mma(SM &S, const R5Params &P, uint32_t tmem, int s) {
     R5_STAT_DECL;
     R5_STAT_ADD(7, -clock64());
     const uint32_t t = tmem + s * C5_SLOT_COLS;
@@ -522,8 +532,8 @@ __device__ __forceinline__ void r5_mma(R5Smem &S, const R5Params &P, uint32_t tm
                    c2l = tc5::smem_u32(S.w.c2[1]);
     for (int64_t it = 0;; ++it) {
         const int64_t n = 2 * it + s;
-        const int b = (int)(n & (R5_TBUF - 1));
-        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> R5_TBUF_LOG2) & 1), 3);
+        const int b = (int)(n & (SM::TBUF - 1));
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)((n >> SM::TBUF_LOG2) & 1), 3);
         if (r5_tile_end(S.tile[b])) break;
         const uint32_t pa = (uint32_t)(4 * it);
         R5_WAIT(bar_ff, (uint32_t)(it & 1), 4);
@@ -558,23 +568,24 @@ __device__ __forceinline__ void r5_mma(R5Smem &S, const R5Params &P, uint32_t tm
 // first tile's next layer is on the tensor core, as in cfield5.cu), otherwise one — waiting for a tile that the marchers
 // can only build once THIS tile's rays have been composited would deadlock.  d_full of a TMEM slot completes 5 times per
 // tile: wait k of the slot's tile number `it` has parity (5 it + k) & 1.
-__device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
+template <class SM>
+__device__ __forceinline__ void r5_chain(SM &S, const R5Params &P, uint32_t tmem, int warp, int lane) {
     const int q = warp & 3, row = 32 * q + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
-    R5Rays &R = S.rays;
+    auto &R = S.rays;
     int64_t n0 = 0;
     uint32_t group = 0;
     R5_STAT_DECL;
     R5_STAT_ADD(10, -clock64());
     for (;;) {
-        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[n0 & (R5_TBUF - 1)]), (uint32_t)((n0 >> R5_TBUF_LOG2) & 1), 8);
-        if (r5_tile_end(S.tile[n0 & (R5_TBUF - 1)])) break;
+        R5_WAIT(tc5::smem_u32(&S.tb.rows_full[n0 & (SM::TBUF - 1)]), (uint32_t)((n0 >> SM::TBUF_LOG2) & 1), 8);
+        if (r5_tile_end(S.tile[n0 & (SM::TBUF - 1)])) break;
         // one decision for the four chain warps (they hand the same tiles to the MMA threads step by step, so taking a tile
         // in one warp and not in another would deadlock): the first chain warp tests, the others read its verdict
         if (warp == C5_CHAIN_WARP0 && lane == 0) {
             const int64_t n1 = n0 + 1;
-            bool ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_full[n1 & (R5_TBUF - 1)]), (uint32_t)((n1 >> R5_TBUF_LOG2) & 1));
-            if (ok && r5_tile_end(S.tile[n1 & (R5_TBUF - 1)])) ok = false;
+            bool ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_full[n1 & (SM::TBUF - 1)]), (uint32_t)((n1 >> SM::TBUF_LOG2) & 1));
+            if (ok && r5_tile_end(S.tile[n1 & (SM::TBUF - 1)])) ok = false;
             S.chain_two[group & 1] = ok ? 1 : 0;
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -585,7 +596,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
 #define R5_TILE_VARS                                                                                \
         const int64_t n = n0 + i;                                                                   \
         const int s = (int)(n & 1);                                                                 \
-        R5Tile &T = S.tile[n & (R5_TBUF - 1)];                                                      \
+        R5Tile &T = S.tile[n & (SM::TBUF - 1)];                                                      \
         const uint32_t par = (uint32_t)(5 * (n >> 1));                                              \
         const uint32_t lane_addr = lane_base + s * C5_SLOT_COLS;                                    \
         const uint32_t bar_d = tc5::smem_u32(&S.bars[s].d_full), bar_a = tc5::smem_u32(&S.bars[s].a_ready);
@@ -669,7 +680,7 @@ __device__ __forceinline__ void r5_chain(R5Smem &S, const R5Params &P, uint32_t 
             // the two samples a ray may have in flight sit in consecutive tiles and in the same 32-row band (its marcher
             // warp's rows), i.e. this warp composites both, one after the other: order and visibility between its lanes
             __syncwarp();
-            tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_free[n & (R5_TBUF - 1)]));
+            tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_free[n & (SM::TBUF - 1)]));
         }
         n0 += n_act;
     }
@@ -713,12 +724,12 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
     const uint32_t tmem = S.tmem;
 
     if (warp < C5_GATHER_WARPS) {
-        if (S.all_safe) r5_gather<true>(S, P, tmem, warp, lane);
-        else r5_gather<false>(S, P, tmem, warp, lane);
+        if (S.all_safe) r5_gather<true, R5Smem>(S, P, tmem, warp, lane);
+        else r5_gather<false, R5Smem>(S, P, tmem, warp, lane);
     } else if (warp < C5_MMA_WARP) {
-        r5_chain(S, P, tmem, warp, lane);
+        r5_chain<R5Smem>(S, P, tmem, warp, lane);
     } else if (warp < R5_MARCH_WARP0) {
-        if (lane == 0) r5_mma(S, P, tmem, warp - C5_MMA_WARP);
+        if (lane == 0) r5_mma<R5Smem>(S, P, tmem, warp - C5_MMA_WARP);
         __syncwarp();
     } else {
         r5_marcher(S, P, cfg, warp - R5_MARCH_WARP0, lane);
@@ -726,6 +737,410 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
     tc5::fence_before_sync();
     __syncthreads();
     if (warp == C5_MMA_WARP) tc5::tmem_dealloc(tmem, 512);
+}
+
+// ================================================================================================ pre-marched variant
+// What bounds the kernel above is its marcher: occupancy marching is a chain of dependent steps (position -> cell -> bit ->
+// next t) that only thread-level parallelism hides, and 8 warps per SM offer 1/8 of what a full-occupancy kernel does
+// (R5_STATS: 2.7 marcher passes of 8,800 cycles per 15 tile rows; gather warps 37 %, chain warps 43 % of their time
+// waiting).  Here the marching moves OUT of the persistent kernel into a thread-per-ray pre-pass at full occupancy
+// (k_r5_premarch: the same cell / exit arithmetic, so the same samples bit for bit) that leaves every ray's (t, dt) list in
+// global memory — a count pass, an inclusive scan, a write pass — and the persistent kernel's 8 "feeder" warps only hand
+// list entries to tiles: classify the slots, retire / refill rays, ballot-compact the eligible ones into rows.  Early
+// termination stays exact (samples after a ray's end are never evaluated; only their marching is wasted), per-ray counts
+// stay the oracle's.  The ray store shrinks (no sample FIFOs, no reciprocal directions, 512 slots, 4 row buffers): 142 KB of
+// shared memory instead of 219 KB, which gives the gathers their L1 back (dfield5.cu: the carve-out is part of the roofline).
+#define R5L_PER_LANE 2
+#define R5L_PER_WARP (32 * R5L_PER_LANE)
+#define R5L_NR (R5_MARCH_WARPS * R5L_PER_WARP)     // 512 ray slots per CTA
+#define R5L_TBUF_LOG2 2
+
+struct R5RaysL {
+    float ox[R5L_NR], oy[R5L_NR], oz[R5L_NR], dx[R5L_NR], dy[R5L_NR], dz[R5L_NR];
+    float near[R5L_NR], far[R5L_NR];
+    int id[R5L_NR];                                  // ray index; -1: slot wants a ray; -2: no rays left
+    uint32_t cursor[R5L_NR], count[R5L_NR];          // samples handed to tiles so far / in the ray's list
+    long long off[R5L_NR];                           // first list entry of the ray
+    float ws[R5L_NR], depth[R5L_NR], r[R5L_NR], g[R5L_NR], b[R5L_NR];
+    uint32_t ncomp[R5L_NR];
+    uint32_t status[R5L_NR];
+};
+
+struct __align__(128) R5SmemL {
+    static constexpr int TBUF = 1 << R5L_TBUF_LOG2, TBUF_LOG2 = R5L_TBUF_LOG2;
+    C5FwdWeights w;
+    FqLevel lv[FQ_L];
+    C5Bars bars[2];
+    R5BarsT<(1 << R5L_TBUF_LOG2)> tb;
+    uint32_t tmem;
+    int all_safe;
+    int chain_two[2];
+    R5Tile tile[1 << R5L_TBUF_LOG2];
+    R5RaysL rays;
+};
+
+static __device__ __noinline__ void r5l_load_ray(R5RaysL &R, const R5Params &P, int slot, int64_t nid) {
+    const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
+    const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
+    float near, far;
+    ngp_near_far_ray(o, d, P.aabb, P.min_near, near, far);
+    R.ox[slot] = o[0]; R.oy[slot] = o[1]; R.oz[slot] = o[2];
+    R.dx[slot] = d[0]; R.dy[slot] = d[1]; R.dz[slot] = d[2];
+    R.near[slot] = near; R.far[slot] = far;
+    R.ws[slot] = 0.0f; R.depth[slot] = 0.0f; R.r[slot] = 0.0f; R.g[slot] = 0.0f; R.b[slot] = 0.0f;
+    R.ncomp[slot] = 0u;
+    const uint32_t cnt = (uint32_t)__ldg(P.plan_counts + nid);
+    R.count[slot] = cnt;
+    R.cursor[slot] = 0u;
+    R.off[slot] = __ldg(P.plan_ends + nid) - (long long)cnt;
+    R.id[slot] = (int)nid;
+}
+
+// One pass of a feeder warp over its R5L_PER_WARP slots: classify (eligible / finished / waiting), retire and refill,
+// build the warp's R5_PART rows of tile n from the eligible slots' next list entries.
+__device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w, int lane) {
+    R5RaysL &R = S.rays;
+    const int slot0 = w * R5L_PER_WARP + lane;
+    const unsigned lt_mask = (1u << lane) - 1u;
+#pragma unroll 1
+    for (int j = 0; j < R5L_PER_LANE; ++j) {
+        const int slot = slot0 + 32 * j;
+        R.id[slot] = -1;
+        r5_st_status(&R.status[slot], R5_IDLE);
+    }
+    bool rays_left = true;
+    unsigned long long evaluated = 0;
+    int64_t n = 0;                                  // next tile to build
+    int rot = 0;
+    unsigned needs = (1u << R5L_PER_LANE) - 1u;     // bit j: slot j of this lane wants a ray
+    bool ended = false;
+    R5_STAT_DECL;
+    R5_STAT_ADD(17, -clock64());
+    for (;;) {
+        R5_STAT_ADD(13, 1);
+        // ---- refill the slots that want a ray: one atomic per warp
+        if (!rays_left) needs = 0u;
+        if (__any_sync(0xffffffffu, needs != 0u)) {
+            const int mine = __popc(needs);
+            int pre = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, pre, o);
+                if (lane >= o) pre += v;
+            }
+            const int total = __shfl_sync(0xffffffffu, pre, 31);
+            unsigned long long base = 0;
+            if (lane == 31) base = atomicAdd(P.counter, (unsigned long long)total);
+            base = __shfl_sync(0xffffffffu, base, 31);
+            int64_t nid = (int64_t)base + pre - mine;
+            while (needs) {
+                const int j = __ffs(needs) - 1;
+                needs &= needs - 1u;
+                const int slot = slot0 + 32 * j;
+                if (nid < P.N) {
+                    r5l_load_ray(R, P, slot, nid);
+                    ++nid;
+                } else {
+                    R.id[slot] = -2;
+                    rays_left = false;
+                }
+            }
+        }
+        // ---- classify
+        unsigned elig = 0u, retire = 0u;
+        bool pending = false;
+#pragma unroll
+        for (int j = 0; j < R5L_PER_LANE; ++j) {
+            const int slot = slot0 + 32 * j;
+            if (R.id[slot] < 0) continue;
+            const uint32_t st = r5_ld_status(&R.status[slot]);
+            const bool dead = (st & R5_DEAD) != 0u, more = R.cursor[slot] < R.count[slot];
+            const uint32_t fly = R5_NFLY(st);
+            if (!dead && more && fly < R5_INFLIGHT) elig |= 1u << j;
+            else if (fly == 0u && (dead || !more)) retire |= 1u << j;
+            else pending = true;   // in flight: comes back
+        }
+        // ---- retire finished rays (their slots are refilled at the top of the next pass)
+        if (retire) pending = true;
+        while (retire) {
+            const int j = __ffs(retire) - 1;
+            retire &= retire - 1u;
+            const int slot = slot0 + 32 * j;
+            __threadfence_block();         // the chain thread wrote the accumulators before the status
+            r5_finish(R, P, slot, R.id[slot]);
+            evaluated += R.ncomp[slot];
+            if (rays_left) {
+                R.id[slot] = -1;
+                needs |= 1u << j;
+            } else {
+                R.id[slot] = -2;
+            }
+            r5_st_status(&R.status[slot], R5_IDLE);
+        }
+        // ---- build this warp's part of tile n: R5_PART eligible slots, or all of them if nothing else can come
+        int E = __popc(elig);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+        const bool any_pending = __any_sync(0xffffffffu, pending);
+        bool build = E >= R5_PART || !any_pending;
+        if (!build) R5_STAT_ADD(15, 1);
+        R5_STAT_ADD(20, E);
+        const int b = (int)(n & (R5SmemL::TBUF - 1));
+        if (build && n >= R5SmemL::TBUF) {
+            uint32_t ok = 0;
+            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> R5L_TBUF_LOG2) - 1) & 1));
+            build = __shfl_sync(0xffffffffu, ok, 0) != 0u;
+            if (!build) R5_STAT_ADD(16, 1);
+        }
+        if (build) {
+            R5Tile &T = S.tile[b];
+            int nrows = 0;
+#pragma unroll 1
+            for (int jj = 0; jj < R5L_PER_LANE && nrows < R5_PART; ++jj) {
+                int j = jj + rot;
+                if (j >= R5L_PER_LANE) j -= R5L_PER_LANE;
+                const bool e = (elig >> j) & 1u;
+                const unsigned m = __ballot_sync(0xffffffffu, e);
+                const int row = nrows + __popc(m & lt_mask);
+                if (e && row < R5_PART) {
+                    const int slot = slot0 + 32 * j;
+                    const uint32_t cur = R.cursor[slot];
+                    const float2 sm = __ldg(P.tdt + R.off[slot] + cur);
+                    R.cursor[slot] = cur + 1u;
+                    const float st = sm.x, sdt = sm.y;
+                    const float dxv = R.dx[slot], dyv = R.dy[slot], dzv = R.dz[slot];
+                    const int tr = w * R5_PART + row;
+                    T.x[tr] = ngp_clampf(fmaf(st, dxv, R.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
+                    T.y[tr] = ngp_clampf(fmaf(st, dyv, R.oy[slot]), -P.bound, P.bound);
+                    T.z[tr] = ngp_clampf(fmaf(st, dzv, R.oz[slot]), -P.bound, P.bound);
+                    T.dx[tr] = dxv; T.dy[tr] = dyv; T.dz[tr] = dzv;
+                    T.tn[tr] = st + sdt;
+                    T.dt[tr] = sdt;
+                    T.slot[tr] = (uint32_t)slot;
+                    atomicAdd(&R.status[slot], 1u);
+                }
+                nrows = min(R5_PART, nrows + __popc(m));
+            }
+            rot = rot + 1 >= R5L_PER_LANE ? 0 : rot + 1;
+            for (int row = nrows + lane; row < R5_PART; row += 32) T.slot[w * R5_PART + row] = R5_INVALID;
+            if (lane == 0) T.nrows[w] = nrows;
+            tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b]));
+            ++n;
+            R5_STAT_ADD(14, 1);
+            R5_STAT_ADD(21, nrows);
+            if (nrows == 0) {
+                // this part is empty for good (every slot is out of rays): the end protocol of r5_marcher
+                R5_WAIT(tc5::smem_u32(&S.tb.rows_full[b]), (uint32_t)(((n - 1) >> R5L_TBUF_LOG2) & 1), 18);
+                if (r5_tile_end(T)) {
+                    const int b2 = (int)(n & (R5SmemL::TBUF - 1));
+                    if (n >= R5SmemL::TBUF)
+                        tc5::mbar_wait_wd(tc5::smem_u32(&S.tb.rows_free[b2]), (uint32_t)(((n >> R5L_TBUF_LOG2) - 1) & 1));
+                    R5Tile &T2 = S.tile[b2];
+                    for (int row = lane; row < R5_PART; row += 32) T2.slot[w * R5_PART + row] = R5_INVALID;
+                    if (lane == 0) T2.nrows[w] = 0;
+                    tc5::mbar_arrive(tc5::smem_u32(&S.tb.rows_full[b2]));
+                    ended = true;
+                }
+            }
+        } else {
+            __nanosleep(100);   // rays are in flight or the row buffer is busy: leave the issue slots to the other roles
+        }
+        if (ended) break;
+        __syncwarp();
+    }
+    if (P.nsamples) {
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) evaluated += __shfl_xor_sync(0xffffffffu, evaluated, o2);
+        if (lane == 0 && evaluated) atomicAdd(P.nsamples, evaluated);
+    }
+    R5_STAT_ADD(17, clock64());
+    R5_STAT_FLUSH(P, lane);
+}
+
+// Thread-per-ray marcher of the pre-pass: r5_marcher's sequence exactly (same cell / exit functions, same end tests).
+// WRITE = false: counts[i] = number of samples; WRITE = true: the samples go to tdt[ends[i] - counts[i] ...].
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+k_r5_premarch(const float *__restrict__ rays_o, const float *__restrict__ rays_d, int64_t N, const float *__restrict__ aabb,
+              float min_near, MarchCfg cfg, uint32_t max_steps, int32_t *__restrict__ counts, const long long *__restrict__ ends,
+              float2 *__restrict__ tdt) {
+    __shared__ float mipb[8], miprb[8];
+    if (threadIdx.x < 8) {
+        mipb[threadIdx.x] = fminf((float)(1 << threadIdx.x), cfg.bound);
+        miprb[threadIdx.x] = 1.0f / mipb[threadIdx.x];
+    }
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const float o[3] = {__ldg(rays_o + i * 3), __ldg(rays_o + i * 3 + 1), __ldg(rays_o + i * 3 + 2)};
+    const float d[3] = {__ldg(rays_d + i * 3), __ldg(rays_d + i * 3 + 1), __ldg(rays_d + i * 3 + 2)};
+    float near, far;
+    ngp_near_far_ray(o, d, aabb, min_near, near, far);
+    MarchRay r;
+    r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = d[0]; r.dy = d[1]; r.dz = d[2];
+    r.rdx = 1.0f / d[0]; r.rdy = 1.0f / d[1]; r.rdz = 1.0f / d[2];
+    float2 *out = nullptr;
+    if (WRITE) out = tdt + (ends[i] - (long long)counts[i]);
+    float t = near;
+    uint32_t marched = 0;
+#pragma unroll 1
+    while (t < far && marched < max_steps) {   // raymarching.cu:730
+        float dt;
+        int lvl;
+        uint32_t nxyz;
+        const uint32_t cell = ngp_march_cell_fast(r, cfg, miprb, t, dt, lvl, nxyz);
+        const uint32_t byte = (uint32_t)__ldg(cfg.grid + (cell >> 3));
+        if ((byte >> (cell & 7u)) & 1u) {
+            const float sdt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+            if (WRITE) out[marched] = make_float2(t, sdt);
+            t += sdt;
+            ++marched;
+        } else {
+            const float tt = ngp_march_exit_fast(r, cfg, mipb, t, nxyz, lvl);
+            if (cfg.lvl_dt >= 0) {
+                do {
+                    t += cfg.dt_min;
+                } while (t < tt);
+            } else {
+                do {
+                    t = ngp_march_advance(t, cfg);
+                } while (t < tt);
+            }
+        }
+    }
+    if (!WRITE) counts[i] = (int32_t)marched;
+}
+
+__global__ void __launch_bounds__(R5_THREADS, 1)
+k_render5_rays_infer_lists(R5Params P, const int32_t *__restrict__ offsets, float S_, uint32_t H, uint32_t gridtype,
+                           const float *__restrict__ Ws0, const float *__restrict__ Ws1, const float *__restrict__ Wc0,
+                           const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
+    extern __shared__ __align__(128) unsigned char r5_smem_raw[];
+    R5SmemL &S = *reinterpret_cast<R5SmemL *>(r5_smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
+    c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
+    if (tid == 0) {
+        for (int s = 0; s < 2; ++s) {
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].f_full), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].f_empty), 1);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].d_full), 1);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].a_ready), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].t_free), 128);
+            tc5::mbar_init(tc5::smem_u32(&S.bars[s].g_full), 1);
+        }
+        for (int b = 0; b < R5SmemL::TBUF; ++b) {
+            tc5::mbar_init(tc5::smem_u32(&S.tb.rows_full[b]), R5_MARCH_WARPS * 32);
+            tc5::mbar_init(tc5::smem_u32(&S.tb.rows_free[b]), 128);
+        }
+        tc5::fence_mbar_init();
+    }
+    if (warp == C5_MMA_WARP) tc5::tmem_alloc(tc5::smem_u32(&S.tmem), 512);
+    tc5::fence_async_smem();
+    tc5::fence_before_sync();
+    __syncthreads();
+    tc5::fence_after_sync();
+    const uint32_t tmem = S.tmem;
+    if (warp < C5_GATHER_WARPS) {
+        if (S.all_safe) r5_gather<true, R5SmemL>(S, P, tmem, warp, lane);
+        else r5_gather<false, R5SmemL>(S, P, tmem, warp, lane);
+    } else if (warp < C5_MMA_WARP) {
+        r5_chain<R5SmemL>(S, P, tmem, warp, lane);
+    } else if (warp < R5_MARCH_WARP0) {
+        if (lane == 0) r5_mma<R5SmemL>(S, P, tmem, warp - C5_MMA_WARP);
+        __syncwarp();
+    } else {
+        r5l_feeder(S, P, warp - R5_MARCH_WARP0, lane);
+    }
+    tc5::fence_before_sync();
+    __syncthreads();
+    if (warp == C5_MMA_WARP) tc5::tmem_dealloc(tmem, 512);
+}
+
+// ---- entry points of the pre-marched renderer (declared in include/ngp_b200.h)
+struct R5ToI64 {
+    __host__ __device__ long long operator()(const int32_t &v) const { return (long long)v; }
+};
+
+extern "C" int64_t ngp_render_plan_workspace_bytes(int64_t N) {
+    size_t need = 0;
+    cub::TransformInputIterator<long long, R5ToI64, const int32_t *> it(nullptr, R5ToI64());
+    cub::DeviceScan::InclusiveSum(nullptr, need, it, (long long *)nullptr, (int)(N < 1 ? 1 : N));
+    return (int64_t)need + 256;
+}
+
+extern "C" int ngp_render_plan(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                               const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C, uint32_t Hgrid,
+                               int32_t *counts, int64_t *ends, void *workspace, int64_t workspace_bytes, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_render_plan");
+    if (N == 0) return NGP_OK;
+    NGP_REQUIRE(rays_o && rays_d && aabb && grid && counts && ends && workspace, NGP_ERR_ARG, "ngp_render_plan: null pointer");
+    NGP_REQUIRE(bound > 0.0f && N > 0 && N < (1ll << 31) && max_steps < (1u << 20), NGP_ERR_ARG, "ngp_render_plan: bad bound / N / max_steps");
+    NGP_REQUIRE(C >= 1 && C <= 8 && Hgrid >= 1 && Hgrid <= 1024, NGP_ERR_ARG, "ngp_render_plan: bad cascade/grid size");
+    NGP_REQUIRE(workspace_bytes >= ngp_render_plan_workspace_bytes(N), NGP_ERR_ARG, "ngp_render_plan: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
+    k_r5_premarch<false><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps, counts, nullptr,
+                                                                      nullptr);
+    NGP_CHECK_LAUNCH("ngp_render_plan(count)");
+    size_t need = (size_t)workspace_bytes;
+    cub::TransformInputIterator<long long, R5ToI64, const int32_t *> it(counts, R5ToI64());
+    cudaError_t e = cub::DeviceScan::InclusiveSum(workspace, need, it, (long long *)ends, (int)N, st);
+    NGP_REQUIRE(e == cudaSuccess, NGP_ERR_CUDA, "ngp_render_plan: scan: %s", cudaGetErrorString(e));
+    return NGP_OK;
+}
+
+extern "C" int ngp_render_rays_infer_planned(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                                             const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                                             uint32_t Hgrid, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                                             uint32_t gridtype, int align_corners, const float *Ws0, const float *Ws1,
+                                             const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
+                                             const float *bg_color, int bg_stride, float *image, float *depth, float *weights_sum,
+                                             int32_t *counts, const int32_t *plan_counts, const int64_t *plan_ends, float *samples,
+                                             int64_t samples_capacity, void *workspace, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_render_rays_infer_planned");
+    if (N == 0) return NGP_OK;
+    NGP_REQUIRE(rays_o && rays_d && aabb && grid && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && image && depth &&
+                    workspace && plan_counts && plan_ends && (samples || samples_capacity == 0),
+                NGP_ERR_ARG, "ngp_render_rays_infer_planned: null pointer");
+    NGP_REQUIRE(bound > 0.0f && N > 0 && N < (1ll << 31) && max_steps < (1u << 20), NGP_ERR_ARG,
+                "ngp_render_rays_infer_planned: bad bound / N / max_steps");
+    NGP_REQUIRE(C >= 1 && C <= 8 && Hgrid >= 1 && Hgrid <= 1024, NGP_ERR_ARG, "ngp_render_rays_infer_planned: bad cascade/grid size");
+    NGP_REQUIRE(bg_stride == 0 || bg_stride == 3, NGP_ERR_ARG, "ngp_render_rays_infer_planned: bg_stride must be 0 or 3");
+    NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0 && ((uintptr_t)workspace & 7u) == 0 && ((uintptr_t)samples & 7u) == 0, NGP_ERR_ARG,
+                "ngp_render_rays_infer_planned: embeddings must be 16-byte, workspace and samples 8-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(workspace, 0, 16 + 24 * 8, st) != cudaSuccess) {
+        ngp_set_error("ngp_render_rays_infer_planned: workspace memset failed");
+        return NGP_ERR_CUDA;
+    }
+    (void)samples_capacity;   // the caller sized `samples` from plan_ends[N - 1] (ngp_render_plan); the lists cannot exceed it
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
+    k_r5_premarch<true><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps,
+                                                                     const_cast<int32_t *>(plan_counts),
+                                                                     (const long long *)plan_ends, (float2 *)samples);
+    NGP_CHECK_LAUNCH("ngp_render_rays_infer_planned(write)");
+    const int smem = (int)sizeof(R5SmemL);
+    if (cudaFuncSetAttribute(k_render5_rays_infer_lists, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+        ngp_set_error("ngp_render_rays_infer_planned: cannot reserve %d B of shared memory", smem);
+        return NGP_ERR_CUDA;
+    }
+    int dev = 0, sms = NGP_SM_COUNT;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    R5Params P;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.aabb = aabb; P.bg = bg_color; P.N = N; P.bg_stride = bg_stride;
+    P.min_near = min_near; P.density_scale = density_scale; P.bound = bound; P.max_steps = max_steps;
+    P.table = embeddings; P.align_corners = align_corners;
+    P.image = image; P.depth = depth; P.weights_sum = weights_sum; P.counts = counts;
+    P.counter = (unsigned long long *)workspace;
+    P.nsamples = (unsigned long long *)workspace + 1;
+    P.plan_counts = plan_counts; P.plan_ends = (const long long *)plan_ends; P.tdt = (const float2 *)samples;
+    const int64_t want = ngp_div_up(N, R5L_NR / 2);
+    const int nblocks = (int)(want < sms ? want : sms);
+    k_render5_rays_infer_lists<<<nblocks, R5_THREADS, smem, st>>>(P, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
+    NGP_CHECK_LAUNCH("ngp_render_rays_infer_planned");
+    return NGP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ launcher (render.cu)
@@ -752,6 +1167,7 @@ int r5_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, co
     P.image = image; P.depth = depth; P.weights_sum = weights_sum; P.counts = counts;
     P.counter = (unsigned long long *)workspace;
     P.nsamples = (unsigned long long *)workspace + 1;
+    P.plan_counts = nullptr; P.plan_ends = nullptr; P.tdt = nullptr;
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
     // one CTA per SM (a CTA owns all 512 TMEM columns); small batches use fewer CTAs so that tiles still fill
     const int64_t want = ngp_div_up(N, R5_NR / 2);

@@ -266,13 +266,20 @@ def field_color(model, x, d):
     return sigma.view(prefix), rgb.view(prefix + [3])
 
 
+PREMARCH = True   # render_rays_infer: march in a full-occupancy pre-pass (ngp_render_plan + ngp_render_rays_infer_planned)
+
+
 @torch.no_grad()
 def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, max_steps=1024, return_stats=False,
-                      return_counts=False):
+                      return_counts=False, premarch=None):
     """Fused eval branch of NeRFRenderer.run_cuda (renderer.py:325-374): near/far, the alive-ray loop of march_rays ->
     forward(x, d) -> composite_rays, and the background / depth post-processing in ONE kernel (csrc/render.cu).
     rays_o, rays_d [N,3] -> image [N,3], depth [N], weights_sum [N] (already post-processed like run_cuda's results);
-    return_stats appends the workspace (its second i64 = samples evaluated), return_counts the per-ray int32 sample counts."""
+    return_stats appends the workspace (its second i64 = samples evaluated), return_counts the per-ray int32 sample counts.
+    premarch (default: module flag PREMARCH, tcgen05 implementation only): the occupancy marching runs as a thread-per-ray
+    pre-pass that leaves every ray's (t, dt) list in a scratch tensor (one host read of the total to size it), and the
+    persistent kernel only evaluates and composites — same samples, same results; False keeps the marcher inside the kernel
+    (no host synchronisation, no scratch)."""
     _lib.require_cuda(rays_o, rays_d, model.density_bitfield)
     rays_o = rays_o.contiguous().float()
     rays_d = rays_d.contiguous().float()
@@ -295,14 +302,33 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
     counts = torch.empty(N, device=dev, dtype=torch.int32) if return_counts else None
     ws = [w.detach().contiguous() for w in (model.sigma_net[0].weight, model.sigma_net[1].weight, model.color_net[0].weight,
                                             model.color_net[1].weight, model.color_net[2].weight)]
+    L = _lib.lib()
+    if premarch is None:
+        premarch = PREMARCH
+    premarch = bool(premarch) and N > 0 and L.ngp_set_field_impl(-1) == 1
+    common = lambda: (_lib.ptr(rays_o), _lib.ptr(rays_d), N, _lib.ptr(aabb), float(model.min_near),
+                      _lib.ptr(model.density_bitfield), float(model.bound), float(dt_gamma), int(max_steps), int(model.cascade),
+                      int(model.grid_size))
+    field = lambda: (_lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets), float(np.log2(enc.per_level_scale)),
+                     int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners), *[_lib.ptr(w) for w in ws],
+                     float(model.density_scale), _lib.ptr(bg), stride, _lib.ptr(image), _lib.ptr(depth), _lib.ptr(wsum),
+                     _lib.ptr(counts))
+    aabb = aabb.contiguous()
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().ngp_render_rays_infer(
-            _lib.ptr(rays_o), _lib.ptr(rays_d), N, _lib.ptr(aabb.contiguous()), float(model.min_near),
-            _lib.ptr(model.density_bitfield), float(model.bound), float(dt_gamma), int(max_steps), int(model.cascade),
-            int(model.grid_size), _lib.ptr(enc.embeddings.detach()), _lib.ptr(enc.offsets),
-            float(np.log2(enc.per_level_scale)), int(enc.base_resolution), enc.gridtype_id, int(enc.align_corners),
-            *[_lib.ptr(w) for w in ws], float(model.density_scale), _lib.ptr(bg), stride, _lib.ptr(image),
-            _lib.ptr(depth), _lib.ptr(wsum), _lib.ptr(counts), _lib.ptr(work), _lib.stream()), "render_rays_infer")
+        if premarch:
+            plan_counts = torch.empty(N, device=dev, dtype=torch.int32)
+            plan_ends = torch.empty(N, device=dev, dtype=torch.int64)
+            pw_bytes = L.ngp_render_plan_workspace_bytes(N)
+            pw = torch.empty(pw_bytes, device=dev, dtype=torch.uint8)
+            _lib.check(L.ngp_render_plan(*common(), _lib.ptr(plan_counts), _lib.ptr(plan_ends), _lib.ptr(pw), pw_bytes,
+                                         _lib.stream()), "render_plan")
+            total = int(plan_ends[-1].item())             # the one host read: sizes the sample lists
+            samples = torch.empty(max(total, 1), 2, device=dev)
+            _lib.check(L.ngp_render_rays_infer_planned(*common(), *field(), _lib.ptr(plan_counts), _lib.ptr(plan_ends),
+                                                       _lib.ptr(samples), total, _lib.ptr(work), _lib.stream()),
+                       "render_rays_infer_planned")
+        else:
+            _lib.check(L.ngp_render_rays_infer(*common(), *field(), _lib.ptr(work), _lib.stream()), "render_rays_infer")
     out = (image, depth, wsum)
     if return_stats:
         out = out + (work,)

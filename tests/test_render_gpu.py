@@ -26,11 +26,16 @@ def model():
     return m.eval()
 
 
-@pytest.fixture(params=["tc5", "mma"])
+@pytest.fixture(params=["tc5", "tc5-inkernel-march", "mma"])
 def impl(request, ngp):
-    """Every test runs on both implementations: the warp-specialised tcgen05 kernel (default) and the mma.sync kernel."""
-    prev = ngp.lib().ngp_set_field_impl(1 if request.param == "tc5" else 0)
+    """Every test runs on the three implementations: the tcgen05 kernel fed by the pre-marched sample lists (default), the
+    tcgen05 kernel with the marcher inside (no host read, no scratch), and the mma.sync kernel."""
+    from nerf_navigation_b200 import field
+    prev = ngp.lib().ngp_set_field_impl(0 if request.param == "mma" else 1)
+    prev_pm = field.PREMARCH
+    field.PREMARCH = request.param == "tc5"
     yield request.param
+    field.PREMARCH = prev_pm
     ngp.lib().ngp_set_field_impl(prev)
 
 
