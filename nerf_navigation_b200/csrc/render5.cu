@@ -748,12 +748,17 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
 // global memory — a count pass, an inclusive scan, a write pass — and the persistent kernel's 8 "feeder" warps only hand
 // list entries to tiles: classify the slots, retire / refill rays, ballot-compact the eligible ones into rows.  Early
 // termination stays exact (samples after a ray's end are never evaluated; only their marching is wasted), per-ray counts
-// stay the oracle's.  The ray store shrinks (no sample FIFOs, no reciprocal directions, 512 slots, 4 row buffers): 142 KB of
-// shared memory instead of 219 KB, which gives the gathers their L1 back (dfield5.cu: the carve-out is part of the roofline).
+// stay the oracle's.  The ray store shrinks (no sample FIFOs, no reciprocal directions, 512 slots): 162 KB of shared memory
+// instead of 219 KB, which gives the gathers L1 back (dfield5.cu: the carve-out is part of the roofline).  Measured on one
+// 800x800 frame: 4 / 8 / 16 row buffers (142 / 162 / 223 KB) -> 22.2 / 20.7 / 29.2 ms.
+#ifndef R5L_PER_LANE
 #define R5L_PER_LANE 2
+#endif
 #define R5L_PER_WARP (32 * R5L_PER_LANE)
 #define R5L_NR (R5_MARCH_WARPS * R5L_PER_WARP)     // 512 ray slots per CTA
-#define R5L_TBUF_LOG2 2
+#ifndef R5L_TBUF_LOG2
+#define R5L_TBUF_LOG2 3
+#endif
 
 struct R5RaysL {
     float ox[R5L_NR], oy[R5L_NR], oz[R5L_NR], dx[R5L_NR], dy[R5L_NR], dz[R5L_NR];
