@@ -60,6 +60,13 @@ k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64
     const int64_t m_end = min(blk_end, m_begin + per);
     const bool active = mtile < mtiles && m_begin < m_end;
     if (active) {
+        // two-level accumulation: the MMA accumulators take 256 samples, then go into a second set — a running fp32 sum over
+        // the CTA's thousands of samples loses ~sqrt(n) ulp (seen as 2.6e-5 of the largest entry between two partitions of
+        // the same 2.6x10^6-sample batch), 256-sample blocks summed in a second level lose a tenth of that
+        float blk[8][4];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) blk[nt][0] = blk[nt][1] = blk[nt][2] = blk[nt][3] = 0.0f;
+        int in_blk = 0;
         WgFrag cur, nxt;
         wg_load(cur, dY, X, m_begin, m_end, n_out, n_in, o0, g, t, ntiles);
         for (int64_t m0 = m_begin; m0 < m_end; m0 += 8) {
@@ -69,9 +76,23 @@ k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64
             for (int c = 0; c < 4; ++c) fq_split(cur.a[c], ahi[c], alo[c]);
 #pragma unroll
             for (int nt = 0; nt < 8; ++nt)
-                if (nt < ntiles) fq_mma3(acc[nt], ahi, alo, fq_split_pair(cur.b[nt][0], cur.b[nt][1]));
+                if (nt < ntiles) fq_mma3(blk[nt], ahi, alo, fq_split_pair(cur.b[nt][0], cur.b[nt][1]));
             cur = nxt;
+            if (++in_blk == 32) {
+                in_blk = 0;
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        acc[nt][c] = __fadd_rn(acc[nt][c], blk[nt][c]);
+                        blk[nt][c] = 0.0f;
+                    }
+            }
         }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[nt][c] = __fadd_rn(acc[nt][c], blk[nt][c]);
     }
     if (ksplit > 1) {   // add the sample slices of a tile in warp order
 #pragma unroll
@@ -104,9 +125,9 @@ k_wgrad_reduce(const float *__restrict__ partials, int nblocks, int n_out, int n
     const int e = blockIdx.x * 256 + threadIdx.x;
     if (e >= n_out * n_in) return;
     const int o = e / n_in, i = e - o * n_in;
-    float s = 0.0f;
-    for (int b = 0; b < nblocks; ++b) s = __fadd_rn(s, partials[(int64_t)b * WG_MAXN * WG_MAXN + o * WG_MAXN + i]);
-    dW[e] = s;
+    double s = 0.0;   // the partials of up to 592 CTAs: summed in CTA order in double, rounded once
+    for (int b = 0; b < nblocks; ++b) s += (double)partials[(int64_t)b * WG_MAXN * WG_MAXN + o * WG_MAXN + i];
+    dW[e] = (float)s;
 }
 
 static int wg_blocks(int64_t M) {

@@ -57,14 +57,17 @@ def parity(dev, rays, rank, world, steps=3):
     model_s, opt_s = setup(dev, rays, rank)[:2]
     ro, rd, target = (torch.cat([s[i] for s in shards]) for i in range(3))
     my = shards[rank]
-    grad_rel = 0.0
+    grad_rel, grad_rel_by = 0.0, {}
+    names = [n for n, p_ in model_d.named_parameters() if p_.requires_grad]
     for it in range(steps):
         training.train_step(model_d, opt_d, my[0], my[1], my[2], world=world, **kw)
         training.train_step(model_s, opt_s, ro, rd, target, world=1, **kw)
         if it == 0:
-            for a, b in zip(training.trainable(model_d), training.trainable(model_s)):
+            for i, (a, b) in enumerate(zip(training.trainable(model_d), training.trainable(model_s))):
                 ga, gb = a.grad / world, b.grad
-                grad_rel = max(grad_rel, float((ga - gb).abs().max() / gb.abs().max().clamp_min(1e-30)))
+                e = float((ga - gb).abs().max() / gb.abs().max().clamp_min(1e-30))
+                grad_rel_by[names[i] if i < len(names) else str(i)] = e
+                grad_rel = max(grad_rel, e)
     worst, inside, total = 0.0, 0, 0
     for a, b in zip(training.trainable(model_d), training.trainable(model_s)):
         d = (a.detach() - b.detach()).abs() / b.detach().abs().max().clamp_min(1e-30)
@@ -75,7 +78,8 @@ def parity(dev, rays, rank, world, steps=3):
         t = torch.tensor([1.0 if ok else 0.0], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         ok = bool(t.item() > 0)
-    return {"train_parity": ok, "reduced_gradient_rel_err": grad_rel, "params_within_1e-5": inside / total,
+    return {"train_parity": ok, "reduced_gradient_rel_err": grad_rel, "reduced_gradient_rel_err_by_tensor": grad_rel_by,
+            "params_within_1e-5": inside / total,
             "params_worst_rel_diff": worst, "steps": steps, "rays": world * rays,
             "what": "rank-mean gradients / post-step parameters vs a single-process run on the concatenated batch"}
 
