@@ -10,6 +10,9 @@
 
 #define WG_THREADS 128
 #define WG_MAXN 64
+#ifndef WG_TWO_LEVEL
+#define WG_TWO_LEVEL 1
+#endif
 
 // One k8-step worth of operands in MMA fragment order.
 struct WgFrag {
@@ -44,6 +47,7 @@ __global__ void __launch_bounds__(WG_THREADS)
 k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64_t M, int n_out, int n_in,
                 int64_t rows_per_block, float *__restrict__ partials) {
     __shared__ float red[WG_THREADS / 32][8][4][32];
+    __shared__ float lvl2[WG_THREADS / 32][8][4][32];   // second accumulation level, private to its thread
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     const int mtiles = (n_out + 15) >> 4;                 // 1..4
     const int ksplit = mtiles == 1 ? 4 : (mtiles == 2 ? 2 : 1);
@@ -60,12 +64,14 @@ k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64
     const int64_t m_end = min(blk_end, m_begin + per);
     const bool active = mtile < mtiles && m_begin < m_end;
     if (active) {
-        // two-level accumulation: the MMA accumulators take 256 samples, then go into a second set — a running fp32 sum over
-        // the CTA's thousands of samples loses ~sqrt(n) ulp (seen as 2.6e-5 of the largest entry between two partitions of
-        // the same 2.6x10^6-sample batch), 256-sample blocks summed in a second level lose a tenth of that
-        float blk[8][4];
+        // two-level accumulation: the MMA accumulators take 256 samples, then go into a second level kept in shared
+        // memory (no extra registers) — a running fp32 sum over the CTA's thousands of samples loses ~sqrt(n) ulp (seen as
+        // 2.6e-5 of the largest entry between two partitions of the same 2.6x10^6-sample batch), 256-sample blocks summed
+        // in a second level lose a hundredth of that (7e-8)
 #pragma unroll
-        for (int nt = 0; nt < 8; ++nt) blk[nt][0] = blk[nt][1] = blk[nt][2] = blk[nt][3] = 0.0f;
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) lvl2[warp][nt][c][lane] = 0.0f;
         int in_blk = 0;
         WgFrag cur, nxt;
         wg_load(cur, dY, X, m_begin, m_end, n_out, n_in, o0, g, t, ntiles);
@@ -76,23 +82,23 @@ k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64
             for (int c = 0; c < 4; ++c) fq_split(cur.a[c], ahi[c], alo[c]);
 #pragma unroll
             for (int nt = 0; nt < 8; ++nt)
-                if (nt < ntiles) fq_mma3(blk[nt], ahi, alo, fq_split_pair(cur.b[nt][0], cur.b[nt][1]));
+                if (nt < ntiles) fq_mma3(acc[nt], ahi, alo, fq_split_pair(cur.b[nt][0], cur.b[nt][1]));
             cur = nxt;
-            if (++in_blk == 32) {
+            if (WG_TWO_LEVEL && ++in_blk == 32) {
                 in_blk = 0;
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
-                        acc[nt][c] = __fadd_rn(acc[nt][c], blk[nt][c]);
-                        blk[nt][c] = 0.0f;
+                        lvl2[warp][nt][c][lane] = __fadd_rn(lvl2[warp][nt][c][lane], acc[nt][c]);
+                        acc[nt][c] = 0.0f;
                     }
             }
         }
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
-            for (int c = 0; c < 4; ++c) acc[nt][c] = __fadd_rn(acc[nt][c], blk[nt][c]);
+            for (int c = 0; c < 4; ++c) acc[nt][c] = __fadd_rn(lvl2[warp][nt][c][lane], acc[nt][c]);
     }
     if (ksplit > 1) {   // add the sample slices of a tile in warp order
 #pragma unroll
@@ -120,14 +126,25 @@ k_wgrad_partial(const float *__restrict__ dY, const float *__restrict__ X, int64
     }
 }
 
+// dW[e] = sum over the CTAs' partials, in double, in a fixed order: 8 lanes per output element take the partials
+// b = j, j + 8, ... each, then the 8 sub-sums are added in lane order (deterministic; 8x shorter dependent chains than one
+// thread per element: 20 -> ~5 us per layer)
 __global__ void __launch_bounds__(256)
 k_wgrad_reduce(const float *__restrict__ partials, int nblocks, int n_out, int n_in, float *__restrict__ dW) {
-    const int e = blockIdx.x * 256 + threadIdx.x;
-    if (e >= n_out * n_in) return;
-    const int o = e / n_in, i = e - o * n_in;
-    double s = 0.0;   // the partials of up to 592 CTAs: summed in CTA order in double, rounded once
-    for (int b = 0; b < nblocks; ++b) s += (double)partials[(int64_t)b * WG_MAXN * WG_MAXN + o * WG_MAXN + i];
-    dW[e] = (float)s;
+    const int e = blockIdx.x * 32 + (threadIdx.x >> 3), j = threadIdx.x & 7;
+    const bool in = e < n_out * n_in;
+    const int o = in ? e / n_in : 0, i = in ? e - o * n_in : 0;
+    double s = 0.0;
+    if (in)
+        for (int b = j; b < nblocks; b += 8) s += (double)__ldg(partials + (int64_t)b * WG_MAXN * WG_MAXN + o * WG_MAXN + i);
+    // ordered sum of the 8 sub-sums: lane 0 of the group adds them 0, 1, ..., 7
+    double tot = s;
+#pragma unroll
+    for (int k = 1; k < 8; ++k) {
+        const double v = __shfl_down_sync(0xffffffffu, s, k, 8);
+        tot += v;
+    }
+    if (in && j == 0) dW[e] = (float)tot;
 }
 
 static int wg_blocks(int64_t M) {
@@ -161,7 +178,7 @@ extern "C" int ngp_linear_wgrad(const float *dY, const float *X, float *dW, int6
     rows = ngp_div_up(rows, 8) * 8;
     k_wgrad_partial<<<blocks, WG_THREADS, 0, st>>>(dY, X, M, n_out, n_in, rows, (float *)workspace);
     NGP_CHECK_LAUNCH("ngp_linear_wgrad(partial)");
-    k_wgrad_reduce<<<(n_out * n_in + 255) / 256, 256, 0, st>>>((const float *)workspace, blocks, n_out, n_in, dW);
+    k_wgrad_reduce<<<(n_out * n_in + 31) / 32, 256, 0, st>>>((const float *)workspace, blocks, n_out, n_in, dW);
     NGP_CHECK_LAUNCH("ngp_linear_wgrad(reduce)");
     return NGP_OK;
 }
@@ -222,7 +239,7 @@ extern "C" int ngp_linear_wgrad_static(const float *dY, const float *X, float *d
     rows = ngp_div_up(rows, 8) * 8;
     k_wgrad_partial<<<blocks, WG_THREADS, 0, st>>>(dY, X, M, n_out, n_in, rows, scratch);
     NGP_CHECK_LAUNCH("ngp_linear_wgrad_static(partial)");
-    k_wgrad_reduce<<<(n_out * n_in + 255) / 256, 256, 0, st>>>(scratch, blocks, n_out, n_in, dW);
+    k_wgrad_reduce<<<(n_out * n_in + 31) / 32, 256, 0, st>>>(scratch, blocks, n_out, n_in, dW);
     NGP_CHECK_LAUNCH("ngp_linear_wgrad_static(reduce)");
     return NGP_OK;
 }
