@@ -892,10 +892,10 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
         R5_STAT_ADD(20, E);
         const int b = (int)(n & (R5SmemL::TBUF - 1));
         if (build && n >= R5SmemL::TBUF) {
-            uint32_t ok = 0;
-            if (lane == 0) ok = tc5::mbar_try(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> R5L_TBUF_LOG2) - 1) & 1));
-            build = __shfl_sync(0xffffffffu, ok, 0) != 0u;
-            if (!build) R5_STAT_ADD(16, 1);
+            // the rows are ready, the buffer is what is missing: block on its barrier (the eligible slots stay eligible —
+            // in-flight counts only fall meanwhile) instead of polling pass after pass in the other roles' issue slots
+            if (lane == 0) R5_WAIT(tc5::smem_u32(&S.tb.rows_free[b]), (uint32_t)(((n >> R5L_TBUF_LOG2) - 1) & 1), 16);
+            __syncwarp();
         }
         if (build) {
             R5Tile &T = S.tile[b];
@@ -948,7 +948,7 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
                 }
             }
         } else {
-            __nanosleep(100);   // rays are in flight or the row buffer is busy: leave the issue slots to the other roles
+            __nanosleep(400);   // too few eligible rays: they come back a tile at a time (several us); leave the issue slots to the others
         }
         if (ended) break;
         __syncwarp();

@@ -46,5 +46,18 @@ for _ in range(2):
     ngp.check(L.ngp_ffmlp_forward(xh.data_ptr(), w.data_ptr(), B, ind, 16, 64, n, 0, 6, fwd.data_ptr(), outp.data_ptr(), st))
     ngp.check(L.ngp_ffmlp_backward(grad.data_ptr(), xh.data_ptr(), w.data_ptr(), fwd.data_ptr(), B, ind, 16, 64, n, 0, 6, 1, None,
                                    gx.data_ptr(), gw.data_ptr(), wsp.data_ptr(), wsb, st))
+# network_ff.density through the fused encode -> FFMLP kernel, and two training steps (fixed-point table gradient, warp-per-ray
+# compositing backward, two-level weight gradient)
+sys.path.insert(0, os.path.join(ROOT, "scripts"))
+from nerf_navigation_b200.nerf.network_ff import NeRFNetwork as NetFF
+mff = NetFF(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+pts = torch.rand(1 << 22, 3, device=dev) * 2 - 1
+with torch.no_grad():
+    for _ in range(2):
+        mff.density(pts)
+import bench_train as BT
+tm, opt, tro, trd, tgt = BT.setup(dev, 4096)
+for _ in range(2):
+    BT.step(tm, opt, tro, trd, tgt, 1)
 torch.cuda.synchronize()
 print("ok", int(out[3][1]), float(xa.grad.abs().sum()))
