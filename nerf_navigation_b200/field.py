@@ -11,11 +11,13 @@ from . import _lib
 
 
 def fused_supported(encoder, W0, W1, x):
-    """The fused kernels cover the configuration nerf-navigation uses: 3-D, 16 levels x 2 features, fp32,
-    sigma net 32 -> 64 -> 16 (network.py:33-47)."""
+    """The fused kernels cover the configuration nerf-navigation uses: 3-D, 16 levels x 2 features, fp32 table,
+    sigma net 32 -> 64 -> 16 (network.py:33-47).  Inside an autocast region they still run (in fp32: the kernels take fp32
+    pointers and autocast does not touch custom Functions); the callers cast geo_feat / rgb to the autocast dtype, which is
+    what the reference's half Linear layers return there (sigma stays fp32: activation.py:7 casts trunc_exp's input)."""
     return (encoder.input_dim == 3 and encoder.num_levels == 16 and encoder.level_dim == 2
             and encoder.embeddings.dtype == torch.float32 and tuple(W0.shape) == (64, 32)
-            and tuple(W1.shape) == (16, 64) and x.dtype == torch.float32 and not torch.is_autocast_enabled())
+            and tuple(W1.shape) == (16, 64) and x.dtype == torch.float32)
 
 
 class _field_query(Function):

@@ -85,6 +85,8 @@ class NeRFNetwork(NeRFRenderer):
                 self._warn_eval_params()
             sigma, geo_feat = field_query(x, self.encoder, self.sigma_net[0].weight.detach(),
                                           self.sigma_net[1].weight.detach(), self.bound)
+            if torch.is_autocast_enabled():   # the reference's half sigma_net output there (sigma is fp32 either way)
+                geo_feat = geo_feat.to(torch.get_autocast_dtype("cuda"))
             return {"sigma": sigma, "geo_feat": geo_feat}
         h = self._sigma_mlp(self.encoder(x, bound=self.bound))
         return {"sigma": trunc_exp(h[..., 0]), "geo_feat": h[..., 1:]}
@@ -110,7 +112,10 @@ class NeRFNetwork(NeRFRenderer):
                 and fused_color_supported(self, x, d)):
             if x.requires_grad or d.requires_grad:
                 self._warn_eval_params()
-            return field_color(self, x, d)
+            sigma, rgb = field_color(self, x, d)
+            if torch.is_autocast_enabled():
+                rgb = rgb.to(torch.get_autocast_dtype("cuda"))
+            return sigma, rgb
         dens = self.density(x)
         return dens["sigma"], self._color_mlp(d, dens["geo_feat"])
 

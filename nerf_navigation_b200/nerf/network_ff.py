@@ -53,8 +53,7 @@ class NeRFNetwork(NeRFRenderer):
         if not (self.fused_eval and x.is_cuda and x.dtype == torch.float32 and hasattr(enc, "embeddings")
                 and not (torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())))
                 and enc.input_dim == 3 and enc.num_levels == 16 and enc.level_dim == 2 and enc.embeddings.dtype == torch.float32
-                and net.input_dim == 32 and net.hidden_dim == 64 and net.padded_output_dim == 16 and net.activation in (0, 6)
-                and not torch.is_autocast_enabled()):
+                and net.input_dim == 32 and net.hidden_dim == 64 and net.padded_output_dim == 16 and net.activation in (0, 6)):
             return None
         x = x.contiguous()
         B = x.shape[0]

@@ -428,3 +428,44 @@ def test_single_pass_density_closure(model):
     assert torch.equal(outs[0][0], outs[1][0])
     assert rel_err(outs[0][1].cpu().numpy(), outs[1][1].cpu().numpy()) < 1e-5
     assert abs(outs[0][2] - outs[1][2]) <= 1e-6 * abs(outs[1][2])
+
+
+def test_fused_kernels_serve_autocast_regions():
+    """Inside torch.autocast (the reference Trainer's fp16 eval) the fused kernels still run — in fp32, more accurate than
+    the half GridEncoder + half Linear path they replace — and return the dtypes that path returns: sigma fp32
+    (activation.py:7), geo_feat / rgb in the autocast dtype.  Values against the unfused autocast path at the fp16 bar."""
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    from nerf_navigation_b200.nerf.network_ff import NeRFNetwork as NetFF
+    torch.manual_seed(3)
+    x = torch.rand(20000, 3, device="cuda") * 2 - 1
+    d = torch.nn.functional.normalize(torch.randn(20000, 3, device="cuda"), dim=-1)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    outs = {}
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.float16):
+        for fused in (True, False):
+            m.fused_eval = fused
+            dens = m.density(x)
+            sigma, rgb = m(x, d)
+            outs[fused] = (dens["sigma"], dens["geo_feat"], sigma, rgb)
+    for a, b in zip(outs[True], outs[False]):
+        assert a.dtype == b.dtype and a.shape == b.shape
+        assert rel_err(a.float().cpu().numpy(), b.float().cpu().numpy()) < 5e-3
+    assert outs[True][0].dtype == torch.float32 and outs[True][1].dtype == torch.float16 and outs[True][3].dtype == torch.float16
+    # and against the fp32 result (what autocast approximates): the fused path is the closer of the two
+    with torch.no_grad():
+        m.fused_eval = True
+        ref = m.density(x)["geo_feat"]
+    e_f = rel_err(outs[True][1].float().cpu().numpy(), ref.cpu().numpy())
+    e_u = rel_err(outs[False][1].float().cpu().numpy(), ref.cpu().numpy())
+    assert e_f <= e_u + 1e-6 and e_f < 1e-3
+    mf = NetFF(encoding="hashgrid", bound=2, cuda_ray=False).cuda().eval()
+    mf.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.float16):
+        mf.fused_eval = True
+        a = mf.density(x)
+        mf.fused_eval = False
+        b = mf.density(x)
+    assert a["sigma"].dtype == b["sigma"].dtype and a["geo_feat"].dtype == b["geo_feat"].dtype
+    assert rel_err(a["sigma"].float().cpu().numpy(), b["sigma"].float().cpu().numpy()) < 5e-3
+    assert rel_err(a["geo_feat"].float().cpu().numpy(), b["geo_feat"].float().cpu().numpy()) < 5e-3
