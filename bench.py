@@ -653,7 +653,7 @@ def run_b200(args):
              KF: B * BYTES_PER_POINT_PASS / (fwd_ms / 1e3) / 1e9 / gather_peak,
              KB: B * BYTES_PER_POINT_PASS / (bwd_ms / 1e3) / 1e9 / gather_peak}
     if not args.no_render and t_ren > 0:
-        fracs["render step (k_r5_premarch x2 + k_render5_rays_infer_lists)"] = ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak
+        fracs["render step (k_r5_premarch + k_render5_rays_infer_lists)"] = ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak
     if not args.no_estimator:
         fracs["estimator step (k_cfield5_forward + k_cfield5_backward + marcher / compositor)"] = \
             args.hypotheses * 4096 * est_spr * 2 * BYTES_PER_POINT_PASS / t_est / 1e9 / world / gather_peak
@@ -736,10 +736,11 @@ def run_b200(args):
             "ms_per_frame": t_ren * 1e3 / args.frames, "frames_per_s": args.frames / t_ren, "rays_per_s": nrays / t_ren,
             "samples": ren_samples, "samples_per_ray": ren_samples / nrays, "samples_per_s": ren_samples / t_ren,
             "scaling": "strong", "sharding": "frames by rank, replicated field + bitfield, no collective",
-            "path": "field.render_rays_infer: ngp_render_plan (thread-per-ray marching pre-pass: count + scan; one host read of the "
-                    "total) -> ngp_render_rays_infer_planned (pre-pass: write the (t, dt) lists; then near/far + field + colour + "
-                    "composite + post in one persistent warp-specialised tcgen05 kernel, csrc/render5.cu); the whole call is timed",
-            "gpu_launches": 4 * args.render_steps * ((ren_frames + args.frames_per_step - 1) // args.frames_per_step),
+            "path": "field.render_rays_infer -> ngp_render_rays_infer_segments: thread-per-ray marching pre-pass at full occupancy "
+                    "(records each ray's runs of samples), then near/far + field + colour + composite + post in one persistent "
+                    "warp-specialised tcgen05 kernel whose feeder warps replay the runs (csrc/render5.cu), then the marcher-inside "
+                    "kernel for rays with more than 32 runs (none here); no host read; the whole call is timed",
+            "gpu_launches": 3 * args.render_steps * ((ren_frames + args.frames_per_step - 1) // args.frames_per_step),
             "l2_gather": {"achieved": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world, "peak": gather_peak,
                           "unit": "GB/s useful per GPU",
                           "frac": ren_samples * BYTES_PER_POINT_PASS / t_ren / 1e9 / world / gather_peak}}

@@ -276,6 +276,24 @@ int ngp_render_rays_infer_planned(const float *rays_o, const float *rays_d, int6
                                   int32_t *counts, const int32_t *plan_counts, const int64_t *plan_ends, float *samples,
                                   int64_t samples_capacity, void *workspace, ngp_stream_t stream);
 
+/* The pre-marched renderer as ONE call without a host read: the pre-pass marches every ray once and records its RUNS of
+ * consecutive samples, (first t, number of samples), at most seg_cap per ray — inside a run the marcher's recurrence is
+ * t += dt(t), which the persistent kernel's feeder warps replay, so a run is all they need (8 bytes per run instead of per
+ * sample, no count pass, no scan, no sizing by the host).  A ray with more than seg_cap runs (their number is known on
+ * the device only) is rendered by the marcher-inside kernel over an overflow list in the same call.  Same samples, outputs
+ * and per-ray counts as ngp_render_rays_infer.  workspace: ngp_render_rays_infer_segments_workspace_bytes(N, seg_cap)
+ * = 512 + 8 N + 8 N seg_cap bytes, 8-byte aligned; after the call its second u64 holds the number of samples evaluated and
+ * u64[26] the number of overflow rays.  seg_cap in 1..1024 (32 covers the occupancy grids of trained scenes). */
+int64_t ngp_render_rays_infer_segments_workspace_bytes(int64_t N, int seg_cap);
+int ngp_render_rays_infer_segments(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                                   const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                                   uint32_t Hgrid, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                                   uint32_t gridtype, int align_corners, const float *Ws0, const float *Ws1,
+                                   const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
+                                   const float *bg_color, int bg_stride, float *image, float *depth, float *weights_sum,
+                                   int32_t *counts, int seg_cap, void *workspace, int64_t workspace_bytes,
+                                   ngp_stream_t stream);
+
 /* ---- training-step tail: torch.optim.Adam(betas=(0.9, 0.99), eps=1e-15) (main_nerf.py:126) + EMA (nerf/utils.py:814) - */
 
 /* One fused pass over a parameter tensor: g *= grad_scale (all-reduce mean), Adam moments and update with torch's

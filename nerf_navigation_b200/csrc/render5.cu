@@ -153,6 +153,17 @@ struct R5Params {
     const int32_t *plan_counts;
     const long long *plan_ends;
     const float2 *tdt;
+    // pre-marched SEGMENTS (k_render5_rays_infer_lists<true>): ray i has nsegs[i] runs of consecutive samples, run k =
+    // (first t, number of samples as int bits) at segs[i * seg_cap + k]; nsegs[i] < 0: more than seg_cap runs, the ray is
+    // rendered by the marcher-inside kernel from ray_list instead
+    const float2 *segs;
+    const int32_t *nsegs;
+    int seg_cap;
+    float dt_min, dt_max, dt_gamma;
+    int lvl_dt;
+    // marcher-inside kernel on a subset: ray indices ray_list[0 .. *ray_list_count) instead of 0 .. N
+    const int32_t *ray_list;
+    const unsigned long long *ray_list_count;
 };
 
 __device__ __forceinline__ uint32_t r5_ld_status(const uint32_t *p) { return *(const volatile uint32_t *)p; }
@@ -243,12 +254,13 @@ __device__ __forceinline__ void r5_marcher(R5Smem &S, const R5Params &P, const M
             if (lane == 31) base = atomicAdd(P.counter, (unsigned long long)total);
             base = __shfl_sync(0xffffffffu, base, 31);
             int64_t nid = (int64_t)base + pre - mine;
+            const int64_t n_rays = P.ray_list ? (int64_t)*P.ray_list_count : P.N;
             while (needs) {
                 const int j = __ffs(needs) - 1;
                 needs &= needs - 1u;
                 const int slot = slot0 + 32 * j;
-                if (nid < P.N) {
-                    r5_load_ray(R, P, slot, nid);
+                if (nid < n_rays) {
+                    r5_load_ray(R, P, slot, P.ray_list ? (int64_t)__ldg(P.ray_list + nid) : nid);
                     ++nid;
                 } else {
                     R.id[slot] = -2;
@@ -745,8 +757,8 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
 // (R5_STATS: 2.7 marcher passes of 8,800 cycles per 15 tile rows; gather warps 37 %, chain warps 43 % of their time
 // waiting).  Here the marching moves OUT of the persistent kernel into a thread-per-ray pre-pass at full occupancy
 // (k_r5_premarch: the same cell / exit arithmetic, so the same samples bit for bit) that leaves every ray's (t, dt) list in
-// global memory — a count pass, an inclusive scan, a write pass — and the persistent kernel's 8 "feeder" warps only hand
-// list entries to tiles: classify the slots, retire / refill rays, ballot-compact the eligible ones into rows.  Early
+// global memory — a count pass, an inclusive scan, a write pass; or, in the single-call form further down, one pass that
+// records each ray's RUNS of samples — and the persistent kernel's 8 "feeder" warps only hand list entries to tiles: classify the slots, retire / refill rays, ballot-compact the eligible ones into rows.  Early
 // termination stays exact (samples after a ray's end are never evaluated; only their marching is wasted), per-ray counts
 // stay the oracle's.  The ray store shrinks (no sample FIFOs, no reciprocal directions, 512 slots): 162 KB of shared memory
 // instead of 219 KB, which gives the gathers L1 back (dfield5.cu: the carve-out is part of the roofline).  Measured on one
@@ -764,8 +776,11 @@ struct R5RaysL {
     float ox[R5L_NR], oy[R5L_NR], oz[R5L_NR], dx[R5L_NR], dy[R5L_NR], dz[R5L_NR];
     float near[R5L_NR], far[R5L_NR];
     int id[R5L_NR];                                  // ray index; -1: slot wants a ray; -2: no rays left
-    uint32_t cursor[R5L_NR], count[R5L_NR];          // samples handed to tiles so far / in the ray's list
-    long long off[R5L_NR];                           // first list entry of the ray
+    uint32_t cursor[R5L_NR], count[R5L_NR];          // lists: samples handed to tiles so far / in the ray's list
+                                                     // segments: runs opened so far / runs of the ray
+    long long off[R5L_NR];                           // first list entry / first segment of the ray
+    uint32_t rem[R5L_NR];                            // segments: samples left in the open run
+    float tcur[R5L_NR];                              // segments: t of the run's next sample
     float ws[R5L_NR], depth[R5L_NR], r[R5L_NR], g[R5L_NR], b[R5L_NR];
     uint32_t ncomp[R5L_NR];
     uint32_t status[R5L_NR];
@@ -784,6 +799,7 @@ struct __align__(128) R5SmemL {
     R5RaysL rays;
 };
 
+template <bool SEG>
 static __device__ __noinline__ void r5l_load_ray(R5RaysL &R, const R5Params &P, int slot, int64_t nid) {
     const float o[3] = {__ldg(P.rays_o + nid * 3), __ldg(P.rays_o + nid * 3 + 1), __ldg(P.rays_o + nid * 3 + 2)};
     const float d[3] = {__ldg(P.rays_d + nid * 3), __ldg(P.rays_d + nid * 3 + 1), __ldg(P.rays_d + nid * 3 + 2)};
@@ -794,15 +810,23 @@ static __device__ __noinline__ void r5l_load_ray(R5RaysL &R, const R5Params &P, 
     R.near[slot] = near; R.far[slot] = far;
     R.ws[slot] = 0.0f; R.depth[slot] = 0.0f; R.r[slot] = 0.0f; R.g[slot] = 0.0f; R.b[slot] = 0.0f;
     R.ncomp[slot] = 0u;
-    const uint32_t cnt = (uint32_t)__ldg(P.plan_counts + nid);
-    R.count[slot] = cnt;
     R.cursor[slot] = 0u;
-    R.off[slot] = __ldg(P.plan_ends + nid) - (long long)cnt;
+    if (SEG) {
+        const int ns = __ldg(P.nsegs + nid);
+        R.count[slot] = ns < 0 ? 0xffffffffu : (uint32_t)ns;   // 0xffffffff: not this kernel's ray (see r5l_feeder)
+        R.off[slot] = (long long)nid * P.seg_cap;
+        R.rem[slot] = 0u;
+    } else {
+        const uint32_t cnt = (uint32_t)__ldg(P.plan_counts + nid);
+        R.count[slot] = cnt;
+        R.off[slot] = __ldg(P.plan_ends + nid) - (long long)cnt;
+    }
     R.id[slot] = (int)nid;
 }
 
 // One pass of a feeder warp over its R5L_PER_WARP slots: classify (eligible / finished / waiting), retire and refill,
 // build the warp's R5_PART rows of tile n from the eligible slots' next list entries.
+template <bool SEG>
 __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w, int lane) {
     R5RaysL &R = S.rays;
     const int slot0 = w * R5L_PER_WARP + lane;
@@ -843,7 +867,7 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
                 needs &= needs - 1u;
                 const int slot = slot0 + 32 * j;
                 if (nid < P.N) {
-                    r5l_load_ray(R, P, slot, nid);
+                    r5l_load_ray<SEG>(R, P, slot, nid);
                     ++nid;
                 } else {
                     R.id[slot] = -2;
@@ -859,7 +883,10 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
             const int slot = slot0 + 32 * j;
             if (R.id[slot] < 0) continue;
             const uint32_t st = r5_ld_status(&R.status[slot]);
-            const bool dead = (st & R5_DEAD) != 0u, more = R.cursor[slot] < R.count[slot];
+            const uint32_t rcount = R.count[slot];
+            const bool foreign = SEG && rcount == 0xffffffffu;   // too many runs: the marcher-inside kernel renders this ray
+            const bool dead = (st & R5_DEAD) != 0u;
+            const bool more = !foreign && (R.cursor[slot] < rcount || (SEG && R.rem[slot] > 0u));
             const uint32_t fly = R5_NFLY(st);
             if (!dead && more && fly < R5_INFLIGHT) elig |= 1u << j;
             else if (fly == 0u && (dead || !more)) retire |= 1u << j;
@@ -872,7 +899,7 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
             retire &= retire - 1u;
             const int slot = slot0 + 32 * j;
             __threadfence_block();         // the chain thread wrote the accumulators before the status
-            r5_finish(R, P, slot, R.id[slot]);
+            if (!(SEG && R.count[slot] == 0xffffffffu)) r5_finish(R, P, slot, R.id[slot]);
             evaluated += R.ncomp[slot];
             if (rays_left) {
                 R.id[slot] = -1;
@@ -909,10 +936,27 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
                 const int row = nrows + __popc(m & lt_mask);
                 if (e && row < R5_PART) {
                     const int slot = slot0 + 32 * j;
-                    const uint32_t cur = R.cursor[slot];
-                    const float2 sm = __ldg(P.tdt + R.off[slot] + cur);
-                    R.cursor[slot] = cur + 1u;
-                    const float st = sm.x, sdt = sm.y;
+                    float st, sdt;
+                    if (SEG) {
+                        uint32_t rem = R.rem[slot];
+                        float tc = R.tcur[slot];
+                        if (rem == 0u) {   // open the ray's next run
+                            const uint32_t cur = R.cursor[slot];
+                            const float2 sg = __ldg(P.segs + R.off[slot] + cur);
+                            R.cursor[slot] = cur + 1u;
+                            tc = sg.x;
+                            rem = (uint32_t)__float_as_int(sg.y);
+                        }
+                        st = tc;   // the marcher's recurrence inside a run: t += dt(t)
+                        sdt = P.lvl_dt >= 0 ? P.dt_min : ngp_clampf(tc * P.dt_gamma, P.dt_min, P.dt_max);
+                        R.tcur[slot] = tc + sdt;
+                        R.rem[slot] = rem - 1u;
+                    } else {
+                        const uint32_t cur = R.cursor[slot];
+                        const float2 sm = __ldg(P.tdt + R.off[slot] + cur);
+                        R.cursor[slot] = cur + 1u;
+                        st = sm.x; sdt = sm.y;
+                    }
                     const float dxv = R.dx[slot], dyv = R.dy[slot], dzv = R.dz[slot];
                     const int tr = w * R5_PART + row;
                     T.x[tr] = ngp_clampf(fmaf(st, dxv, R.ox[slot]), -P.bound, P.bound);   // = the marcher's sample position
@@ -963,12 +1007,15 @@ __device__ __forceinline__ void r5l_feeder(R5SmemL &S, const R5Params &P, int w,
 }
 
 // Thread-per-ray marcher of the pre-pass: r5_marcher's sequence exactly (same cell / exit functions, same end tests).
-// WRITE = false: counts[i] = number of samples; WRITE = true: the samples go to tdt[ends[i] - counts[i] ...].
-template <bool WRITE>
+// MODE 0: counts[i] = number of samples.  MODE 1: the samples go to tdt[ends[i] - counts[i] ...].
+// MODE 2: the RUNS of consecutive samples go to segs[i * seg_cap ...] as (t of the first sample, number of samples): inside
+// a run the marcher's recurrence is t += dt(t), which the feeder replays, so a run is all it needs; a ray with more than
+// seg_cap runs gets nsegs[i] = -1 and its index is appended to ovf_list (rendered by the marcher-inside kernel).
+template <int MODE>
 __global__ void __launch_bounds__(256)
 k_r5_premarch(const float *__restrict__ rays_o, const float *__restrict__ rays_d, int64_t N, const float *__restrict__ aabb,
               float min_near, MarchCfg cfg, uint32_t max_steps, int32_t *__restrict__ counts, const long long *__restrict__ ends,
-              float2 *__restrict__ tdt) {
+              float2 *__restrict__ tdt, int seg_cap, int32_t *__restrict__ ovf_list, unsigned long long *__restrict__ ovf_count) {
     __shared__ float mipb[8], miprb[8];
     if (threadIdx.x < 8) {
         mipb[threadIdx.x] = fminf((float)(1 << threadIdx.x), cfg.bound);
@@ -985,9 +1032,14 @@ k_r5_premarch(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     r.ox = o[0]; r.oy = o[1]; r.oz = o[2]; r.dx = d[0]; r.dy = d[1]; r.dz = d[2];
     r.rdx = 1.0f / d[0]; r.rdy = 1.0f / d[1]; r.rdz = 1.0f / d[2];
     float2 *out = nullptr;
-    if (WRITE) out = tdt + (ends[i] - (long long)counts[i]);
+    if (MODE == 1) out = tdt + (ends[i] - (long long)counts[i]);
+    if (MODE == 2) out = tdt + i * seg_cap;
     float t = near;
     uint32_t marched = 0;
+    int nseg = 0;               // MODE 2: runs closed so far, the open run (run_n > 0) and whether the ray ran out of room
+    float run_t0 = 0.0f;
+    uint32_t run_n = 0;
+    bool overflow = false;
 #pragma unroll 1
     while (t < far && marched < max_steps) {   // raymarching.cu:730
         float dt;
@@ -997,10 +1049,24 @@ k_r5_premarch(const float *__restrict__ rays_o, const float *__restrict__ rays_d
         const uint32_t byte = (uint32_t)__ldg(cfg.grid + (cell >> 3));
         if ((byte >> (cell & 7u)) & 1u) {
             const float sdt = cfg.lvl_dt >= 0 ? cfg.dt_min : ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
-            if (WRITE) out[marched] = make_float2(t, sdt);
+            if (MODE == 1) out[marched] = make_float2(t, sdt);
+            if (MODE == 2) {
+                if (run_n == 0) {
+                    if (nseg == seg_cap) {
+                        overflow = true;
+                        break;
+                    }
+                    run_t0 = t;
+                }
+                ++run_n;
+            }
             t += sdt;
             ++marched;
         } else {
+            if (MODE == 2 && run_n > 0) {
+                out[nseg++] = make_float2(run_t0, __int_as_float((int)run_n));
+                run_n = 0;
+            }
             const float tt = ngp_march_exit_fast(r, cfg, mipb, t, nxyz, lvl);
             if (cfg.lvl_dt >= 0) {
                 do {
@@ -1013,9 +1079,19 @@ k_r5_premarch(const float *__restrict__ rays_o, const float *__restrict__ rays_d
             }
         }
     }
-    if (!WRITE) counts[i] = (int32_t)marched;
+    if (MODE == 0) counts[i] = (int32_t)marched;
+    if (MODE == 2) {
+        if (overflow) {
+            counts[i] = -1;
+            ovf_list[atomicAdd(ovf_count, 1ull)] = (int32_t)i;
+        } else {
+            if (run_n > 0) out[nseg++] = make_float2(run_t0, __int_as_float((int)run_n));
+            counts[i] = nseg;
+        }
+    }
 }
 
+template <bool SEG>
 __global__ void __launch_bounds__(R5_THREADS, 1)
 k_render5_rays_infer_lists(R5Params P, const int32_t *__restrict__ offsets, float S_, uint32_t H, uint32_t gridtype,
                            const float *__restrict__ Ws0, const float *__restrict__ Ws1, const float *__restrict__ Wc0,
@@ -1055,7 +1131,7 @@ k_render5_rays_infer_lists(R5Params P, const int32_t *__restrict__ offsets, floa
         if (lane == 0) r5_mma<R5SmemL>(S, P, tmem, warp - C5_MMA_WARP);
         __syncwarp();
     } else {
-        r5l_feeder(S, P, warp - R5_MARCH_WARP0, lane);
+        r5l_feeder<SEG>(S, P, warp - R5_MARCH_WARP0, lane);
     }
     tc5::fence_before_sync();
     __syncthreads();
@@ -1085,8 +1161,8 @@ extern "C" int ngp_render_plan(const float *rays_o, const float *rays_d, int64_t
     NGP_REQUIRE(workspace_bytes >= ngp_render_plan_workspace_bytes(N), NGP_ERR_ARG, "ngp_render_plan: workspace too small");
     cudaStream_t st = (cudaStream_t)stream;
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
-    k_r5_premarch<false><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps, counts, nullptr,
-                                                                      nullptr);
+    k_r5_premarch<0><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps, counts, nullptr,
+                                                                  nullptr, 0, nullptr, nullptr);
     NGP_CHECK_LAUNCH("ngp_render_plan(count)");
     size_t need = (size_t)workspace_bytes;
     cub::TransformInputIterator<long long, R5ToI64, const int32_t *> it(counts, R5ToI64());
@@ -1121,12 +1197,12 @@ extern "C" int ngp_render_rays_infer_planned(const float *rays_o, const float *r
     }
     (void)samples_capacity;   // the caller sized `samples` from plan_ends[N - 1] (ngp_render_plan); the lists cannot exceed it
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
-    k_r5_premarch<true><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps,
-                                                                     const_cast<int32_t *>(plan_counts),
-                                                                     (const long long *)plan_ends, (float2 *)samples);
+    k_r5_premarch<1><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps,
+                                                                  const_cast<int32_t *>(plan_counts), (const long long *)plan_ends,
+                                                                  (float2 *)samples, 0, nullptr, nullptr);
     NGP_CHECK_LAUNCH("ngp_render_rays_infer_planned(write)");
     const int smem = (int)sizeof(R5SmemL);
-    if (cudaFuncSetAttribute(k_render5_rays_infer_lists, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+    if (cudaFuncSetAttribute(k_render5_rays_infer_lists<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
         ngp_set_error("ngp_render_rays_infer_planned: cannot reserve %d B of shared memory", smem);
         return NGP_ERR_CUDA;
     }
@@ -1141,10 +1217,98 @@ extern "C" int ngp_render_rays_infer_planned(const float *rays_o, const float *r
     P.counter = (unsigned long long *)workspace;
     P.nsamples = (unsigned long long *)workspace + 1;
     P.plan_counts = plan_counts; P.plan_ends = (const long long *)plan_ends; P.tdt = (const float2 *)samples;
+    P.segs = nullptr; P.nsegs = nullptr; P.seg_cap = 0; P.dt_min = cfg.dt_min; P.dt_max = cfg.dt_max; P.dt_gamma = cfg.dt_gamma;
+    P.lvl_dt = cfg.lvl_dt; P.ray_list = nullptr; P.ray_list_count = nullptr;
     const int64_t want = ngp_div_up(N, R5L_NR / 2);
     const int nblocks = (int)(want < sms ? want : sms);
-    k_render5_rays_infer_lists<<<nblocks, R5_THREADS, smem, st>>>(P, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
+    k_render5_rays_infer_lists<false><<<nblocks, R5_THREADS, smem, st>>>(P, offsets, S, H, gridtype, Ws0, Ws1, Wc0, Wc1, Wc2);
     NGP_CHECK_LAUNCH("ngp_render_rays_infer_planned");
+    return NGP_OK;
+}
+
+// ---- single-call form: runs instead of lists, no host read
+// Layout of the workspace: 512-byte header (u64[0] ray counter of the segment kernel, [1] samples evaluated, [2..25] stats,
+// [26] rays with more than seg_cap runs, [32] ray counter of the marcher-inside kernel, [34..57] its stats), nsegs i32 [N],
+// overflow ray list i32 [N], segs float2 [N x seg_cap].
+static int64_t r5_align8(int64_t v) { return (v + 7) & ~7ll; }
+extern "C" int64_t ngp_render_rays_infer_segments_workspace_bytes(int64_t N, int seg_cap) {
+    if (N < 0 || seg_cap < 1) return -1;
+    return 512 + r5_align8(4 * N) + r5_align8(4 * N) + N * (int64_t)seg_cap * 8;
+}
+
+extern "C" int ngp_render_rays_infer_segments(const float *rays_o, const float *rays_d, int64_t N, const float *aabb, float min_near,
+                                              const uint8_t *grid, float bound, float dt_gamma, uint32_t max_steps, uint32_t C,
+                                              uint32_t Hgrid, const float *embeddings, const int32_t *offsets, float S, uint32_t H,
+                                              uint32_t gridtype, int align_corners, const float *Ws0, const float *Ws1,
+                                              const float *Wc0, const float *Wc1, const float *Wc2, float density_scale,
+                                              const float *bg_color, int bg_stride, float *image, float *depth, float *weights_sum,
+                                              int32_t *counts, int seg_cap, void *workspace, int64_t workspace_bytes,
+                                              ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(rays_o, "ngp_render_rays_infer_segments");
+    if (N == 0) return NGP_OK;
+    NGP_REQUIRE(rays_o && rays_d && aabb && grid && embeddings && offsets && Ws0 && Ws1 && Wc0 && Wc1 && Wc2 && image && depth &&
+                    workspace,
+                NGP_ERR_ARG, "ngp_render_rays_infer_segments: null pointer");
+    NGP_REQUIRE(bound > 0.0f && N > 0 && N < (1ll << 31) && max_steps < (1u << 20), NGP_ERR_ARG,
+                "ngp_render_rays_infer_segments: bad bound / N / max_steps");
+    NGP_REQUIRE(C >= 1 && C <= 8 && Hgrid >= 1 && Hgrid <= 1024, NGP_ERR_ARG, "ngp_render_rays_infer_segments: bad cascade/grid size");
+    NGP_REQUIRE(bg_stride == 0 || bg_stride == 3, NGP_ERR_ARG, "ngp_render_rays_infer_segments: bg_stride must be 0 or 3");
+    NGP_REQUIRE(seg_cap >= 1 && seg_cap <= 1024, NGP_ERR_ARG, "ngp_render_rays_infer_segments: seg_cap must be in 1..1024");
+    NGP_REQUIRE(((uintptr_t)embeddings & 15u) == 0 && ((uintptr_t)workspace & 7u) == 0, NGP_ERR_ARG,
+                "ngp_render_rays_infer_segments: embeddings must be 16-byte aligned, workspace 8-byte aligned");
+    NGP_REQUIRE(workspace_bytes >= ngp_render_rays_infer_segments_workspace_bytes(N, seg_cap), NGP_ERR_ARG,
+                "ngp_render_rays_infer_segments: workspace too small");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (cudaMemsetAsync(workspace, 0, 512, st) != cudaSuccess) {
+        ngp_set_error("ngp_render_rays_infer_segments: workspace memset failed");
+        return NGP_ERR_CUDA;
+    }
+    unsigned long long *hdr = (unsigned long long *)workspace;
+    int32_t *nsegs = (int32_t *)((char *)workspace + 512);
+    int32_t *ovf = (int32_t *)((char *)nsegs + r5_align8(4 * N));
+    float2 *segs = (float2 *)((char *)ovf + r5_align8(4 * N));
+    const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
+    k_r5_premarch<2><<<(unsigned)ngp_div_up(N, 256), 256, 0, st>>>(rays_o, rays_d, N, aabb, min_near, cfg, max_steps, nsegs, nullptr,
+                                                                  segs, seg_cap, ovf, hdr + 26);
+    NGP_CHECK_LAUNCH("ngp_render_rays_infer_segments(pre-pass)");
+    int dev = 0, sms = NGP_SM_COUNT;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    R5Params P;
+    P.rays_o = rays_o; P.rays_d = rays_d; P.aabb = aabb; P.bg = bg_color; P.N = N; P.bg_stride = bg_stride;
+    P.min_near = min_near; P.density_scale = density_scale; P.bound = bound; P.max_steps = max_steps;
+    P.table = embeddings; P.align_corners = align_corners;
+    P.image = image; P.depth = depth; P.weights_sum = weights_sum; P.counts = counts;
+    P.counter = hdr; P.nsamples = hdr + 1;
+    P.plan_counts = nullptr; P.plan_ends = nullptr; P.tdt = nullptr;
+    P.segs = segs; P.nsegs = nsegs; P.seg_cap = seg_cap; P.dt_min = cfg.dt_min; P.dt_max = cfg.dt_max; P.dt_gamma = cfg.dt_gamma;
+    P.lvl_dt = cfg.lvl_dt; P.ray_list = nullptr; P.ray_list_count = nullptr;
+    {
+        const int smem = (int)sizeof(R5SmemL);
+        if (cudaFuncSetAttribute(k_render5_rays_infer_lists<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+            ngp_set_error("ngp_render_rays_infer_segments: cannot reserve %d B of shared memory", smem);
+            return NGP_ERR_CUDA;
+        }
+        const int64_t want = ngp_div_up(N, R5L_NR / 2);
+        k_render5_rays_infer_lists<true><<<(int)(want < sms ? want : sms), R5_THREADS, smem, st>>>(P, offsets, S, H, gridtype, Ws0, Ws1,
+                                                                                                   Wc0, Wc1, Wc2);
+        NGP_CHECK_LAUNCH("ngp_render_rays_infer_segments");
+    }
+    {   // rays with more than seg_cap runs (their number is only known on the device): the kernel with the marcher inside,
+        // over the overflow list; CTAs that find no ray leave through the end protocol at once
+        const int smem = (int)sizeof(R5Smem);
+        if (cudaFuncSetAttribute(k_render5_rays_infer, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+            ngp_set_error("ngp_render_rays_infer_segments: cannot reserve %d B of shared memory", smem);
+            return NGP_ERR_CUDA;
+        }
+        P.counter = hdr + 32;
+        P.segs = nullptr; P.nsegs = nullptr;
+        P.ray_list = ovf; P.ray_list_count = hdr + 26;
+        const int64_t want = ngp_div_up(N, R5_NR / 2);
+        k_render5_rays_infer<<<(int)(want < sms ? want : sms), R5_THREADS, smem, st>>>(P, cfg, offsets, S, H, gridtype, Ws0, Ws1, Wc0,
+                                                                                      Wc1, Wc2);
+        NGP_CHECK_LAUNCH("ngp_render_rays_infer_segments(overflow rays)");
+    }
     return NGP_OK;
 }
 
@@ -1174,6 +1338,8 @@ int r5_render_rays_infer(const float *rays_o, const float *rays_d, int64_t N, co
     P.nsamples = (unsigned long long *)workspace + 1;
     P.plan_counts = nullptr; P.plan_ends = nullptr; P.tdt = nullptr;
     const MarchCfg cfg = ngp_march_cfg(grid, bound, dt_gamma, max_steps, C, Hgrid);
+    P.segs = nullptr; P.nsegs = nullptr; P.seg_cap = 0; P.dt_min = cfg.dt_min; P.dt_max = cfg.dt_max; P.dt_gamma = cfg.dt_gamma;
+    P.lvl_dt = cfg.lvl_dt; P.ray_list = nullptr; P.ray_list_count = nullptr;
     // one CTA per SM (a CTA owns all 512 TMEM columns); small batches use fewer CTAs so that tiles still fill
     const int64_t want = ngp_div_up(N, R5_NR / 2);
     const int nblocks = (int)(want < sms ? want : sms);

@@ -268,7 +268,12 @@ def field_color(model, x, d):
     return sigma.view(prefix), rgb.view(prefix + [3])
 
 
-PREMARCH = True   # render_rays_infer: march in a full-occupancy pre-pass (ngp_render_plan + ngp_render_rays_infer_planned)
+# render_rays_infer: where the occupancy marching happens (tcgen05 implementation):
+#   "segments" (or True)  full-occupancy pre-pass that records every ray's runs of samples; one C call, no host read
+#   "lists"               pre-pass in two passes that leaves explicit (t, dt) lists; one host read sizes them
+#   False                 inside the persistent kernel
+PREMARCH = "segments"
+SEGMENT_CAPACITY = 32   # runs per ray kept by the "segments" pre-pass; rays with more go through the marcher-inside kernel
 
 
 @torch.no_grad()
@@ -279,9 +284,9 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
     rays_o, rays_d [N,3] -> image [N,3], depth [N], weights_sum [N] (already post-processed like run_cuda's results);
     return_stats appends the workspace (its second i64 = samples evaluated), return_counts the per-ray int32 sample counts.
     premarch (default: module flag PREMARCH, tcgen05 implementation only): the occupancy marching runs as a thread-per-ray
-    pre-pass that leaves every ray's (t, dt) list in a scratch tensor (one host read of the total to size it), and the
-    persistent kernel only evaluates and composites — same samples, same results; False keeps the marcher inside the kernel
-    (no host synchronisation, no scratch)."""
+    pre-pass at full occupancy and the persistent kernel only evaluates and composites — same samples, same results.
+    "segments": one pass records each ray's runs of samples (SEGMENT_CAPACITY per ray), no host read; "lists": count + write
+    passes leave explicit (t, dt) lists sized by one host read; False keeps the marcher inside the kernel (no scratch)."""
     _lib.require_cuda(rays_o, rays_d, model.density_bitfield)
     rays_o = rays_o.contiguous().float()
     rays_d = rays_d.contiguous().float()
@@ -307,7 +312,10 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
     L = _lib.lib()
     if premarch is None:
         premarch = PREMARCH
-    premarch = bool(premarch) and N > 0 and L.ngp_set_field_impl(-1) == 1
+    if premarch is True:
+        premarch = "segments"
+    if not (N > 0 and L.ngp_set_field_impl(-1) == 1):
+        premarch = False
     common = lambda: (_lib.ptr(rays_o), _lib.ptr(rays_d), N, _lib.ptr(aabb), float(model.min_near),
                       _lib.ptr(model.density_bitfield), float(model.bound), float(dt_gamma), int(max_steps), int(model.cascade),
                       int(model.grid_size))
@@ -317,7 +325,13 @@ def render_rays_infer(model, rays_o, rays_d, aabb, bg_color=None, dt_gamma=0.0, 
                      _lib.ptr(counts))
     aabb = aabb.contiguous()
     with torch.cuda.device(dev):
-        if premarch:
+        if premarch == "segments":
+            sw_bytes = L.ngp_render_rays_infer_segments_workspace_bytes(N, SEGMENT_CAPACITY)
+            work = torch.empty(sw_bytes // 8, device=dev, dtype=torch.int64)
+            _lib.check(L.ngp_render_rays_infer_segments(*common(), *field(), SEGMENT_CAPACITY, _lib.ptr(work), sw_bytes,
+                                                        _lib.stream()), "render_rays_infer_segments")
+            work = work[:64]      # the header: [1] = samples evaluated, [26] = rays that took the overflow path
+        elif premarch:
             plan_counts = torch.empty(N, device=dev, dtype=torch.int32)
             plan_ends = torch.empty(N, device=dev, dtype=torch.int64)
             pw_bytes = L.ngp_render_plan_workspace_bytes(N)

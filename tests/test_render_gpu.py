@@ -26,16 +26,20 @@ def model():
     return m.eval()
 
 
-@pytest.fixture(params=["tc5", "tc5-inkernel-march", "mma"])
+@pytest.fixture(params=["tc5", "tc5-overflow", "tc5-lists", "tc5-inkernel-march", "mma"])
 def impl(request, ngp):
-    """Every test runs on the three implementations: the tcgen05 kernel fed by the pre-marched sample lists (default), the
-    tcgen05 kernel with the marcher inside (no host read, no scratch), and the mma.sync kernel."""
+    """Every test runs on all implementations: the tcgen05 kernel fed by pre-marched runs of samples (default), the same
+    with room for ONE run per ray (so most rays take the overflow path: the marcher-inside kernel over a ray list, in the
+    same call), the tcgen05 kernel fed by explicit sample lists, the tcgen05 kernel with the marcher inside, and the
+    mma.sync kernel."""
     from nerf_navigation_b200 import field
     prev = ngp.lib().ngp_set_field_impl(0 if request.param == "mma" else 1)
-    prev_pm = field.PREMARCH
-    field.PREMARCH = request.param == "tc5"
+    prev_pm, prev_cap = field.PREMARCH, field.SEGMENT_CAPACITY
+    field.PREMARCH = {"tc5": "segments", "tc5-overflow": "segments", "tc5-lists": "lists"}.get(request.param, False)
+    if request.param == "tc5-overflow":
+        field.SEGMENT_CAPACITY = 1
     yield request.param
-    field.PREMARCH = prev_pm
+    field.PREMARCH, field.SEGMENT_CAPACITY = prev_pm, prev_cap
     ngp.lib().ngp_set_field_impl(prev)
 
 
