@@ -85,7 +85,8 @@ int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_layout, int
 /* The same gradient (gridencoder.cu:227-314), bit-reproducible WITHOUT a sort: contributions are scaled by one power of two
  * (from max |grad| and the bound 2^D B on contributions per row, so no sum overflows), rounded to int64 and added with
  * 64-bit integer atomics — integer addition is associative, any arrival order gives the same bits — then converted back.
- * Resolution 2^-(61 - ceil(log2(2^D B))) of max |grad| per contribution.  workspace: 16-byte aligned,
+ * Resolution 2^-(61 - ceil(log2(2^D B))) of max |grad| per contribution.  An inf / NaN anywhere in grad makes the whole
+ * result NaN (integers cannot carry it; it is what an AMP inf check needs to see).  workspace: 16-byte aligned,
  * ngp_grid_backward_table_fixed_workspace_bytes(total_rows, C) = 256 + 8 total_rows C bytes; grad_embeddings is overwritten. */
 int64_t ngp_grid_backward_table_fixed_workspace_bytes(int64_t total_rows, int C);
 int ngp_grid_encode_backward_table_fixed(const void *grad, int grad_layout, int grad_dtype, const float *inputs,

@@ -353,19 +353,23 @@ extern "C" int ngp_grid_encode_backward_table_atomic(const void *grad, int grad_
 struct TgFixedHdr {
     unsigned int max_bits;   // float bits of max |grad| (atomicMax on the bit pattern of non-negative floats)
     int shift;               // contributions are scaled by 2^shift
-    unsigned int pad[2];
+    unsigned int nonfinite;  // an upstream gradient was inf / NaN: the result is all NaN (what GradScaler's inf check looks for)
+    unsigned int pad;
 };
 
 template <typename G>
 __global__ void __launch_bounds__(TG_THREADS) k_tg_absmax(const G *__restrict__ grad, int64_t n, TgFixedHdr *hdr) {
     float m = 0.0f;
+    bool bad = false;
     for (int64_t i = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * TG_THREADS) {
         const float v = fabsf((float)grad[i]);
-        m = v > m ? v : m;   // NaN never wins: a NaN gradient stays NaN in the sums below anyway
+        if (!(v <= 3.402823466e38f)) bad = true;   // inf or NaN: integers cannot carry it, the finish pass writes NaN
+        else m = v > m ? v : m;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0 && m > 0.0f) atomicMax(&hdr->max_bits, __float_as_uint(m));
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(&hdr->nonfinite, 1u);
 }
 
 __global__ void k_tg_fixed_shift(TgFixedHdr *hdr, int count_bits) {
@@ -431,7 +435,7 @@ k_tg_fixed(const G *__restrict__ grad, int grad_layout, const float *__restrict_
 #pragma unroll
         for (int d = 0; d < D; ++d) w *= (k >> d) & 1 ? frac[d] : 1.0f - frac[d];
 #pragma unroll
-        for (int c = 0; c < C; ++c) val[k][c] = live ? __float2ll_rn(__fmul_rn(__fmul_rn(w, gv[c]), scale)) : 0ll;
+        for (int c = 0; c < C; ++c) val[k][c] = live ? __float2ll_rn(__fmul_rn(__fmul_rn(w, gv[c]), scale)) : 0ll;   // (inf / NaN: see nonfinite)
     }
     if (__popc(heads) <= 24) {
         const int seg = __popc(heads & (0xffffffffu >> (31 - lane)));
@@ -462,8 +466,9 @@ k_tg_fixed(const G *__restrict__ grad, int grad_layout, const float *__restrict_
 __global__ void __launch_bounds__(TG_THREADS)
 k_tg_fixed_finish(const long long *__restrict__ acc, const TgFixedHdr *__restrict__ hdr, float *__restrict__ out, int64_t n) {
     const double inv = __longlong_as_double((long long)(1023 - hdr->shift) << 52);   // 2^-shift
+    const bool bad = hdr->nonfinite != 0u;
     for (int64_t i = (int64_t)blockIdx.x * TG_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * TG_THREADS)
-        out[i] = (float)((double)acc[i] * inv);
+        out[i] = bad ? __int_as_float(0x7fc00000) : (float)((double)acc[i] * inv);
 }
 
 extern "C" int64_t ngp_grid_backward_table_fixed_workspace_bytes(int64_t total_rows, int C) {

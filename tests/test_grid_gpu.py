@@ -154,6 +154,14 @@ def test_table_gradient_vs_oracle_and_deterministic(ngp, oracle, method):
             # fp16 upstream gradient (autocast training) and the [L, B, C] layout take the same path
             gl0 = gt.view(B, 16, 2).permute(1, 0, 2).contiguous()
             assert torch.equal(_table_grad(ngp, gl0, xt, cfg, layout=0), a)
+        if method == "fixed":
+            # integers cannot carry inf / NaN: an overflowed upstream gradient (fp16 training) gives an all-NaN table
+            # gradient, which is what GradScaler's inf check needs to skip the step
+            gbad = gt.clone(); gbad[17, 3] = float("inf")
+            assert not torch.isfinite(_table_grad(ngp, gbad, xt, cfg)).any()
+            gbad[17, 3] = float("nan")
+            assert not torch.isfinite(_table_grad(ngp, gbad, xt, cfg)).any()
+            assert torch.equal(_table_grad(ngp, gt, xt, cfg), a)      # and the next call is clean again
     finally:
         table_grad.METHOD = prev
     assert rel_err(a.cpu().numpy(), ref) < 1e-5
