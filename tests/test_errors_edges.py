@@ -31,6 +31,27 @@ def test_argument_validation_without_a_gpu(ngp):
     assert L.ngp_occ_grid_partial_workspace_bytes(128) > 4 * 128 ** 3
     rc = L.ngp_occ_grid_mark_untrained(None, 3, 1.0, 1.0, 1.0, 1.0, 2, 128, 2.0, None, None)
     assert rc == 1 and b"mark_untrained" in L.ngp_last_error()
+    # round-2 entry points
+    rargs = (None, None, 8, None, 0.2, None, 2.0, 0.0, 1024, 2, 128, None, None, 0.5, 16, 0, 0, None, None, None, None, None, 1.0,
+             None, 0, None, None, None, None)
+    rc = L.ngp_render_rays_infer_segments(*rargs, 32, None, 0, None)
+    assert rc == 1 and b"ngp_render_rays_infer_segments" in L.ngp_last_error()
+    assert L.ngp_render_rays_infer_segments_workspace_bytes(1000, 32) == 512 + 4000 + 4000 + 1000 * 32 * 8
+    assert L.ngp_render_rays_infer_segments_workspace_bytes(1000, 0) < 0
+    rc = L.ngp_render_rays_infer_planned(*rargs, None, None, None, 0, None, None)
+    assert rc == 1 and b"ngp_render_rays_infer_planned" in L.ngp_last_error()
+    rc = L.ngp_render_plan(None, None, 8, None, 0.2, None, 2.0, 0.0, 1024, 2, 128, None, None, None, 0, None)
+    assert rc == 1 and b"ngp_render_plan" in L.ngp_last_error()
+    assert L.ngp_render_plan_workspace_bytes(1000) >= 256
+    rc = L.ngp_field_query_forward_jacobian(None, 2.0, None, None, 0.5, 16, 0, 0, None, None, None, None, None, None, 8, None)
+    assert rc == 1 and b"forward_jacobian" in L.ngp_last_error()
+    rc = L.ngp_field_query_ff_forward(None, 2.0, None, None, 0.5, 16, 0, 0, None, 2, 0, None, 8, None)
+    assert rc == 1 and b"ngp_field_query_ff_forward" in L.ngp_last_error()
+    rc = L.ngp_grid_encode_backward_table_fixed(None, 1, 0, None, None, 100, None, 8, 3, 2, 16, 0.5, 16, 0, 0, None, 0, None)
+    assert rc == 1 and b"backward_table_fixed" in L.ngp_last_error()
+    assert L.ngp_grid_backward_table_fixed_workspace_bytes(1000, 2) == 256 + 1000 * 2 * 8
+    rc = L.ngp_linear_wgrad_static(p, p, p, 65537, 16, 32, None)        # beyond the static scratch
+    assert rc == 3 and b"static scratch limit" in L.ngp_last_error()
     L.ngp_set_device_check(prev)
 
 
