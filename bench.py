@@ -676,7 +676,7 @@ def run_b200(args):
                                           f"{args.e2e_chunk} points, H2D / single-pass value+grad kernel / D2H on 3 streams (the "
                                           "upstream gradient restricted to a0 + b0 sigma)"},
                 "callable_api": {"value": world * B * e2e_steps / t_e2e_callable / 1e6,
-                                 "api": "same call with dloss_dsigma as a Python callable: forward + backward kernels per chunk"},
+                                 "api": "same call with dloss_dsigma as a Python callable: Jacobian-returning forward (one table pass) + dL/dsigma * jac per chunk"},
                 "autograd_api": {"value": world * B * e2e_steps / t_e2e_autograd / 1e6,
                                  "api": "x.cuda() -> NeRFNetwork.density(x)['sigma'] -> mean(sigma^2).backward() -> x.grad.cpu()"}},
         "gpu_launches": 2 * args.steps,  # device-resident region: forward_jacobian + backward_jacobian per step

@@ -128,7 +128,8 @@ int ngp_field_query_forward_jacobian(const float *x, float bound, const float *e
                                      float *sigma, float *geo, uint64_t *relu_mask, float *jac, int64_t B,
                                      ngp_stream_t stream);
 
-/* grad_x [B,3] = grad_sigma_i * jac_i: the backward of sigma after ngp_field_query_forward_jacobian (no table pass). */
+/* grad_x [B,3] = grad_sigma_i * jac_i: the backward of sigma after ngp_field_query_forward_jacobian (no table pass).
+ * grad_x may be jac itself (in place). */
 int ngp_field_query_backward_jacobian(const float *jac, const float *grad_sigma, float *grad_x, int64_t B,
                                       ngp_stream_t stream);
 

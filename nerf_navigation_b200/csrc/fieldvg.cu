@@ -347,9 +347,10 @@ extern "C" int ngp_field_query_forward(const float *x, float bound, const float 
 
 // ---- density forward that also returns the Jacobian rows: what autograd's density(x) runs when x requires a gradient.
 // The backward of sigma = f(x_i) is then grad_sigma_i * jac_i: one streaming kernel instead of a second table pass.
-__global__ void k_scale_rows3(const float *__restrict__ jac, const float *__restrict__ gs, float *__restrict__ out, int64_t n3) {
+// `out` may be `jac` itself (in place): every element is read and written by the same thread, no read-only path for it
+__global__ void k_scale_rows3(const float *jac, const float *__restrict__ gs, float *out, int64_t n3) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n3; i += (int64_t)gridDim.x * blockDim.x)
-        out[i] = __ldg(gs + i / 3) * __ldg(jac + i);
+        out[i] = __ldg(gs + i / 3) * jac[i];
 }
 
 extern "C" int ngp_field_query_forward_jacobian(const float *x, float bound, const float *embeddings, const int32_t *offsets,

@@ -360,7 +360,8 @@ class HostFieldQuery:
     consecutive chunks overlap on three streams (PCIe is full duplex), so the step costs max(copies, kernels) instead of
     their sum.  `dloss_dsigma(sigma_chunk) -> grad_chunk` supplies the upstream gradient (elementwise in sigma); a pair
     `(a0, b0)` instead of a callable means dL/dsigma_i = a0 + b0 * sigma_i (b0 = 2/B: mean(sigma^2), the planner's density
-    cost) and runs each chunk as ONE kernel (ngp_field_query_value_grad).  `sigma_hook(sigma_chunk)`, if given, is called
+    cost) and runs each chunk as ONE kernel (ngp_field_query_value_grad); a callable costs one more streaming kernel
+    (Jacobian-returning forward, then dL/dsigma * jac): the table is gathered once either way.  `sigma_hook(sigma_chunk)`, if given, is called
     on the compute stream for every chunk (e.g. to accumulate the loss value on the device).  With `ramp=True` the first
     and last chunks are shorter (chunk/4, chunk/2) so less of the first upload and last download is exposed."""
 
@@ -431,16 +432,16 @@ class HostFieldQuery:
                         if sigma_hook is not None:
                             sigma_hook(b["sigma"][:n])
                     else:
-                        _lib.check(L.ngp_field_query_forward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
-                                                             gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(), None,
-                                                             b["mask"].data_ptr(), n, st), "field_query_forward")
+                        # sigma and d sigma / dx from ONE table pass (b["gx"] holds the Jacobian rows), then dL/dx = dL/dsigma * jac
+                        _lib.check(L.ngp_field_query_forward_jacobian(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(),
+                                                                      self.S, H, gt, al, W0.data_ptr(), W1.data_ptr(),
+                                                                      b["sigma"].data_ptr(), None, None, b["gx"].data_ptr(), n, st),
+                                   "field_query_forward_jacobian")
                         if sigma_hook is not None:
                             sigma_hook(b["sigma"][:n])
-                        gs = dloss_dsigma(b["sigma"][:n]).contiguous()
-                        _lib.check(L.ngp_field_query_backward(b["x"].data_ptr(), bound, tab.data_ptr(), off.data_ptr(), self.S, H,
-                                                              gt, al, W0.data_ptr(), W1.data_ptr(), b["sigma"].data_ptr(),
-                                                              b["mask"].data_ptr(), gs.data_ptr(), None, b["gx"].data_ptr(), n,
-                                                              st), "field_query_backward")
+                        gs = dloss_dsigma(b["sigma"][:n]).contiguous().float()
+                        _lib.check(L.ngp_field_query_backward_jacobian(b["gx"].data_ptr(), gs.data_ptr(), b["gx"].data_ptr(), n, st),
+                                   "field_query_backward_jacobian")
                         gs.record_stream(self.s_cmp)
                     b["e_cmp"].record(self.s_cmp)
                 with torch.cuda.stream(self.s_out):
