@@ -376,8 +376,7 @@ class HostFieldQuery:
         self.s_in, self.s_cmp, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
         self.nbuf = 3
         c = self.chunk
-        self.bufs = [dict(x=torch.empty(c, 3, device=dev), sigma=torch.empty(c, device=dev),
-                          mask=torch.empty(c, device=dev, dtype=torch.int64), gx=torch.empty(c, 3, device=dev),
+        self.bufs = [dict(x=torch.empty(c, 3, device=dev), sigma=torch.empty(c, device=dev), gx=torch.empty(c, 3, device=dev),
                           e_in=torch.cuda.Event(), e_cmp=torch.cuda.Event(), e_out=torch.cuda.Event())
                      for _ in range(self.nbuf)]
         self.S = float(np.log2(enc.per_level_scale))
