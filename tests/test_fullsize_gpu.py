@@ -4,7 +4,11 @@ plus oracle parity on random subsamples.
             consistency (bit-exact: a point's result must not depend on its neighbours in the batch), backward linearity,
             out-of-range points, 4096-point subsample vs the CPU oracle.
   config 3: 1,048,576 rays: offsets are the exclusive scan of the counts (ray order), sum = sample count, composited
-            weights in [0, 1], 2048-ray subsample vs the CPU oracle (bit-exact counts)."""
+            weights in [0, 1], 2048-ray subsample vs the CPU oracle (bit-exact counts).
+  config 4: one 800x800 frame (640,000 rays) through the fused renderer: run-to-run and implementation-to-implementation
+            bit equality (pre-marched runs, runs with overflow, explicit lists, marcher inside the kernel), permutation
+            equivariance (a ray's pixel must not depend on which rays share its tiles), counts summing to the samples
+            evaluated, and the pre-pass plan against the composited counts."""
 import numpy as np
 import pytest
 import torch
@@ -147,3 +151,46 @@ def test_config3_full_size_march_and_composite(ngp, oracle):
         ra = int(rrays[j, 1])
         assert np.array_equal(xyzs[a:a + n].cpu().numpy(), rx[ra:ra + n])
         assert np.array_equal(deltas[a:a + n].cpu().numpy(), rdl[ra:ra + n])
+
+
+def test_config4_full_frame_properties(ngp):
+    from nerf_navigation_b200 import field, raymarching as rm
+    from nerf_navigation_b200.nerf.network import NeRFNetwork
+    torch.manual_seed(0)
+    m = NeRFNetwork(encoding="hashgrid", bound=2, cuda_ray=True, density_scale=25, min_near=0.2, density_thresh=10).cuda().eval()
+    m.encoder.embeddings.data.uniform_(-0.5, 0.5)
+    m.density_grid.copy_(torch.from_numpy(stonehenge_grid()))
+    m.density_bitfield = rm.packbits(m.density_grid, 10.0, m.density_bitfield)
+    N = 800 * 800
+    o, d = orbit_rays(N, 3)
+    ro, rd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    ren = lambda a, b, mode: field.render_rays_infer(m, a, b, m.aabb_infer, 1.0, premarch=mode, return_stats=True, return_counts=True)
+    img, dep, ws, stats, cnt = ren(ro, rd, "segments")
+    assert torch.isfinite(img).all() and (ws >= 0).all() and (ws <= 1 + 1e-5).all() and (cnt >= 0).all() and (cnt <= 1024).all()
+    assert int(stats[1]) == int(cnt.sum()) and int(stats[26]) == 0             # samples evaluated; no ray needed > 32 runs
+    assert (ws > 0.9999).float().mean() > 0.05                                  # density_scale 25: early termination is exercised
+    # the same frame again, and through the other three feeds of the same kernel core: bit-identical
+    prev_cap = field.SEGMENT_CAPACITY
+    try:
+        for mode, cap in (("segments", 32), ("segments", 2), ("lists", 32), (False, 32)):
+            field.SEGMENT_CAPACITY = cap
+            i2, d2, w2, st2, c2 = ren(ro, rd, mode)
+            assert torch.equal(i2, img) and torch.equal(d2, dep) and torch.equal(w2, ws) and torch.equal(c2, cnt), (mode, cap)
+            if mode == "segments" and cap == 2:
+                assert int(st2[26]) > 1000                                      # the overflow path really carried rays
+    finally:
+        field.SEGMENT_CAPACITY = prev_cap
+    # permutation equivariance
+    perm = torch.randperm(N, device="cuda")
+    ip, dp, wp, _, cp = ren(ro[perm].contiguous(), rd[perm].contiguous(), "segments")
+    assert torch.equal(ip, img[perm]) and torch.equal(dp, dep[perm]) and torch.equal(cp, cnt[perm])
+    # the pre-pass plan: samples marched per ray >= samples composited, equal where the ray did not terminate early
+    L = ngp.lib()
+    plan = torch.empty(N, device="cuda", dtype=torch.int32); ends = torch.empty(N, device="cuda", dtype=torch.int64)
+    wb = L.ngp_render_plan_workspace_bytes(N); wsb = torch.empty(wb, device="cuda", dtype=torch.uint8)
+    ngp.check(L.ngp_render_plan(ro.data_ptr(), rd.data_ptr(), N, m.aabb_infer.data_ptr(), float(m.min_near),
+                                m.density_bitfield.data_ptr(), 2.0, 0.0, 1024, 2, 128, plan.data_ptr(), ends.data_ptr(),
+                                wsb.data_ptr(), wb, ngp.stream()), "plan")
+    assert torch.equal(ends, torch.cumsum(plan.long(), 0)) and (plan >= cnt).all()
+    open_rays = ws < 0.999
+    assert torch.equal(plan[open_rays], cnt[open_rays])
