@@ -62,9 +62,40 @@ class _Field:
         return gx
 
 
+    def fwd_jac(self, x):
+        B = x.shape[0]
+        sigma = torch.empty(B, device="cuda"); geo = torch.empty(B, 15, device="cuda"); jac = torch.empty(B, 3, device="cuda")
+        mask = torch.empty(B, device="cuda", dtype=torch.int64)
+        c = self.cfg
+        self.ngp.check(self.L.ngp_field_query_forward_jacobian(x.data_ptr(), c["bound"], self.tab.data_ptr(), self.off.data_ptr(),
+                                                               c["S"], c["H"], 0, 0, self.W0.data_ptr(), self.W1.data_ptr(),
+                                                               sigma.data_ptr(), geo.data_ptr(), mask.data_ptr(), jac.data_ptr(), B,
+                                                               self.ngp.stream()), "fwd_jac")
+        return sigma, geo, mask, jac
+
+
 @pytest.fixture(scope="module")
 def field(ngp):
     return _Field(ngp)
+
+
+@pytest.mark.parametrize("kind", ["uniform", "clustered"])
+def test_config2_single_table_pass_full_size(field, kind):
+    """The headline kernel (sigma, geo_feat, ReLU bits and d sigma / dx from ONE table pass) at 4,194,304 points: same
+    forward bits as the forward kernel, Jacobian rows x dL/dsigma == the second-table-pass backward (1e-6), permutation
+    equivariance and ragged-chunk consistency of the Jacobian (bit-exact), and the saved bits drive the backward kernel."""
+    x = _points(kind)
+    sigma, geo, mask = field.fwd(x)
+    sj, gj, mj, jac = field.fwd_jac(x)
+    assert torch.equal(sj, sigma) and torch.equal(gj, geo) and torch.equal(mj, mask)
+    gs = sigma * (2.0 / B_FULL)
+    gx = field.bwd(x, sigma, mask, gs)
+    assert rel_err((jac * gs[:, None]).cpu().numpy(), gx.cpu().numpy()) < 1e-6
+    perm = torch.randperm(B_FULL, device="cuda", generator=torch.Generator(device="cuda").manual_seed(4))
+    assert torch.equal(field.fwd_jac(x[perm].contiguous())[3], jac[perm])
+    a, n = 333_333, 2_000_001
+    assert torch.equal(field.fwd_jac(x[a:a + n].contiguous())[3], jac[a:a + n])
+    assert torch.equal(field.bwd(x, sj, mj, gs), gx)
 
 
 @pytest.mark.parametrize("kind", ["uniform", "clustered"])
