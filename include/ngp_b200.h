@@ -237,6 +237,16 @@ int ngp_pose_rays_forward(const float *poses, const int64_t *pix, int P, int R, 
 int ngp_pose_rays_backward(const float *grad_o, const float *grad_d, const int64_t *pix, int P, int R, int W, float fx, float fy,
                            float cx, float cy, float *grad_poses, ngp_stream_t stream);
 
+/* The estimator's 12-state (position 3, velocity 3, rotation vector 3, angular velocity 3) -> the cam2world pose its
+ * measurement renders: nav/estimator_helpers.py:293-327 (measurement_fn) with nav/math_utils.py:159-174 (vec_to_rot_matrix,
+ * axis = v / (1e-10 + |v|)) and :26-38 (Blender -> NGP axes): pose = [flip_yz (rot_x(pi/2) R) neg_yz | flip_yz p].
+ * states [P,12] -> poses [P,4,4]; the backward is the analytic derivative (dL/dposes [P,4,4] -> dL/dstates [P,12], zero for
+ * the velocities; zero for v = 0 as autograd gives).  cos_half_pi / sin_half_pi: cos / sin of the float32 pi / 2 the
+ * reference evaluates.  One launch each instead of ~25 / ~40 eager torch ops. */
+int ngp_state_to_pose_forward(const float *states, int P, float cos_half_pi, float sin_half_pi, float *poses, ngp_stream_t stream);
+int ngp_state_to_pose_backward(const float *states, const float *grad_poses, int P, float cos_half_pi, float sin_half_pi,
+                               float *grad_states, ngp_stream_t stream);
+
 /* ---- fused inference renderer: NeRFRenderer.run_cuda eval branch, nerf/renderer.py:325-374 ----------------------- */
 
 /* One persistent kernel for: near_far_from_aabb -> loop { march_rays -> NeRFNetwork.forward(x, d) -> composite_rays ->

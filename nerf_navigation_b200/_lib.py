@@ -63,6 +63,8 @@ _SIGNATURES = {
     "ngp_render_rays_infer_segments_workspace_bytes": ([I64, I], I64),
     "ngp_render_rays_infer_segments": ([P, P, I64, P, F, P, F, F, U32, U32, U32, P, P, F, U32, U32, I, P, P, P, P, P, F, P, I, P, P,
                                        P, P, I, P, I64, P], I),
+    "ngp_state_to_pose_forward": ([P, I, F, F, P, P], I),
+    "ngp_state_to_pose_backward": ([P, P, I, F, F, P, P], I),
     "ngp_adam_step": ([P, P, P, P, P, I64, F, F, F, F, I64, F, F, P, P, P], I),
     "ngp_linear_wgrad_workspace_bytes": ([I64], I64),
     "ngp_linear_wgrad": ([P, P, P, I64, I, I, P, I64, P], I),

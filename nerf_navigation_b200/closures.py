@@ -74,15 +74,51 @@ def rotvec_to_matrix(v):
     return torch.eye(3, dtype=v.dtype, device=v.device) + torch.sin(a) * K + (1 - torch.cos(a)) * (K @ K)
 
 
+class _state_to_pose(torch.autograd.Function):
+    """state_to_pose on the GPU: one kernel forward, one backward (csrc/rays.cu), instead of ~65 eager ops per step — at a few
+    dozen hypotheses per GPU the estimator step is bound by the host's launch rate, not by the kernels."""
+
+    @staticmethod
+    def forward(ctx, states):
+        from . import _lib
+        states = states.contiguous()
+        P = states.shape[0]
+        poses = torch.empty(P, 4, 4, device=states.device)
+        c, s = _half_pi_cos_sin()
+        with torch.cuda.device(states.device):
+            _lib.check(_lib.lib().ngp_state_to_pose_forward(_lib.ptr(states), P, c, s, _lib.ptr(poses), _lib.stream()),
+                       "state_to_pose_forward")
+        ctx.save_for_backward(states)
+        return poses
+
+    @staticmethod
+    def backward(ctx, grad_poses):
+        from . import _lib
+        (states,) = ctx.saved_tensors
+        P = states.shape[0]
+        grad_states = torch.empty(P, 12, device=states.device)
+        c, s = _half_pi_cos_sin()
+        with torch.cuda.device(states.device):
+            _lib.check(_lib.lib().ngp_state_to_pose_backward(_lib.ptr(states), _lib.ptr(grad_poses.contiguous().float()), P, c, s,
+                                                             _lib.ptr(grad_states), _lib.stream()), "state_to_pose_backward")
+        return grad_states
+
+
+def _half_pi_cos_sin():
+    half_pi = torch.tensor(math.pi / 2, dtype=torch.float32)           # the reference evaluates cos / sin of a float32 pi / 2
+    return float(torch.cos(half_pi)), float(torch.sin(half_pi))
+
+
 def state_to_pose(states):
     """The estimator's 12-state (position 3, velocity 3, rotation vector 3, angular velocity 3) -> the cam2world pose the
     renderer sees (nav/estimator_helpers.py:293-327 measurement_fn): R = vec_to_rot_matrix(state[6:9]); the camera looks
     along the body y axis, hence rot_x(pi/2) @ R; then Blender -> NGP axes (nav/math_utils.py:26-38): flip_yz @ rot @ neg_yz
     and flip_yz @ position.  states [P,12] -> poses [P,4,4], differentiable (dL/d(12-state) by autograd: velocity and
     angular velocity take no gradient from the measurement)."""
+    if states.is_cuda and states.dtype == torch.float32 and states.dim() == 2 and states.shape[1] == 12:
+        return _state_to_pose.apply(states)      # the torch formulation below is the host / reference-shaped form (golden-pinned)
     dt, dev = states.dtype, states.device
-    half_pi = torch.tensor(math.pi / 2, dtype=torch.float32)           # the reference evaluates cos / sin of a float32 pi / 2
-    c, s = float(torch.cos(half_pi)), float(torch.sin(half_pi))
+    c, s = _half_pi_cos_sin()
     rot_x = torch.tensor([[1.0, 0.0, 0.0], [0.0, c, -s], [0.0, s, c]], dtype=dt, device=dev)
     flip_yz = torch.tensor([[0.0, 1.0, 0.0], [0.0, 0.0, 1.0], [1.0, 0.0, 0.0]], dtype=dt, device=dev)
     neg_yz = torch.tensor([[1.0, 0.0, 0.0], [0.0, -1.0, 0.0], [0.0, 0.0, -1.0]], dtype=dt, device=dev)

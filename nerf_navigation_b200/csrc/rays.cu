@@ -825,3 +825,132 @@ extern "C" int ngp_pose_rays_backward(const float *grad_o, const float *grad_d, 
     NGP_CHECK_LAUNCH("ngp_pose_rays_backward");
     return NGP_OK;
 }
+
+// ---------------------------------------------------------------- 12-state -> cam2world pose  (estimator closure)
+// nav/estimator_helpers.py:293-327 + nav/math_utils.py:26-38, 159-174: R = I + sin(a) K + (1 - cos(a)) K K with
+// a = |v|, K = skew(v / (1e-10 + a)), v = state[6:9]; pose = [flip_yz (rot_x(pi/2) R) neg_yz | flip_yz p], p = state[0:3].
+// One thread per hypothesis, evaluated in double and rounded once (a few dozen flops per state); the backward is the
+// analytic derivative of the same expression (v = 0: zero gradient, as autograd gives through the 1e-10).
+// c, s = cos / sin of the float32 pi / 2 the reference evaluates.
+struct PoseMat {
+    double m[3][3];
+};
+__device__ __forceinline__ void state_rotation(const double v[3], double c, double s, PoseMat &K, PoseMat &R, double &ang, double &sn,
+                                               double &cs) {
+    ang = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    const double inv = 1.0 / (1e-10 + ang);
+    const double k[3] = {v[0] * inv, v[1] * inv, v[2] * inv};
+    const double Km[3][3] = {{0.0, -k[2], k[1]}, {k[2], 0.0, -k[0]}, {-k[1], k[0], 0.0}};
+    sn = sin(ang);
+    cs = cos(ang);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            double kk = 0.0;
+            for (int l = 0; l < 3; ++l) kk += Km[i][l] * Km[l][j];
+            K.m[i][j] = Km[i][j];
+            R.m[i][j] = (i == j ? 1.0 : 0.0) + sn * Km[i][j] + (1.0 - cs) * kk;
+        }
+    (void)c; (void)s;
+}
+
+__global__ void k_state_to_pose_fwd(const float *__restrict__ states, int P, float c, float s, float *__restrict__ poses) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float *st = states + (int64_t)p * 12;
+    const double v[3] = {st[6], st[7], st[8]};
+    PoseMat K, R;
+    double ang, sn, cs;
+    state_rotation(v, c, s, K, R, ang, sn, cs);
+    // XR = rot_x R: row 0 = R0, row 1 = c R1 - s R2, row 2 = s R1 + c R2
+    double XR[3][3];
+    for (int j = 0; j < 3; ++j) {
+        XR[0][j] = R.m[0][j];
+        XR[1][j] = (double)c * R.m[1][j] - (double)s * R.m[2][j];
+        XR[2][j] = (double)s * R.m[1][j] + (double)c * R.m[2][j];
+    }
+    // flip_yz A: rows (A1, A2, A0); A neg_yz: columns 1, 2 negated
+    float *out = poses + (int64_t)p * 16;
+    const int src[3] = {1, 2, 0};
+    for (int i = 0; i < 3; ++i) {
+        out[i * 4 + 0] = (float)XR[src[i]][0];
+        out[i * 4 + 1] = (float)-XR[src[i]][1];
+        out[i * 4 + 2] = (float)-XR[src[i]][2];
+        out[i * 4 + 3] = st[src[i]];   // flip_yz p = (p1, p2, p0)
+    }
+    out[12] = 0.0f; out[13] = 0.0f; out[14] = 0.0f; out[15] = 1.0f;
+}
+
+__global__ void k_state_to_pose_bwd(const float *__restrict__ states, const float *__restrict__ grad_poses, int P, float c, float s,
+                                    float *__restrict__ grad_states) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const float *st = states + (int64_t)p * 12;
+    const float *G = grad_poses + (int64_t)p * 16;
+    float *gs = grad_states + (int64_t)p * 12;
+    for (int i = 0; i < 12; ++i) gs[i] = 0.0f;   // velocity and angular velocity take no gradient from the measurement
+    const int src[3] = {1, 2, 0};
+    // translation: pose[i][3] = p[src[i]]
+    for (int i = 0; i < 3; ++i) gs[src[i]] = G[i * 4 + 3];
+    // dL/dXR[src[i]][j] = G[i][j] * (j == 0 ? 1 : -1)
+    double gXR[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) gXR[src[i]][j] = (double)G[i * 4 + j] * (j == 0 ? 1.0 : -1.0);
+    // dL/dR = rot_x^T dL/dXR
+    double gR[3][3];
+    for (int j = 0; j < 3; ++j) {
+        gR[0][j] = gXR[0][j];
+        gR[1][j] = (double)c * gXR[1][j] + (double)s * gXR[2][j];
+        gR[2][j] = -(double)s * gXR[1][j] + (double)c * gXR[2][j];
+    }
+    const double v[3] = {st[6], st[7], st[8]};
+    PoseMat K, R;
+    double ang, sn, cs;
+    state_rotation(v, c, s, K, R, ang, sn, cs);
+    if (!(ang > 0.0)) return;   // v = 0: K = 0, sin = 0, 1 - cos = 0 -> every path to v carries a zero factor
+    // R = I + sn K + (1 - cs) K K
+    double KK[3][3], gK[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            KK[i][j] = 0.0;
+            for (int l = 0; l < 3; ++l) KK[i][j] += K.m[i][l] * K.m[l][j];
+        }
+    double g_ang = 0.0;   // explicit dependence on the angle: dR/da = cs K + sn K K
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) g_ang += gR[i][j] * (cs * K.m[i][j] + sn * KK[i][j]);
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {   // d(K K)/dK: gR K^T + K^T gR
+            double a = 0.0, b = 0.0;
+            for (int l = 0; l < 3; ++l) {
+                a += gR[i][l] * K.m[j][l];
+                b += K.m[l][i] * gR[l][j];
+            }
+            gK[i][j] = sn * gR[i][j] + (1.0 - cs) * (a + b);
+        }
+    const double gk[3] = {gK[2][1] - gK[1][2], gK[0][2] - gK[2][0], gK[1][0] - gK[0][1]};
+    // k = v / (1e-10 + a), a = |v|
+    const double den = 1e-10 + ang;
+    const double gkv = gk[0] * v[0] + gk[1] * v[1] + gk[2] * v[2];
+    for (int j = 0; j < 3; ++j) gs[6 + j] = (float)(gk[j] / den - gkv * v[j] / (ang * den * den) + g_ang * v[j] / ang);
+}
+
+extern "C" int ngp_state_to_pose_forward(const float *states, int P, float cos_half_pi, float sin_half_pi, float *poses,
+                                         ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(states, "ngp_state_to_pose_forward");
+    if (P == 0) return NGP_OK;
+    NGP_REQUIRE(states && poses && P > 0, NGP_ERR_ARG, "ngp_state_to_pose_forward: null pointer / bad P");
+    k_state_to_pose_fwd<<<(unsigned)ngp_div_up((int64_t)P, 128), 128, 0, (cudaStream_t)stream>>>(states, P, cos_half_pi, sin_half_pi,
+                                                                                                poses);
+    NGP_CHECK_LAUNCH("ngp_state_to_pose_forward");
+    return NGP_OK;
+}
+
+extern "C" int ngp_state_to_pose_backward(const float *states, const float *grad_poses, int P, float cos_half_pi, float sin_half_pi,
+                                          float *grad_states, ngp_stream_t stream) {
+    NGP_REQUIRE_DEVICE(states, "ngp_state_to_pose_backward");
+    if (P == 0) return NGP_OK;
+    NGP_REQUIRE(states && grad_poses && grad_states && P > 0, NGP_ERR_ARG, "ngp_state_to_pose_backward: null pointer / bad P");
+    k_state_to_pose_bwd<<<(unsigned)ngp_div_up((int64_t)P, 128), 128, 0, (cudaStream_t)stream>>>(states, grad_poses, P, cos_half_pi,
+                                                                                                sin_half_pi, grad_states);
+    NGP_CHECK_LAUNCH("ngp_state_to_pose_backward");
+    return NGP_OK;
+}

@@ -294,3 +294,31 @@ def test_measurement_loss_backpropagates_to_states():
     s2 = states.detach().clone().requires_grad_(True)
     l2 = closures.measurement_loss(model, s2, pix, target, intr, 800, start_states=st0[None].cuda(), sig_inv=sig_inv, **kw)
     assert torch.allclose(l2.detach() - losses.detach(), 3.0 * (noise.cuda() ** 2).sum(-1), atol=1e-7)
+
+
+def test_state_to_pose_kernels_vs_torch_formulation():
+    """ngp_state_to_pose_forward / backward (one launch each) against the torch formulation of the same algebra in float64
+    (the one tests/golden/pose_algebra.npz pins to nav/math_utils.py): poses 1e-6, dL/dstate 1e-5, incl. the zero rotation
+    vector (identity, zero gradient), tiny and near-pi angles; velocity / angular-velocity gradients are exactly zero."""
+    from nerf_navigation_b200 import closures as C
+    g = torch.Generator().manual_seed(5)
+    P = 257
+    st = torch.randn(P, 12, generator=g)
+    st[:, 6:9] *= torch.rand(P, 1, generator=g) * 3.0
+    st[0, 6:9] = 0.0
+    st[1, 6:9] = torch.tensor([1e-6, -2e-6, 5e-7])
+    st[2, 6:9] = torch.tensor([3.1, 0.3, -0.2])
+    G = torch.randn(P, 4, 4, generator=g)
+    sd = st.double().requires_grad_(True)
+    pose_ref = C.state_to_pose(sd)                       # CPU float64: the host formulation
+    (pose_ref * G.double()).sum().backward()
+    sc = st.cuda().requires_grad_(True)
+    pose = C.state_to_pose(sc)                           # CUDA float32: the kernels
+    (pose * G.cuda()).sum().backward()
+    assert pose.shape == (P, 4, 4)
+    assert float((pose.cpu().double() - pose_ref.detach()).abs().max()) < 1e-6
+    gr, gk = sd.grad, sc.grad.cpu().double()
+    assert float((gk - gr).abs().max() / gr.abs().max()) < 1e-5
+    assert (gk[:, 3:6] == 0).all() and (gk[:, 9:12] == 0).all() and (gk[0, 6:9] == 0).all()
+    rows = (gk[:, 6:9] - gr[:, 6:9]).abs().amax(-1) / gr[:, 6:9].abs().amax(-1).clamp_min(1e-12)
+    assert float(rows[1:].max()) < 1e-4                  # per hypothesis, against its own scale
