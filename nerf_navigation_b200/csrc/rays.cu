@@ -497,6 +497,62 @@ k_march_train_bwd(const float *__restrict__ grad_xyzs, const float *__restrict__
     }
 }
 
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+// the same reduction with one WARP per ray (coalesced; the running t is a warp scan of deltas[:, 1])
+__global__ void __launch_bounds__(256)
+k_march_train_bwd_warp(const float *__restrict__ grad_xyzs, const float *__restrict__ grad_dirs,
+                       const float *__restrict__ rays_o, const float *__restrict__ rays_d, const float *__restrict__ nears,
+                       const float *__restrict__ deltas, const int32_t *__restrict__ rays, float bound, float dt_min,
+                       uint32_t perturb, int64_t N, int64_t M, float *__restrict__ grad_o, float *__restrict__ grad_d) {
+    const int64_t i = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (i >= N) return;
+    const int64_t n = rays[i * 3], off = rays[i * 3 + 1];
+    const uint32_t cnt = (uint32_t)rays[i * 3 + 2];
+    float go[3] = {0.f, 0.f, 0.f}, gd[3] = {0.f, 0.f, 0.f};
+    if (cnt != 0 && off + cnt < M) {
+        const float o[3] = {rays_o[n * 3], rays_o[n * 3 + 1], rays_o[n * 3 + 2]};
+        const float d[3] = {rays_d[n * 3], rays_d[n * 3 + 1], rays_d[n * 3 + 2]};
+        float tc = nears[n];
+        if (perturb) tc = fmaf(dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), tc);
+        for (uint32_t base = 0; base < cnt; base += 32) {
+            const uint32_t s = base + lane;
+            const bool in = s < cnt;
+            const int64_t k = off + s;
+            const float2 dl = in ? __ldg(reinterpret_cast<const float2 *>(deltas) + k) : make_float2(0.0f, 0.0f);
+            float te = dl.y;   // inclusive scan -> t_k + dt_k - t_start of the block
+#pragma unroll
+            for (int sh = 1; sh < 32; sh <<= 1) {
+                const float v = __shfl_up_sync(0xffffffffu, te, sh);
+                if (lane >= sh) te += v;
+            }
+            te += tc;
+            const float t = te - dl.x;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                const float p = fmaf(t, d[a], o[a]);
+                const float g = (in && p >= -bound && p <= bound) ? __ldg(grad_xyzs + k * 3 + a) : 0.0f;
+                go[a] += g;
+                gd[a] = fmaf(t, g, gd[a]);
+                if (grad_dirs && in) gd[a] += __ldg(grad_dirs + k * 3 + a);
+            }
+            tc = __shfl_sync(0xffffffffu, te, 31);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float so = warp_sum(go[a]), sd = warp_sum(gd[a]);
+        if (lane == 0) {
+            grad_o[n * 3 + a] = so;
+            grad_d[n * 3 + a] = sd;
+        }
+    }
+}
+
 extern "C" int ngp_march_rays_train_backward(const float *grad_xyzs, const float *grad_dirs, const float *rays_o,
                                              const float *rays_d, const float *nears, const float *deltas,
                                              const int32_t *rays, float bound, uint32_t max_steps, uint32_t perturb,
@@ -508,7 +564,7 @@ extern "C" int ngp_march_rays_train_backward(const float *grad_xyzs, const float
                 "ngp_march_rays_train_backward: null pointer");
     NGP_REQUIRE(M == 0 || (grad_xyzs && deltas), NGP_ERR_ARG, "ngp_march_rays_train_backward: null sample buffers");
     const float dt_min = 2.0f * 1.7320508075688772f / (float)max_steps;
-    k_march_train_bwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+    k_march_train_bwd_warp<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, (cudaStream_t)stream>>>(
         grad_xyzs, grad_dirs, rays_o, rays_d, nears, deltas, rays, bound, dt_min, perturb, N, M, grad_rays_o, grad_rays_d);
     NGP_CHECK_LAUNCH("ngp_march_rays_train_backward");
     return NGP_OK;
@@ -543,6 +599,58 @@ k_composite_train_fwd(const float *__restrict__ sigmas, const float *__restrict_
     weights_sum[id] = ws;
     depth[id] = d;
     image[id * 3] = r; image[id * 3 + 1] = g; image[id * 3 + 2] = b;
+}
+
+// One WARP per ray (lanes = 32 consecutive samples, coalesced loads; warp scans for the transmittance and the running t,
+// warp sums for the accumulators): the thread-per-ray loop above reads four strided streams per lane.
+__global__ void __launch_bounds__(256)
+k_composite_train_fwd_warp(const float *__restrict__ sigmas, const float *__restrict__ rgbs, const float *__restrict__ deltas,
+                           const int32_t *__restrict__ rays, int64_t M, int64_t N, float *__restrict__ weights_sum,
+                           float *__restrict__ depth, float *__restrict__ image) {
+    const int64_t n = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (n >= N) return;
+    const uint32_t id = (uint32_t)__ldg(rays + n * 3), off = (uint32_t)__ldg(rays + n * 3 + 1), cnt = (uint32_t)__ldg(rays + n * 3 + 2);
+    float r = 0.0f, g = 0.0f, b = 0.0f, ws = 0.0f, d = 0.0f;
+    if (cnt != 0 && (int64_t)off + cnt < M) {
+        float Tc = 1.0f, tc = 0.0f;
+        for (uint32_t base = 0; base < cnt; base += 32) {
+            const uint32_t s = base + lane;
+            const bool in = s < cnt;
+            const int64_t k = (int64_t)off + s;
+            const float2 dl = in ? __ldg(reinterpret_cast<const float2 *>(deltas) + k) : make_float2(0.0f, 0.0f);
+            const float alpha = in ? 1.0f - __expf(-__ldg(sigmas + k) * dl.x) : 0.0f;
+            float P = 1.0f - alpha, t = dl.y;   // inclusive scans: transmittance after the sample, t of the sample
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const float vp = __shfl_up_sync(0xffffffffu, P, o), vt = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) {
+                    P *= vp;
+                    t += vt;
+                }
+            }
+            float Pb = __shfl_up_sync(0xffffffffu, P, 1);
+            if (lane == 0) Pb = 1.0f;
+            const float w = alpha * (Tc * Pb), Tafter = Tc * P;
+            t += tc;
+            const unsigned brk = __ballot_sync(0xffffffffu, in && Tafter < 1e-4f);
+            const int last = brk ? __ffs(brk) - 1 : 31;   // the sample that saw T < 1e-4 is still accumulated (:560-570)
+            const bool use = in && lane <= last;
+            r += warp_sum(use ? w * __ldg(rgbs + k * 3) : 0.0f);
+            g += warp_sum(use ? w * __ldg(rgbs + k * 3 + 1) : 0.0f);
+            b += warp_sum(use ? w * __ldg(rgbs + k * 3 + 2) : 0.0f);
+            d += warp_sum(use ? w * t : 0.0f);
+            ws += warp_sum(use ? w : 0.0f);
+            if (brk) break;
+            Tc = __shfl_sync(0xffffffffu, Tafter, 31);
+            tc = __shfl_sync(0xffffffffu, t, 31);
+        }
+    }
+    if (lane == 0) {
+        weights_sum[id] = ws;
+        depth[id] = d;
+        image[id * 3] = r; image[id * 3 + 1] = g; image[id * 3 + 2] = b;
+    }
 }
 
 __global__ void __launch_bounds__(RAY_THREADS)
@@ -641,8 +749,17 @@ extern "C" int ngp_composite_rays_train_forward(const float *sigmas, const float
     if (N == 0) return NGP_OK;
     NGP_REQUIRE(rays && weights_sum && depth && image, NGP_ERR_ARG, "ngp_composite_rays_train_forward: null pointer");
     NGP_REQUIRE(M == 0 || (sigmas && rgbs && deltas), NGP_ERR_ARG, "ngp_composite_rays_train_forward: null samples");
-    k_composite_train_fwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
-        sigmas, rgbs, deltas, rays, M, N, weights_sum, depth, image);
+    static int serial = -1;   // NGP_B200_COMPOSITE_BWD=serial also selects the thread-per-ray forward
+    if (serial < 0) {
+        const char *e = getenv("NGP_B200_COMPOSITE_BWD");
+        serial = (e && strcmp(e, "serial") == 0) ? 1 : 0;
+    }
+    if (serial)
+        k_composite_train_fwd<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, (cudaStream_t)stream>>>(
+            sigmas, rgbs, deltas, rays, M, N, weights_sum, depth, image);
+    else
+        k_composite_train_fwd_warp<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+            sigmas, rgbs, deltas, rays, M, N, weights_sum, depth, image);
     NGP_CHECK_LAUNCH("ngp_composite_rays_train_forward");
     return NGP_OK;
 }
