@@ -415,6 +415,14 @@ def run_b200(args):
         del xc, xs, q, key
 
     # ---- end-to-end: public API, pinned host input, H2D + D2H inside the timed region
+    # The rank's thread is bound to the CPUs of its GPU's NUMA node for this leg (nerf_navigation_b200/hostmem.py): the
+    # pinned buffers below and the ones the host-fed query allocates are first touched here, so they land on the
+    # memory of the socket the GPU hangs off (eight ranks otherwise share one socket's controllers and the
+    # inter-socket link).  Affinity is restored after the leg (the CPU legs use every core).
+    from nerf_navigation_b200 import hostmem
+    numa_info = hostmem.describe(dev)
+    numa_ctx = hostmem.numa_local(dev)
+    numa_ctx.__enter__()
     xh = x.cpu().pin_memory()
     gxh = torch.empty(B, 3).pin_memory()
     xd = torch.empty(B, 3, device=dev)
@@ -488,6 +496,7 @@ def run_b200(args):
     e3.record()
     barrier()
     t_e2e = e2.elapsed_time(e3) / 1e3
+    numa_ctx.__exit__(None, None, None)
     t_end = time.perf_counter()
     clocks = sampler.stop(t_begin, t_end) if sampler else None
 
@@ -668,6 +677,8 @@ def run_b200(args):
                    "l2": "streams ~400 MB/step (> 126 MB L2) of points/outputs; the 48 MiB table is L2-resident by design"},
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": B * 12, "d2h_bytes_per_step": B * 12 + 4,
                 "steps": e2e_steps,
+                "numa": dict(numa_info, what="rank 0's GPU -> NUMA node (sysfs); each rank binds its thread to its node's CPUs "
+                                             "for this leg so the pinned buffers are first touched there (hostmem.numa_local)"),
                 "api": "the reference-level call on host data: x = pinned host tensor; s = NeRFNetwork.density(x)['sigma']; "
                        "(s ** 2).mean().backward(); x.grad (pinned host) + loss.item() — uploads pipelined with the "
                        "(Jacobian-returning) forward kernels, downloads with the backward kernels, inside density() itself",

@@ -103,25 +103,52 @@ __device__ __forceinline__ MarchRay load_ray(const float *__restrict__ rays_o, c
     return r;
 }
 
-// pass 1: per-ray sample count (and jittered start t0 when perturb)
+// pass 1: per-ray sample count (and jittered start t0 when perturb).  SEGS: the pass also leaves the ray's RUNS — maximal
+// stretches of consecutive samples, (t of the first sample, length) — in segs[run * N + ray] (coalesced across the rays of a
+// warp) and their number in nseg[ray].  Inside a run t_{k+1} = t_k + clamp(t_k dt_gamma, dt_min, dt_max) and nothing else,
+// so the write pass (k_march_replay) rebuilds the samples from the runs without looking at the occupancy grid again.  A ray
+// with more than MARCH_SEG_CAP runs keeps its count in nseg and is marched again by the write pass.
+#ifndef MARCH_SEG_CAP
+#define MARCH_SEG_CAP 16
+#endif
+template <bool SEGS>
 __global__ void __launch_bounds__(RAY_THREADS)
 k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, uint32_t max_steps,
               int64_t N, const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
-              int32_t *__restrict__ counts, float *__restrict__ t_first) {
+              int32_t *__restrict__ counts, float *__restrict__ t_first, int32_t *__restrict__ nseg,
+              float2 *__restrict__ segs) {
     const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
     if (n >= N) return;
     const MarchRay r = load_ray(rays_o, rays_d, n);
     float t = nears[n];
     if (perturb) t = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t);  // :352-355, seed :489
     const float far = fars[n];
-    uint32_t steps = 0;
-    float px, py, pz, dt, tf = t;
+    uint32_t steps = 0, run_start = 0;
+    int32_t runs = 0;
+    bool in_run = false;
+    float px, py, pz, dt, tf = t, run_t = t;
     while (t < far && steps < max_steps) {
         if (ngp_march_step(r, cfg, t, px, py, pz, dt)) {
             if (steps == 0) tf = t;   // the march is memoryless in t: pass 2 resumes here, skipping the leading empty space
+            if (SEGS && !in_run) {
+                in_run = true;
+                run_t = t;
+                run_start = steps;
+            }
             ++steps;
             t += dt;
+        } else if (SEGS && in_run) {
+            if (runs < MARCH_SEG_CAP) segs[(int64_t)runs * N + n] = make_float2(run_t, __int_as_float((int)(steps - run_start)));
+            ++runs;
+            in_run = false;
         }
+    }
+    if (SEGS) {
+        if (in_run) {
+            if (runs < MARCH_SEG_CAP) segs[(int64_t)runs * N + n] = make_float2(run_t, __int_as_float((int)(steps - run_start)));
+            ++runs;
+        }
+        nseg[n] = runs;
     }
     counts[n] = (int32_t)steps;
     t_first[n] = tf;
@@ -272,6 +299,83 @@ k_march_expand(const float *__restrict__ rays_o, const float *__restrict__ rays_
     }
 }
 
+// Write pass from the runs of k_march_count<true>: one WARP per ray.  Lane j replays run j — t_{k+1} = t_k + dt(t_k), the
+// marcher's own recurrence, no occupancy lookups — and leaves (t_k, deltas_k) at the ray's offset plus the lengths of the
+// runs before it; the first delta of a run is measured from the end of the run before (from the ray's start for run 0), as
+// the marcher's last_t is (:470-473).  Then all 32 lanes expand the parameters into positions and directions, as
+// k_march_expand does.  Same values as k_march_write, bit for bit: the same float operations in the same order per
+// sample.  A ray with more runs than MARCH_SEG_CAP is marched by lane 0 the way k_march_write marches it.
+__global__ void __launch_bounds__(256)
+k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
+               const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
+               const int32_t *__restrict__ rays, const int32_t *__restrict__ nseg, const float2 *__restrict__ segs,
+               float *xyzs, float *__restrict__ dirs, float *__restrict__ deltas) {
+    const int64_t n = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (n >= N) return;
+    const int64_t off = rays[n * 3 + 1];
+    const uint32_t cnt = (uint32_t)rays[n * 3 + 2];
+    if (cnt == 0 || off + cnt >= M) return;  // :419-420
+    const MarchRay r = load_ray(rays_o, rays_d, n);
+    float t0 = nears[n];
+    if (perturb) t0 = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t0);
+    const int ns = nseg[n];
+    if (ns <= MARCH_SEG_CAP) {
+        float t = 0.0f;
+        int len = 0;
+        if (lane < ns) {
+            const float2 sg = __ldg(segs + (int64_t)lane * N + n);
+            t = sg.x;
+            len = __float_as_int(sg.y);
+        }
+        int pre = len;   // inclusive scan of the run lengths
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, pre, o);
+            if (lane >= o) pre += v;
+        }
+        const int64_t k0 = off + (pre - len);
+        float dt0 = 0.0f, t1 = 0.0f;   // step and end of the run's first sample
+        for (int i = 0; i < len; ++i) {
+            const float dt = ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+            const float tn = t + dt;
+            xyzs[(k0 + i) * 3] = t;
+            if (i == 0) {
+                dt0 = dt;
+                t1 = tn;
+            } else {
+                *reinterpret_cast<float2 *>(deltas + (k0 + i) * 2) = make_float2(dt, tn - t);
+            }
+            t = tn;
+        }
+        float prev_end = __shfl_up_sync(0xffffffffu, t, 1);   // where the run before stopped
+        if (lane == 0) prev_end = t0;
+        if (len > 0) *reinterpret_cast<float2 *>(deltas + k0 * 2) = make_float2(dt0, t1 - prev_end);
+    } else if (lane == 0) {
+        float last_t = t0, t = __ldg(segs + n).x, px, py, pz, dt;   // run 0 starts at the first occupied sample
+        const float far = fars[n];
+        uint32_t step = 0;
+        while (t < far && step < cnt) {
+            if (!ngp_march_step(r, cfg, t, px, py, pz, dt)) continue;
+            const int64_t k = off + step;
+            xyzs[k * 3] = t;
+            t += dt;
+            *reinterpret_cast<float2 *>(deltas + k * 2) = make_float2(dt, t - last_t);
+            last_t = t;
+            ++step;
+        }
+    }
+    __syncwarp();   // the parameters written above are read by other lanes below
+    for (uint32_t s = lane; s < cnt; s += 32) {
+        const int64_t k = off + s;
+        const float t = xyzs[k * 3];
+        xyzs[k * 3] = ngp_clampf(fmaf(t, r.dx, r.ox), -cfg.bound, cfg.bound);
+        xyzs[k * 3 + 1] = ngp_clampf(fmaf(t, r.dy, r.oy), -cfg.bound, cfg.bound);
+        xyzs[k * 3 + 2] = ngp_clampf(fmaf(t, r.dz, r.oz), -cfg.bound, cfg.bound);
+        dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+    }
+}
+
 // ---- warp-per-ray variants for small ray batches (training step: 4096 rays; the estimator's real use: 1024 rays).
 // With one thread per ray a batch of a few thousand rays is pure latency: < 1 warp per SM walking ~10^3 dependent
 // steps.  The parameter sequence t_k of a ray does not depend on the occupancy (march.cuh: ngp_march_advance), so the 32
@@ -378,8 +482,19 @@ k_march_write_warp(const float *__restrict__ rays_o, const float *__restrict__ r
     march_ray_warp<true>(r, cfg, t_first[n], fars[n], cnt, t, off, xyzs, dirs, deltas, tf);
 }
 
+// workspace: counts [N], tile totals [tiles + 8], t_first [N]; for batches marched one thread per ray also nseg [N] and,
+// 8-byte aligned, segs [MARCH_SEG_CAP][N] (only the runs that exist are touched)
+static int64_t march_ws_head_words(int64_t N) { return 2 * N + ngp_div_up(N, SCAN_TILE) + 8; }
+static int64_t march_ws_segs_offset(int64_t N) { return ((march_ws_head_words(N) + N) * 4 + 7) & ~(int64_t)7; }
+// NGP_B200_MARCH_WRITE=remarch: the write pass marches the grid again (k_march_write + k_march_expand, the form before
+// the runs existed) — kept as the cross-check of k_march_replay (tests/test_rays_gpu.py compares the two bit for bit)
+static bool march_write_remarch() {
+    const char *e = getenv("NGP_B200_MARCH_WRITE");
+    return e && strcmp(e, "remarch") == 0;
+}
 extern "C" int64_t ngp_march_rays_train_workspace_bytes(int64_t N) {
-    return (2 * N + ngp_div_up(N, SCAN_TILE) + 8) * (int64_t)sizeof(int32_t);  // counts, tile totals, t_first
+    if (N <= MARCH_WARP_MAX_RAYS) return march_ws_head_words(N) * (int64_t)sizeof(int32_t);
+    return march_ws_segs_offset(N) + (int64_t)MARCH_SEG_CAP * N * (int64_t)sizeof(float2);
 }
 
 extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound,
@@ -405,20 +520,25 @@ extern "C" int ngp_march_rays_train(const float *rays_o, const float *rays_d, co
     const unsigned gr = (unsigned)ngp_div_up(N, RAY_THREADS);
     const bool by_warp = N <= MARCH_WARP_MAX_RAYS;
     const unsigned gw = (unsigned)ngp_div_up(N * 32, RAY_THREADS);
+    int32_t *nseg = (int32_t *)workspace + march_ws_head_words(N);
+    float2 *segs = (float2 *)((char *)workspace + march_ws_segs_offset(N));
     if (by_warp)
         k_march_count_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
     else
-        k_march_count<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first);
+        k_march_count<true><<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, max_steps, N, nears, fars, perturb, counts, t_first,
+                                                        nseg, segs);
     k_scan_tile_totals<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, N, tile_totals);
     k_scan_totals<<<1, SCAN_THREADS, 0, st>>>(tile_totals, n_tiles, counter, N);
     k_scan_write_rays<<<(unsigned)n_tiles, SCAN_THREADS, 0, st>>>(counts, tile_totals, N, rays);
     if (M > 0) {
         if (by_warp)
             k_march_write_warp<<<gw, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
-        else {
+        else if (march_write_remarch()) {
             k_march_write<<<gr, RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, t_first, xyzs, dirs, deltas);
             k_march_expand<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, st>>>(rays_o, rays_d, bound, N, M, rays, xyzs, dirs);
-        }
+        } else
+            k_march_replay<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays,
+                                                                              nseg, segs, xyzs, dirs, deltas);
     }
     NGP_CHECK_LAUNCH("ngp_march_rays_train");
     return NGP_OK;
@@ -445,11 +565,14 @@ extern "C" int ngp_march_rays_train_write(const float *rays_o, const float *rays
     if (N <= MARCH_WARP_MAX_RAYS)
         k_march_write_warp<<<(unsigned)ngp_div_up(N * 32, RAY_THREADS), RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars,
                                                                                               perturb, rays, t_first, xyzs, dirs, deltas);
-    else {
+    else if (march_write_remarch()) {
         k_march_write<<<(unsigned)ngp_div_up(N, RAY_THREADS), RAY_THREADS, 0, st>>>(rays_o, rays_d, cfg, N, M, nears, fars, perturb,
                                                                                     rays, t_first, xyzs, dirs, deltas);
         k_march_expand<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, st>>>(rays_o, rays_d, bound, N, M, rays, xyzs, dirs);
-    }
+    } else
+        k_march_replay<<<(unsigned)ngp_div_up(N * 32, 256), 256, 0, st>>>(
+            rays_o, rays_d, cfg, N, M, nears, fars, perturb, rays, (const int32_t *)workspace + march_ws_head_words(N),
+            (const float2 *)((const char *)workspace + march_ws_segs_offset(N)), xyzs, dirs, deltas);
     NGP_CHECK_LAUNCH("ngp_march_rays_train_write");
     return NGP_OK;
 }

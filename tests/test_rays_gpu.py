@@ -102,6 +102,58 @@ def test_march_rays_train_both_kernels_and_cone_steps(ngp, oracle, scene, N, dt_
         assert torch.equal(x2[:m2], xyzs[:m2]) and torch.equal(dl2[:m2], deltas[:m2])
 
 
+@pytest.mark.parametrize("grid_kind,dt_gamma", [("scene", 1.0 / 128), ("scene", 0.0), ("noise", 0.0), ("noise", 1.0 / 64)])
+def test_march_write_pass_from_runs(ngp, oracle, scene, grid_kind, dt_gamma, monkeypatch):
+    """Thread-per-ray form (N > 8192): the count pass leaves each ray's runs of consecutive samples and the write pass
+    (k_march_replay) rebuilds the samples from them without reading the grid.  Bit for bit the oracle's samples, and the
+    samples of the write pass that marches again (NGP_B200_MARCH_WRITE=remarch), directions included.  A random
+    occupancy grid gives most rays more runs than MARCH_SEG_CAP (16): those take the kernel's in-place march.  The
+    one-call form with a sample budget drops the same rays as the reference (raymarching.cu:419-420)."""
+    from nerf_navigation_b200 import raymarching as rm
+    if grid_kind == "scene":
+        bits = scene[1]
+    else:
+        bits = np.random.default_rng(5).integers(0, 256, size=CAS * H ** 3 // 8, dtype=np.uint8)
+    N, max_steps = 9000, 256
+    o, d = _rays(N, 11)
+    aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
+    nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
+    rx, rd, rdl, rrays, rcnt = oracle.march_rays_train(o, d, BOUND, bits, CAS, H, nears, fars, N * max_steps, dt_gamma=dt_gamma,
+                                                       max_steps=max_steps, perturb=True)
+    m = int(rcnt[0])
+    assert m > 0
+    t = lambda a: torch.from_numpy(a).cuda()
+
+    def run(mean_count, force_all):
+        counter = torch.zeros(2, dtype=torch.int32, device="cuda")
+        out = rm.march_rays_train(t(o), t(d), BOUND, t(bits), CAS, H, t(nears), t(fars), counter, mean_count, True, 128,
+                                  force_all, dt_gamma, max_steps)
+        return out, counter
+
+    (xyzs, dirs, deltas, rays), counter = run(-1, True)
+    assert np.array_equal(rays.cpu().numpy(), rrays) and np.array_equal(counter.cpu().numpy(), rcnt)
+    assert np.array_equal(xyzs[:m].cpu().numpy(), rx[:m]) and np.array_equal(deltas[:m].cpu().numpy(), rdl[:m])
+    assert np.array_equal(dirs[:m].cpu().numpy(), rd[:m])
+    if grid_kind == "noise":      # the point of the random grid: rays with more than 16 runs
+        cnt = rrays[:, 2]
+        gaps = np.array([np.count_nonzero(rdl[a:a + c, 1] > 1.5 * rdl[a:a + c, 0]) for _, a, c in rrays[:200]])   # run starts
+        assert cnt.max() > 16 and gaps.max() > 16
+    budget = (m // 2) - (m // 2) % 128
+    (bx, bd, bdl, brays), _ = run(budget, False)          # one call, count + scan + write, M = budget + 128
+    monkeypatch.setenv("NGP_B200_MARCH_WRITE", "remarch")
+    (x2, d2, dl2, r2), _ = run(-1, True)
+    (bx2, bd2, bdl2, brays2), _ = run(budget, False)
+    monkeypatch.delenv("NGP_B200_MARCH_WRITE")
+    assert torch.equal(r2, rays) and torch.equal(x2, xyzs) and torch.equal(d2, dirs) and torch.equal(dl2, deltas)
+    assert torch.equal(brays2, brays) and torch.equal(bx2, bx) and torch.equal(bd2, bd) and torch.equal(bdl2, bdl)
+    M = bx.shape[0]
+    kept = (rrays[:, 1].astype(np.int64) + rrays[:, 2] < M) & (rrays[:, 2] > 0)
+    assert 0 < kept.sum() < N
+    last = rrays[kept][-1]
+    end = int(last[1] + last[2])
+    assert np.array_equal(bx[:end].cpu().numpy(), rx[:end]) and float(bx[end:].abs().max()) == 0.0
+
+
 def test_march_budget_drops_rays_like_reference(ngp, oracle, scene):
     """mean_count budget: rays whose offset+count >= M write nothing (raymarching.cu:420)."""
     from nerf_navigation_b200 import raymarching as rm
