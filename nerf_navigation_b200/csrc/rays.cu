@@ -117,6 +117,14 @@ k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d
               int64_t N, const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
               int32_t *__restrict__ counts, float *__restrict__ t_first, int32_t *__restrict__ nseg,
               float2 *__restrict__ segs) {
+    // the marcher iteration of march.cuh in its cheaper, value-identical form (ngp_march_cell_fast / ngp_march_exit_fast:
+    // levels from the exponent bits, min(2^level, bound) and its reciprocal from tables, no Morton decode for the exit)
+    __shared__ float mipb[8], miprb[8];
+    if (threadIdx.x < 8) {
+        mipb[threadIdx.x] = fminf((float)(1 << threadIdx.x), cfg.bound);
+        miprb[threadIdx.x] = 1.0f / mipb[threadIdx.x];
+    }
+    __syncthreads();
     const int64_t n = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
     if (n >= N) return;
     const MarchRay r = load_ray(rays_o, rays_d, n);
@@ -126,9 +134,14 @@ k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d
     uint32_t steps = 0, run_start = 0;
     int32_t runs = 0;
     bool in_run = false;
-    float px, py, pz, dt, tf = t, run_t = t;
+    float tf = t, run_t = t;
+#pragma unroll 1
     while (t < far && steps < max_steps) {
-        if (ngp_march_step(r, cfg, t, px, py, pz, dt)) {
+        float dt;
+        int lvl;
+        uint32_t nxyz;
+        const uint32_t cell = ngp_march_cell_fast(r, cfg, miprb, t, dt, lvl, nxyz);
+        if ((__ldg(cfg.grid + (cell >> 3)) >> (cell & 7u)) & 1u) {
             if (steps == 0) tf = t;   // the march is memoryless in t: pass 2 resumes here, skipping the leading empty space
             if (SEGS && !in_run) {
                 in_run = true;
@@ -137,10 +150,22 @@ k_march_count(const float *__restrict__ rays_o, const float *__restrict__ rays_d
             }
             ++steps;
             t += dt;
-        } else if (SEGS && in_run) {
-            if (runs < MARCH_SEG_CAP) segs[(int64_t)runs * N + n] = make_float2(run_t, __int_as_float((int)(steps - run_start)));
-            ++runs;
-            in_run = false;
+        } else {
+            if (SEGS && in_run) {
+                if (runs < MARCH_SEG_CAP) segs[(int64_t)runs * N + n] = make_float2(run_t, __int_as_float((int)(steps - run_start)));
+                ++runs;
+                in_run = false;
+            }
+            const float tt = ngp_march_exit_fast(r, cfg, mipb, t, nxyz, lvl);
+            if (cfg.lvl_dt >= 0) {    // raymarching.cu:398-402; dt_gamma == 0: the step is dt_min
+                do {
+                    t += cfg.dt_min;
+                } while (t < tt);
+            } else {
+                do {
+                    t = ngp_march_advance(t, cfg);
+                } while (t < tt);
+            }
         }
     }
     if (SEGS) {
