@@ -324,17 +324,20 @@ k_march_expand(const float *__restrict__ rays_o, const float *__restrict__ rays_
     }
 }
 
-// Write pass from the runs of k_march_count<true>: one WARP per ray.  Lane j replays run j — t_{k+1} = t_k + dt(t_k), the
-// marcher's own recurrence, no occupancy lookups — and leaves (t_k, deltas_k) at the ray's offset plus the lengths of the
-// runs before it; the first delta of a run is measured from the end of the run before (from the ray's start for run 0), as
-// the marcher's last_t is (:470-473).  Then all 32 lanes expand the parameters into positions and directions, as
-// k_march_expand does.  Same values as k_march_write, bit for bit: the same float operations in the same order per
-// sample.  A ray with more runs than MARCH_SEG_CAP is marched by lane 0 the way k_march_write marches it.
+// Write pass from the runs of k_march_count<true>: one WARP per ray.  Phase 1: lane j replays run j — t_{k+1} = t_k +
+// dt(t_k), the marcher's own recurrence, no occupancy lookups — and leaves the parameters t_k in the warp's shared-memory
+// strip (in xyzs[k][0] for a ray with more than MARCH_REPLAY_STRIP samples); a ray with more runs than MARCH_SEG_CAP is
+// marched by lane 0 the way k_march_write marches it.  Phase 2: lanes = consecutive samples, everything else follows
+// from t_k alone and is stored coalesced: dt_k = dt(t_k), the position clamp(o + t_k d), the direction, and
+// deltas_k = (dt_k, (t_k + dt_k) - (t_{k-1} + dt_{k-1})) with the ray's start for k = 0 — the marcher's t - last_t
+// (:470-473), since inside a run t_{k-1} + dt_{k-1} IS t_k.  Same float operations per sample as k_march_write: same bits.
+#define MARCH_REPLAY_STRIP 1024
 __global__ void __launch_bounds__(256)
 k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
                const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
                const int32_t *__restrict__ rays, const int32_t *__restrict__ nseg, const float2 *__restrict__ segs,
                float *xyzs, float *__restrict__ dirs, float *__restrict__ deltas) {
+    __shared__ float strips[8][MARCH_REPLAY_STRIP];
     const int64_t n = ((int64_t)blockIdx.x * 256 + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (n >= N) return;
@@ -344,6 +347,8 @@ k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_
     const MarchRay r = load_ray(rays_o, rays_d, n);
     float t0 = nears[n];
     if (perturb) t0 = fmaf(cfg.dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), t0);
+    const bool in_strip = cnt <= MARCH_REPLAY_STRIP;
+    float *strip = strips[(threadIdx.x >> 5) & 7];
     const int ns = nseg[n];
     if (ns <= MARCH_SEG_CAP) {
         float t = 0.0f;
@@ -359,45 +364,49 @@ k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_
             const int v = __shfl_up_sync(0xffffffffu, pre, o);
             if (lane >= o) pre += v;
         }
-        const int64_t k0 = off + (pre - len);
-        float dt0 = 0.0f, t1 = 0.0f;   // step and end of the run's first sample
-        for (int i = 0; i < len; ++i) {
-            const float dt = ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
-            const float tn = t + dt;
-            xyzs[(k0 + i) * 3] = t;
-            if (i == 0) {
-                dt0 = dt;
-                t1 = tn;
-            } else {
-                *reinterpret_cast<float2 *>(deltas + (k0 + i) * 2) = make_float2(dt, tn - t);
+        const int s0 = pre - len;
+        if (in_strip) {
+            for (int i = 0; i < len; ++i) {
+                strip[s0 + i] = t;
+                t += ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
             }
-            t = tn;
+        } else {
+            for (int i = 0; i < len; ++i) {
+                xyzs[(off + s0 + i) * 3] = t;
+                t += ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+            }
         }
-        float prev_end = __shfl_up_sync(0xffffffffu, t, 1);   // where the run before stopped
-        if (lane == 0) prev_end = t0;
-        if (len > 0) *reinterpret_cast<float2 *>(deltas + k0 * 2) = make_float2(dt0, t1 - prev_end);
     } else if (lane == 0) {
-        float last_t = t0, t = __ldg(segs + n).x, px, py, pz, dt;   // run 0 starts at the first occupied sample
+        float t = __ldg(segs + n).x, px, py, pz, dt;   // run 0 starts at the first occupied sample
         const float far = fars[n];
         uint32_t step = 0;
         while (t < far && step < cnt) {
             if (!ngp_march_step(r, cfg, t, px, py, pz, dt)) continue;
-            const int64_t k = off + step;
-            xyzs[k * 3] = t;
+            if (in_strip) strip[step] = t;
+            else xyzs[(off + step) * 3] = t;
             t += dt;
-            *reinterpret_cast<float2 *>(deltas + k * 2) = make_float2(dt, t - last_t);
-            last_t = t;
             ++step;
         }
     }
     __syncwarp();   // the parameters written above are read by other lanes below
-    for (uint32_t s = lane; s < cnt; s += 32) {
+    float carry = t0;   // t + dt of the sample before this block of 32 (the ray's start before the first)
+    for (uint32_t base = 0; base < cnt; base += 32) {
+        const uint32_t s = base + lane;
+        const bool in = s < cnt;
         const int64_t k = off + s;
-        const float t = xyzs[k * 3];
-        xyzs[k * 3] = ngp_clampf(fmaf(t, r.dx, r.ox), -cfg.bound, cfg.bound);
-        xyzs[k * 3 + 1] = ngp_clampf(fmaf(t, r.dy, r.oy), -cfg.bound, cfg.bound);
-        xyzs[k * 3 + 2] = ngp_clampf(fmaf(t, r.dz, r.oz), -cfg.bound, cfg.bound);
-        dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+        const float t = !in ? 0.0f : (in_strip ? strip[s] : xyzs[k * 3]);
+        const float dt = ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
+        const float tn = t + dt;
+        float prev = __shfl_up_sync(0xffffffffu, tn, 1);
+        if (lane == 0) prev = carry;
+        carry = __shfl_sync(0xffffffffu, tn, 31);
+        if (in) {
+            xyzs[k * 3] = ngp_clampf(fmaf(t, r.dx, r.ox), -cfg.bound, cfg.bound);
+            xyzs[k * 3 + 1] = ngp_clampf(fmaf(t, r.dy, r.oy), -cfg.bound, cfg.bound);
+            xyzs[k * 3 + 2] = ngp_clampf(fmaf(t, r.dz, r.oz), -cfg.bound, cfg.bound);
+            dirs[k * 3] = r.dx; dirs[k * 3 + 1] = r.dy; dirs[k * 3 + 2] = r.dz;
+            *reinterpret_cast<float2 *>(deltas + k * 2) = make_float2(dt, tn - prev);
+        }
     }
 }
 

@@ -102,19 +102,24 @@ def test_march_rays_train_both_kernels_and_cone_steps(ngp, oracle, scene, N, dt_
         assert torch.equal(x2[:m2], xyzs[:m2]) and torch.equal(dl2[:m2], deltas[:m2])
 
 
-@pytest.mark.parametrize("grid_kind,dt_gamma", [("scene", 1.0 / 128), ("scene", 0.0), ("noise", 0.0), ("noise", 1.0 / 64)])
-def test_march_write_pass_from_runs(ngp, oracle, scene, grid_kind, dt_gamma, monkeypatch):
+@pytest.mark.parametrize("grid_kind,dt_gamma,max_steps", [("scene", 1.0 / 128, 256), ("scene", 0.0, 256), ("noise", 0.0, 256),
+                                                          ("noise", 1.0 / 64, 256), ("full", 0.0, 3000), ("noise", 0.0, 3000)])
+def test_march_write_pass_from_runs(ngp, oracle, scene, grid_kind, dt_gamma, max_steps, monkeypatch):
     """Thread-per-ray form (N > 8192): the count pass leaves each ray's runs of consecutive samples and the write pass
     (k_march_replay) rebuilds the samples from them without reading the grid.  Bit for bit the oracle's samples, and the
     samples of the write pass that marches again (NGP_B200_MARCH_WRITE=remarch), directions included.  A random
     occupancy grid gives most rays more runs than MARCH_SEG_CAP (16): those take the kernel's in-place march.  The
-    one-call form with a sample budget drops the same rays as the reference (raymarching.cu:419-420)."""
+    one-call form with a sample budget drops the same rays as the reference (raymarching.cu:419-420).  max_steps = 3000
+    gives rays with more samples than the kernel's 1024-entry shared-memory strip (a fully occupied grid: one long run
+    per ray; the random grid: the in-place march)."""
     from nerf_navigation_b200 import raymarching as rm
     if grid_kind == "scene":
         bits = scene[1]
+    elif grid_kind == "full":
+        bits = np.full(CAS * H ** 3 // 8, 255, np.uint8)
     else:
         bits = np.random.default_rng(5).integers(0, 256, size=CAS * H ** 3 // 8, dtype=np.uint8)
-    N, max_steps = 9000, 256
+    N = 9000
     o, d = _rays(N, 11)
     aabb = np.array([-BOUND] * 3 + [BOUND] * 3, np.float32)
     nears, fars = oracle.near_far_from_aabb(o, d, aabb, 0.2)
@@ -138,6 +143,8 @@ def test_march_write_pass_from_runs(ngp, oracle, scene, grid_kind, dt_gamma, mon
         cnt = rrays[:, 2]
         gaps = np.array([np.count_nonzero(rdl[a:a + c, 1] > 1.5 * rdl[a:a + c, 0]) for _, a, c in rrays[:200]])   # run starts
         assert cnt.max() > 16 and gaps.max() > 16
+    if max_steps > 1024:
+        assert rrays[:, 2].max() > 1024
     budget = (m // 2) - (m // 2) % 128
     (bx, bd, bdl, brays), _ = run(budget, False)          # one call, count + scan + write, M = budget + 128
     monkeypatch.setenv("NGP_B200_MARCH_WRITE", "remarch")
