@@ -181,7 +181,10 @@ int ngp_packbits(const float *grid, int64_t N, float thresh, uint8_t *bitfield, 
 /* march_rays_train (raymarching.cu:313-495).  Deterministic: rays[n] = (n, offset, count) with offsets the exclusive
  * scan of counts in ray order starting at counter[0]; counter[0] += total samples, counter[1] += N.  xyzs/dirs [M,3],
  * deltas [M,2] must be pre-zeroed by the caller (raymarching.py:209-211); a ray with offset+count >= M writes nothing.
- * workspace: ngp_march_rays_train_workspace_bytes(N) bytes of device scratch. */
+ * workspace: ngp_march_rays_train_workspace_bytes(N) bytes of device scratch: per-ray counts, scan totals and first-sample
+ * parameters (about 8 N bytes) and, for N > 8192 (one thread per ray), room for 16 runs of consecutive samples per ray
+ * (132 N bytes more, of which only the runs that exist are touched): the count pass leaves each ray's runs there and the
+ * write pass rebuilds the samples from them instead of marching the occupancy grid a second time. */
 int64_t ngp_march_rays_train_workspace_bytes(int64_t N);
 int ngp_march_rays_train(const float *rays_o, const float *rays_d, const uint8_t *grid, float bound, float dt_gamma,
                          uint32_t max_steps, int64_t N, uint32_t C, uint32_t H, int64_t M, const float *nears,

@@ -11,8 +11,9 @@ from device tensors (nav/quad_plot.py:224-250) and runs one process on one GPU.
         x_host = torch.empty(B, 3).pin_memory()
         hq = HostFieldQuery(model, B)
 
-Everything here is host-side bookkeeping read from sysfs; where sysfs has no answer (numa_node = -1 in a VM, no
-/sys/bus/pci) the context manager does nothing and `describe()` says so.
+Everything here is host-side bookkeeping read from sysfs, with NVML's ideal CPU affinity of the GPU as the second source
+(containers often hide the PCI device's numa_node); where neither has an answer (numa_node = -1 in a VM, an NVML set
+that covers every CPU) the context manager does nothing and `describe()` says so.
 """
 import contextlib
 import os
@@ -65,25 +66,56 @@ def node_cpus(node, sysfs="/sys"):
     return cpus & os.sched_getaffinity(0)
 
 
-def describe(device, sysfs="/sys"):
-    """What numa_local(device) would do, for the bench line: {'pci', 'node', 'cpus', 'bound'}."""
+def nvml_cpus(device):
+    """The driver's own answer (NVML's ideal CPU affinity of the GPU, what `nvidia-smi topo -m` prints), for boxes whose
+    sysfs hides the PCI device's numa_node (containers): the CPUs in it that this process may run on, or an empty set.
+    An answer that covers the whole current affinity carries no placement information and counts as none."""
+    addr = pci_address(device)
+    if addr is None:
+        return set()
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(addr.encode())
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(os.cpu_count() or 64, 64) + 63) // 64)
+        finally:
+            pynvml.nvmlShutdown()
+    except Exception:
+        return set()
+    cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+    mine = os.sched_getaffinity(0)
+    cpus &= mine
+    return set() if cpus == mine else cpus
+
+
+def _local_cpus(device, sysfs):
     node = gpu_numa_node(device, sysfs)
     cpus = node_cpus(node, sysfs) if node is not None else set()
-    return {"pci": pci_address(device), "node": node, "cpus": len(cpus), "bound": bool(cpus)}
+    source = "sysfs" if cpus else None
+    if not cpus:
+        cpus = nvml_cpus(device)
+        source = "nvml" if cpus else None
+    return node, cpus, source
+
+
+def describe(device, sysfs="/sys"):
+    """What numa_local(device) would do, for the bench line: {'pci', 'node', 'cpus', 'bound', 'source'}."""
+    node, cpus, source = _local_cpus(device, sysfs)
+    return {"pci": pci_address(device), "node": node, "cpus": len(cpus), "bound": bool(cpus), "source": source}
 
 
 @contextlib.contextmanager
 def numa_local(device, sysfs="/sys"):
     """Run the body with the calling thread bound to the CPUs of `device`'s NUMA node (no-op when sysfs does not say).
     Threads started inside inherit the binding; the previous affinity of the calling thread is restored on exit."""
-    node = gpu_numa_node(device, sysfs)
-    cpus = node_cpus(node, sysfs) if node is not None else set()
+    node, cpus, source = _local_cpus(device, sysfs)
     if not cpus:
         yield None
         return
     before = os.sched_getaffinity(0)
     os.sched_setaffinity(0, cpus)
     try:
-        yield node
+        yield node if node is not None else -1      # -1: bound from NVML's CPU set, node number unknown
     finally:
         os.sched_setaffinity(0, before)

@@ -33,7 +33,7 @@ def test_binding_and_restore(tmp_path, monkeypatch):
     sysfs = _fake_sysfs(tmp_path, addr, 1, {0: "100000-100003", 1: ",".join(map(str, half))})
     monkeypatch.setattr(hostmem, "pci_address", lambda device: addr)
     assert hostmem.gpu_numa_node(0, sysfs) == 1
-    assert hostmem.describe(0, sysfs) == {"pci": addr, "node": 1, "cpus": len(half), "bound": True}
+    assert hostmem.describe(0, sysfs) == {"pci": addr, "node": 1, "cpus": len(half), "bound": True, "source": "sysfs"}
     with hostmem.numa_local(0, sysfs) as node:
         assert node == 1 and os.sched_getaffinity(0) == set(half)
     assert os.sched_getaffinity(0) == set(mine)
@@ -49,8 +49,24 @@ def test_no_answer_is_a_no_op(tmp_path, monkeypatch, node, lists):
     addr = "0000:1b:00.0"
     sysfs = _fake_sysfs(tmp_path, addr, node, lists)
     monkeypatch.setattr(hostmem, "pci_address", lambda device: addr)
+    monkeypatch.setattr(hostmem, "nvml_cpus", lambda device: set())       # no driver on this box
     assert hostmem.describe(0, sysfs)["bound"] is False
     with hostmem.numa_local(0, sysfs) as got:
         assert got is None and os.sched_getaffinity(0) == mine
     monkeypatch.setattr(hostmem, "pci_address", lambda device: None)       # no GPU / no PCI address
     assert hostmem.gpu_numa_node(0, sysfs) is None
+
+
+def test_nvml_answer_is_used_when_sysfs_has_none(tmp_path, monkeypatch):
+    mine = sorted(os.sched_getaffinity(0))
+    if len(mine) < 2:
+        pytest.skip("needs two CPUs in the affinity mask")
+    half = set(mine[: len(mine) // 2])
+    addr = "0000:c0:00.0"
+    sysfs = _fake_sysfs(tmp_path, addr, -1, {0: "0-3"})
+    monkeypatch.setattr(hostmem, "pci_address", lambda device: addr)
+    monkeypatch.setattr(hostmem, "nvml_cpus", lambda device: half)
+    assert hostmem.describe(0, sysfs) == {"pci": addr, "node": None, "cpus": len(half), "bound": True, "source": "nvml"}
+    with hostmem.numa_local(0, sysfs) as node:
+        assert node == -1 and os.sched_getaffinity(0) == half
+    assert os.sched_getaffinity(0) == set(mine)
