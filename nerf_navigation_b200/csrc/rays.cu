@@ -617,49 +617,13 @@ extern "C" int ngp_march_rays_train_write(const float *rays_o, const float *rays
 // sampler differentiates (renderer.py:159-160):
 //   dL/do = sum_k m_k * dL/dx_k,   dL/dd = sum_k t_k (m_k * dL/dx_k) + sum_k dL/ddir_k,   m_k = per-axis "not clamped".
 // t_k is rebuilt from the emitted deltas: t_k + dt_k = t_start + cumsum(deltas[:,1])_k.
-__global__ void __launch_bounds__(RAY_THREADS)
-k_march_train_bwd(const float *__restrict__ grad_xyzs, const float *__restrict__ grad_dirs,
-                  const float *__restrict__ rays_o, const float *__restrict__ rays_d, const float *__restrict__ nears,
-                  const float *__restrict__ deltas, const int32_t *__restrict__ rays, float bound, float dt_min,
-                  uint32_t perturb, int64_t N, int64_t M, float *__restrict__ grad_o, float *__restrict__ grad_d) {
-    const int64_t i = (int64_t)blockIdx.x * RAY_THREADS + threadIdx.x;
-    if (i >= N) return;
-    const int64_t n = rays[i * 3], off = rays[i * 3 + 1];
-    const uint32_t cnt = (uint32_t)rays[i * 3 + 2];
-    float go[3] = {0.f, 0.f, 0.f}, gd[3] = {0.f, 0.f, 0.f};
-    if (cnt != 0 && off + cnt < M) {
-        const float o[3] = {rays_o[n * 3], rays_o[n * 3 + 1], rays_o[n * 3 + 2]};
-        const float d[3] = {rays_d[n * 3], rays_d[n * 3 + 1], rays_d[n * 3 + 2]};
-        float tc = nears[n];
-        if (perturb) tc = fmaf(dt_min, ngp_pcg_jitter(42ull, (uint64_t)n), tc);
-        for (uint32_t s = 0; s < cnt; ++s) {
-            const int64_t k = off + s;
-            const float2 dl = __ldg(reinterpret_cast<const float2 *>(deltas) + k);
-            tc += dl.y;
-            const float t = tc - dl.x;
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                const float p = fmaf(t, d[a], o[a]);
-                const float g = (p >= -bound && p <= bound) ? __ldg(grad_xyzs + k * 3 + a) : 0.0f;
-                go[a] += g;
-                gd[a] = fmaf(t, g, gd[a]);
-                if (grad_dirs) gd[a] += __ldg(grad_dirs + k * 3 + a);
-            }
-        }
-    }
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-        grad_o[n * 3 + a] = go[a];
-        grad_d[n * 3 + a] = gd[a];
-    }
-}
-
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
-// the same reduction with one WARP per ray (coalesced; the running t is a warp scan of deltas[:, 1])
+// One WARP per ray: lanes = 32 consecutive samples (coalesced loads), the running t is a warp scan of deltas[:, 1], the
+// sums over the ray's samples are warp reductions.
 __global__ void __launch_bounds__(256)
 k_march_train_bwd_warp(const float *__restrict__ grad_xyzs, const float *__restrict__ grad_dirs,
                        const float *__restrict__ rays_o, const float *__restrict__ rays_d, const float *__restrict__ nears,
@@ -768,13 +732,20 @@ k_composite_train_fwd_warp(const float *__restrict__ sigmas, const float *__rest
     const int lane = threadIdx.x & 31;
     if (n >= N) return;
     const uint32_t id = (uint32_t)__ldg(rays + n * 3), off = (uint32_t)__ldg(rays + n * 3 + 1), cnt = (uint32_t)__ldg(rays + n * 3 + 2);
-    float r = 0.0f, g = 0.0f, b = 0.0f, ws = 0.0f, d = 0.0f;
+    // rgbs are read as the block's 96 consecutive floats (flat element lane + 32 j, j = 0..2: three coalesced loads instead
+    // of three stride-3 ones); element f belongs to sample f / 3, whose weight comes by shuffle, and to component f % 3 =
+    // (lane + 2 j) % 3, so the three per-lane partial sums are sorted into r, g, b once, after the loop.
+    const int sj0 = lane / 3, sj1 = (lane + 32) / 3, sj2 = (lane + 64) / 3;
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, wsum = 0.0f, dsum = 0.0f;
     if (cnt != 0 && (int64_t)off + cnt < M) {
         float Tc = 1.0f, tc = 0.0f;
         for (uint32_t base = 0; base < cnt; base += 32) {
-            const uint32_t s = base + lane;
+            const uint32_t s = base + lane, left = cnt - base;
             const bool in = s < cnt;
             const int64_t k = (int64_t)off + s;
+            const float *cb = rgbs + ((int64_t)off + base) * 3;
+            const float v0 = (uint32_t)sj0 < left ? __ldg(cb + lane) : 0.0f, v1 = (uint32_t)sj1 < left ? __ldg(cb + lane + 32) : 0.0f,
+                        v2 = (uint32_t)sj2 < left ? __ldg(cb + lane + 64) : 0.0f;
             const float2 dl = in ? __ldg(reinterpret_cast<const float2 *>(deltas) + k) : make_float2(0.0f, 0.0f);
             const float alpha = in ? 1.0f - __expf(-__ldg(sigmas + k) * dl.x) : 0.0f;
             float P = 1.0f - alpha, t = dl.y;   // inclusive scans: transmittance after the sample, t of the sample
@@ -793,16 +764,26 @@ k_composite_train_fwd_warp(const float *__restrict__ sigmas, const float *__rest
             const unsigned brk = __ballot_sync(0xffffffffu, in && Tafter < 1e-4f);
             const int last = brk ? __ffs(brk) - 1 : 31;   // the sample that saw T < 1e-4 is still accumulated (:560-570)
             const bool use = in && lane <= last;
-            r += warp_sum(use ? w * __ldg(rgbs + k * 3) : 0.0f);
-            g += warp_sum(use ? w * __ldg(rgbs + k * 3 + 1) : 0.0f);
-            b += warp_sum(use ? w * __ldg(rgbs + k * 3 + 2) : 0.0f);
-            d += warp_sum(use ? w * t : 0.0f);
-            ws += warp_sum(use ? w : 0.0f);
+            const unsigned um = __ballot_sync(0xffffffffu, use);   // samples past the end never touch the sums (a NaN there stays out)
+            const float wu = use ? w : 0.0f;
+            const float w0 = __shfl_sync(0xffffffffu, wu, sj0), w1 = __shfl_sync(0xffffffffu, wu, sj1), w2 = __shfl_sync(0xffffffffu, wu, sj2);
+            if ((um >> sj0) & 1u) a0 = fmaf(w0, v0, a0);
+            if ((um >> sj1) & 1u) a1 = fmaf(w1, v1, a1);
+            if ((um >> sj2) & 1u) a2 = fmaf(w2, v2, a2);
+            if (use) {
+                dsum = fmaf(w, t, dsum);
+                wsum += w;
+            }
             if (brk) break;
             Tc = __shfl_sync(0xffffffffu, Tafter, 31);
             tc = __shfl_sync(0xffffffffu, t, 31);
         }
     }
+    const int c0 = lane % 3;   // component of a0; a1 holds (c0 + 2) % 3, a2 holds (c0 + 1) % 3
+    const float r = warp_sum(c0 == 0 ? a0 : (c0 == 1 ? a1 : a2));
+    const float g = warp_sum(c0 == 1 ? a0 : (c0 == 2 ? a1 : a2));
+    const float b = warp_sum(c0 == 2 ? a0 : (c0 == 0 ? a1 : a2));
+    const float ws = warp_sum(wsum), d = warp_sum(dsum);
     if (lane == 0) {
         weights_sum[id] = ws;
         depth[id] = d;
