@@ -327,11 +327,15 @@ k_march_expand(const float *__restrict__ rays_o, const float *__restrict__ rays_
 // Write pass from the runs of k_march_count<true>: one WARP per ray.  Phase 1: lane j replays run j — t_{k+1} = t_k +
 // dt(t_k), the marcher's own recurrence, no occupancy lookups — and leaves the parameters t_k in the warp's shared-memory
 // strip (in xyzs[k][0] for a ray with more than MARCH_REPLAY_STRIP samples); a ray with more runs than MARCH_SEG_CAP is
-// marched by lane 0 the way k_march_write marches it.  Phase 2: lanes = consecutive samples, everything else follows
+// marched again by the whole warp (march_ray_warp, the small-batch write pass).  Phase 2: lanes = consecutive samples, everything else follows
 // from t_k alone and is stored coalesced: dt_k = dt(t_k), the position clamp(o + t_k d), the direction, and
 // deltas_k = (dt_k, (t_k + dt_k) - (t_{k-1} + dt_{k-1})) with the ray's start for k = 0 — the marcher's t - last_t
 // (:470-473), since inside a run t_{k-1} + dt_{k-1} IS t_k.  Same float operations per sample as k_march_write: same bits.
 #define MARCH_REPLAY_STRIP 1024
+template <bool WRITE>
+__device__ __forceinline__ uint32_t march_ray_warp(const MarchRay &r, const MarchCfg &cfg, float t_cur, float far,
+                                                   uint32_t limit, float last_t, int64_t off, float *__restrict__ xyzs,
+                                                   float *__restrict__ dirs, float *__restrict__ deltas, float &t_first);
 __global__ void __launch_bounds__(256)
 k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_d, MarchCfg cfg, int64_t N, int64_t M,
                const float *__restrict__ nears, const float *__restrict__ fars, uint32_t perturb,
@@ -376,17 +380,10 @@ k_march_replay(const float *__restrict__ rays_o, const float *__restrict__ rays_
                 t += ngp_clampf(t * cfg.dt_gamma, cfg.dt_min, cfg.dt_max);
             }
         }
-    } else if (lane == 0) {
-        float t = __ldg(segs + n).x, px, py, pz, dt;   // run 0 starts at the first occupied sample
-        const float far = fars[n];
-        uint32_t step = 0;
-        while (t < far && step < cnt) {
-            if (!ngp_march_step(r, cfg, t, px, py, pz, dt)) continue;
-            if (in_strip) strip[step] = t;
-            else xyzs[(off + step) * 3] = t;
-            t += dt;
-            ++step;
-        }
+    } else {   // (warp-uniform) more runs than the workspace holds: the warp marches the ray again, 32 probes at a time, and
+        float tf;   // writes the samples itself — the small-batch write pass; run 0 starts at the first occupied sample
+        march_ray_warp<true>(r, cfg, __ldg(segs + n).x, fars[n], cnt, t0, off, xyzs, dirs, deltas, tf);
+        return;
     }
     __syncwarp();   // the parameters written above are read by other lanes below
     float carry = t0;   // t + dt of the sample before this block of 32 (the ray's start before the first)

@@ -108,10 +108,10 @@ def test_march_write_pass_from_runs(ngp, oracle, scene, grid_kind, dt_gamma, max
     """Thread-per-ray form (N > 8192): the count pass leaves each ray's runs of consecutive samples and the write pass
     (k_march_replay) rebuilds the samples from them without reading the grid.  Bit for bit the oracle's samples, and the
     samples of the write pass that marches again (NGP_B200_MARCH_WRITE=remarch), directions included.  A random
-    occupancy grid gives most rays more runs than MARCH_SEG_CAP (16): those take the kernel's in-place march.  The
+    occupancy grid gives most rays more runs than MARCH_SEG_CAP (16): those are marched again by their warp (march_ray_warp).  The
     one-call form with a sample budget drops the same rays as the reference (raymarching.cu:419-420).  max_steps = 3000
     gives rays with more samples than the kernel's 1024-entry shared-memory strip (a fully occupied grid: one long run
-    per ray; the random grid: the in-place march)."""
+    per ray; the random grid: the warp's own march)."""
     from nerf_navigation_b200 import raymarching as rm
     if grid_kind == "scene":
         bits = scene[1]
