@@ -52,6 +52,26 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
         const int64_t b = tile * C5_ROWS + row;
         float x01[3];
         const bool valid = fq_load_point(P.x, b, P.B, P.bound, x01);
+#ifdef C5_PREFETCH
+        // Experiment, measured and NOT the default: the next pair's 16 gathers in flight while the current pair is
+        // interpolated.  At the 128 registers per thread that 448 threads get, it spills 116 bytes and the estimator's
+        // forward goes 20.5 -> 22.6 ms (7.9x10^7 ray-ordered samples): more loads per gather thread is not what this
+        // kernel is short of.
+        FqRaw raw[2][2];
+        float frac[2][2][3];
+        c5_pair_issue<SAFE>(P.table, S.lv, 0, x01, P.align_corners, raw[0], frac[0]);
+#pragma unroll
+        for (int lp = 0; lp < 8; ++lp) {
+            if (lp + 1 < 8) c5_pair_issue<SAFE>(P.table, S.lv, lp + 1, x01, P.align_corners, raw[(lp + 1) & 1], frac[(lp + 1) & 1]);
+            float feat[4];
+            c5_pair_consume(raw[lp & 1], frac[lp & 1], valid, feat);
+            if (lp == 0) {
+                if (it > 0) tc5::mbar_wait_wd(bar_empty, (uint32_t)((it - 1) & 1));
+                tc5::fence_after_sync();
+            }
+            c5_put_features(lane_addr, lp, feat);
+        }
+#else
 #pragma unroll 1
         for (int lp = 0; lp < 8; ++lp) {
             float feat[4];
@@ -63,6 +83,7 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
             }
             c5_put_features(lane_addr, lp, feat);
         }
+#endif
         tc5::tmem_st_wait();
         tc5::fence_before_sync();
         tc5::mbar_arrive(bar_full);

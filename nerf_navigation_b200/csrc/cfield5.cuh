@@ -167,6 +167,38 @@ __device__ __forceinline__ void c5_encode_pair(const float *__restrict__ table, 
     }
 }
 
+// The same in two halves, for a gather loop that keeps the NEXT pair's 16 gathers in flight while it interpolates the
+// current one (C5_PREFETCH): issue (cell, fractions, loads into `raw`), then consume.
+template <bool SAFE>
+__device__ __forceinline__ void c5_pair_issue(const float *__restrict__ table, const FqLevel *__restrict__ lvs, int lp,
+                                              const float (&x01)[3], int align_corners, FqRaw (&raw)[2], float (&frac)[2][3]) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const FqLevel lv = lvs[2 * lp + h];
+        uint32_t cell[3];
+        fq_cell(x01, lv.scale, align_corners, cell, frac[h]);
+        fq_issue<1, SAFE>(table, lv, cell, raw[h]);
+    }
+}
+__device__ __forceinline__ void c5_pair_consume(const FqRaw (&raw)[2], const float (&frac)[2][3], bool valid, float (&feat)[4]) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float2 v[8];
+        fq_select(raw[h], v);
+        float f0 = 0.0f, f1 = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            float w = (k & 1) ? frac[h][0] : 1.0f - frac[h][0];
+            w *= (k & 2) ? frac[h][1] : 1.0f - frac[h][1];
+            w *= (k & 4) ? frac[h][2] : 1.0f - frac[h][2];
+            f0 = fmaf(w, v[k].x, f0);
+            f1 = fmaf(w, v[k].y, f1);
+        }
+        feat[2 * h] = valid ? f0 : 0.0f;
+        feat[2 * h + 1] = valid ? f1 : 0.0f;
+    }
+}
+
 // 4 features -> TMEM columns [4*lp, 4*lp + 4) of the feature operand (hi at C5_FHI, lo at C5_FLO)
 __device__ __forceinline__ void c5_put_features(uint32_t lane_addr, int lp, const float (&feat)[4]) {
     uint32_t hi[4], lo[4];
