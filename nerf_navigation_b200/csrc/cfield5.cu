@@ -22,6 +22,26 @@ extern "C" int ngp_set_field_impl(int impl) {
     return prev;
 }
 
+// -DC5_STATS (dev builds only, scripts/c5_roles.py): cycles each role of the forward spends inside its barrier waits and
+// in total, summed over the CTAs' reporting threads (one lane per warp).  [0,1] gather: wait on f_empty, total;
+// [2,3] chain: wait on d_full, total; [4..7] MMA thread: wait on f_full, t_free, a_ready, total.
+#ifdef C5_STATS
+__device__ unsigned long long g_c5_stats[8];
+#define C5_CLK() clock64()
+#define C5_STAT_ADD(i, v) atomicAdd(&g_c5_stats[i], (unsigned long long)(v))
+extern "C" int ngp_c5_stats(unsigned long long *out8, int reset) {
+    if (out8 && cudaMemcpyFromSymbol(out8, g_c5_stats, sizeof(g_c5_stats)) != cudaSuccess) return 1;
+    if (reset) {
+        unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (cudaMemcpyToSymbol(g_c5_stats, z, sizeof(z)) != cudaSuccess) return 1;
+    }
+    return 0;
+}
+#else
+#define C5_CLK() 0ll
+#define C5_STAT_ADD(i, v) ((void)(v))
+#endif
+
 struct __align__(128) C5FwdSmem {
     C5FwdWeights w;
     FqLevel lv[FQ_L];
@@ -46,6 +66,8 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
     const uint32_t lane_addr = tmem + s * C5_SLOT_COLS + ((uint32_t)(32 * q) << 16);
     const uint32_t bar_full = tc5::smem_u32(&S.bars[s].f_full), bar_empty = tc5::smem_u32(&S.bars[s].f_empty);
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
+    long long st_wait = 0;
+    const long long st_t0 = C5_CLK();
     for (int64_t it = 0;; ++it) {
         const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
         if (tile >= ntiles) break;
@@ -78,7 +100,9 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
             c5_encode_pair<SAFE>(P.table, S.lv, lp, x01, valid, P.align_corners, feat);
             if (lp == 0) {
                 // the previous tile's first-layer products have read the feature columns (long done unless the chain is behind)
+                const long long st_a = C5_CLK();
                 if (it > 0) tc5::mbar_wait_wd(bar_empty, (uint32_t)((it - 1) & 1));
+                st_wait += C5_CLK() - st_a;
                 tc5::fence_after_sync();
             }
             c5_put_features(lane_addr, lp, feat);
@@ -87,6 +111,10 @@ __device__ __forceinline__ void c5_forward_gather(C5FwdSmem &S, const C5FwdParam
         tc5::tmem_st_wait();
         tc5::fence_before_sync();
         tc5::mbar_arrive(bar_full);
+    }
+    if (lane == 0) {
+        C5_STAT_ADD(0, st_wait);
+        C5_STAT_ADD(1, C5_CLK() - st_t0);
     }
 }
 
@@ -100,6 +128,8 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
     const int q = warp & 3, row = 32 * q + lane;
     const int64_t ntiles = (P.B + C5_ROWS - 1) / C5_ROWS;
     const uint32_t lane_base = tmem + ((uint32_t)(32 * q) << 16);
+    long long st_wait = 0;
+    const long long st_t0 = C5_CLK();
     for (int64_t it = 0;; ++it) {
         const int64_t tile0 = blockIdx.x + (int64_t)gridDim.x * (2 * it);
         const int n_act = tile0 >= ntiles ? 0 : (tile0 + gridDim.x >= ntiles ? 1 : 2);
@@ -114,7 +144,7 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
 #pragma unroll 1
         for (int s = 0; s < n_act; ++s) {
             C5_SLOT_VARS
-            tc5::mbar_wait_wd(bar_d, (par + 0u) & 1u);
+            { const long long st_a = C5_CLK(); tc5::mbar_wait_wd(bar_d, (par + 0u) & 1u); st_wait += C5_CLK() - st_a; }
             tc5::fence_after_sync();
             const uint64_t m = c5_relu_to_a<MASK>(lane_addr);
             c5_chain_arrive(bar_a);
@@ -127,7 +157,7 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
             float dir[3];
 #pragma unroll
             for (int a = 0; a < 3; ++a) dir[a] = inb ? __ldg(P.dirs + b * 3 + a) : 0.0f;
-            tc5::mbar_wait_wd(bar_d, (par + 1u) & 1u);
+            { const long long st_a = C5_CLK(); tc5::mbar_wait_wd(bar_d, (par + 1u) & 1u); st_wait += C5_CLK() - st_a; }
             tc5::fence_after_sync();
             float o[16];
             c5_get16(lane_addr, 0, o);
@@ -146,7 +176,7 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
 #pragma unroll 1
             for (int s = 0; s < n_act; ++s) {
                 C5_SLOT_VARS
-                tc5::mbar_wait_wd(bar_d, (par + 2u + (uint32_t)k) & 1u);
+                { const long long st_a = C5_CLK(); tc5::mbar_wait_wd(bar_d, (par + 2u + (uint32_t)k) & 1u); st_wait += C5_CLK() - st_a; }
                 tc5::fence_after_sync();
                 const uint64_t m = c5_relu_to_a<MASK>(lane_addr);
                 c5_chain_arrive(bar_a);
@@ -158,7 +188,7 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
         for (int s = 0; s < n_act; ++s) {
             C5_SLOT_VARS
             (void)bar_a;
-            tc5::mbar_wait_wd(bar_d, (par + 4u) & 1u);
+            { const long long st_a = C5_CLK(); tc5::mbar_wait_wd(bar_d, (par + 4u) & 1u); st_wait += C5_CLK() - st_a; }
             tc5::fence_after_sync();
             uint32_t r[4];
             tc5::tmem_ld4_nowait(lane_addr + C5_D, r);
@@ -170,6 +200,10 @@ __device__ __forceinline__ void c5_forward_chain(C5FwdSmem &S, const C5FwdParams
                 for (int c = 0; c < 3; ++c) P.rgb[b * 3 + c] = 1.0f / (1.0f + expf(-__uint_as_float(r[c])));
             }
         }
+    }
+    if (lane == 0) {
+        C5_STAT_ADD(2, st_wait);
+        C5_STAT_ADD(3, C5_CLK() - st_t0);
     }
 }
 
@@ -184,33 +218,39 @@ __device__ __forceinline__ void c5_forward_mma(C5FwdSmem &S, const C5FwdParams &
                    s1l = tc5::smem_u32(S.w.s1[1]), c0h = tc5::smem_u32(S.w.c0[0]), c0l = tc5::smem_u32(S.w.c0[1]),
                    c1h = tc5::smem_u32(S.w.c1[0]), c1l = tc5::smem_u32(S.w.c1[1]), c2h = tc5::smem_u32(S.w.c2[0]),
                    c2l = tc5::smem_u32(S.w.c2[1]);
+    long long st_ff = 0, st_t = 0, st_a_ = 0;
+    const long long st_t0 = C5_CLK();
     for (int64_t it = 0;; ++it) {
         const int64_t tile = blockIdx.x + (int64_t)gridDim.x * (2 * it + s);
         if (tile >= ntiles) break;
         const uint32_t pa = (uint32_t)(4 * it);
-        tc5::mbar_wait_wd(bar_ff, (uint32_t)(it & 1));
-        if (it > 0) tc5::mbar_wait_wd(bar_t, (uint32_t)((it - 1) & 1));
+        { const long long c = C5_CLK(); tc5::mbar_wait_wd(bar_ff, (uint32_t)(it & 1)); st_ff += C5_CLK() - c; }
+        { const long long c = C5_CLK(); if (it > 0) tc5::mbar_wait_wd(bar_t, (uint32_t)((it - 1) & 1)); st_t += C5_CLK() - c; }
         tc5::fence_after_sync();
         c5_issue_layer<64, 32>(t + C5_D, t + C5_FHI, t + C5_FLO, s0h, s0l);   // sigma L1: features -> 64
         tc5::mma_commit(bar_fe);
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u);
+        { const long long c = C5_CLK(); tc5::mbar_wait_wd(bar_a, (pa + 0u) & 1u); st_a_ += C5_CLK() - c; }
         tc5::fence_after_sync();
         c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, s1h, s1l);   // sigma L2: 64 -> 16
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u);
+        { const long long c = C5_CLK(); tc5::mbar_wait_wd(bar_a, (pa + 1u) & 1u); st_a_ += C5_CLK() - c; }
         tc5::fence_after_sync();
         c5_issue_layer<64, 32>(t + C5_D, t + C5_HHI, t + C5_HLO, c0h, c0l);   // colour L1: [SH | o] (32) -> 64
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u);
+        { const long long c = C5_CLK(); tc5::mbar_wait_wd(bar_a, (pa + 2u) & 1u); st_a_ += C5_CLK() - c; }
         tc5::fence_after_sync();
         c5_issue_layer<64, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c1h, c1l);   // colour L2: 64 -> 64
         tc5::mma_commit(bar_d);
-        tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u);
+        { const long long c = C5_CLK(); tc5::mbar_wait_wd(bar_a, (pa + 3u) & 1u); st_a_ += C5_CLK() - c; }
         tc5::fence_after_sync();
         c5_issue_layer<16, 64>(t + C5_D, t + C5_HHI, t + C5_HLO, c2h, c2l);   // colour L3: 64 -> 3 (16)
         tc5::mma_commit(bar_d);
     }
+    C5_STAT_ADD(4, st_ff);
+    C5_STAT_ADD(5, st_t);
+    C5_STAT_ADD(6, st_a_);
+    C5_STAT_ADD(7, C5_CLK() - st_t0);
 }
 
 __device__ __forceinline__ void c5_init_bars(C5Bars *bars) {
@@ -231,7 +271,12 @@ k_cfield5_forward(C5FwdParams P, const int32_t *__restrict__ offsets, float S_, 
                   const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
     extern __shared__ __align__(128) unsigned char c5_smem_raw[];
     C5FwdSmem &S = *reinterpret_cast<C5FwdSmem *>(c5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // warp index and (below) the TMEM base as values the compiler can PROVE warp-uniform (a broadcast shuffle, the
+    // canonical_warp_idx_sync idiom): tcgen05.mma takes its TMEM addresses and descriptors from uniform registers, and
+    // for operands it cannot prove uniform the compiler wraps every MMA in an ELECT / R2UR.BROADCAST / branch loop
+    // (~100 cycles per MMA for the issuing thread, 96 MMAs per tile: scripts/c5_roles.py had the MMA threads issuing
+    // 58 % of the time and never waiting for features)
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
     if (tid == 0) c5_init_bars(S.bars);
@@ -240,7 +285,7 @@ k_cfield5_forward(C5FwdParams P, const int32_t *__restrict__ offsets, float S_, 
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
 
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) c5_forward_gather<true>(S, P, tmem, warp, lane);
@@ -466,7 +511,7 @@ k_cfield5_backward(C5BwdParams P, const int32_t *__restrict__ offsets, float S_,
                    const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
     extern __shared__ __align__(128) unsigned char c5_smem_raw[];
     C5BwdSmem &S = *reinterpret_cast<C5BwdSmem *>(c5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_tile(S.w.c2[0], S.w.c2[1], 64, 8, [&](int n, int k) { return k < 3 ? Wc2[k * FQ_HID + n] : 0.0f; });
     c5_stage_tile(S.w.c1[0], S.w.c1[1], 64, 64, [&](int n, int k) { return Wc1[k * FQ_HID + n]; });
@@ -481,7 +526,7 @@ k_cfield5_backward(C5BwdParams P, const int32_t *__restrict__ offsets, float S_,
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
 
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) c5_backward_gather<true>(S, P, tmem, warp, lane);

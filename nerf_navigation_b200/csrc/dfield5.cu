@@ -188,7 +188,7 @@ k_dfield5_forward(D5FwdParams P, const int32_t *__restrict__ offsets, float S_, 
                   const float *__restrict__ W0, const float *__restrict__ W1) {
     extern __shared__ __align__(128) unsigned char d5_smem_raw[];
     D5Smem &S = *reinterpret_cast<D5Smem *>(d5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_tile(S.w.s0[0], S.w.s0[1], 64, 32, [&](int n, int k) { return W0[n * FQ_F + k]; });
     c5_stage_tile(S.w.s1[0], S.w.s1[1], 16, 64, [&](int n, int k) { return W1[n * FQ_HID + k]; });
@@ -198,7 +198,7 @@ k_dfield5_forward(D5FwdParams P, const int32_t *__restrict__ offsets, float S_, 
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) d5_forward_gather<true>(S, P, tmem, warp, lane);
         else d5_forward_gather<false>(S, P, tmem, warp, lane);
@@ -333,7 +333,7 @@ k_dfield5_backward(D5BwdParams P, const int32_t *__restrict__ offsets, float S_,
                    const float *__restrict__ W0, const float *__restrict__ W1) {
     extern __shared__ __align__(128) unsigned char d5_smem_raw[];
     D5Smem &S = *reinterpret_cast<D5Smem *>(d5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_tile(S.w.s1[0], S.w.s1[1], 64, 16, [&](int n, int k) { return W1[k * FQ_HID + n]; });
     c5_stage_tile(S.w.s0[0], S.w.s0[1], 32, 64, [&](int n, int k) { return W0[k * FQ_F + n]; });
@@ -343,7 +343,7 @@ k_dfield5_backward(D5BwdParams P, const int32_t *__restrict__ offsets, float S_,
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) d5_backward_gather<true>(S, P, tmem, warp, lane);
         else d5_backward_gather<false>(S, P, tmem, warp, lane);
@@ -657,7 +657,7 @@ k_dfield5_value_grad(D5VgParams P, const int32_t *__restrict__ offsets, float S_
                      const float *__restrict__ W0, const float *__restrict__ W1) {
     extern __shared__ __align__(128) unsigned char d5_smem_raw[];
     D5VgSmem &S = *reinterpret_cast<D5VgSmem *>(d5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_tile(S.w.s0[0], S.w.s0[1], 64, 32, [&](int n, int k) { return W0[n * FQ_F + k]; });
     c5_stage_tile(S.w.s1[0], S.w.s1[1], 16, 64, [&](int n, int k) { return W1[n * FQ_HID + k]; });
@@ -673,7 +673,7 @@ k_dfield5_value_grad(D5VgParams P, const int32_t *__restrict__ offsets, float S_
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) d5_vg_gather<true>(S, P, tmem, warp, lane);
         else d5_vg_gather<false>(S, P, tmem, warp, lane);

@@ -71,7 +71,7 @@ k_ffmlp_forward(const __half *__restrict__ x, const __half *__restrict__ w, __ha
     unsigned char *Win = Hs + FF_ROWS * FF_HID * 2;             // [64 x in]
     unsigned char *Wh = Win + FF_HID * in_dim * 2;              // (n-1) x [64 x 64]
     unsigned char *Wout = Wh + (n_layers - 1) * FF_HID * FF_HID * 2;  // [16 x 64]
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const uint32_t bar = tc5::smem_u32(&sh->bar);
 
     if (tid == 0) {
@@ -87,7 +87,7 @@ k_ffmlp_forward(const __half *__restrict__ x, const __half *__restrict__ w, __ha
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = sh->tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, sh->tmem, 0);
     const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);  // this warp's 32 TMEM lanes
     const uint32_t xs_a = tc5::smem_u32(Xs), hs_a = tc5::smem_u32(Hs), win_a = tc5::smem_u32(Win),
                    wh_a = tc5::smem_u32(Wh), wout_a = tc5::smem_u32(Wout);
@@ -300,7 +300,7 @@ k_ffmlp_backward(const __half *__restrict__ grad, const __half *__restrict__ x, 
     unsigned char *WoutT = Fs1 + FF_ROWS * fw * 2;                  // [64 x 16]   W_out^T
     unsigned char *WhT = WoutT + FF_HID * FF_OUT * 2;               // (n-1) x [64 x 64]  W_h^T
     unsigned char *WinT = WhT + (n_layers - 1) * FF_HID * FF_HID * 2;  // [in x 64]  W_in^T
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const uint32_t bar = tc5::smem_u32(&sh->bar);
     const FFBwdLayout TL = ff_bwd_layout(in_dim, n_layers);
 
@@ -317,7 +317,7 @@ k_ffmlp_backward(const __half *__restrict__ grad, const __half *__restrict__ x, 
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = sh->tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, sh->tmem, 0);
     const uint32_t trow = tmem + ((uint32_t)(warp * 32) << 16);
     const uint32_t gs_a = tc5::smem_u32(Gs), hs_a = tc5::smem_u32(Hs), f_a[2] = {tc5::smem_u32(Fs0), tc5::smem_u32(Fs1)},
                    woutT_a = tc5::smem_u32(WoutT), whT_a = tc5::smem_u32(WhT), winT_a = tc5::smem_u32(WinT);

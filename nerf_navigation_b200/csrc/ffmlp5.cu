@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(F5_THREADS, 1) k_ffmlp5_forward(F5Params P, ui
     unsigned char *Wout = Wh + (n - 1) * F5_HID * F5_HID * 2;               // [16 x 64]
     unsigned char *Xs = Wout + F5_OUT * F5_HID * 2;                         // slots x [128 x in]
     unsigned char *Hs = Xs + (size_t)P.slots * F5_ROWS * P.in_dim * 2;      // slots x [128 x 64]
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     if (tid == 0) {
         for (int s = 0; s < P.slots; ++s) {
             tc5::mbar_init(tc5::smem_u32(&sh->bars[s].x_full), F5_LOAD_WARPS * 32);
@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(F5_THREADS, 1) k_ffmlp5_forward(F5Params P, ui
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = sh->tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, sh->tmem, 0);
     if (warp < F5_LOAD_WARPS) {
         f5_loader(P, sh, Xs, tid);
     } else if (warp < F5_EPI_WARP0) {
@@ -345,7 +345,7 @@ k_ffield5_forward(F5Params P, FF5Field G, const int32_t *__restrict__ offsets, f
     unsigned char *Wout = Wh + (n - 1) * F5_HID * F5_HID * 2;
     unsigned char *Xs = Wout + F5_OUT * F5_HID * 2;
     unsigned char *Hs = Xs + (size_t)FF5_SLOTS * F5_ROWS * 32 * 2;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(sh->lv, &sh->all_safe, offsets, S_, H, gridtype, G.align_corners);
     if (tid == 0) {
         for (int s = 0; s < FF5_SLOTS; ++s) {
@@ -365,7 +365,7 @@ k_ffield5_forward(F5Params P, FF5Field G, const int32_t *__restrict__ offsets, f
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = sh->f.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, sh->f.tmem, 0);
     if (warp < FF5_GATHER_WARPS) {
         if (sh->all_safe) ff5_gather<true>(P, G, sh, Xs, warp, lane);
         else ff5_gather<false>(P, G, sh, Xs, warp, lane);

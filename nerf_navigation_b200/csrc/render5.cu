@@ -706,7 +706,7 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
                      const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
     extern __shared__ __align__(128) unsigned char r5_smem_raw[];
     R5Smem &S = *reinterpret_cast<R5Smem *>(r5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
     if (tid == 0) {
@@ -733,7 +733,7 @@ k_render5_rays_infer(R5Params P, MarchCfg cfg, const int32_t *__restrict__ offse
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
 
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) r5_gather<true, R5Smem>(S, P, tmem, warp, lane);
@@ -1098,7 +1098,7 @@ k_render5_rays_infer_lists(R5Params P, const int32_t *__restrict__ offsets, floa
                            const float *__restrict__ Wc1, const float *__restrict__ Wc2) {
     extern __shared__ __align__(128) unsigned char r5_smem_raw[];
     R5SmemL &S = *reinterpret_cast<R5SmemL *>(r5_smem_raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     fq_stage_levels(S.lv, &S.all_safe, offsets, S_, H, gridtype, P.align_corners);
     c5_stage_forward_weights(S.w, Ws0, Ws1, Wc0, Wc1, Wc2);
     if (tid == 0) {
@@ -1121,7 +1121,7 @@ k_render5_rays_infer_lists(R5Params P, const int32_t *__restrict__ offsets, floa
     tc5::fence_before_sync();
     __syncthreads();
     tc5::fence_after_sync();
-    const uint32_t tmem = S.tmem;
+    const uint32_t tmem = __shfl_sync(0xffffffffu, S.tmem, 0);
     if (warp < C5_GATHER_WARPS) {
         if (S.all_safe) r5_gather<true, R5SmemL>(S, P, tmem, warp, lane);
         else r5_gather<false, R5SmemL>(S, P, tmem, warp, lane);

@@ -91,28 +91,6 @@ def _host_chunks(B, chunk=1 << 20):
     return head + [chunk] * (mid // chunk) + ([mid % chunk] if mid % chunk else []) + head[::-1]
 
 
-def _host_chunks_upload(B, chunk=1 << 20):
-    """Chunk sizes for a pass that only UPLOADS (the forward of _field_query_host): the same short first chunks, but no
-    short ones at the end — the uploads finish well before the kernels do (12 B/point over PCIe against ~0.34 ns/point of
-    kernel), so the tail is kernel time only and every extra launch there costs its fill and drain (measured at
-    4,194,304 points: 7 launches 1.56 ms of kernels, the single launch 1.42 ms).  A remainder under half a chunk joins
-    the last full chunk."""
-    if B <= chunk:
-        return [B] if B else []
-    head = [chunk // 4, chunk // 2]
-    if B < sum(head) + chunk:
-        return [min(chunk, B - a) for a in range(0, B, chunk)]
-    mid = B - sum(head)
-    out = head + [chunk] * (mid // chunk)
-    rem = mid % chunk
-    if rem:
-        if rem < chunk // 2:
-            out[-1] += rem
-        else:
-            out.append(rem)
-    return out
-
-
 _host_streams = {}
 
 
@@ -149,7 +127,7 @@ class _field_query_host(Function):
             cur = torch.cuda.current_stream()
             s_in.wait_stream(cur)                   # the buffers above were allocated on the current stream
             a = 0
-            for n in _host_chunks_upload(B):
+            for n in _host_chunks(B):
                 with torch.cuda.stream(s_in):
                     xd[a:a + n].copy_(x[a:a + n], non_blocking=True)
                     ev = torch.cuda.Event()
